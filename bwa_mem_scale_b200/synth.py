@@ -1,0 +1,114 @@
+"""Deterministic synthetic inputs for the seeding + extension hot path.
+
+Shapes follow BASELINE.json `configs` / SURVEY.md §8(d): i.i.d. ACGT references, 151-bp reads with
+1 % substitutions and random strand, and seed-extension `SeqPair` sets for the isolated banded-SW
+sweep (config 5).  Everything is seeded numpy; nothing here touches the GPU.
+"""
+from __future__ import annotations
+
+import numpy as np
+
+# byte-for-byte mirror of SeqPair (reference src/bandedSWA.h:90-99)
+SEQPAIR_DTYPE = np.dtype(
+    [("idr", "<i4"), ("idq", "<i4"), ("id", "<i4"), ("len1", "<i4"), ("len2", "<i4"),
+     ("h0", "<i4"), ("seqid", "<i4"), ("regid", "<i4"), ("score", "<i4"), ("tle", "<i4"),
+     ("gtle", "<i4"), ("qle", "<i4"), ("gscore", "<i4"), ("max_off", "<i4")])
+assert SEQPAIR_DTYPE.itemsize == 56
+
+RESULT_FIELDS = ("score", "qle", "tle", "gtle", "gscore", "max_off")
+
+
+def random_reference(n_bp: int, seed: int) -> np.ndarray:
+    """Uniform i.i.d. reference, values 0..3 (A,C,G,T)."""
+    return np.random.default_rng(seed).integers(0, 4, size=n_bp, dtype=np.uint8)
+
+
+def simulate_reads(ref: np.ndarray, n_reads: int, read_len: int = 151, err: float = 0.01,
+                   seed: int = 1, n_frac: float = 0.0) -> tuple[np.ndarray, np.ndarray, np.ndarray]:
+    """Reads as an (n, read_len) uint8 matrix of codes 0..4, plus true start and strand.
+
+    Each base is substituted (to a different base) with probability `err`; strand flipped with
+    probability 0.5.  `n_frac` sprinkles N (code 4).
+    """
+    rng = np.random.default_rng(seed)
+    start = rng.integers(0, len(ref) - read_len + 1, size=n_reads)
+    idx = start[:, None] + np.arange(read_len)[None, :]
+    reads = ref[idx]
+    sub = rng.random(reads.shape) < err
+    reads = np.where(sub, (reads + rng.integers(1, 4, size=reads.shape)) & 3, reads).astype(np.uint8)
+    rev = rng.random(n_reads) < 0.5
+    rc = (3 - reads[:, ::-1])
+    reads = np.where(rev[:, None], rc, reads).astype(np.uint8)
+    if n_frac > 0:
+        reads = np.where(rng.random(reads.shape) < n_frac, 4, reads).astype(np.uint8)
+    return reads, start, rev
+
+
+def extension_pairs(n_pairs: int, seed: int = 7, max_len2: int = 150, min_len2: int = 1,
+                    sub_rate: float = 0.01, indel_rate: float = 0.001, n_rate: float = 0.0,
+                    h0_lo: int = 19, h0_hi: int = 151, eight_bit: bool = False,
+                    tiny_frac: float = 0.0, a: int = 1, o: int = 6, e: int = 1, w: int = 100,
+                    end_bonus: int = 5):
+    """Seed-extension jobs shaped like those mem_chain2aln_across_reads_V2 emits.
+
+    Query = the read part beyond the seed (len2), target = reference window of len2 + max-gap
+    (cal_max_gap, reference src/bwamem.cpp:94-104) that begins with a mutated copy of the query.
+    Returns (pairs[SEQPAIR_DTYPE], ref_buf u8, qer_buf u8).  With `eight_bit` every pair satisfies
+    the 8-bit routing rule len1,len2 < 128 and h0 + min(len)*a < 128 (bwamem.cpp:2684-2694).
+    """
+    rng = np.random.default_rng(seed)
+    if eight_bit:
+        max_len2 = min(max_len2, 100)
+    len2 = rng.integers(min_len2, max_len2 + 1, size=n_pairs)
+    # max gap the extension could afford (cal_max_gap): (len*a - o)/e + 1, clipped to [1, 2w]
+    gap = np.maximum(((len2 * a + end_bonus - o) / e + 1.0).astype(np.int64), 1)
+    gap = np.minimum(gap, w << 1)
+    len1 = len2 + gap
+    if tiny_frac > 0:
+        tiny = rng.random(n_pairs) < tiny_frac
+        len1 = np.where(tiny, rng.integers(0, 5, size=n_pairs), len1)
+    if eight_bit:
+        len1 = np.minimum(len1, 127)
+        h0 = rng.integers(h0_lo, 128, size=n_pairs)
+        h0 = np.minimum(h0, 127 - np.minimum(len1, len2) * a)
+        h0 = np.maximum(h0, 1)
+    else:
+        h0 = rng.integers(h0_lo, h0_hi + 1, size=n_pairs)
+
+    pairs = np.zeros(n_pairs, dtype=SEQPAIR_DTYPE)
+    offq = np.concatenate(([0], np.cumsum(len2)))
+    offr = np.concatenate(([0], np.cumsum(len1)))
+    qer = rng.integers(0, 4, size=int(offq[-1]), dtype=np.uint8)
+    ref = rng.integers(0, 4, size=int(offr[-1]), dtype=np.uint8)
+    # copy query into the head of the target with substitutions and (rare) indels
+    for i in range(n_pairs):
+        q = qer[offq[i]:offq[i + 1]]
+        t = ref[offr[i]:offr[i + 1]]
+        m = q.copy()
+        s = rng.random(len(m)) < sub_rate
+        m[s] = (m[s] + rng.integers(1, 4, size=int(s.sum()))) & 3
+        if indel_rate > 0 and len(m) > 2:
+            k = rng.random(len(m)) < indel_rate
+            if k.any():
+                keep = []
+                for pos in range(len(m)):
+                    if k[pos]:
+                        if rng.random() < 0.5:
+                            continue                       # deletion from the target copy
+                        keep.append(rng.integers(0, 4))    # insertion into the target copy
+                    keep.append(m[pos])
+                m = np.asarray(keep, dtype=np.uint8)
+        n = min(len(m), len(t))
+        t[:n] = m[:n]
+    if n_rate > 0:
+        qer[rng.random(len(qer)) < n_rate] = 4
+        ref[rng.random(len(ref)) < n_rate] = 4
+    pairs["idr"] = offr[:-1]
+    pairs["idq"] = offq[:-1]
+    pairs["id"] = np.arange(n_pairs)
+    pairs["len1"] = len1
+    pairs["len2"] = len2
+    pairs["h0"] = h0
+    pairs["seqid"] = np.arange(n_pairs) // 3
+    pairs["regid"] = np.arange(n_pairs) % 3
+    return pairs, ref, qer
