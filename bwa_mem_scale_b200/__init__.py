@@ -1,0 +1,7 @@
+"""B200-native seeding + extension hot path of bwa-mem-scale.
+
+The compute lives in `libbwagpu.so` (CUDA, sm_100a) behind the C ABI in include/bwagpu.h; this
+package is the host-side mirror of the reference's interface for that path.
+"""
+from .lib import BwaGpuError, BswParams, Context, LIB_PATH, load  # noqa: F401
+from .bsw import BandedPairWiseSW  # noqa: F401

@@ -1,0 +1,161 @@
+// S2 extension seam of the C ABI: bwagpu_bsw_get_scores{,_device}  (include/bwagpu.h).
+// Replaces BandedPairWiseSW::getScores16 / getScores8 / scalarBandedSWAWrapper
+// (reference src/bandedSWA.h:130-172).
+#include "ctx.cuh"
+#include "bsw_thread.cuh"
+
+#define BSW_TPB 128
+
+// Persistent grid: each thread walks pairs tid, tid+T, ... and owns one column of the
+// interleaved scratch (word j of thread t lives at work[j*T + t]).
+template <int KIND>
+__global__ void __launch_bounds__(BSW_TPB)
+bsw_thread_kernel(bwagpu_bsw_params prm, bwagpu_seqpair *__restrict__ pairs,
+                  const uint8_t *__restrict__ ref, const uint8_t *__restrict__ qer, int n, int w,
+                  uint32_t *__restrict__ work)
+{
+    const int64_t T = (int64_t)gridDim.x * blockDim.x;
+    const int64_t t0 = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    uint32_t *col = work + t0;
+    for (int64_t i = t0; i < n; i += T) {
+        bwagpu_seqpair sp = pairs[i];
+        const uint8_t *tg = ref + sp.idr, *qr = qer + sp.idq;
+        BswOut o;
+        if (KIND == BWAGPU_BSW_SCALAR)
+            o = bsw_scalar_pair(prm, qr, sp.len2, tg, sp.len1, w, sp.h0, col, T);
+        else
+            o = bsw_lane_pair<KIND>(prm, qr, sp.len2, tg, sp.len1, w, sp.h0, col, T);
+        bwagpu_seqpair *d = &pairs[i];
+        d->score = o.score; d->tle = o.tle; d->gtle = o.gtle; d->qle = o.qle;
+        d->gscore = o.gscore; d->max_off = o.max_off;
+    }
+}
+
+// max len2 over the batch (device reduction; result read back by the launcher)
+__global__ void bsw_maxlen_kernel(const bwagpu_seqpair *__restrict__ pairs, int n, int *out)
+{
+    int m1 = 0, m2 = 0;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n;
+         i += (int64_t)gridDim.x * blockDim.x) {
+        m1 = max(m1, pairs[i].len1);
+        m2 = max(m2, pairs[i].len2);
+    }
+    m1 = __reduce_max_sync(0xffffffffu, m1);
+    m2 = __reduce_max_sync(0xffffffffu, m2);
+    if ((threadIdx.x & 31) == 0) { atomicMax(&out[0], m1); atomicMax(&out[1], m2); }
+}
+
+static int bsw_check(bwagpu_ctx *ctx, const bwagpu_bsw_params *prm, int kind, int32_t n, int32_t w)
+{
+    if (!ctx) return BWAGPU_ERR_ARG;
+    if (!prm) BWAGPU_FAIL(ctx, BWAGPU_ERR_ARG, "bsw: params is NULL");
+    if (kind != BWAGPU_BSW_SCALAR && kind != BWAGPU_BSW_8BIT && kind != BWAGPU_BSW_16BIT)
+        BWAGPU_FAIL(ctx, BWAGPU_ERR_ARG, "bsw: kind must be 0, 8 or 16 (got %d)", kind);
+    if (n < 0 || w < 0) BWAGPU_FAIL(ctx, BWAGPU_ERR_ARG, "bsw: negative numPairs or w");
+    if (prm->e_del <= 0 || prm->e_ins <= 0)
+        BWAGPU_FAIL(ctx, BWAGPU_ERR_ARG, "bsw: gap extension penalties must be positive");
+    return BWAGPU_OK;
+}
+
+static int bsw_launch(bwagpu_ctx *ctx, const bwagpu_bsw_params *prm, int kind,
+                      bwagpu_seqpair *d_pairs, const uint8_t *d_ref, const uint8_t *d_qer,
+                      int32_t n, int32_t w, int max_len2)
+{
+    if (n == 0) return BWAGPU_OK;
+    int blocks = ctx->sm_count * 8;
+    int need = (n + BSW_TPB - 1) / BSW_TPB;
+    if (blocks > need) blocks = need;
+    const int64_t T = (int64_t)blocks * BSW_TPB;
+    const int64_t words = (kind == BWAGPU_BSW_SCALAR ? 2 : 1) * (int64_t)(max_len2 + 4) * T;
+    void *work;
+    int rc = bwagpu_scratch(ctx, SCR_BSW_WORK, words * 4, &work);
+    if (rc) return rc;
+    switch (kind) {
+    case BWAGPU_BSW_16BIT:
+        bsw_thread_kernel<16><<<blocks, BSW_TPB, 0, ctx->stream>>>(*prm, d_pairs, d_ref, d_qer, n,
+                                                                  w, (uint32_t *)work);
+        break;
+    case BWAGPU_BSW_8BIT:
+        bsw_thread_kernel<8><<<blocks, BSW_TPB, 0, ctx->stream>>>(*prm, d_pairs, d_ref, d_qer, n,
+                                                                 w, (uint32_t *)work);
+        break;
+    default:
+        bsw_thread_kernel<0><<<blocks, BSW_TPB, 0, ctx->stream>>>(*prm, d_pairs, d_ref, d_qer, n,
+                                                                 w, (uint32_t *)work);
+    }
+    ctx->launches++;
+    BWAGPU_CUDA(ctx, cudaGetLastError());
+    return BWAGPU_OK;
+}
+
+static int bsw_device_maxlen(bwagpu_ctx *ctx, const bwagpu_seqpair *d_pairs, int32_t n, int out[2])
+{
+    int *d_m;
+    int rc = bwagpu_scratch(ctx, SCR_MISC0, 64, (void **)&d_m);
+    if (rc) return rc;
+    BWAGPU_CUDA(ctx, cudaMemsetAsync(d_m, 0, 8, ctx->stream));
+    int blocks = ctx->sm_count * 4;
+    bsw_maxlen_kernel<<<blocks, 256, 0, ctx->stream>>>(d_pairs, n, d_m);
+    ctx->launches++;
+    BWAGPU_CUDA(ctx, cudaMemcpyAsync(out, d_m, 8, cudaMemcpyDeviceToHost, ctx->stream));
+    BWAGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return BWAGPU_OK;
+}
+
+extern "C" int bwagpu_bsw_get_scores_device(bwagpu_ctx *ctx, const bwagpu_bsw_params *prm,
+                                            int kind, bwagpu_seqpair *d_pairArray,
+                                            const uint8_t *d_seqBufRef, int64_t ref_bytes,
+                                            const uint8_t *d_seqBufQer, int64_t qer_bytes,
+                                            int32_t numPairs, int32_t w)
+{
+    int rc = bsw_check(ctx, prm, kind, numPairs, w);
+    if (rc) return rc;
+    (void)ref_bytes; (void)qer_bytes;
+    BWAGPU_CUDA(ctx, cudaSetDevice(ctx->device));
+    if (numPairs == 0) return BWAGPU_OK;
+    int ml[2];
+    rc = bsw_device_maxlen(ctx, d_pairArray, numPairs, ml);
+    if (rc) return rc;
+    return bsw_launch(ctx, prm, kind, d_pairArray, d_seqBufRef, d_seqBufQer, numPairs, w, ml[1]);
+}
+
+extern "C" int bwagpu_bsw_get_scores(bwagpu_ctx *ctx, const bwagpu_bsw_params *prm, int kind,
+                                     bwagpu_seqpair *pairArray, const uint8_t *seqBufRef,
+                                     const uint8_t *seqBufQer, int32_t numPairs, int32_t w)
+{
+    int rc = bsw_check(ctx, prm, kind, numPairs, w);
+    if (rc) return rc;
+    if (numPairs == 0) return BWAGPU_OK;
+    if (!pairArray || !seqBufRef || !seqBufQer)
+        BWAGPU_FAIL(ctx, BWAGPU_ERR_ARG, "bsw: NULL buffer with numPairs=%d", numPairs);
+    BWAGPU_CUDA(ctx, cudaSetDevice(ctx->device));
+    // extents of the two byte arenas actually referenced by this batch
+    int64_t ref_bytes = 0, qer_bytes = 0;
+    int max_len2 = 0;
+    for (int32_t i = 0; i < numPairs; ++i) {
+        const bwagpu_seqpair &sp = pairArray[i];
+        if (sp.len1 < 0 || sp.len2 < 0 || sp.idr < 0 || sp.idq < 0)
+            BWAGPU_FAIL(ctx, BWAGPU_ERR_ARG, "bsw: pair %d has a negative length/offset", i);
+        int64_t r = (int64_t)sp.idr + sp.len1, q = (int64_t)sp.idq + sp.len2;
+        if (r > ref_bytes) ref_bytes = r;
+        if (q > qer_bytes) qer_bytes = q;
+        if (sp.len2 > max_len2) max_len2 = sp.len2;
+    }
+    bwagpu_seqpair *d_pairs; uint8_t *d_ref, *d_qer;
+    if ((rc = bwagpu_scratch(ctx, SCR_BSW_PAIRS, (int64_t)numPairs * sizeof(bwagpu_seqpair),
+                             (void **)&d_pairs))) return rc;
+    if ((rc = bwagpu_scratch(ctx, SCR_BSW_REF, ref_bytes + 16, (void **)&d_ref))) return rc;
+    if ((rc = bwagpu_scratch(ctx, SCR_BSW_QER, qer_bytes + 16, (void **)&d_qer))) return rc;
+    BWAGPU_CUDA(ctx, cudaMemcpyAsync(d_pairs, pairArray, (size_t)numPairs * sizeof(bwagpu_seqpair),
+                                     cudaMemcpyHostToDevice, ctx->stream));
+    BWAGPU_CUDA(ctx, cudaMemcpyAsync(d_ref, seqBufRef, (size_t)ref_bytes, cudaMemcpyHostToDevice,
+                                     ctx->stream));
+    BWAGPU_CUDA(ctx, cudaMemcpyAsync(d_qer, seqBufQer, (size_t)qer_bytes, cudaMemcpyHostToDevice,
+                                     ctx->stream));
+    rc = bsw_launch(ctx, prm, kind, d_pairs, d_ref, d_qer, numPairs, w, max_len2);
+    if (rc) return rc;
+    BWAGPU_CUDA(ctx, cudaMemcpyAsync(pairArray, d_pairs, (size_t)numPairs * sizeof(bwagpu_seqpair),
+                                     cudaMemcpyDeviceToHost, ctx->stream));
+    BWAGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return BWAGPU_OK;
+}

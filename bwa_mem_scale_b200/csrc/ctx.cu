@@ -1,0 +1,146 @@
+// Context, memory and timing entry points of the C ABI (include/bwagpu.h).
+#include "ctx.cuh"
+#include <stdlib.h>
+
+static char g_err[512] = "";
+
+extern "C" int bwagpu_device_count(void)
+{
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+    return n;
+}
+
+extern "C" int bwagpu_create(int device, bwagpu_ctx **out)
+{
+    if (!out) return BWAGPU_ERR_ARG;
+    *out = nullptr;
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess || n == 0) {
+        snprintf(g_err, sizeof g_err, "no CUDA device available (%s); libbwagpu has no CPU path",
+                 e == cudaSuccess ? "0 devices" : cudaGetErrorString(e));
+        cudaGetLastError();
+        return BWAGPU_ERR_NO_DEVICE;
+    }
+    if (device < 0 || device >= n) {
+        snprintf(g_err, sizeof g_err, "device %d out of range [0,%d)", device, n);
+        return BWAGPU_ERR_ARG;
+    }
+    bwagpu_ctx *ctx = (bwagpu_ctx *)calloc(1, sizeof(bwagpu_ctx));
+    if (!ctx) return BWAGPU_ERR_NOMEM;
+    ctx->device = device;
+    ctx->err[0] = 0;
+#define CK(call)                                                                         \
+    do {                                                                                 \
+        cudaError_t e__ = (call);                                                        \
+        if (e__ != cudaSuccess) {                                                        \
+            snprintf(g_err, sizeof g_err, "%s -> %s", #call, cudaGetErrorString(e__));   \
+            free(ctx);                                                                   \
+            return BWAGPU_ERR_CUDA;                                                      \
+        }                                                                                \
+    } while (0)
+    CK(cudaSetDevice(device));
+    CK(cudaDeviceGetAttribute(&ctx->sm_count, cudaDevAttrMultiProcessorCount, device));
+    CK(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
+    CK(cudaEventCreate(&ctx->ev_start));
+    CK(cudaEventCreate(&ctx->ev_stop));
+#undef CK
+    *out = ctx;
+    return BWAGPU_OK;
+}
+
+extern "C" void bwagpu_destroy(bwagpu_ctx *ctx)
+{
+    if (!ctx) return;
+    cudaSetDevice(ctx->device);
+    cudaStreamSynchronize(ctx->stream);
+    for (int i = 0; i < 8; ++i)
+        if (ctx->scratch[i]) cudaFree(ctx->scratch[i]);
+    cudaEventDestroy(ctx->ev_start);
+    cudaEventDestroy(ctx->ev_stop);
+    cudaStreamDestroy(ctx->stream);
+    free(ctx);
+}
+
+extern "C" const char *bwagpu_last_error(const bwagpu_ctx *ctx) { return ctx ? ctx->err : g_err; }
+
+extern "C" int64_t bwagpu_launch_count(const bwagpu_ctx *ctx) { return ctx ? ctx->launches : 0; }
+
+extern "C" int bwagpu_synchronize(bwagpu_ctx *ctx)
+{
+    if (!ctx) return BWAGPU_ERR_ARG;
+    BWAGPU_CUDA(ctx, cudaSetDevice(ctx->device));
+    BWAGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return BWAGPU_OK;
+}
+
+extern "C" int bwagpu_timer_start(bwagpu_ctx *ctx)
+{
+    if (!ctx) return BWAGPU_ERR_ARG;
+    BWAGPU_CUDA(ctx, cudaSetDevice(ctx->device));
+    BWAGPU_CUDA(ctx, cudaEventRecord(ctx->ev_start, ctx->stream));
+    return BWAGPU_OK;
+}
+
+extern "C" int bwagpu_timer_stop(bwagpu_ctx *ctx, float *elapsed_ms)
+{
+    if (!ctx || !elapsed_ms) return BWAGPU_ERR_ARG;
+    BWAGPU_CUDA(ctx, cudaSetDevice(ctx->device));
+    BWAGPU_CUDA(ctx, cudaEventRecord(ctx->ev_stop, ctx->stream));
+    BWAGPU_CUDA(ctx, cudaEventSynchronize(ctx->ev_stop));
+    BWAGPU_CUDA(ctx, cudaEventElapsedTime(elapsed_ms, ctx->ev_start, ctx->ev_stop));
+    return BWAGPU_OK;
+}
+
+extern "C" int bwagpu_malloc(bwagpu_ctx *ctx, int64_t bytes, void **dptr)
+{
+    if (!ctx || !dptr || bytes < 0) return BWAGPU_ERR_ARG;
+    BWAGPU_CUDA(ctx, cudaSetDevice(ctx->device));
+    BWAGPU_CUDA(ctx, cudaMalloc(dptr, (size_t)(bytes ? bytes : 1)));
+    return BWAGPU_OK;
+}
+
+extern "C" int bwagpu_free(bwagpu_ctx *ctx, void *dptr)
+{
+    if (!ctx) return BWAGPU_ERR_ARG;
+    BWAGPU_CUDA(ctx, cudaSetDevice(ctx->device));
+    BWAGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    BWAGPU_CUDA(ctx, cudaFree(dptr));
+    return BWAGPU_OK;
+}
+
+extern "C" int bwagpu_h2d(bwagpu_ctx *ctx, void *dst, const void *src, int64_t bytes)
+{
+    if (!ctx || bytes < 0) return BWAGPU_ERR_ARG;
+    BWAGPU_CUDA(ctx, cudaSetDevice(ctx->device));
+    BWAGPU_CUDA(ctx, cudaMemcpyAsync(dst, src, (size_t)bytes, cudaMemcpyHostToDevice, ctx->stream));
+    BWAGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return BWAGPU_OK;
+}
+
+extern "C" int bwagpu_d2h(bwagpu_ctx *ctx, void *dst, const void *src, int64_t bytes)
+{
+    if (!ctx || bytes < 0) return BWAGPU_ERR_ARG;
+    BWAGPU_CUDA(ctx, cudaSetDevice(ctx->device));
+    BWAGPU_CUDA(ctx, cudaMemcpyAsync(dst, src, (size_t)bytes, cudaMemcpyDeviceToHost, ctx->stream));
+    BWAGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return BWAGPU_OK;
+}
+
+int bwagpu_scratch(bwagpu_ctx *ctx, int slot, int64_t bytes, void **out)
+{
+    if (bytes > ctx->scratch_bytes[slot]) {
+        if (ctx->scratch[slot]) {
+            BWAGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+            BWAGPU_CUDA(ctx, cudaFree(ctx->scratch[slot]));
+            ctx->scratch[slot] = nullptr;
+            ctx->scratch_bytes[slot] = 0;
+        }
+        int64_t want = bytes + bytes / 4 + 4096;
+        BWAGPU_CUDA(ctx, cudaMalloc(&ctx->scratch[slot], (size_t)want));
+        ctx->scratch_bytes[slot] = want;
+    }
+    *out = ctx->scratch[slot];
+    return BWAGPU_OK;
+}

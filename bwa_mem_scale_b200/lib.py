@@ -1,0 +1,139 @@
+"""ctypes loader for libbwagpu.so — the C ABI declared in include/bwagpu.h.
+
+There is no CPU path: if the library is missing it must be built (`__graft_entry__.build()` or
+`make -C bwa_mem_scale_b200/csrc`); if no CUDA device is present `Context()` raises.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+PKG_DIR = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(PKG_DIR, "libbwagpu.so")
+
+
+class BwaGpuError(RuntimeError):
+    pass
+
+
+class BswParams(C.Structure):
+    """bwagpu_bsw_params — constructor arguments of the reference's BandedPairWiseSW
+    (reference src/bandedSWA.cpp:51-98)."""
+    _fields_ = [(n, C.c_int32) for n in
+                ("o_del", "e_del", "o_ins", "e_ins", "zdrop", "end_bonus", "w_match", "w_mismatch")]
+
+
+_lib = None
+
+# name -> (restype, argtypes); every symbol include/bwagpu.h declares
+_SIGS = {
+    "bwagpu_create": (C.c_int, [C.c_int, C.POINTER(C.c_void_p)]),
+    "bwagpu_destroy": (None, [C.c_void_p]),
+    "bwagpu_last_error": (C.c_char_p, [C.c_void_p]),
+    "bwagpu_device_count": (C.c_int, []),
+    "bwagpu_synchronize": (C.c_int, [C.c_void_p]),
+    "bwagpu_launch_count": (C.c_int64, [C.c_void_p]),
+    "bwagpu_timer_start": (C.c_int, [C.c_void_p]),
+    "bwagpu_timer_stop": (C.c_int, [C.c_void_p, C.POINTER(C.c_float)]),
+    "bwagpu_malloc": (C.c_int, [C.c_void_p, C.c_int64, C.POINTER(C.c_void_p)]),
+    "bwagpu_free": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "bwagpu_h2d": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64]),
+    "bwagpu_d2h": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64]),
+    "bwagpu_bsw_get_scores": (C.c_int, [C.c_void_p, C.POINTER(BswParams), C.c_int, C.c_void_p,
+                                        C.c_void_p, C.c_void_p, C.c_int32, C.c_int32]),
+    "bwagpu_bsw_get_scores_device": (C.c_int, [C.c_void_p, C.POINTER(BswParams), C.c_int,
+                                               C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p,
+                                               C.c_int64, C.c_int32, C.c_int32]),
+}
+
+
+def load() -> C.CDLL:
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise BwaGpuError(
+                f"{LIB_PATH} not built: run `python -c 'import __graft_entry__ as g; g.build()'` "
+                "(there is no CPU fallback)")
+        lib = C.CDLL(LIB_PATH)
+        for name, (res, args) in _SIGS.items():
+            fn = getattr(lib, name)          # AttributeError if the ABI lost a symbol
+            fn.restype = res
+            fn.argtypes = args
+        _lib = lib
+    return _lib
+
+
+def exported_symbols() -> list[str]:
+    return sorted(_SIGS)
+
+
+class Context:
+    """One GPU context (bwagpu_ctx): device, stream, scratch and (later) the index replica."""
+
+    def __init__(self, device: int = 0):
+        self.lib = load()
+        h = C.c_void_p()
+        rc = self.lib.bwagpu_create(device, C.byref(h))
+        if rc != 0:
+            raise BwaGpuError(f"bwagpu_create({device}) failed ({rc}): "
+                              f"{self.lib.bwagpu_last_error(None).decode()}")
+        self.h = h
+        self.device = device
+
+    def check(self, rc: int, what: str = "") -> None:
+        if rc != 0:
+            raise BwaGpuError(f"{what} failed ({rc}): {self.lib.bwagpu_last_error(self.h).decode()}")
+
+    def close(self) -> None:
+        if getattr(self, "h", None):
+            self.lib.bwagpu_destroy(self.h)
+            self.h = None
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # -- helpers ---------------------------------------------------------------------------
+    def synchronize(self) -> None:
+        self.check(self.lib.bwagpu_synchronize(self.h), "synchronize")
+
+    def launch_count(self) -> int:
+        return int(self.lib.bwagpu_launch_count(self.h))
+
+    def timer_start(self) -> None:
+        self.check(self.lib.bwagpu_timer_start(self.h), "timer_start")
+
+    def timer_stop(self) -> float:
+        ms = C.c_float()
+        self.check(self.lib.bwagpu_timer_stop(self.h, C.byref(ms)), "timer_stop")
+        return float(ms.value)
+
+    def malloc(self, nbytes: int) -> int:
+        p = C.c_void_p()
+        self.check(self.lib.bwagpu_malloc(self.h, int(nbytes), C.byref(p)), "malloc")
+        return int(p.value)
+
+    def free(self, dptr: int) -> None:
+        self.check(self.lib.bwagpu_free(self.h, C.c_void_p(dptr)), "free")
+
+    def h2d(self, dptr: int, arr) -> None:
+        self.check(self.lib.bwagpu_h2d(self.h, C.c_void_p(dptr), arr.ctypes.data, arr.nbytes), "h2d")
+
+    def d2h(self, arr, dptr: int) -> None:
+        self.check(self.lib.bwagpu_d2h(self.h, arr.ctypes.data, C.c_void_p(dptr), arr.nbytes), "d2h")
+
+    def upload(self, arr) -> int:
+        import numpy as np
+        arr = np.ascontiguousarray(arr)
+        p = self.malloc(max(arr.nbytes, 1))
+        if arr.nbytes:
+            self.h2d(p, arr)
+        return p

@@ -112,3 +112,51 @@ def extension_pairs(n_pairs: int, seed: int = 7, max_len2: int = 150, min_len2: 
     pairs["seqid"] = np.arange(n_pairs) // 3
     pairs["regid"] = np.arange(n_pairs) % 3
     return pairs, ref, qer
+
+
+def extension_pairs_fast(n_pairs: int, seed: int = 7, max_len2: int = 150, min_len2: int = 1,
+                         sub_rate: float = 0.01, indel_frac: float = 0.1, h0_lo: int = 19,
+                         h0_hi: int = 151, eight_bit: bool = False, a: int = 1, o: int = 6,
+                         e: int = 1, w: int = 100, end_bonus: int = 5):
+    """Vectorised variant of `extension_pairs` for bench-sized sets (millions of pairs): same
+    length/h0 distributions; a fraction `indel_frac` of pairs carries one 1-3 bp indel."""
+    rng = np.random.default_rng(seed)
+    if eight_bit:
+        max_len2 = min(max_len2, 100)
+    len2 = rng.integers(min_len2, max_len2 + 1, size=n_pairs)
+    gap = np.maximum(((len2 * a + end_bonus - o) / e + 1.0).astype(np.int64), 1)
+    gap = np.minimum(gap, w << 1)
+    len1 = len2 + gap
+    if eight_bit:
+        len1 = np.minimum(len1, 127)
+        h0 = np.maximum(np.minimum(rng.integers(h0_lo, 128, size=n_pairs),
+                                   127 - np.minimum(len1, len2) * a), 1)
+    else:
+        h0 = rng.integers(h0_lo, h0_hi + 1, size=n_pairs)
+    offq = np.concatenate(([0], np.cumsum(len2)))
+    offr = np.concatenate(([0], np.cumsum(len1)))
+    qer = rng.integers(0, 4, size=int(offq[-1]), dtype=np.uint8)
+    ref = rng.integers(0, 4, size=int(offr[-1]), dtype=np.uint8)
+    # target position p (within its pair) copies query position p + shift(p); shift models one indel
+    pid = np.repeat(np.arange(n_pairs), len1)
+    pos = np.arange(int(offr[-1])) - offr[:-1][pid]
+    has = rng.random(n_pairs) < indel_frac
+    ipos = (rng.random(n_pairs) * len2).astype(np.int64)
+    ilen = rng.integers(1, 4, size=n_pairs) * np.where(rng.random(n_pairs) < 0.5, 1, -1)
+    shift = np.where(has[pid] & (pos >= ipos[pid]), ilen[pid], 0)
+    src = pos + shift
+    ok = (src >= 0) & (src < len2[pid]) & (pos < len2[pid] + 3)
+    vals = qer[np.minimum(offq[:-1][pid] + np.clip(src, 0, None), len(qer) - 1)]
+    sub = rng.random(len(vals)) < sub_rate
+    vals = np.where(sub, (vals + rng.integers(1, 4, size=len(vals))) & 3, vals).astype(np.uint8)
+    ref = np.where(ok, vals, ref).astype(np.uint8)
+    pairs = np.zeros(n_pairs, dtype=SEQPAIR_DTYPE)
+    pairs["idr"] = offr[:-1]
+    pairs["idq"] = offq[:-1]
+    pairs["id"] = np.arange(n_pairs)
+    pairs["len1"] = len1
+    pairs["len2"] = len2
+    pairs["h0"] = h0
+    pairs["seqid"] = np.arange(n_pairs) // 3
+    pairs["regid"] = np.arange(n_pairs) % 3
+    return pairs, ref, qer
