@@ -160,3 +160,47 @@ def extension_pairs_fast(n_pairs: int, seed: int = 7, max_len2: int = 150, min_l
     pairs["seqid"] = np.arange(n_pairs) // 3
     pairs["regid"] = np.arange(n_pairs) % 3
     return pairs, ref, qer
+
+
+def repeat_reference(n_bp: int, seed: int, n_families: int = 50, repeat_frac: float = 0.10,
+                     divergence: float = 0.02, unit_lo: int = 200, unit_hi: int = 2000) -> np.ndarray:
+    """Random reference in which `repeat_frac` of the sequence is drawn from `n_families` repeat
+    families, each copy mutated at `divergence`: keeps SMEM intervals
+    wider than 1 for longer, as on real genomes."""
+    rng = np.random.default_rng(seed)
+    ref = rng.integers(0, 4, size=n_bp, dtype=np.uint8)
+    fams = [rng.integers(0, 4, size=int(rng.integers(unit_lo, unit_hi + 1)), dtype=np.uint8)
+            for _ in range(n_families)]
+    target = int(n_bp * repeat_frac)
+    placed = 0
+    while placed < target:
+        f = fams[int(rng.integers(0, n_families))]
+        if len(f) >= n_bp:
+            break
+        cp = f.copy()
+        mut = rng.random(len(cp)) < divergence
+        cp[mut] = (cp[mut] + rng.integers(1, 4, size=int(mut.sum()))) & 3
+        if rng.random() < 0.5:
+            cp = (3 - cp[::-1]).astype(np.uint8)
+        p = int(rng.integers(0, n_bp - len(cp)))
+        ref[p:p + len(cp)] = cp
+        placed += len(cp)
+    return ref
+
+
+def ragged_reads(ref: np.ndarray, n_reads: int, seed: int, len_lo: int = 10, len_hi: int = 200,
+                 err: float = 0.01, n_frac: float = 0.002):
+    """Reads of mixed lengths (incl. shorter than the minimum seed length) as a list of arrays."""
+    rng = np.random.default_rng(seed)
+    out = []
+    for _ in range(n_reads):
+        L = int(rng.integers(len_lo, len_hi + 1))
+        s = int(rng.integers(0, len(ref) - L + 1))
+        r = ref[s:s + L].copy()
+        sub = rng.random(L) < err
+        r[sub] = (r[sub] + rng.integers(1, 4, size=int(sub.sum()))) & 3
+        if rng.random() < 0.5:
+            r = (3 - r[::-1]).astype(np.uint8)
+        r[rng.random(L) < n_frac] = 4
+        out.append(r)
+    return out

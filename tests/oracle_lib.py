@@ -67,3 +67,138 @@ def reference_bsw(lib, params: BswParams, kind: int, pairs: np.ndarray, ref: np.
     lib.ref_bsw_run(C.byref(params), kind, out.ctypes.data, len(out), ref.ctypes.data, len(ref),
                     qer.ctypes.data, len(qer), w)
     return out
+
+
+# ---- FM-index seeding -------------------------------------------------------------------------
+# byte-for-byte mirror of SMEM (reference src/FMI_search.h:85-93)
+SMEM_DTYPE = np.dtype([("rid", "<u4"), ("m", "<u4"), ("n", "<u4"), ("pad_", "<u4"),
+                       ("k", "<i8"), ("l", "<i8"), ("s", "<i8")])
+assert SMEM_DTYPE.itemsize == 40
+
+
+class OrcFmi(C.Structure):
+    _fields_ = [("ref_seq_len", C.c_int64), ("count", C.c_int64 * 5), ("cp_occ", C.c_void_p),
+                ("sa_ms_byte", C.c_void_p), ("sa_ls_word", C.c_void_p),
+                ("sentinel_index", C.c_int64)]
+
+
+class OrcSeedOpt(C.Structure):
+    _fields_ = [("min_seed_len", C.c_int32), ("split_factor", C.c_float),
+                ("split_width", C.c_int32), ("max_mem_intv", C.c_int64)]
+
+
+def default_seed_opt(**kw) -> OrcSeedOpt:
+    d = dict(min_seed_len=19, split_factor=1.5, split_width=10, max_mem_intv=20)
+    d.update(kw)
+    return OrcSeedOpt(**d)
+
+
+def orc_fmi(idx) -> OrcFmi:
+    """idx: bwa_mem_scale_b200.fmindex.FMIndex (arrays must stay alive while the struct is used)."""
+    f = OrcFmi()
+    f.ref_seq_len = idx.ref_seq_len
+    for i, v in enumerate(idx.count_loaded()):
+        f.count[i] = int(v)
+    f.cp_occ = idx.cp_occ.ctypes.data
+    f.sa_ms_byte = idx.sa_ms_byte.ctypes.data
+    f.sa_ls_word = idx.sa_ls_word.ctypes.data
+    f.sentinel_index = idx.sentinel_index
+    return f
+
+
+def pack_reads(reads, lens=None):
+    """(n, L) matrix or list of arrays -> (flat u8, off i64, len i32)."""
+    if isinstance(reads, np.ndarray) and reads.ndim == 2:
+        n, L = reads.shape
+        ln = np.full(n, L, np.int32) if lens is None else np.asarray(lens, np.int32)
+        rows = [reads[i, :ln[i]] for i in range(n)] if lens is not None else None
+        flat = np.ascontiguousarray(reads).reshape(-1) if rows is None else np.concatenate(rows)
+    else:
+        ln = np.array([len(r) for r in reads], np.int32)
+        flat = np.concatenate([np.asarray(r, np.uint8) for r in reads]) if len(reads) else np.zeros(0, np.uint8)
+    off = np.zeros(len(ln), np.int64)
+    if len(ln):
+        off[1:] = np.cumsum(ln[:-1])
+    return np.ascontiguousarray(flat, dtype=np.uint8), off, ln
+
+
+def oracle_collect_smem(idx, opt: OrcSeedOpt, flat, off, ln, skip=None):
+    lib = oracle()
+    lib.orc_collect_smem.restype = C.c_int64
+    lib.orc_collect_smem.argtypes = [C.POINTER(OrcFmi), C.POINTER(OrcSeedOpt), C.c_void_p,
+                                     C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p,
+                                     C.c_int64, C.POINTER(C.c_int64)]
+    f = orc_fmi(idx)
+    cap = max(int(ln.sum()) * 4, 1024)
+    n_ext = C.c_int64(0)
+    while True:
+        out = np.zeros(cap, SMEM_DTYPE)
+        n_ext.value = 0
+        tot = lib.orc_collect_smem(C.byref(f), C.byref(opt), flat.ctypes.data, off.ctypes.data,
+                                   ln.ctypes.data, None if skip is None else skip.ctypes.data,
+                                   len(ln), out.ctypes.data, cap, C.byref(n_ext))
+        if tot <= cap:
+            return out[:tot].copy(), int(n_ext.value)
+        cap = tot
+
+
+def oracle_sa_lookup(idx, smems, max_occ=500):
+    lib = oracle()
+    lib.orc_sa_lookup.restype = C.c_int64
+    lib.orc_sa_lookup.argtypes = [C.POINTER(OrcFmi), C.c_void_p, C.c_int64, C.c_int32, C.c_void_p,
+                                  C.POINTER(C.c_int64)]
+    f = orc_fmi(idx)
+    cap = int(np.minimum(smems["s"], max_occ).sum()) + 1
+    coords = np.zeros(cap, np.int64)
+    n_lf = C.c_int64(0)
+    smems = np.ascontiguousarray(smems)
+    n = lib.orc_sa_lookup(C.byref(f), smems.ctypes.data, len(smems), max_occ, coords.ctypes.data,
+                          C.byref(n_lf))
+    return coords[:n].copy(), int(n_lf.value)
+
+
+def ref_binary(flavor="plain", isa="sse41"):
+    p = os.path.join(ORACLE_DIR, "_ref", f"bwa-mem2.{flavor}.{isa}")
+    return p if os.path.exists(p) else None
+
+
+def ref_api(flavor="plain", isa="sse41"):
+    path = os.path.join(ORACLE_DIR, "_ref", f"libref_api_{flavor}_{isa}.so")
+    if not os.path.exists(path):
+        return None
+    lib = C.CDLL(path)
+    lib.ref_fmi_open.restype = C.c_void_p
+    lib.ref_fmi_open.argtypes = [C.c_char_p]
+    lib.ref_fmi_close.argtypes = [C.c_void_p]
+    lib.ref_collect_smem.restype = C.c_int64
+    lib.ref_collect_smem.argtypes = [C.c_void_p, C.c_int, C.c_float, C.c_int, C.c_int64,
+                                     C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p,
+                                     C.c_int64]
+    lib.ref_sa_lookup.restype = C.c_int64
+    lib.ref_sa_lookup.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_void_p]
+    return lib
+
+
+def ref_index(prefix: str, fasta: str, flavor="plain", isa="sse41") -> None:
+    """Run the reference's own `index` sub-command (writes <prefix>.bwt.2bit.64, .0123, .ann ...)."""
+    subprocess.run([ref_binary(flavor, isa), "index", "-p", prefix, fasta], check=True,
+                   stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+
+
+def reference_collect_smem(lib, h, opt: OrcSeedOpt, flat, off, ln):
+    cap = max(int(ln.sum()) * 4, 1024)
+    out = np.zeros(cap, SMEM_DTYPE)
+    # the reference rewrites nothing in `flat` here (mem_collect_smem only reads seq)
+    tot = lib.ref_collect_smem(h, opt.min_seed_len, opt.split_factor, opt.split_width,
+                               opt.max_mem_intv, flat.ctypes.data, off.ctypes.data, ln.ctypes.data,
+                               len(ln), out.ctypes.data, cap)
+    assert tot <= cap
+    return out[:tot].copy()
+
+
+def reference_sa_lookup(lib, h, smems, max_occ=500):
+    cap = int(np.minimum(smems["s"], max_occ).sum()) + 1
+    coords = np.zeros(cap, np.int64)
+    smems = np.ascontiguousarray(smems)
+    n = lib.ref_sa_lookup(h, smems.ctypes.data, len(smems), max_occ, coords.ctypes.data)
+    return coords[:n].copy()
