@@ -164,10 +164,13 @@ def bench_bsw(args, rank, world):
     sampler = ClockSampler(local)
     sampler.start()
     l0 = ctx.launch_count()
-    ctx.timer_start()
+    ms = 0.0
     for _ in range(args.steps):
+        if flush:
+            ctx.memset(flush, 1, 256 << 20)
+        ctx.timer_start()
         step_dev()
-    ms = ctx.timer_stop()
+        ms += ctx.timer_stop()
     launches = ctx.launch_count() - l0
     ms = allreduce_max(ms)
     # e2e: host buffers through the drop-in call
@@ -207,6 +210,134 @@ def bench_bsw(args, rank, world):
     return out
 
 
+
+# ------------------------------------------------------------------------------------------------
+def seed_inputs(args, rank):
+    """Synthetic reference + FM-index + reads of BASELINE config 2's shape (per GPU)."""
+    from bwa_mem_scale_b200 import fmindex, synth
+    n_bp = int(args.ref_mbp * 1e6)
+    ref = synth.repeat_reference(n_bp, 43, n_families=50, repeat_frac=0.10, divergence=0.02)
+    idx = fmindex.build_fm_index(ref)
+    reads, _, _ = synth.simulate_reads(ref, args.reads, seed=500 + rank)
+    return ref, idx, reads
+
+
+def cpu_seed(idx, reads, threads, max_occ=500):
+    """CPU baseline for seeding: the oracle port (oracle/fmi_oracle.c) over `reads`, chunked over
+    host threads.  Returns seconds."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import oracle_lib as ol
+    chunks = [c for c in np.array_split(np.arange(len(reads)), threads) if len(c)]
+
+    def work(c):
+        flat, off, ln = ol.pack_reads(reads[c])
+        sm, _ = ol.oracle_collect_smem(idx, ol.default_seed_opt(), flat, off, ln)
+        ol.oracle_sa_lookup(idx, sm, max_occ)
+
+    from concurrent.futures import ThreadPoolExecutor
+    ol.oracle()
+    t0 = time.perf_counter()
+    with ThreadPoolExecutor(threads) as ex:
+        list(ex.map(work, chunks))
+    return time.perf_counter() - t0
+
+
+def bench_seed(args, rank, world):
+    from bwa_mem_scale_b200 import Context, FMI_search, seed_opt, pack_reads
+    from bwa_mem_scale_b200.seeding import SMEM_DTYPE  # noqa: F401
+    ref, idx, reads = seed_inputs(args, rank)
+    n = len(reads)
+    cfg = {"workload": f"FM-index seeding (SMEM rounds 1-3 + SA look-up), BASELINE config 2 shape: "
+                       f"{args.ref_mbp:g} Mbp synthetic reference (10% repeats), {n} x 151 bp SE reads/GPU, "
+                       f"1% substitutions, FM-index only (no FMA tables)",
+           "reads_per_gpu": n, "ref_mbp": args.ref_mbp,
+           "l2_policy": "index (%.0f MB) + reads larger than L2" % (idx.nbytes() / 1e6)
+           if idx.nbytes() > 126e6 else "flush between steps"}
+    if args.impl == "reference":
+        if rank != 0:
+            return None
+        thr = cpu_threads()
+        sample = reads[: min(n, 4000 * thr)]
+        for _ in range(args.warmup):
+            cpu_seed(idx, sample[:200 * thr], thr)
+        t = sum(cpu_seed(idx, sample, thr) for _ in range(args.steps))
+        v = len(sample) * args.steps / t
+        return {"impl": "reference", "metric": "reads/s (151bp SE, seeding)", "value": v, "unit": "reads/s",
+                "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+                "ms_per_step": 1e3 * t / args.steps, "higher_is_better": True, "scaling": "weak",
+                "vs_baseline": None, "dtype": "int64", "data": "synthetic", "config": cfg,
+                "cpu_baseline": {"value": v, "unit": "reads/s", "cores": thr, "kind": "port",
+                                 "sample": f"{len(sample)} reads of the same set"},
+                "e2e": {"value": v, "unit": "reads/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    local = int(os.environ.get("LOCAL_RANK", rank))
+    ctx = Context(local)
+    fmi = FMI_search(idx, ctx=ctx)
+    opt = seed_opt()
+    flat, off, ln = pack_reads(reads)
+    d_reads, d_off, d_len = ctx.upload(flat), ctx.upload(off), ctx.upload(ln)
+    flush = ctx.malloc(256 << 20) if "flush" in cfg["l2_policy"] else None
+
+    def step():
+        return fmi.seed_device(opt, d_reads, d_off, d_len, None, n, 151)
+
+    for _ in range(args.warmup):
+        res = step()
+    ctx.synchronize()
+    barrier()
+    sampler = ClockSampler(local)
+    sampler.start()
+    l0 = ctx.launch_count()
+    ms = 0.0
+    for _ in range(args.steps):
+        if flush:
+            ctx.memset(flush, 1, 256 << 20)
+        ctx.timer_start()
+        res = step()
+        ms += ctx.timer_stop()
+    ms = allreduce_max(ms)
+    launches = ctx.launch_count() - l0
+    # e2e: host reads in, SMEMs + coordinates back out through the drop-in calls
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        sm = fmi.collect_smem(opt, flat, off, ln)
+        sa = fmi.get_sa_entries_prefetch(sm, opt.max_occ)
+    e2e_s = allreduce_max(time.perf_counter() - t0)
+    clocks = sampler.stop()
+    # per-kernel device time of the dominant kernel (profiling serialises: separate pass)
+    ctx.set_profiling(True)
+    for _ in range(args.steps):
+        res = step()
+    k_ms, k_n = ctx.kernel_time(0)
+    sa_ms, sa_n = ctx.kernel_time(2)
+    ctx.set_profiling(False)
+    if rank != 0:
+        return None
+    pk, pk_kind = peaks()
+    alg_bytes = res.n_cp_records * 64          # per launch: 64 B per CP_OCC record fetched
+    ach = alg_bytes / (k_ms / k_n * 1e-3) / 1e9
+    out = {"metric": "reads/s (151bp SE, seeding)", "value": n * world * args.steps / (ms * 1e-3), "unit": "reads/s",
+           "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps,
+           "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "int64",
+           "data": "synthetic", "config": cfg, "clocks": clocks, "gpu_launches": int(launches),
+           "e2e": {"value": n * world * args.steps / e2e_s, "unit": "reads/s",
+                   "h2d_bytes_per_step": int(flat.nbytes + off.nbytes + ln.nbytes + sm.nbytes),
+                   "d2h_bytes_per_step": int(sm.nbytes + sa.nbytes)},
+           "roofline": {"bound": "hbm", "kernel": "seed_collect_kernel", "achieved": ach, "peak": pk["hbm_gbs"],
+                        "unit": "GB/s", "frac": ach / pk["hbm_gbs"], "traffic": None, "peak_kind": pk_kind,
+                        "kernel_ms": k_ms / k_n, "bext_per_read": res.n_ext / n,
+                        "cp_records_per_read": res.n_cp_records / n, "smem_per_read": res.n_smem / n,
+                        "sa_rows_per_read": res.n_coords / n, "lf_steps_per_row": res.n_lf_steps / max(res.n_coords, 1),
+                        "sa_walk_ms": sa_ms / max(sa_n, 1),
+                        "sa_walk_gbs": (res.n_lf_steps * 64 + res.n_coords * 5) / (sa_ms / max(sa_n, 1) * 1e-3) / 1e9}}
+    if not args.no_cpu:
+        thr = cpu_threads()
+        sample = reads[: min(n, 3000 * thr)]
+        dt = cpu_seed(idx, sample, thr)
+        out["cpu_baseline"] = {"value": len(sample) / dt, "unit": "reads/s", "cores": thr, "kind": "port",
+                               "sample": f"{len(sample)} reads of the same set, oracle port, {dt:.1f}s"}
+    return out
+
 # ------------------------------------------------------------------------------------------------
 _dist = None
 
@@ -242,7 +373,9 @@ def main():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="bsw", choices=["bsw"])
+    ap.add_argument("--workload", default="bsw", choices=["bsw", "seed"])
+    ap.add_argument("--ref-mbp", type=float, default=100.0)
+    ap.add_argument("--reads", type=int, default=1_000_000)
     ap.add_argument("--pairs", type=int, default=1_000_000)
     ap.add_argument("--band", type=int, default=100)
     ap.add_argument("--kind", type=int, default=16, choices=[8, 16])
@@ -250,12 +383,13 @@ def main():
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", 0))
     world = int(os.environ.get("WORLD_SIZE", 1))
+    fn = {"bsw": bench_bsw, "seed": bench_seed}[args.workload]
     if args.impl == "reference":
         if rank == 0:
-            print(json.dumps(bench_bsw(args, 0, world)))
+            print(json.dumps(fn(args, 0, world)))
         return
     init_dist(world)
-    out = bench_bsw(args, rank, world)
+    out = fn(args, rank, world)
     if rank == 0 and out is not None:
         print(json.dumps(out))
     if _dist is not None:

@@ -5,3 +5,5 @@ package is the host-side mirror of the reference's interface for that path.
 """
 from .lib import BwaGpuError, BswParams, Context, LIB_PATH, load  # noqa: F401
 from .bsw import BandedPairWiseSW  # noqa: F401
+from .seeding import FMI_search, SMEM_DTYPE, seed_opt, pack_reads  # noqa: F401
+from .fmindex import FMIndex, build_fm_index  # noqa: F401

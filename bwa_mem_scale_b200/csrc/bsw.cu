@@ -70,6 +70,7 @@ static int bsw_launch(bwagpu_ctx *ctx, const bwagpu_bsw_params *prm, int kind,
     void *work;
     int rc = bwagpu_scratch(ctx, SCR_BSW_WORK, words * 4, &work);
     if (rc) return rc;
+    BWAGPU_KERNEL_BEGIN(ctx);
     switch (kind) {
     case BWAGPU_BSW_16BIT:
         bsw_thread_kernel<16><<<blocks, BSW_TPB, 0, ctx->stream>>>(*prm, d_pairs, d_ref, d_qer, n,
@@ -83,7 +84,7 @@ static int bsw_launch(bwagpu_ctx *ctx, const bwagpu_bsw_params *prm, int kind,
         bsw_thread_kernel<0><<<blocks, BSW_TPB, 0, ctx->stream>>>(*prm, d_pairs, d_ref, d_qer, n,
                                                                  w, (uint32_t *)work);
     }
-    ctx->launches++;
+    BWAGPU_KERNEL_END(ctx, BWAGPU_KERN_BSW);
     BWAGPU_CUDA(ctx, cudaGetLastError());
     return BWAGPU_OK;
 }

@@ -45,6 +45,8 @@ extern "C" int bwagpu_create(int device, bwagpu_ctx **out)
     CK(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
     CK(cudaEventCreate(&ctx->ev_start));
     CK(cudaEventCreate(&ctx->ev_stop));
+    CK(cudaEventCreate(&ctx->kev0));
+    CK(cudaEventCreate(&ctx->kev1));
 #undef CK
     *out = ctx;
     return BWAGPU_OK;
@@ -55,10 +57,15 @@ extern "C" void bwagpu_destroy(bwagpu_ctx *ctx)
     if (!ctx) return;
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->stream);
-    for (int i = 0; i < 8; ++i)
+    for (int i = 0; i < BWAGPU_NSCRATCH; ++i)
         if (ctx->scratch[i]) cudaFree(ctx->scratch[i]);
+    if (ctx->d_cp_occ) cudaFree(ctx->d_cp_occ);
+    if (ctx->d_sa_ms) cudaFree(ctx->d_sa_ms);
+    if (ctx->d_sa_ls) cudaFree(ctx->d_sa_ls);
     cudaEventDestroy(ctx->ev_start);
     cudaEventDestroy(ctx->ev_stop);
+    cudaEventDestroy(ctx->kev0);
+    cudaEventDestroy(ctx->kev1);
     cudaStreamDestroy(ctx->stream);
     free(ctx);
 }
@@ -66,6 +73,22 @@ extern "C" void bwagpu_destroy(bwagpu_ctx *ctx)
 extern "C" const char *bwagpu_last_error(const bwagpu_ctx *ctx) { return ctx ? ctx->err : g_err; }
 
 extern "C" int64_t bwagpu_launch_count(const bwagpu_ctx *ctx) { return ctx ? ctx->launches : 0; }
+
+extern "C" int bwagpu_set_profiling(bwagpu_ctx *ctx, int on)
+{
+    if (!ctx) return BWAGPU_ERR_ARG;
+    ctx->profiling = on ? 1 : 0;
+    for (int i = 0; i < BWAGPU_KERN_N; ++i) { ctx->kern_ms[i] = 0; ctx->kern_n[i] = 0; }
+    return BWAGPU_OK;
+}
+
+extern "C" int bwagpu_kernel_time(const bwagpu_ctx *ctx, int which, double *ms, int64_t *launches)
+{
+    if (!ctx || which < 0 || which >= BWAGPU_KERN_N) return BWAGPU_ERR_ARG;
+    if (ms) *ms = ctx->kern_ms[which];
+    if (launches) *launches = ctx->kern_n[which];
+    return BWAGPU_OK;
+}
 
 extern "C" int bwagpu_synchronize(bwagpu_ctx *ctx)
 {
@@ -125,6 +148,14 @@ extern "C" int bwagpu_d2h(bwagpu_ctx *ctx, void *dst, const void *src, int64_t b
     BWAGPU_CUDA(ctx, cudaSetDevice(ctx->device));
     BWAGPU_CUDA(ctx, cudaMemcpyAsync(dst, src, (size_t)bytes, cudaMemcpyDeviceToHost, ctx->stream));
     BWAGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return BWAGPU_OK;
+}
+
+extern "C" int bwagpu_memset(bwagpu_ctx *ctx, void *dst, int value, int64_t bytes)
+{
+    if (!ctx || bytes < 0) return BWAGPU_ERR_ARG;
+    BWAGPU_CUDA(ctx, cudaSetDevice(ctx->device));
+    BWAGPU_CUDA(ctx, cudaMemsetAsync(dst, value, (size_t)bytes, ctx->stream));
     return BWAGPU_OK;
 }
 

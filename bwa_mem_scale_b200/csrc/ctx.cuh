@@ -6,6 +6,11 @@
 #include <string.h>
 #include "../../include/bwagpu.h"
 
+enum { SCR_BSW_PAIRS = 0, SCR_BSW_REF, SCR_BSW_QER, SCR_BSW_WORK, SCR_MISC0, SCR_MISC1, SCR_MISC2,
+       SCR_MISC3, SCR_SEED_READS, SCR_SEED_OFF, SCR_SEED_LEN, SCR_SEED_SKIP, SCR_SEED_TMP,
+       SCR_SEED_CNT, SCR_SEED_SCAN, SCR_SEED_PREV, SCR_SEED_OUT, SCR_SA_CNT, SCR_SA_OFF,
+       SCR_SA_COORD, SCR_CUB, SCR_STATS, SCR_SA_IN, BWAGPU_NSCRATCH };
+
 struct bwagpu_ctx {
     int device;
     int sm_count;
@@ -15,12 +20,37 @@ struct bwagpu_ctx {
     char err[512];
     // grow-only device scratch owned by the context (one chunk of reads at a time is in flight,
     // SURVEY.md §3.1, so no locking is needed)
-    void *scratch[8];
-    int64_t scratch_bytes[8];
+    void *scratch[BWAGPU_NSCRATCH];
+    int64_t scratch_bytes[BWAGPU_NSCRATCH];
+    // FM-index replica in this GPU's HBM (bwagpu_index_load_fm)
+    bool has_fm;
+    void *d_cp_occ, *d_sa_ms, *d_sa_ls;
+    int64_t fm_count[5], fm_sentinel, fm_ref_seq_len;
+    int seed_read_cap;          // per-read SMEM capacity of the seeding scratch (grows on overflow)
+    // optional per-kernel CUDA-event timing (bwagpu_set_profiling): bench.py's roofline numbers
+    int profiling;
+    cudaEvent_t kev0, kev1;
+    double kern_ms[BWAGPU_KERN_N];
+    int64_t kern_n[BWAGPU_KERN_N];
 };
 
-enum { SCR_BSW_PAIRS = 0, SCR_BSW_REF = 1, SCR_BSW_QER = 2, SCR_BSW_WORK = 3,
-       SCR_MISC0 = 4, SCR_MISC1 = 5, SCR_MISC2 = 6, SCR_MISC3 = 7 };
+// Brackets one kernel launch with events on the context's stream when profiling is on.
+#define BWAGPU_KERNEL_BEGIN(ctx) \
+    do { if ((ctx)->profiling) cudaEventRecord((ctx)->kev0, (ctx)->stream); } while (0)
+#define BWAGPU_KERNEL_END(ctx, which)                                        \
+    do {                                                                     \
+        (ctx)->launches++;                                                   \
+        if ((ctx)->profiling) {                                              \
+            float ms__ = 0.f;                                                \
+            cudaEventRecord((ctx)->kev1, (ctx)->stream);                     \
+            cudaEventSynchronize((ctx)->kev1);                               \
+            cudaEventElapsedTime(&ms__, (ctx)->kev0, (ctx)->kev1);           \
+            (ctx)->kern_ms[which] += ms__;                                   \
+            (ctx)->kern_n[which]++;                                          \
+        }                                                                    \
+    } while (0)
+
+
 
 #define BWAGPU_CUDA(ctx, call)                                                              \
     do {                                                                                    \

@@ -1,0 +1,331 @@
+// FM-index seeding core: backward extension over CP_OCC, the per-read SMEM state machine
+// (seeding rounds 1-3) and the suffix-array walk.  Everything here is per-thread code shared by
+// the CUDA kernels in seed.cu; it is also compilable as plain host C++ so that tests can single-step
+// the exact same logic without a GPU (tests/hostsim), which is test scaffolding, not a product path.
+//
+// Reference behaviour reproduced:
+//   fm_bext              FMI_search::backwardExt + GET_OCC     src/FMI_search.cpp:2029-2056, .h:76-83
+//   SeedMachine          getSMEMsOnePosOneThread (rounds 1, 2)  src/FMI_search.cpp:1372-1606
+//                        bwtSeedStrategyAllPosOneThread (3)     src/FMI_search.cpp:1662-1816
+//                        round orchestration of mem_collect_smem src/bwamem.cpp:648-786
+//   fm_sa_walk           call_one_step / get_sa_entries_prefetch src/FMI_search.cpp:2206-2379
+#pragma once
+#include <stdint.h>
+#include "../../include/bwagpu.h"
+
+#if defined(__CUDACC__)
+#define BWAGPU_HD __host__ __device__ __forceinline__
+#else
+#define BWAGPU_HD inline
+#endif
+
+// Device view of the FM-index replica held in HBM.  count[] is the loaded form (file value + 1).
+struct FmView {
+    const int64_t *cp_occ;       // 8 x 64-bit words per record: cp_count[4], one_hot_bwt_str[4]
+    const int8_t *sa_ms_byte;
+    const uint32_t *sa_ls_word;
+    int64_t count[5];
+    int64_t sentinel_index;
+    int64_t ref_seq_len;
+};
+
+struct FmRec { int64_t cnt[4]; uint64_t bits[4]; };
+
+BWAGPU_HD void fm_load_rec(const FmView &f, int64_t block, FmRec &r)
+{
+#if defined(__CUDA_ARCH__)
+    // one 64-byte record = four 16-byte loads of the same two sectors
+    const uint4 *p = reinterpret_cast<const uint4 *>(f.cp_occ + block * 8);
+    uint4 a = __ldg(p), b = __ldg(p + 1), c = __ldg(p + 2), d = __ldg(p + 3);
+    r.cnt[0] = (int64_t)(((uint64_t)a.y << 32) | a.x); r.cnt[1] = (int64_t)(((uint64_t)a.w << 32) | a.z);
+    r.cnt[2] = (int64_t)(((uint64_t)b.y << 32) | b.x); r.cnt[3] = (int64_t)(((uint64_t)b.w << 32) | b.z);
+    r.bits[0] = ((uint64_t)c.y << 32) | c.x; r.bits[1] = ((uint64_t)c.w << 32) | c.z;
+    r.bits[2] = ((uint64_t)d.y << 32) | d.x; r.bits[3] = ((uint64_t)d.w << 32) | d.z;
+#else
+    const int64_t *p = f.cp_occ + block * 8;
+    for (int i = 0; i < 4; ++i) { r.cnt[i] = p[i]; r.bits[i] = (uint64_t)p[4 + i]; }
+#endif
+}
+
+BWAGPU_HD int fm_popc(uint64_t v)
+{
+#if defined(__CUDA_ARCH__)
+    return __popcll(v);
+#else
+    return __builtin_popcountll(v);
+#endif
+}
+
+// mask selecting the first y symbols of a block (one-hot words are MSB-first)
+BWAGPU_HD uint64_t fm_prefix_mask(int y) { return y ? (~0ULL << (64 - y)) : 0ULL; }
+
+struct Biv { int64_t k, l, s; };
+
+// backward extension of (k,l,s) by base a
+BWAGPU_HD Biv fm_bext(const FmView &f, const Biv &v, int a)
+{
+    const int64_t sp = v.k, ep = v.k + v.s;
+    FmRec rs, re;
+    fm_load_rec(f, sp >> 6, rs);
+    if ((ep >> 6) == (sp >> 6)) re = rs; else fm_load_rec(f, ep >> 6, re);
+    const uint64_t ms = fm_prefix_mask((int)(sp & 63)), me = fm_prefix_mask((int)(ep & 63));
+    int64_t osp[4], sz[4];
+#pragma unroll
+    for (int b = 0; b < 4; ++b) {
+        osp[b] = rs.cnt[b] + fm_popc(rs.bits[b] & ms);
+        sz[b] = re.cnt[b] + fm_popc(re.bits[b] & me) - osp[b];
+    }
+    const int64_t sent = (v.k <= f.sentinel_index && ep > f.sentinel_index) ? 1 : 0;
+    int64_t l3 = v.l + sent, l2 = l3 + sz[3], l1 = l2 + sz[2], l0 = l1 + sz[1];
+    Biv r;
+    r.k = f.count[a] + (a == 0 ? osp[0] : a == 1 ? osp[1] : a == 2 ? osp[2] : osp[3]);
+    r.s = a == 0 ? sz[0] : a == 1 ? sz[1] : a == 2 ? sz[2] : sz[3];
+    r.l = a == 0 ? l0 : a == 1 ? l1 : a == 2 ? l2 : l3;
+    return r;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Per-read seeding state machine.  One bext per step() so that the threads of a warp meet at a
+// single load site; all the bookkeeping between two extensions is register/scratch work.
+//
+// Scratch `prev`: the bi-intervals found while extending forward from a pivot, kept from the END
+// of the buffer downwards so that reading upwards from `base` visits them longest-first (the
+// reference reverses its prevArray in place).  Entry = 3 words: k | n<<40, l, s.
+// Output: up to `cap` SMEMs in `out` (40-byte reference layout); `n_out` keeps counting past cap
+// so the launcher can detect overflow and retry with a larger capacity.
+struct SeedOpt { int min_seed_len, split_len, split_width; int64_t max_mem_intv; };
+
+template <class PrevStore>
+struct SeedMachine {
+    enum { ST_PIVOT, ST_FWD, ST_BROW, ST_BITEM, ST_BEND, ST_NEXT, ST_LSTART, ST_LFWD, ST_DONE };
+    const uint8_t *q;
+    int len, rid;
+    PrevStore prev;
+    bwagpu_smem *out;
+    int cap, n_out;
+    int state, round, x, j, next_x, min_intv;
+    int np, base, p, nc, decided, r1_count, r2_idx;
+    int32_t last_s;
+    Biv cur; int cur_n;
+    Biv req; int req_a;          // pending extension request
+    int64_t n_ext;
+
+    BWAGPU_HD void init(const uint8_t *q_, int len_, int rid_, PrevStore prev_, bwagpu_smem *out_, int cap_)
+    {
+        q = q_; len = len_; rid = rid_; prev = prev_; out = out_; cap = cap_; n_out = 0;
+        round = 1; x = 0; min_intv = 1; state = len > 0 ? ST_PIVOT : ST_DONE; n_ext = 0;
+        np = base = p = nc = decided = r1_count = r2_idx = 0; last_s = -1; j = next_x = 0;
+        cur.k = cur.l = cur.s = 0; cur_n = 0; req = cur; req_a = 0;
+    }
+
+    BWAGPU_HD void emit(int m, int n, const Biv &v)
+    {
+        if (n_out < cap) {
+            bwagpu_smem e;
+            e.rid = (uint32_t)rid; e.m = (uint32_t)m; e.n = (uint32_t)n; e.pad_ = 0;
+            e.k = v.k; e.l = v.l; e.s = v.s;
+            out[n_out] = e;
+        }
+        ++n_out;
+    }
+
+    BWAGPU_HD void single_base(const FmView &f, int a)
+    {
+        cur.k = f.count[a]; cur.l = f.count[3 - a]; cur.s = f.count[a + 1] - f.count[a];
+    }
+
+    BWAGPU_HD void push_prev()                 // forward phase: store below the previous entry
+    {
+        prev.put(len - 1 - np, cur, cur_n);
+    }
+
+    BWAGPU_HD void request_fwd(int a)          // forward ext = backward ext of the complement on (l,k,s)
+    {
+        req.k = cur.l; req.l = cur.k; req.s = cur.s; req_a = 3 - a;
+    }
+
+    // Runs bookkeeping until an extension is needed (returns true, request in req/req_a) or the
+    // read is finished (returns false).
+    BWAGPU_HD bool advance(const FmView &f, const SeedOpt &o)
+    {
+        for (;;) {
+            switch (state) {
+            case ST_PIVOT: {                     // start of a pivot search (rounds 1 and 2)
+                next_x = x + 1;
+                const int a = q[x];
+                if (a > 3) { state = ST_NEXT; break; }
+                single_base(f, a); cur_n = x; np = 0; j = x + 1;
+                state = ST_FWD;
+                break;
+            }
+            case ST_FWD: {
+                if (j < len) {
+                    next_x = j + 1;
+                    const int a = q[j];
+                    if (a < 4) { request_fwd(a); return true; }
+                }
+                // forward phase over: the last interval joins the list if still wide enough
+                if (cur.s >= min_intv) { push_prev(); ++np; }
+                base = len - np; j = x - 1;
+                state = ST_BROW;
+                break;
+            }
+            case ST_BROW: {
+                if (j < 0 || q[j] > 3) { state = ST_BEND; break; }
+                nc = 0; decided = 0; last_s = -1; p = 0;
+                state = ST_BITEM;
+                break;
+            }
+            case ST_BITEM: {
+                if (p < np) {
+                    int n_;
+                    prev.get(base + p, req, n_);
+                    cur_n = n_;                  // span end of the entry being extended
+                    req_a = q[j];
+                    return true;
+                }
+                np = nc;
+                if (np == 0) { state = ST_NEXT; break; }
+                --j;
+                state = ST_BROW;
+                break;
+            }
+            case ST_BEND: {                      // ran off the read start (or hit N) with survivors
+                if (np != 0) {
+                    Biv v; int n_;
+                    prev.get(base, v, n_);
+                    if (n_ - (j + 1) + 1 >= o.min_seed_len) emit(j + 1, n_, v);
+                }
+                state = ST_NEXT;
+                break;
+            }
+            case ST_NEXT: {                      // pivot finished: choose the next piece of work
+                if (round == 1) {
+                    x = next_x;
+                    if (x < len) { state = ST_PIVOT; break; }
+                    round = 2; r1_count = n_out < cap ? n_out : cap; r2_idx = 0;
+                }
+                if (round == 2) {
+                    bool found = false;
+                    while (r2_idx < r1_count) {
+                        const bwagpu_smem e = out[r2_idx++];
+                        const int start = (int)e.m, end = (int)e.n + 1;
+                        if (end - start < o.split_len || e.s > o.split_width) continue;
+                        x = (end + start) >> 1; min_intv = (int)(e.s + 1);
+                        found = true;
+                        break;
+                    }
+                    if (found) { state = ST_PIVOT; break; }
+                    round = 3; x = 0;
+                    if (o.max_mem_intv <= 0) { state = ST_DONE; break; }
+                    state = ST_LSTART;
+                    break;
+                }
+                state = ST_DONE;
+                break;
+            }
+            case ST_LSTART: {                    // round 3: forward-only, restart after each seed
+                if (x >= len) { state = ST_DONE; break; }
+                next_x = x + 1;
+                const int a = q[x];
+                if (a > 3) { x = next_x; break; }
+                single_base(f, a); cur_n = x; j = x + 1;
+                state = ST_LFWD;
+                break;
+            }
+            case ST_LFWD: {
+                if (j < len) {
+                    next_x = j + 1;
+                    const int a = q[j];
+                    if (a < 4) { request_fwd(a); return true; }
+                }
+                x = next_x;
+                state = ST_LSTART;
+                break;
+            }
+            default:
+                return false;
+            }
+        }
+    }
+
+    // Consumes the result of the requested extension.
+    BWAGPU_HD void consume(const Biv &r, const SeedOpt &o)
+    {
+        ++n_ext;
+        if (state == ST_FWD) {
+            Biv nw; nw.k = r.l; nw.l = r.k; nw.s = r.s;
+            if (nw.s != cur.s) { push_prev(); ++np; }
+            if (nw.s < min_intv) {
+                next_x = j;
+                // The reference stores `cur` a second time here (its post-loop push sees the
+                // un-replaced interval).  The twin can never change an outcome in the backward
+                // phase (it dies, or survives with the same s, exactly as its original does), so
+                // it is not materialised: one backward extension fewer per pivot.
+                base = len - np; j = x - 1;
+                state = ST_BROW;
+                return;
+            }
+            cur = nw; cur_n = j; ++j;
+        } else if (state == ST_BITEM) {
+            // r extends entry p to the left by q[j]; entries of this row start at m = j + 1
+            if (r.s < min_intv) {
+                if (!decided && cur_n - (j + 1) + 1 >= o.min_seed_len) {
+                    emit(j + 1, cur_n, req);
+                    decided = 1;
+                }
+            } else if (r.s != (int64_t)last_s) {
+                last_s = (int32_t)r.s;
+                prev.put(base + nc, r, cur_n);
+                ++nc;
+                decided = 1;
+            }
+            ++p;
+        } else {                                 // ST_LFWD
+            cur.k = r.l; cur.l = r.k; cur.s = r.s; cur_n = j;
+            if (cur.s < o.max_mem_intv && cur_n - x + 1 >= o.min_seed_len + 1) {
+                if (cur.s > 0) emit(x, cur_n, cur);
+                x = next_x;
+                state = ST_LSTART;
+            } else {
+                ++j;
+            }
+        }
+    }
+};
+
+// SA look-up of one BWT row: LF-walk to the next sampled row (every 8th), add the steps walked.
+// A walk that lands on the sentinel row yields 0 (the steps are discarded), as call_one_step does.
+BWAGPU_HD int64_t fm_sa_walk(const FmView &f, int64_t pos, int *steps)
+{
+    int64_t walked = 0;
+    for (;;) {
+        if ((pos & 7) == 0) {
+            if (steps) *steps = (int)walked;
+            return ((int64_t)f.sa_ms_byte[pos >> 3] << 32) + (int64_t)f.sa_ls_word[pos >> 3] + walked;
+        }
+        FmRec r;
+        fm_load_rec(f, pos >> 6, r);
+        const int sh = 63 - (int)(pos & 63);
+        int b = 4;
+        if ((r.bits[0] >> sh) & 1) b = 0;
+        else if ((r.bits[1] >> sh) & 1) b = 1;
+        else if ((r.bits[2] >> sh) & 1) b = 2;
+        else if ((r.bits[3] >> sh) & 1) b = 3;
+        if (b == 4) { if (steps) *steps = (int)walked; return 0; }
+        const uint64_t m = fm_prefix_mask((int)(pos & 63));
+        pos = f.count[b] + r.cnt[b] + fm_popc(r.bits[b] & m);
+        ++walked;
+    }
+}
+
+// rows an SMEM contributes: k, k+step, ... below k+s, at most max_occ of them
+BWAGPU_HD int fm_sa_rows(int64_t s, int max_occ, int64_t *step_out)
+{
+    const int64_t step = s > max_occ ? s / max_occ : 1;
+    if (step_out) *step_out = step;
+    int64_t c = (s + step - 1) / step;
+    if (c > max_occ) c = max_occ;
+    if (c < 0) c = 0;
+    return (int)c;
+}

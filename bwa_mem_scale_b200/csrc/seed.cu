@@ -1,0 +1,401 @@
+// S1 seeding seam of the C ABI (include/bwagpu.h): FM-index replica upload, SMEM collection
+// (three seeding rounds + canonical order) and batched suffix-array look-up.
+// Replaces mem_collect_smem (reference src/bwamem.cpp:648-786) and
+// FMI_search::get_sa_entries_prefetch (reference src/FMI_search.cpp:2261-2379).
+//
+// Kernels:
+//   seed_collect_kernel  one read per thread, persistent threads; every loop iteration performs
+//                        exactly one backward extension (two 64-byte CP_OCC records, one when
+//                        k and k+s share a block), so a warp's 32 reads meet at one load site.
+//   seed_sort_kernel     per read: order its SMEMs by (m, n) and copy them to their final slot.
+//   sa_count_kernel      rows each SMEM contributes (min(max_occ, ceil(s/step))).
+//   sa_walk_kernel       one thread per output coordinate: LF walk to the next sampled row.
+#include <cub/device/device_scan.cuh>
+#include "ctx.cuh"
+#include "fmi_core.cuh"
+
+#define SEED_TPB 128
+
+// prev list of one thread inside the interleaved scratch: word w of entry e of thread t lives at
+// buf[(e*3 + w) * stride + t]
+struct DevPrev {
+    int64_t *buf;
+    int64_t stride;
+    __device__ __forceinline__ void put(int e, const Biv &v, int n)
+    {
+        int64_t *p = buf + (int64_t)e * 3 * stride;
+        p[0] = v.k | ((int64_t)n << 40); p[stride] = v.l; p[2 * stride] = v.s;
+    }
+    __device__ __forceinline__ void get(int e, Biv &v, int &n) const
+    {
+        const int64_t *p = buf + (int64_t)e * 3 * stride;
+        const int64_t w0 = p[0];
+        v.k = w0 & ((1LL << 40) - 1); n = (int)(w0 >> 40); v.l = p[stride]; v.s = p[2 * stride];
+    }
+};
+
+struct SeedStats { unsigned long long n_ext, n_rec, n_lf, max_cnt; };
+
+__global__ void __launch_bounds__(SEED_TPB)
+seed_collect_kernel(FmView f, SeedOpt o, const uint8_t *__restrict__ reads,
+                    const int64_t *__restrict__ off, const int32_t *__restrict__ len,
+                    const uint8_t *__restrict__ skip, int nseq, bwagpu_smem *__restrict__ tmp,
+                    int cap, int32_t *__restrict__ cnt, int64_t *__restrict__ prev_buf,
+                    SeedStats *__restrict__ stats)
+{
+    const int64_t T = (int64_t)gridDim.x * blockDim.x;
+    const int64_t t0 = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    DevPrev pv; pv.buf = prev_buf + t0; pv.stride = T;
+    SeedMachine<DevPrev> m;
+    int64_t next = t0;
+    bool active = false;
+    unsigned long long n_ext = 0, n_rec = 0;
+    unsigned int max_cnt = 0;
+    for (;;) {
+        if (!active) {
+            // pick up the next read of this thread's stride
+            bool got = false;
+            while (next < nseq) {
+                const int i = (int)next; next += T;
+                if (skip && skip[i]) { cnt[i] = 0; continue; }
+                m.init(reads + off[i], len[i], i, pv, tmp + (int64_t)i * cap, cap);
+                got = true;
+                break;
+            }
+            if (!got) break;
+            active = true;
+        }
+        if (!m.advance(f, o)) {
+            cnt[m.rid] = m.n_out;
+            max_cnt = max(max_cnt, (unsigned)m.n_out);
+            active = false;
+            continue;
+        }
+        n_rec += ((m.req.k >> 6) == ((m.req.k + m.req.s) >> 6)) ? 1 : 2;
+        ++n_ext;
+        const Biv r = fm_bext(f, m.req, m.req_a);
+        m.consume(r, o);
+    }
+    // per-warp then global statistics
+    for (int d = 16; d; d >>= 1) {
+        n_ext += __shfl_down_sync(0xffffffffu, n_ext, d);
+        n_rec += __shfl_down_sync(0xffffffffu, n_rec, d);
+        max_cnt = max(max_cnt, __shfl_down_sync(0xffffffffu, max_cnt, d));
+    }
+    if ((threadIdx.x & 31) == 0) {
+        atomicAdd(&stats->n_ext, n_ext);
+        atomicAdd(&stats->n_rec, n_rec);
+        atomicMax(&stats->max_cnt, (unsigned long long)max_cnt);
+    }
+}
+
+// Per read: rank its SMEMs by (m, n) and write them to out[offs[i] ..].  Equal keys are
+// identical entries (same substring => same interval), so any order among them is the reference's.
+__global__ void seed_sort_kernel(const bwagpu_smem *__restrict__ tmp, int cap,
+                                 const int32_t *__restrict__ cnt, const int64_t *__restrict__ offs,
+                                 int nseq, bwagpu_smem *__restrict__ out)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= nseq) return;
+    const int n = cnt[i];
+    const bwagpu_smem *src = tmp + (int64_t)i * cap;
+    bwagpu_smem *dst = out + offs[i];
+    for (int e = 0; e < n; ++e) {
+        const uint64_t key = ((uint64_t)src[e].m << 32) | src[e].n;
+        int rank = 0;
+        for (int g = 0; g < n; ++g) {
+            const uint64_t kg = ((uint64_t)src[g].m << 32) | src[g].n;
+            rank += (kg < key) || (kg == key && g < e);
+        }
+        dst[rank] = src[e];
+    }
+}
+
+__global__ void sa_count_kernel(const bwagpu_smem *__restrict__ sm, int64_t n, int max_occ,
+                                int64_t *__restrict__ rows)
+{
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) rows[i] = fm_sa_rows(sm[i].s, max_occ, nullptr);
+}
+
+__global__ void sa_walk_kernel(FmView f, const bwagpu_smem *__restrict__ sm, int64_t n_smem,
+                               const int64_t *__restrict__ offs, int64_t n_coords, int max_occ,
+                               int64_t *__restrict__ coords, SeedStats *__restrict__ stats)
+{
+    const int64_t c = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    unsigned long long lf = 0;
+    if (c < n_coords) {
+        // the SMEM this coordinate belongs to: last i with offs[i] <= c
+        int64_t lo = 0, hi = n_smem - 1;
+        while (lo < hi) {
+            const int64_t mid = (lo + hi + 1) >> 1;
+            if (offs[mid] <= c) lo = mid; else hi = mid - 1;
+        }
+        const int64_t s = sm[lo].s, k = sm[lo].k;
+        const int64_t step = s > max_occ ? s / max_occ : 1;
+        int steps = 0;
+        coords[c] = fm_sa_walk(f, k + (c - offs[lo]) * step, &steps);
+        lf = (unsigned long long)steps;
+    }
+    for (int d = 16; d; d >>= 1) lf += __shfl_down_sync(0xffffffffu, lf, d);
+    if ((threadIdx.x & 31) == 0 && lf) atomicAdd(&stats->n_lf, lf);
+}
+
+// ---------------------------------------------------------------------------------------------
+static FmView fm_view(const bwagpu_ctx *ctx)
+{
+    FmView f;
+    f.cp_occ = (const int64_t *)ctx->d_cp_occ;
+    f.sa_ms_byte = (const int8_t *)ctx->d_sa_ms;
+    f.sa_ls_word = (const uint32_t *)ctx->d_sa_ls;
+    for (int i = 0; i < 5; ++i) f.count[i] = ctx->fm_count[i];
+    f.sentinel_index = ctx->fm_sentinel;
+    f.ref_seq_len = ctx->fm_ref_seq_len;
+    return f;
+}
+
+extern "C" int bwagpu_index_load_fm(bwagpu_ctx *ctx, const bwagpu_fm_index_desc *d)
+{
+    if (!ctx) return BWAGPU_ERR_ARG;
+    if (!d || !d->cp_occ || !d->sa_ms_byte || !d->sa_ls_word || d->reference_seq_len <= 0)
+        BWAGPU_FAIL(ctx, BWAGPU_ERR_ARG, "index_load_fm: incomplete index descriptor");
+    BWAGPU_CUDA(ctx, cudaSetDevice(ctx->device));
+    BWAGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    if (ctx->d_cp_occ) { cudaFree(ctx->d_cp_occ); cudaFree(ctx->d_sa_ms); cudaFree(ctx->d_sa_ls); }
+    ctx->d_cp_occ = ctx->d_sa_ms = ctx->d_sa_ls = nullptr;
+    ctx->has_fm = false;
+    const int64_t n_cp = (d->reference_seq_len >> 6) + 1, n_sa = (d->reference_seq_len >> 3) + 1;
+    BWAGPU_CUDA(ctx, cudaMalloc(&ctx->d_cp_occ, (size_t)n_cp * 64));
+    BWAGPU_CUDA(ctx, cudaMalloc(&ctx->d_sa_ms, (size_t)n_sa));
+    BWAGPU_CUDA(ctx, cudaMalloc(&ctx->d_sa_ls, (size_t)n_sa * 4));
+    BWAGPU_CUDA(ctx, cudaMemcpyAsync(ctx->d_cp_occ, d->cp_occ, (size_t)n_cp * 64, cudaMemcpyHostToDevice, ctx->stream));
+    BWAGPU_CUDA(ctx, cudaMemcpyAsync(ctx->d_sa_ms, d->sa_ms_byte, (size_t)n_sa, cudaMemcpyHostToDevice, ctx->stream));
+    BWAGPU_CUDA(ctx, cudaMemcpyAsync(ctx->d_sa_ls, d->sa_ls_word, (size_t)n_sa * 4, cudaMemcpyHostToDevice, ctx->stream));
+    BWAGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    for (int i = 0; i < 5; ++i) ctx->fm_count[i] = d->count[i];
+    ctx->fm_sentinel = d->sentinel_index;
+    ctx->fm_ref_seq_len = d->reference_seq_len;
+    ctx->has_fm = true;
+    return BWAGPU_OK;
+}
+
+static int seed_check(bwagpu_ctx *ctx, const bwagpu_seed_opt *opt)
+{
+    if (!ctx) return BWAGPU_ERR_ARG;
+    if (!opt) BWAGPU_FAIL(ctx, BWAGPU_ERR_ARG, "seed: options are NULL");
+    if (!ctx->has_fm) BWAGPU_FAIL(ctx, BWAGPU_ERR_ARG, "seed: no FM-index loaded (bwagpu_index_load_fm)");
+    if (opt->min_seed_len < 1 || opt->max_occ < 1)
+        BWAGPU_FAIL(ctx, BWAGPU_ERR_ARG, "seed: min_seed_len and max_occ must be positive");
+    return BWAGPU_OK;
+}
+
+static int scan_i32_to_i64(bwagpu_ctx *ctx, const int32_t *d_in, int64_t *d_out, int64_t n)
+{
+    size_t bytes = 0;
+    cub::DeviceScan::ExclusiveScan((void *)nullptr, bytes, d_in, d_out, cub::Sum(), (int64_t)0, (int)n, ctx->stream);
+    void *tmp;
+    int rc = bwagpu_scratch(ctx, SCR_CUB, (int64_t)bytes + 256, &tmp);
+    if (rc) return rc;
+    BWAGPU_CUDA(ctx, cub::DeviceScan::ExclusiveScan(tmp, bytes, d_in, d_out, cub::Sum(), (int64_t)0, (int)n, ctx->stream));
+    ctx->launches += 2;      // CUB's scan is two kernels (tile state init + scan)
+    return BWAGPU_OK;
+}
+
+static int scan_i64(bwagpu_ctx *ctx, const int64_t *d_in, int64_t *d_out, int64_t n)
+{
+    size_t bytes = 0;
+    cub::DeviceScan::ExclusiveSum((void *)nullptr, bytes, d_in, d_out, (int)n, ctx->stream);
+    void *tmp;
+    int rc = bwagpu_scratch(ctx, SCR_CUB, (int64_t)bytes + 256, &tmp);
+    if (rc) return rc;
+    BWAGPU_CUDA(ctx, cub::DeviceScan::ExclusiveSum(tmp, bytes, d_in, d_out, (int)n, ctx->stream));
+    ctx->launches += 2;
+    return BWAGPU_OK;
+}
+
+// SMEM collection with device-resident reads; *d_out is context-owned (SCR_SEED_OUT).
+static int seed_collect_dev(bwagpu_ctx *ctx, const bwagpu_seed_opt *opt, const uint8_t *d_reads,
+                            const int64_t *d_off, const int32_t *d_len, const uint8_t *d_skip,
+                            int32_t nseq, int32_t max_len, bwagpu_smem **d_out, int64_t *tot,
+                            SeedStats *h_stats)
+{
+    *tot = 0; *d_out = nullptr;
+    memset(h_stats, 0, sizeof *h_stats);
+    if (nseq == 0) return BWAGPU_OK;
+    SeedOpt so;
+    so.min_seed_len = opt->min_seed_len;
+    so.split_len = (int)(opt->min_seed_len * opt->split_factor + .499);
+    so.split_width = opt->split_width;
+    so.max_mem_intv = opt->max_mem_intv;
+    int per_sm = 0;
+    BWAGPU_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, seed_collect_kernel, SEED_TPB, 0));
+    if (per_sm < 1) per_sm = 1;
+    int blocks = ctx->sm_count * per_sm;
+    const int need = (nseq + SEED_TPB - 1) / SEED_TPB;
+    if (blocks > need) blocks = need;
+    const int64_t T = (int64_t)blocks * SEED_TPB;
+    if (ctx->seed_read_cap < 32) ctx->seed_read_cap = 32;
+    int32_t *d_cnt; int64_t *d_offs, *d_prev; SeedStats *d_stats; bwagpu_smem *d_tmp;
+    int rc;
+    if ((rc = bwagpu_scratch(ctx, SCR_SEED_CNT, (int64_t)(nseq + 1) * 4, (void **)&d_cnt))) return rc;
+    if ((rc = bwagpu_scratch(ctx, SCR_SEED_SCAN, (int64_t)(nseq + 1) * 8, (void **)&d_offs))) return rc;
+    if ((rc = bwagpu_scratch(ctx, SCR_SEED_PREV, T * 3 * (int64_t)(max_len + 1) * 8, (void **)&d_prev))) return rc;
+    if ((rc = bwagpu_scratch(ctx, SCR_STATS, sizeof(SeedStats), (void **)&d_stats))) return rc;
+    for (;;) {
+        const int cap = ctx->seed_read_cap;
+        if ((rc = bwagpu_scratch(ctx, SCR_SEED_TMP, (int64_t)nseq * cap * sizeof(bwagpu_smem), (void **)&d_tmp))) return rc;
+        BWAGPU_CUDA(ctx, cudaMemsetAsync(d_stats, 0, sizeof(SeedStats), ctx->stream));
+        BWAGPU_CUDA(ctx, cudaMemsetAsync(d_cnt + nseq, 0, 4, ctx->stream));
+        BWAGPU_KERNEL_BEGIN(ctx);
+        seed_collect_kernel<<<blocks, SEED_TPB, 0, ctx->stream>>>(fm_view(ctx), so, d_reads, d_off, d_len, d_skip,
+                                                                 nseq, d_tmp, cap, d_cnt, d_prev, d_stats);
+        BWAGPU_KERNEL_END(ctx, BWAGPU_KERN_SEED_COLLECT);
+        BWAGPU_CUDA(ctx, cudaGetLastError());
+        BWAGPU_CUDA(ctx, cudaMemcpyAsync(h_stats, d_stats, sizeof(SeedStats), cudaMemcpyDeviceToHost, ctx->stream));
+        BWAGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+        if ((int64_t)h_stats->max_cnt <= cap) break;
+        int ncap = cap;
+        while (ncap < (int64_t)h_stats->max_cnt) ncap *= 2;     // some read overflowed: redo with room
+        ctx->seed_read_cap = ncap;
+    }
+    if ((rc = scan_i32_to_i64(ctx, d_cnt, d_offs, nseq + 1))) return rc;
+    int64_t total = 0;
+    BWAGPU_CUDA(ctx, cudaMemcpyAsync(&total, d_offs + nseq, 8, cudaMemcpyDeviceToHost, ctx->stream));
+    BWAGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    bwagpu_smem *out;
+    if ((rc = bwagpu_scratch(ctx, SCR_SEED_OUT, (total + 1) * (int64_t)sizeof(bwagpu_smem), (void **)&out))) return rc;
+    BWAGPU_KERNEL_BEGIN(ctx);
+    seed_sort_kernel<<<(nseq + 127) / 128, 128, 0, ctx->stream>>>(d_tmp, ctx->seed_read_cap, d_cnt, d_offs, nseq, out);
+    BWAGPU_KERNEL_END(ctx, BWAGPU_KERN_SEED_SORT);
+    BWAGPU_CUDA(ctx, cudaGetLastError());
+    *d_out = out; *tot = total;
+    return BWAGPU_OK;
+}
+
+// SA look-up with device-resident SMEMs; outputs context-owned (SCR_SA_COORD / SCR_SA_OFF).
+static int sa_lookup_dev(bwagpu_ctx *ctx, const bwagpu_smem *d_sm, int64_t n, int32_t max_occ,
+                         int64_t **d_coords, int64_t **d_coord_off, int64_t *n_coords, SeedStats *h_stats)
+{
+    *n_coords = 0; *d_coords = nullptr; *d_coord_off = nullptr;
+    int64_t *rows, *offs; SeedStats *d_stats;
+    int rc;
+    if ((rc = bwagpu_scratch(ctx, SCR_SA_CNT, (n + 1) * 8, (void **)&rows))) return rc;
+    if ((rc = bwagpu_scratch(ctx, SCR_SA_OFF, (n + 1) * 8, (void **)&offs))) return rc;
+    if ((rc = bwagpu_scratch(ctx, SCR_STATS, sizeof(SeedStats), (void **)&d_stats))) return rc;
+    *d_coord_off = offs;
+    BWAGPU_CUDA(ctx, cudaMemsetAsync(rows + n, 0, 8, ctx->stream));
+    BWAGPU_CUDA(ctx, cudaMemsetAsync(&d_stats->n_lf, 0, 8, ctx->stream));
+    if (n > 0) {
+        sa_count_kernel<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(d_sm, n, max_occ, rows);
+        ctx->launches++;
+    }
+    if ((rc = scan_i64(ctx, rows, offs, n + 1))) return rc;
+    int64_t total = 0;
+    BWAGPU_CUDA(ctx, cudaMemcpyAsync(&total, offs + n, 8, cudaMemcpyDeviceToHost, ctx->stream));
+    BWAGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    int64_t *coords;
+    if ((rc = bwagpu_scratch(ctx, SCR_SA_COORD, (total + 1) * 8, (void **)&coords))) return rc;
+    if (total > 0) {
+        BWAGPU_KERNEL_BEGIN(ctx);
+        sa_walk_kernel<<<(unsigned)((total + 255) / 256), 256, 0, ctx->stream>>>(fm_view(ctx), d_sm, n, offs, total,
+                                                                               max_occ, coords, d_stats);
+        BWAGPU_KERNEL_END(ctx, BWAGPU_KERN_SA_WALK);
+        BWAGPU_CUDA(ctx, cudaGetLastError());
+    }
+    if (h_stats) {
+        BWAGPU_CUDA(ctx, cudaMemcpyAsync(&h_stats->n_lf, &d_stats->n_lf, 8, cudaMemcpyDeviceToHost, ctx->stream));
+        BWAGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    }
+    *d_coords = coords; *n_coords = total;
+    return BWAGPU_OK;
+}
+
+extern "C" int bwagpu_seed_fm_device(bwagpu_ctx *ctx, const bwagpu_seed_opt *opt, const uint8_t *d_reads,
+                                     const int64_t *d_off, const int32_t *d_len, const uint8_t *d_skip,
+                                     int32_t nseq, int32_t max_len, bwagpu_seed_result *res)
+{
+    int rc = seed_check(ctx, opt);
+    if (rc) return rc;
+    if (!res || nseq < 0 || max_len < 0) BWAGPU_FAIL(ctx, BWAGPU_ERR_ARG, "seed_fm_device: bad argument");
+    memset(res, 0, sizeof *res);
+    BWAGPU_CUDA(ctx, cudaSetDevice(ctx->device));
+    bwagpu_smem *d_sm; int64_t tot;
+    SeedStats st;
+    if ((rc = seed_collect_dev(ctx, opt, d_reads, d_off, d_len, d_skip, nseq, max_len, &d_sm, &tot, &st))) return rc;
+    int64_t *d_coords, *d_coff, nc;
+    SeedStats st2; memset(&st2, 0, sizeof st2);
+    if (tot > 0) {
+        if ((rc = sa_lookup_dev(ctx, d_sm, tot, opt->max_occ, &d_coords, &d_coff, &nc, &st2))) return rc;
+        res->d_coords = d_coords; res->n_coords = nc; res->d_coord_off = d_coff;
+    }
+    res->d_smems = d_sm; res->n_smem = tot;
+    res->n_ext = (int64_t)st.n_ext; res->n_cp_records = (int64_t)st.n_rec; res->n_lf_steps = (int64_t)st2.n_lf;
+    return BWAGPU_OK;
+}
+
+extern "C" int bwagpu_collect_smem(bwagpu_ctx *ctx, const bwagpu_seed_opt *opt, const uint8_t *enc_reads,
+                                   const int64_t *off, const int32_t *len, const uint8_t *skip, int32_t nseq,
+                                   bwagpu_smem *out, int64_t out_cap, int64_t *tot_smem)
+{
+    int rc = seed_check(ctx, opt);
+    if (rc) return rc;
+    if (!tot_smem || nseq < 0) BWAGPU_FAIL(ctx, BWAGPU_ERR_ARG, "collect_smem: bad argument");
+    *tot_smem = 0;
+    if (nseq == 0) return BWAGPU_OK;
+    if (!enc_reads || !off || !len) BWAGPU_FAIL(ctx, BWAGPU_ERR_ARG, "collect_smem: NULL buffer");
+    BWAGPU_CUDA(ctx, cudaSetDevice(ctx->device));
+    int64_t bytes = 0; int max_len = 0;
+    for (int i = 0; i < nseq; ++i) {
+        if (len[i] < 0 || off[i] < 0) BWAGPU_FAIL(ctx, BWAGPU_ERR_ARG, "collect_smem: read %d has a negative length/offset", i);
+        if (len[i] > 32767) BWAGPU_FAIL(ctx, BWAGPU_ERR_RANGE, "collect_smem: read %d longer than 32767 (int16 query positions upstream)", i);
+        if (off[i] + len[i] > bytes) bytes = off[i] + len[i];
+        if (len[i] > max_len) max_len = len[i];
+    }
+    uint8_t *d_reads, *d_skip = nullptr; int64_t *d_off; int32_t *d_len;
+    if ((rc = bwagpu_scratch(ctx, SCR_SEED_READS, bytes + 16, (void **)&d_reads))) return rc;
+    if ((rc = bwagpu_scratch(ctx, SCR_SEED_OFF, (int64_t)nseq * 8, (void **)&d_off))) return rc;
+    if ((rc = bwagpu_scratch(ctx, SCR_SEED_LEN, (int64_t)nseq * 4, (void **)&d_len))) return rc;
+    BWAGPU_CUDA(ctx, cudaMemcpyAsync(d_reads, enc_reads, (size_t)bytes, cudaMemcpyHostToDevice, ctx->stream));
+    BWAGPU_CUDA(ctx, cudaMemcpyAsync(d_off, off, (size_t)nseq * 8, cudaMemcpyHostToDevice, ctx->stream));
+    BWAGPU_CUDA(ctx, cudaMemcpyAsync(d_len, len, (size_t)nseq * 4, cudaMemcpyHostToDevice, ctx->stream));
+    if (skip) {
+        if ((rc = bwagpu_scratch(ctx, SCR_SEED_SKIP, nseq, (void **)&d_skip))) return rc;
+        BWAGPU_CUDA(ctx, cudaMemcpyAsync(d_skip, skip, (size_t)nseq, cudaMemcpyHostToDevice, ctx->stream));
+    }
+    bwagpu_smem *d_sm; int64_t tot; SeedStats st;
+    if ((rc = seed_collect_dev(ctx, opt, d_reads, d_off, d_len, d_skip, nseq, max_len, &d_sm, &tot, &st))) return rc;
+    *tot_smem = tot;
+    if (tot > out_cap) BWAGPU_FAIL(ctx, BWAGPU_ERR_RANGE, "collect_smem: %lld SMEMs do not fit out_cap=%lld", (long long)tot, (long long)out_cap);
+    if (tot > 0) {
+        if (!out) BWAGPU_FAIL(ctx, BWAGPU_ERR_ARG, "collect_smem: out is NULL");
+        BWAGPU_CUDA(ctx, cudaMemcpyAsync(out, d_sm, (size_t)tot * sizeof(bwagpu_smem), cudaMemcpyDeviceToHost, ctx->stream));
+    }
+    BWAGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return BWAGPU_OK;
+}
+
+extern "C" int bwagpu_get_sa_entries(bwagpu_ctx *ctx, const bwagpu_smem *smems, int64_t n_smem, int32_t max_occ,
+                                     int64_t *coords, int64_t coords_cap, int64_t *n_coords)
+{
+    if (!ctx) return BWAGPU_ERR_ARG;
+    if (!ctx->has_fm) BWAGPU_FAIL(ctx, BWAGPU_ERR_ARG, "get_sa_entries: no FM-index loaded");
+    if (!n_coords || n_smem < 0 || max_occ < 1) BWAGPU_FAIL(ctx, BWAGPU_ERR_ARG, "get_sa_entries: bad argument");
+    *n_coords = 0;
+    if (n_smem == 0) return BWAGPU_OK;
+    if (!smems) BWAGPU_FAIL(ctx, BWAGPU_ERR_ARG, "get_sa_entries: smems is NULL");
+    BWAGPU_CUDA(ctx, cudaSetDevice(ctx->device));
+    bwagpu_smem *d_sm;
+    int rc;
+    if ((rc = bwagpu_scratch(ctx, SCR_SA_IN, n_smem * (int64_t)sizeof(bwagpu_smem), (void **)&d_sm))) return rc;
+    BWAGPU_CUDA(ctx, cudaMemcpyAsync(d_sm, smems, (size_t)n_smem * sizeof(bwagpu_smem), cudaMemcpyHostToDevice, ctx->stream));
+    int64_t *d_coords, *d_coff, nc;
+    if ((rc = sa_lookup_dev(ctx, d_sm, n_smem, max_occ, &d_coords, &d_coff, &nc, nullptr))) return rc;
+    *n_coords = nc;
+    if (nc > coords_cap) BWAGPU_FAIL(ctx, BWAGPU_ERR_RANGE, "get_sa_entries: %lld coordinates do not fit coords_cap=%lld", (long long)nc, (long long)coords_cap);
+    if (nc > 0) {
+        if (!coords) BWAGPU_FAIL(ctx, BWAGPU_ERR_ARG, "get_sa_entries: coords is NULL");
+        BWAGPU_CUDA(ctx, cudaMemcpyAsync(coords, d_coords, (size_t)nc * 8, cudaMemcpyDeviceToHost, ctx->stream));
+    }
+    BWAGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return BWAGPU_OK;
+}

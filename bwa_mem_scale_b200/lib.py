@@ -23,6 +23,25 @@ class BswParams(C.Structure):
                 ("o_del", "e_del", "o_ins", "e_ins", "zdrop", "end_bonus", "w_match", "w_mismatch")]
 
 
+class FmIndexDesc(C.Structure):
+    """bwagpu_fm_index_desc — the arrays FMI_search::load_index leaves in memory
+    (reference src/FMI_search.cpp:1251-1351); count[] in loaded form (file value + 1)."""
+    _fields_ = [("reference_seq_len", C.c_int64), ("count", C.c_int64 * 5), ("cp_occ", C.c_void_p),
+                ("sa_ms_byte", C.c_void_p), ("sa_ls_word", C.c_void_p), ("sentinel_index", C.c_int64)]
+
+
+class SeedOpt(C.Structure):
+    """bwagpu_seed_opt — the mem_opt_t fields seeding reads (reference src/bwamem.h:89-124)."""
+    _fields_ = [("min_seed_len", C.c_int32), ("split_factor", C.c_float), ("split_width", C.c_int32),
+                ("max_occ", C.c_int32), ("max_mem_intv", C.c_int64)]
+
+
+class SeedResult(C.Structure):
+    _fields_ = [("d_smems", C.c_void_p), ("n_smem", C.c_int64), ("d_coords", C.c_void_p),
+                ("n_coords", C.c_int64), ("d_coord_off", C.c_void_p), ("n_ext", C.c_int64),
+                ("n_cp_records", C.c_int64), ("n_lf_steps", C.c_int64)]
+
+
 _lib = None
 
 # name -> (restype, argtypes); every symbol include/bwagpu.h declares
@@ -33,17 +52,29 @@ _SIGS = {
     "bwagpu_device_count": (C.c_int, []),
     "bwagpu_synchronize": (C.c_int, [C.c_void_p]),
     "bwagpu_launch_count": (C.c_int64, [C.c_void_p]),
+    "bwagpu_set_profiling": (C.c_int, [C.c_void_p, C.c_int]),
+    "bwagpu_kernel_time": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_int64)]),
     "bwagpu_timer_start": (C.c_int, [C.c_void_p]),
     "bwagpu_timer_stop": (C.c_int, [C.c_void_p, C.POINTER(C.c_float)]),
     "bwagpu_malloc": (C.c_int, [C.c_void_p, C.c_int64, C.POINTER(C.c_void_p)]),
     "bwagpu_free": (C.c_int, [C.c_void_p, C.c_void_p]),
     "bwagpu_h2d": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64]),
     "bwagpu_d2h": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64]),
+    "bwagpu_memset": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int64]),
     "bwagpu_bsw_get_scores": (C.c_int, [C.c_void_p, C.POINTER(BswParams), C.c_int, C.c_void_p,
                                         C.c_void_p, C.c_void_p, C.c_int32, C.c_int32]),
     "bwagpu_bsw_get_scores_device": (C.c_int, [C.c_void_p, C.POINTER(BswParams), C.c_int,
                                                C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p,
                                                C.c_int64, C.c_int32, C.c_int32]),
+    "bwagpu_index_load_fm": (C.c_int, [C.c_void_p, C.POINTER(FmIndexDesc)]),
+    "bwagpu_collect_smem": (C.c_int, [C.c_void_p, C.POINTER(SeedOpt), C.c_void_p, C.c_void_p,
+                                      C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p, C.c_int64,
+                                      C.POINTER(C.c_int64)]),
+    "bwagpu_get_sa_entries": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_void_p,
+                                        C.c_int64, C.POINTER(C.c_int64)]),
+    "bwagpu_seed_fm_device": (C.c_int, [C.c_void_p, C.POINTER(SeedOpt), C.c_void_p, C.c_void_p,
+                                        C.c_void_p, C.c_void_p, C.c_int32, C.c_int32,
+                                        C.POINTER(SeedResult)]),
 }
 
 
@@ -116,6 +147,14 @@ class Context:
         self.check(self.lib.bwagpu_timer_stop(self.h, C.byref(ms)), "timer_stop")
         return float(ms.value)
 
+    def set_profiling(self, on: bool) -> None:
+        self.check(self.lib.bwagpu_set_profiling(self.h, 1 if on else 0), "set_profiling")
+
+    def kernel_time(self, which: int) -> tuple[float, int]:
+        ms, n = C.c_double(), C.c_int64()
+        self.check(self.lib.bwagpu_kernel_time(self.h, which, C.byref(ms), C.byref(n)), "kernel_time")
+        return float(ms.value), int(n.value)
+
     def malloc(self, nbytes: int) -> int:
         p = C.c_void_p()
         self.check(self.lib.bwagpu_malloc(self.h, int(nbytes), C.byref(p)), "malloc")
@@ -129,6 +168,9 @@ class Context:
 
     def d2h(self, arr, dptr: int) -> None:
         self.check(self.lib.bwagpu_d2h(self.h, arr.ctypes.data, C.c_void_p(dptr), arr.nbytes), "d2h")
+
+    def memset(self, dptr: int, value: int, nbytes: int) -> None:
+        self.check(self.lib.bwagpu_memset(self.h, C.c_void_p(dptr), value, int(nbytes)), "memset")
 
     def upload(self, arr) -> int:
         import numpy as np

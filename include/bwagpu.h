@@ -41,11 +41,20 @@ int64_t bwagpu_launch_count(const bwagpu_ctx *ctx);
 int bwagpu_timer_start(bwagpu_ctx *ctx);
 int bwagpu_timer_stop(bwagpu_ctx *ctx, float *elapsed_ms);   /* records, synchronises, reports */
 
+/* Per-kernel device time, for roofline reporting: when profiling is on every launch of the listed
+ * kernels is bracketed by CUDA events on the context's stream (this serialises the stream, so
+ * leave it off when measuring whole-step throughput).  set_profiling also clears the counters. */
+enum { BWAGPU_KERN_SEED_COLLECT = 0, BWAGPU_KERN_SEED_SORT = 1, BWAGPU_KERN_SA_WALK = 2,
+       BWAGPU_KERN_BSW = 3, BWAGPU_KERN_N = 8 };
+int bwagpu_set_profiling(bwagpu_ctx *ctx, int on);
+int bwagpu_kernel_time(const bwagpu_ctx *ctx, int which, double *ms, int64_t *launches);
+
 /* raw device memory helpers for callers that keep inputs resident in HBM */
 int bwagpu_malloc(bwagpu_ctx *ctx, int64_t bytes, void **dptr);
 int bwagpu_free(bwagpu_ctx *ctx, void *dptr);
 int bwagpu_h2d(bwagpu_ctx *ctx, void *dst_dev, const void *src_host, int64_t bytes);
 int bwagpu_d2h(bwagpu_ctx *ctx, void *dst_host, const void *src_dev, int64_t bytes);
+int bwagpu_memset(bwagpu_ctx *ctx, void *dst_dev, int value, int64_t bytes);   /* async on ctx's stream */
 
 /* ---- S2: banded Smith-Waterman extension ------------------------------------------------------
  * bwagpu_seqpair mirrors SeqPair (reference src/bandedSWA.h:90-99), 56 bytes. */
@@ -84,6 +93,67 @@ int bwagpu_bsw_get_scores_device(bwagpu_ctx *ctx, const bwagpu_bsw_params *prm, 
                                  bwagpu_seqpair *d_pairArray, const uint8_t *d_seqBufRef,
                                  int64_t ref_bytes, const uint8_t *d_seqBufQer, int64_t qer_bytes,
                                  int32_t numPairs, int32_t w);
+
+/* ---- S1: FM-index seeding --------------------------------------------------------------------
+ * bwagpu_smem mirrors SMEM (reference src/FMI_search.h:85-93, non-DEBUG build), 40 bytes. */
+typedef struct {
+    uint32_t rid, m, n, pad_;
+    int64_t k, l, s;
+} bwagpu_smem;
+
+/* The arrays FMI_search::load_index leaves in host memory (reference src/FMI_search.cpp:1251-1351,
+ * members at src/FMI_search.h:230-254).  count[] is the LOADED form (file value + 1,
+ * cpp:1304-1307).  bwagpu_index_load_fm copies them into this GPU's HBM (one replica per GPU). */
+typedef struct {
+    int64_t reference_seq_len;          /* 2*l_pac + 1 */
+    int64_t count[5];
+    const void *cp_occ;                 /* CP_OCC[(reference_seq_len >> 6) + 1], 64 B each */
+    const int8_t *sa_ms_byte;           /* [(reference_seq_len >> 3) + 1] */
+    const uint32_t *sa_ls_word;         /* [(reference_seq_len >> 3) + 1] */
+    int64_t sentinel_index;
+} bwagpu_fm_index_desc;
+
+int bwagpu_index_load_fm(bwagpu_ctx *ctx, const bwagpu_fm_index_desc *desc);
+
+/* the mem_opt_t fields the seeding stage reads (reference src/bwamem.h:89-124) */
+typedef struct {
+    int32_t min_seed_len;     /* opt->min_seed_len  (19) */
+    float   split_factor;     /* opt->split_factor  (1.5) */
+    int32_t split_width;      /* opt->split_width   (10) */
+    int32_t max_occ;          /* opt->max_occ       (500) */
+    int64_t max_mem_intv;     /* opt->max_mem_intv  (20); 0 disables the third round */
+} bwagpu_seed_opt;
+
+/* Replaces mem_collect_smem (reference src/bwamem.cpp:648-786), i.e. FMI_search::
+ * getSMEMsAllPosOneThread + getSMEMsOnePosOneThread + bwtSeedStrategyAllPosOneThread + sortSMEMs
+ * and the per-read introsort: writes the SMEMs of all reads in the reference's final order
+ * (rid, m, n ascending, duplicates kept).  enc_reads: 2-bit codes (>= 4 = N), read i at
+ * enc_reads[off[i] .. off[i]+len[i]).  skip (may be NULL): non-zero = read answered by the EMF
+ * (seq_[i].perfect.exist).  HOST buffers.  *tot_smem is always the full count; if it exceeds
+ * out_cap nothing is written and BWAGPU_ERR_RANGE is returned. */
+int bwagpu_collect_smem(bwagpu_ctx *ctx, const bwagpu_seed_opt *opt, const uint8_t *enc_reads,
+                        const int64_t *off, const int32_t *len, const uint8_t *skip, int32_t nseq,
+                        bwagpu_smem *out, int64_t out_cap, int64_t *tot_smem);
+
+/* Replaces FMI_search::get_sa_entries_prefetch (reference src/FMI_search.cpp:2261-2379) over a
+ * whole batch: for each SMEM the rows k, k+step, ... (at most max_occ), coordinates in SMEM
+ * order then row order, as mem_chain_seeds consumes them (src/bwamem.cpp:866-893).  HOST buffers. */
+int bwagpu_get_sa_entries(bwagpu_ctx *ctx, const bwagpu_smem *smems, int64_t n_smem,
+                          int32_t max_occ, int64_t *coords, int64_t coords_cap, int64_t *n_coords);
+
+/* Both stages with every buffer resident in HBM (device pointers in, context-owned device
+ * buffers out; asynchronous except for two scalar read-backs).  Results stay valid until the
+ * next seeding call on this context. */
+typedef struct {
+    const bwagpu_smem *d_smems; int64_t n_smem;
+    const int64_t *d_coords;    int64_t n_coords;
+    const int64_t *d_coord_off;          /* [n_smem + 1] first coordinate of each SMEM */
+    int64_t n_ext, n_cp_records;         /* backward extensions done, CP_OCC records fetched */
+    int64_t n_lf_steps;                  /* LF steps of the SA stage */
+} bwagpu_seed_result;
+int bwagpu_seed_fm_device(bwagpu_ctx *ctx, const bwagpu_seed_opt *opt, const uint8_t *d_reads,
+                          const int64_t *d_off, const int32_t *d_len, const uint8_t *d_skip,
+                          int32_t nseq, int32_t max_len, bwagpu_seed_result *res);
 
 #ifdef __cplusplus
 }

@@ -1,0 +1,90 @@
+"""GPU parity tests (through the C ABI): CUDA FM-index seeding vs the oracle / golden digests."""
+import hashlib
+import os
+
+import numpy as np
+import pytest
+
+import fmi_cases as fc
+import oracle_lib as ol
+from bwa_mem_scale_b200 import FMI_search, fmindex, seed_opt, synth
+
+pytestmark = pytest.mark.gpu
+GOLD = np.load(os.path.join(fc.HERE, "golden", "fmi_golden.npz"))
+
+
+def sha(a):
+    return np.frombuffer(hashlib.sha256(np.ascontiguousarray(a).tobytes()).digest(), np.uint8)
+
+
+@pytest.fixture(scope="module")
+def small_fmi(gpu_ctx):
+    ref, idx = fc.small_index()
+    return ref, idx, FMI_search(idx, ctx=gpu_ctx)
+
+
+@pytest.mark.parametrize("case", fc.OPT_CASES, ids=[c[0] for c in fc.OPT_CASES])
+def test_gpu_seeding_matches_golden_and_oracle(small_fmi, case):
+    name, kw, max_occ = case
+    ref, idx, fmi = small_fmi
+    flat, off, ln = ol.pack_reads(fc.small_reads(ref))
+    oo = ol.default_seed_opt(**kw)
+    got = fmi.collect_smem(seed_opt(oo.min_seed_len, oo.split_factor, oo.split_width, max_occ, oo.max_mem_intv),
+                           flat, off, ln)
+    sa = fmi.get_sa_entries_prefetch(got, max_occ)
+    assert list(GOLD[f"{name}_counts"]) == [len(got), len(sa)]
+    assert np.array_equal(sha(fc.smem_matrix(got)), GOLD[f"{name}_smem_sha256"])
+    assert np.array_equal(sha(sa), GOLD[f"{name}_sa_sha256"])
+    want, _ = ol.oracle_collect_smem(idx, oo, flat, off, ln)
+    assert np.array_equal(fc.smem_matrix(got), fc.smem_matrix(want))
+    assert np.array_equal(sa, ol.oracle_sa_lookup(idx, want, max_occ)[0])
+
+
+def test_gpu_seeding_skip_empty_and_overflow(small_fmi, gpu_ctx):
+    ref, idx, fmi = small_fmi
+    reads = fc.small_reads(ref)[:300]
+    flat, off, ln = ol.pack_reads(reads)
+    opt = seed_opt()
+    skip = np.zeros(len(reads), np.uint8)
+    skip[::3] = 1
+    got = fmi.collect_smem(opt, flat, off, ln, skip)
+    want, _ = ol.oracle_collect_smem(idx, ol.default_seed_opt(), flat, off, ln, skip)
+    assert np.array_equal(fc.smem_matrix(got), fc.smem_matrix(want))
+    assert len(fmi.collect_smem(opt, flat[:0], off[:0], ln[:0])) == 0
+    assert len(fmi.get_sa_entries_prefetch(got[:0], 500)) == 0
+    # a read made of a short tandem repeat yields far more SMEMs than the default per-read
+    # capacity of the kernel's scratch: exercises the overflow-and-retry path
+    unit = np.array([0, 1, 2, 3, 0, 0, 1], np.uint8)
+    rep = np.tile(unit, 60)
+    ref2 = np.concatenate([synth.random_reference(5000, 3), rep, synth.random_reference(5000, 4)])
+    idx2 = fmindex.build_fm_index(ref2, device="cpu")
+    fmi2 = FMI_search(idx2, ctx=gpu_ctx)
+    r0 = rep[5:305].copy()
+    r0[::23] = (r0[::23] + 1) & 3          # periodic mismatches: hundreds of SMEMs in one read
+    rd = [r0, ref2[100:251].copy(), rep[:200].copy()]
+    f2, o2, l2 = ol.pack_reads(rd)
+    o = ol.default_seed_opt(min_seed_len=5, split_width=1000, max_mem_intv=1000)
+    got2 = fmi2.collect_smem(seed_opt(5, 1.5, 1000, 500, 1000), f2, o2, l2)
+    want2, _ = ol.oracle_collect_smem(idx2, o, f2, o2, l2)
+    assert np.bincount(want2["rid"]).max() > 200
+    assert np.array_equal(fc.smem_matrix(got2), fc.smem_matrix(want2))
+    assert np.array_equal(fmi2.get_sa_entries_prefetch(got2, 500), ol.oracle_sa_lookup(idx2, want2, 500)[0])
+    FMI_search(idx, ctx=gpu_ctx)      # restore the module's index replica on the shared context
+
+
+def test_gpu_seeding_config1_shape(gpu_ctx):
+    """BASELINE config 1 shape: 1 Mbp random reference, 10 k x 151 bp reads, 1 % substitutions."""
+    ref = synth.random_reference(1_000_000, 42)
+    idx = fmindex.build_fm_index(ref)
+    reads, _, _ = synth.simulate_reads(ref, 10000, seed=1)
+    fmi = FMI_search(idx, ctx=gpu_ctx)
+    flat, off, ln = ol.pack_reads(reads)
+    got = fmi.collect_smem(seed_opt(), flat, off, ln)
+    want, _ = ol.oracle_collect_smem(idx, ol.default_seed_opt(), flat, off, ln)
+    assert np.array_equal(fc.smem_matrix(got), fc.smem_matrix(want))
+    assert np.array_equal(fmi.get_sa_entries_prefetch(got, 500), ol.oracle_sa_lookup(idx, want, 500)[0])
+    # size-independent properties: canonical order, spans inside the read, interval inside the text
+    key = (got["rid"].astype(np.int64) << 32) | (got["m"].astype(np.int64) << 16) | got["n"]
+    assert np.all(np.diff(key) >= 0)
+    assert np.all(got["n"] < 151) and np.all(got["m"] <= got["n"])
+    assert np.all(got["s"] >= 1) and np.all(got["k"] + got["s"] <= idx.ref_seq_len)
