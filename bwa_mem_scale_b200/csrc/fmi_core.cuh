@@ -61,6 +61,12 @@ BWAGPU_HD uint64_t fm_prefix_mask(int y) { return y ? (~0ULL << (64 - y)) : 0ULL
 
 struct Biv { int64_t k, l, s; };
 
+// count[a] without dynamic indexing of the kernel-parameter struct (keeps it out of local memory)
+BWAGPU_HD int64_t fm_count(const FmView &f, int a)
+{
+    return a == 0 ? f.count[0] : a == 1 ? f.count[1] : a == 2 ? f.count[2] : a == 3 ? f.count[3] : f.count[4];
+}
+
 // backward extension of (k,l,s) by base a
 BWAGPU_HD Biv fm_bext(const FmView &f, const Biv &v, int a)
 {
@@ -78,7 +84,7 @@ BWAGPU_HD Biv fm_bext(const FmView &f, const Biv &v, int a)
     const int64_t sent = (v.k <= f.sentinel_index && ep > f.sentinel_index) ? 1 : 0;
     int64_t l3 = v.l + sent, l2 = l3 + sz[3], l1 = l2 + sz[2], l0 = l1 + sz[1];
     Biv r;
-    r.k = f.count[a] + (a == 0 ? osp[0] : a == 1 ? osp[1] : a == 2 ? osp[2] : osp[3]);
+    r.k = fm_count(f, a) + (a == 0 ? osp[0] : a == 1 ? osp[1] : a == 2 ? osp[2] : osp[3]);
     r.s = a == 0 ? sz[0] : a == 1 ? sz[1] : a == 2 ? sz[2] : sz[3];
     r.l = a == 0 ? l0 : a == 1 ? l1 : a == 2 ? l2 : l3;
     return r;
@@ -131,7 +137,7 @@ struct SeedMachine {
 
     BWAGPU_HD void single_base(const FmView &f, int a)
     {
-        cur.k = f.count[a]; cur.l = f.count[3 - a]; cur.s = f.count[a + 1] - f.count[a];
+        cur.k = fm_count(f, a); cur.l = fm_count(f, 3 - a); cur.s = fm_count(f, a + 1) - cur.k;
     }
 
     BWAGPU_HD void push_prev()                 // forward phase: store below the previous entry
@@ -292,6 +298,37 @@ struct SeedMachine {
             }
         }
     }
+
+    // consume() followed by the common-case transition to the next request, as straight-line
+    // code: forward step -> forward step, backward item -> next item, backward row -> next row.
+    // Returns true when the next request is ready; false when the rarer bookkeeping of advance()
+    // is needed (phase changes, pivot ends, round changes, read end).
+    BWAGPU_HD bool step_fast(const Biv &r, const SeedOpt &o)
+    {
+        consume(r, o);
+        if (state == ST_FWD || state == ST_LFWD) {
+            if (j < len) {
+                const int a = q[j];
+                if (a < 4) { next_x = j + 1; request_fwd(a); return true; }
+            }
+            return false;
+        }
+        if (state == ST_BITEM) {
+            if (p >= np) {                       // row finished
+                np = nc;
+                if (np == 0) { state = ST_NEXT; return false; }
+                --j;
+                if (j < 0 || q[j] > 3) { state = ST_BEND; return false; }
+                nc = 0; decided = 0; last_s = -1; p = 0;
+            }
+            int n_;
+            prev.get(base + p, req, n_);
+            cur_n = n_;
+            req_a = q[j];
+            return true;
+        }
+        return false;
+    }
 };
 
 // SA look-up of one BWT row: LF-walk to the next sampled row (every 8th), add the steps walked.
@@ -314,7 +351,8 @@ BWAGPU_HD int64_t fm_sa_walk(const FmView &f, int64_t pos, int *steps)
         else if ((r.bits[3] >> sh) & 1) b = 3;
         if (b == 4) { if (steps) *steps = (int)walked; return 0; }
         const uint64_t m = fm_prefix_mask((int)(pos & 63));
-        pos = f.count[b] + r.cnt[b] + fm_popc(r.bits[b] & m);
+        pos = fm_count(f, b) + (b == 0 ? r.cnt[0] + fm_popc(r.bits[0] & m) : b == 1 ? r.cnt[1] + fm_popc(r.bits[1] & m)
+                                  : b == 2 ? r.cnt[2] + fm_popc(r.bits[2] & m) : r.cnt[3] + fm_popc(r.bits[3] & m));
         ++walked;
     }
 }

@@ -15,20 +15,21 @@
 #include "fmi_core.cuh"
 
 #define SEED_TPB 128
+#define SLOW_BATCH 8
 
 // prev list of one thread inside the interleaved scratch: word w of entry e of thread t lives at
 // buf[(e*3 + w) * stride + t]
 struct DevPrev {
     int64_t *buf;
-    int64_t stride;
+    int stride;
     __device__ __forceinline__ void put(int e, const Biv &v, int n)
     {
-        int64_t *p = buf + (int64_t)e * 3 * stride;
+        int64_t *p = buf + (int64_t)(e * 3) * stride;
         p[0] = v.k | ((int64_t)n << 40); p[stride] = v.l; p[2 * stride] = v.s;
     }
     __device__ __forceinline__ void get(int e, Biv &v, int &n) const
     {
-        const int64_t *p = buf + (int64_t)e * 3 * stride;
+        const int64_t *p = buf + (int64_t)(e * 3) * stride;
         const int64_t w0 = p[0];
         v.k = w0 & ((1LL << 40) - 1); n = (int)(w0 >> 40); v.l = p[stride]; v.s = p[2 * stride];
     }
@@ -45,36 +46,49 @@ seed_collect_kernel(FmView f, SeedOpt o, const uint8_t *__restrict__ reads,
 {
     const int64_t T = (int64_t)gridDim.x * blockDim.x;
     const int64_t t0 = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    DevPrev pv; pv.buf = prev_buf + t0; pv.stride = T;
+    DevPrev pv; pv.buf = prev_buf + t0; pv.stride = (int)T;
     SeedMachine<DevPrev> m;
     int64_t next = t0;
-    bool active = false;
+    bool active = false, ready = false, finished = false;
     unsigned long long n_ext = 0, n_rec = 0;
     unsigned int max_cnt = 0;
+    // Warp-level scheduling: lanes whose next extension request is ready run the extension
+    // together; lanes that need the rarer bookkeeping (advance(): phase / pivot / round changes,
+    // fetching the next read) wait until SLOW_BATCH of them have gathered, or nobody is ready,
+    // and then run it together.  Scheduling only: per-read results do not depend on it.
     for (;;) {
-        if (!active) {
-            // pick up the next read of this thread's stride
-            bool got = false;
-            while (next < nseq) {
-                const int i = (int)next; next += T;
-                if (skip && skip[i]) { cnt[i] = 0; continue; }
-                m.init(reads + off[i], len[i], i, pv, tmp + (int64_t)i * cap, cap);
-                got = true;
-                break;
+        const unsigned m_ready = __ballot_sync(0xffffffffu, ready);
+        const unsigned m_slow = __ballot_sync(0xffffffffu, !ready && !finished);
+        if (m_slow && (__popc(m_slow) >= SLOW_BATCH || !m_ready)) {
+            if (!ready && !finished) {
+                for (;;) {
+                    if (!active) {
+                        bool got = false;
+                        while (next < nseq) {
+                            const int i = (int)next; next += T;
+                            if (skip && skip[i]) { cnt[i] = 0; continue; }
+                            m.init(reads + off[i], len[i], i, pv, tmp + (int64_t)i * cap, cap);
+                            got = true;
+                            break;
+                        }
+                        if (!got) { finished = true; break; }
+                        active = true;
+                    }
+                    if (m.advance(f, o)) { ready = true; break; }
+                    cnt[m.rid] = m.n_out;
+                    max_cnt = max(max_cnt, (unsigned)m.n_out);
+                    active = false;
+                }
             }
-            if (!got) break;
-            active = true;
-        }
-        if (!m.advance(f, o)) {
-            cnt[m.rid] = m.n_out;
-            max_cnt = max(max_cnt, (unsigned)m.n_out);
-            active = false;
             continue;
         }
-        n_rec += ((m.req.k >> 6) == ((m.req.k + m.req.s) >> 6)) ? 1 : 2;
-        ++n_ext;
-        const Biv r = fm_bext(f, m.req, m.req_a);
-        m.consume(r, o);
+        if (!m_ready) break;
+        if (ready) {
+            n_rec += ((m.req.k >> 6) == ((m.req.k + m.req.s) >> 6)) ? 1 : 2;
+            ++n_ext;
+            const Biv r = fm_bext(f, m.req, m.req_a);
+            ready = m.step_fast(r, o);
+        }
     }
     // per-warp then global statistics
     for (int d = 16; d; d >>= 1) {

@@ -33,9 +33,12 @@ extern "C" int64_t hostsim_collect_smem(const bwagpu_fm_index_desc *d, const bwa
         SeedMachine<HostPrev> m;
         HostPrev hp; hp.buf = pv.data();
         m.init(reads + off[i], len[i], i, hp, tmp.data(), per_read_cap);
-        while (m.advance(f, so)) {
+        // same driver shape as the kernel: common transitions inline, the rest through advance()
+        bool ready = false;
+        for (;;) {
+            if (!ready && !m.advance(f, so)) break;
             Biv r = fm_bext(f, m.req, m.req_a);
-            m.consume(r, so);
+            ready = m.step_fast(r, so);
         }
         if (m.n_out > per_read_cap) return -(int64_t)m.n_out;     // caller retries with more room
         if (n_ext) *n_ext += m.n_ext;
