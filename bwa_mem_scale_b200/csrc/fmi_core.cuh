@@ -31,17 +31,38 @@ struct FmView {
 
 struct FmRec { int64_t cnt[4]; uint64_t bits[4]; };
 
-BWAGPU_HD void fm_load_rec(const FmView &f, int64_t block, FmRec &r)
+#ifndef SEED_LD_MODE
+#define SEED_LD_MODE 1      // 0: 4x128-bit __ldg; 1: 2x256-bit cached; 2: 256-bit, L1 no_allocate for narrow intervals
+#endif
+
+// `deep`: the interval is narrow, i.e. this record is a random touch with no reuse inside the SM
+BWAGPU_HD void fm_load_rec(const FmView &f, int64_t block, FmRec &r, bool deep = false)
 {
 #if defined(__CUDA_ARCH__)
-    // one 64-byte record = four 16-byte loads of the same two sectors
-    const uint4 *p = reinterpret_cast<const uint4 *>(f.cp_occ + block * 8);
-    uint4 a = __ldg(p), b = __ldg(p + 1), c = __ldg(p + 2), d = __ldg(p + 3);
+    const int64_t *p = f.cp_occ + block * 8;
+#if SEED_LD_MODE == 0
+    const uint4 *p4 = reinterpret_cast<const uint4 *>(p);
+    uint4 a = __ldg(p4), b = __ldg(p4 + 1), c = __ldg(p4 + 2), d = __ldg(p4 + 3);
     r.cnt[0] = (int64_t)(((uint64_t)a.y << 32) | a.x); r.cnt[1] = (int64_t)(((uint64_t)a.w << 32) | a.z);
     r.cnt[2] = (int64_t)(((uint64_t)b.y << 32) | b.x); r.cnt[3] = (int64_t)(((uint64_t)b.w << 32) | b.z);
     r.bits[0] = ((uint64_t)c.y << 32) | c.x; r.bits[1] = ((uint64_t)c.w << 32) | c.z;
     r.bits[2] = ((uint64_t)d.y << 32) | d.x; r.bits[3] = ((uint64_t)d.w << 32) | d.z;
 #else
+    // one 64-byte record = two 256-bit loads (sm_100: LDG.256), one per 32-byte sector
+    if (SEED_LD_MODE == 2 && deep) {
+        asm("ld.global.nc.L1::no_allocate.v4.u64 {%0,%1,%2,%3}, [%4];"
+            : "=l"(r.cnt[0]), "=l"(r.cnt[1]), "=l"(r.cnt[2]), "=l"(r.cnt[3]) : "l"(p));
+        asm("ld.global.nc.L1::no_allocate.v4.u64 {%0,%1,%2,%3}, [%4];"
+            : "=l"(r.bits[0]), "=l"(r.bits[1]), "=l"(r.bits[2]), "=l"(r.bits[3]) : "l"(p + 4));
+    } else {
+        asm("ld.global.nc.v4.u64 {%0,%1,%2,%3}, [%4];"
+            : "=l"(r.cnt[0]), "=l"(r.cnt[1]), "=l"(r.cnt[2]), "=l"(r.cnt[3]) : "l"(p));
+        asm("ld.global.nc.v4.u64 {%0,%1,%2,%3}, [%4];"
+            : "=l"(r.bits[0]), "=l"(r.bits[1]), "=l"(r.bits[2]), "=l"(r.bits[3]) : "l"(p + 4));
+    }
+#endif
+#else
+    (void)deep;
     const int64_t *p = f.cp_occ + block * 8;
     for (int i = 0; i < 4; ++i) { r.cnt[i] = p[i]; r.bits[i] = (uint64_t)p[4 + i]; }
 #endif
@@ -72,8 +93,9 @@ BWAGPU_HD Biv fm_bext(const FmView &f, const Biv &v, int a)
 {
     const int64_t sp = v.k, ep = v.k + v.s;
     FmRec rs, re;
-    fm_load_rec(f, sp >> 6, rs);
-    if ((ep >> 6) == (sp >> 6)) re = rs; else fm_load_rec(f, ep >> 6, re);
+    const bool deep = v.s < (1 << 14);
+    fm_load_rec(f, sp >> 6, rs, deep);
+    if ((ep >> 6) == (sp >> 6)) re = rs; else fm_load_rec(f, ep >> 6, re, deep);
     const uint64_t ms = fm_prefix_mask((int)(sp & 63)), me = fm_prefix_mask((int)(ep & 63));
     int64_t osp[4], sz[4];
 #pragma unroll
@@ -101,10 +123,12 @@ BWAGPU_HD Biv fm_bext(const FmView &f, const Biv &v, int a)
 // so the launcher can detect overflow and retry with a larger capacity.
 struct SeedOpt { int min_seed_len, split_len, split_width; int64_t max_mem_intv; };
 
-template <class PrevStore>
+// ReadStore: anything indexable as q[j] -> base code (a plain pointer on the host, a shared-memory
+// view in the kernel).
+template <class PrevStore, class ReadStore = const uint8_t *>
 struct SeedMachine {
     enum { ST_PIVOT, ST_FWD, ST_BROW, ST_BITEM, ST_BEND, ST_NEXT, ST_LSTART, ST_LFWD, ST_DONE };
-    const uint8_t *q;
+    ReadStore q;
     int len, rid;
     PrevStore prev;
     bwagpu_smem *out;
@@ -116,7 +140,7 @@ struct SeedMachine {
     Biv req; int req_a;          // pending extension request
     int64_t n_ext;
 
-    BWAGPU_HD void init(const uint8_t *q_, int len_, int rid_, PrevStore prev_, bwagpu_smem *out_, int cap_)
+    BWAGPU_HD void init(ReadStore q_, int len_, int rid_, PrevStore prev_, bwagpu_smem *out_, int cap_)
     {
         q = q_; len = len_; rid = rid_; prev = prev_; out = out_; cap = cap_; n_out = 0;
         round = 1; x = 0; min_intv = 1; state = len > 0 ? ST_PIVOT : ST_DONE; n_ext = 0;

@@ -15,7 +15,9 @@
 #include "fmi_core.cuh"
 
 #define SEED_TPB 128
-#define SLOW_BATCH 8
+#ifndef SLOW_BATCH
+#define SLOW_BATCH 4
+#endif
 
 // prev list of one thread inside the interleaved scratch: word w of entry e of thread t lives at
 // buf[(e*3 + w) * stride + t]
@@ -173,6 +175,8 @@ extern "C" int bwagpu_index_load_fm(bwagpu_ctx *ctx, const bwagpu_fm_index_desc 
     if (!ctx) return BWAGPU_ERR_ARG;
     if (!d || !d->cp_occ || !d->sa_ms_byte || !d->sa_ls_word || d->reference_seq_len <= 0)
         BWAGPU_FAIL(ctx, BWAGPU_ERR_ARG, "index_load_fm: incomplete index descriptor");
+    if (d->reference_seq_len >= (1LL << 39))
+        BWAGPU_FAIL(ctx, BWAGPU_ERR_RANGE, "index_load_fm: text longer than 2^39 symbols is not supported");
     BWAGPU_CUDA(ctx, cudaSetDevice(ctx->device));
     BWAGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     if (ctx->d_cp_occ) { cudaFree(ctx->d_cp_occ); cudaFree(ctx->d_sa_ms); cudaFree(ctx->d_sa_ls); }

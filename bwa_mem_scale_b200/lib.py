@@ -9,7 +9,8 @@ import ctypes as C
 import os
 
 PKG_DIR = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(PKG_DIR, "libbwagpu.so")
+# BWAGPU_LIB selects a differently-tuned build of the same library (kernel A/B runs)
+LIB_PATH = os.environ.get("BWAGPU_LIB") or os.path.join(PKG_DIR, "libbwagpu.so")
 
 
 class BwaGpuError(RuntimeError):
