@@ -1,10 +1,68 @@
 // S2 extension seam of the C ABI: bwagpu_bsw_get_scores{,_device}  (include/bwagpu.h).
 // Replaces BandedPairWiseSW::getScores16 / getScores8 / scalarBandedSWAWrapper
 // (reference src/bandedSWA.h:130-172).
+#include <cub/device/device_radix_sort.cuh>
+#include <stdlib.h>
 #include "ctx.cuh"
 #include "bsw_thread.cuh"
+#include "bsw_fast.cuh"
 
 #define BSW_TPB 128
+#define BSW_FAST_TPB 64          // threads per block of the shared-memory kernel
+#define BSW_FAST_MAX_LEN2 512    // longest query whose column state is kept in shared memory
+
+// Fast path: block b works on the 64 pairs order[b*64 ..], which the sort has made similar in
+// shape (longest first), so the lanes of a warp run rows of similar width for a similar number
+// of rows.  Dynamic shared memory: (max_len2 + 3) column words per thread.
+template <int KIND>
+__global__ void __launch_bounds__(BSW_FAST_TPB)
+bsw_fast_kernel(bwagpu_bsw_params prm, bwagpu_seqpair *__restrict__ pairs,
+                const uint8_t *__restrict__ ref, const uint8_t *__restrict__ qer,
+                const uint32_t *__restrict__ order, int first, int n, int w)
+{
+    extern __shared__ uint32_t colmem[];
+    const int slot = first + blockIdx.x * BSW_FAST_TPB + threadIdx.x;
+    if (slot >= n) return;
+    const uint32_t i = order[slot];
+    const bwagpu_seqpair sp = pairs[i];
+    const BswOut o = bsw_lane_fast<KIND, BSW_FAST_TPB>(prm, qer + sp.idq, sp.len2, ref + sp.idr, sp.len1, w,
+                                                        sp.h0, colmem + threadIdx.x);
+    bwagpu_seqpair *d = &pairs[i];
+    d->score = o.score; d->tle = o.tle; d->gtle = o.gtle; d->qle = o.qle;
+    d->gscore = o.gscore; d->max_off = o.max_off;
+}
+
+// generic path over order[0 .. n_long): pairs too long for the shared-memory kernel
+template <int KIND>
+__global__ void __launch_bounds__(BSW_TPB)
+bsw_thread_order_kernel(bwagpu_bsw_params prm, bwagpu_seqpair *__restrict__ pairs,
+                        const uint8_t *__restrict__ ref, const uint8_t *__restrict__ qer,
+                        const uint32_t *__restrict__ order, int n, int w, uint32_t *__restrict__ work)
+{
+    const int64_t T = (int64_t)gridDim.x * blockDim.x;
+    const int64_t t0 = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    uint32_t *col = work + t0;
+    for (int64_t s = t0; s < n; s += T) {
+        const uint32_t i = order[s];
+        const bwagpu_seqpair sp = pairs[i];
+        const BswOut o = bsw_lane_pair<KIND>(prm, qer + sp.idq, sp.len2, ref + sp.idr, sp.len1, w, sp.h0, col, T);
+        bwagpu_seqpair *d = &pairs[i];
+        d->score = o.score; d->tle = o.tle; d->gtle = o.gtle; d->qle = o.qle;
+        d->gscore = o.gscore; d->max_off = o.max_off;
+    }
+}
+
+// sort key: query length, then target length (descending order puts the longest pairs first)
+__global__ void bsw_key_kernel(const bwagpu_seqpair *__restrict__ pairs, int n, uint32_t *__restrict__ keys,
+                               uint32_t *__restrict__ idx, int *__restrict__ n_long)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const int l2 = min(pairs[i].len2, 0xFFFF), l1 = min(pairs[i].len1, 0xFFFF);
+    keys[i] = ((uint32_t)l2 << 16) | (uint32_t)l1;
+    idx[i] = (uint32_t)i;
+    if (l2 > BSW_FAST_MAX_LEN2) atomicAdd(n_long, 1);
+}
 
 // Persistent grid: each thread walks pairs tid, tid+T, ... and owns one column of the
 // interleaved scratch (word j of thread t lives at work[j*T + t]).
@@ -57,11 +115,11 @@ static int bsw_check(bwagpu_ctx *ctx, const bwagpu_bsw_params *prm, int kind, in
     return BWAGPU_OK;
 }
 
-static int bsw_launch(bwagpu_ctx *ctx, const bwagpu_bsw_params *prm, int kind,
-                      bwagpu_seqpair *d_pairs, const uint8_t *d_ref, const uint8_t *d_qer,
-                      int32_t n, int32_t w, int max_len2)
+// generic kernel over all pairs in input order (scalar kind, or BWAGPU_BSW_PATH=thread)
+static int bsw_launch_thread(bwagpu_ctx *ctx, const bwagpu_bsw_params *prm, int kind,
+                             bwagpu_seqpair *d_pairs, const uint8_t *d_ref, const uint8_t *d_qer,
+                             int32_t n, int32_t w, int max_len2)
 {
-    if (n == 0) return BWAGPU_OK;
     int blocks = ctx->sm_count * 8;
     int need = (n + BSW_TPB - 1) / BSW_TPB;
     if (blocks > need) blocks = need;
@@ -87,6 +145,72 @@ static int bsw_launch(bwagpu_ctx *ctx, const bwagpu_bsw_params *prm, int kind,
     BWAGPU_KERNEL_END(ctx, BWAGPU_KERN_BSW);
     BWAGPU_CUDA(ctx, cudaGetLastError());
     return BWAGPU_OK;
+}
+
+template <int KIND>
+static int bsw_launch_sorted(bwagpu_ctx *ctx, const bwagpu_bsw_params *prm, bwagpu_seqpair *d_pairs,
+                             const uint8_t *d_ref, const uint8_t *d_qer, int32_t n, int32_t w)
+{
+    // 1. order the pairs by (len2, len1) descending; count those too long for shared memory
+    uint32_t *keys, *order; int *d_m;
+    int rc;
+    if ((rc = bwagpu_scratch(ctx, SCR_BSW_KEYS, (int64_t)n * 8, (void **)&keys))) return rc;
+    if ((rc = bwagpu_scratch(ctx, SCR_BSW_ORDER, (int64_t)n * 8, (void **)&order))) return rc;
+    if ((rc = bwagpu_scratch(ctx, SCR_MISC0, 64, (void **)&d_m))) return rc;
+    uint32_t *keys_out = keys + n, *idx_in = order + n;
+    BWAGPU_CUDA(ctx, cudaMemsetAsync(d_m, 0, 16, ctx->stream));
+    bsw_key_kernel<<<(n + 255) / 256, 256, 0, ctx->stream>>>(d_pairs, n, keys, idx_in, d_m + 2);
+    bsw_maxlen_kernel<<<ctx->sm_count * 4, 256, 0, ctx->stream>>>(d_pairs, n, d_m);
+    ctx->launches += 2;
+    size_t bytes = 0;
+    cub::DeviceRadixSort::SortPairsDescending((void *)nullptr, bytes, keys, keys_out, idx_in, order, n, 0, 32, ctx->stream);
+    void *tmp;
+    if ((rc = bwagpu_scratch(ctx, SCR_CUB, (int64_t)bytes + 256, &tmp))) return rc;
+    BWAGPU_CUDA(ctx, cub::DeviceRadixSort::SortPairsDescending(tmp, bytes, keys, keys_out, idx_in, order, n, 0, 32, ctx->stream));
+    ctx->launches += 5;      // CUB onesweep: histogram + 4 digit passes
+    int h_m[4];
+    BWAGPU_CUDA(ctx, cudaMemcpyAsync(h_m, d_m, 16, cudaMemcpyDeviceToHost, ctx->stream));
+    BWAGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    const int max_len2 = h_m[1], n_long = h_m[2];
+    // 2. the few long pairs (front of the order) take the generic global-scratch kernel
+    if (n_long > 0) {
+        int blocks = ctx->sm_count * 8;
+        const int need = (n_long + BSW_TPB - 1) / BSW_TPB;
+        if (blocks > need) blocks = need;
+        const int64_t T = (int64_t)blocks * BSW_TPB;
+        void *work;
+        if ((rc = bwagpu_scratch(ctx, SCR_BSW_WORK, (int64_t)(max_len2 + 4) * T * 4, &work))) return rc;
+        BWAGPU_KERNEL_BEGIN(ctx);
+        bsw_thread_order_kernel<KIND><<<blocks, BSW_TPB, 0, ctx->stream>>>(*prm, d_pairs, d_ref, d_qer, order, n_long, w,
+                                                                         (uint32_t *)work);
+        BWAGPU_KERNEL_END(ctx, BWAGPU_KERN_BSW_GENERIC);
+        BWAGPU_CUDA(ctx, cudaGetLastError());
+    }
+    // 3. everything else: shared-memory kernel
+    const int n_fast = n - n_long;
+    if (n_fast > 0) {
+        const int cols = (max_len2 < BSW_FAST_MAX_LEN2 ? max_len2 : BSW_FAST_MAX_LEN2) + 3;
+        const size_t smem = (size_t)cols * BSW_FAST_TPB * 4;
+        BWAGPU_CUDA(ctx, cudaFuncSetAttribute(bsw_fast_kernel<KIND>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        BWAGPU_KERNEL_BEGIN(ctx);
+        bsw_fast_kernel<KIND><<<(n_fast + BSW_FAST_TPB - 1) / BSW_FAST_TPB, BSW_FAST_TPB, smem, ctx->stream>>>(
+            *prm, d_pairs, d_ref, d_qer, order, n_long, n, w);
+        BWAGPU_KERNEL_END(ctx, BWAGPU_KERN_BSW);
+        BWAGPU_CUDA(ctx, cudaGetLastError());
+    }
+    return BWAGPU_OK;
+}
+
+static int bsw_launch(bwagpu_ctx *ctx, const bwagpu_bsw_params *prm, int kind,
+                      bwagpu_seqpair *d_pairs, const uint8_t *d_ref, const uint8_t *d_qer,
+                      int32_t n, int32_t w, int max_len2)
+{
+    if (n == 0) return BWAGPU_OK;
+    static const bool force_thread = getenv("BWAGPU_BSW_PATH") && !strcmp(getenv("BWAGPU_BSW_PATH"), "thread");
+    if (kind == BWAGPU_BSW_SCALAR || force_thread)
+        return bsw_launch_thread(ctx, prm, kind, d_pairs, d_ref, d_qer, n, w, max_len2);
+    if (kind == BWAGPU_BSW_16BIT) return bsw_launch_sorted<16>(ctx, prm, d_pairs, d_ref, d_qer, n, w);
+    return bsw_launch_sorted<8>(ctx, prm, d_pairs, d_ref, d_qer, n, w);
 }
 
 static int bsw_device_maxlen(bwagpu_ctx *ctx, const bwagpu_seqpair *d_pairs, int32_t n, int out[2])

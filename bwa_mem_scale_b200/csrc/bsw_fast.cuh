@@ -1,0 +1,173 @@
+// Banded SW extension, one pair per thread, column state in shared memory ("fast" path for
+// short-read shapes: len2 small enough that every thread's H/F column fits in shared memory).
+//
+// Same per-pair semantics as bsw_lane_pair (bsw_thread.cuh), i.e. one SIMD lane of the reference's
+// smithWaterman128_16 / _8 with its batch wrapper (reference src/bandedSWA.cpp:3448-4121,
+// 4172-4837).  What differs is only how a row is executed:
+//   * the row is cut into [lo, head) | [head, tail) | [tail, hi): the middle part is the lane's
+//     live range, where neither the head/tail masks nor the "past the tail" rule apply, and runs a
+//     short straight-line cell (DPX three-way max / add-max-relu);
+//   * the substitution score is one PRMT: the target base selects a per-row byte table
+//     (match/mismatch/ambiguous), the query base selects the byte, sign-extended by the permute;
+//   * the running (row maximum, last column attaining it) is one packed max: h<<16 | (j+1).
+// Column word j of thread t lives at col[j * STRIDE] (bank = t: conflict-free).
+#pragma once
+#include <stdint.h>
+#include "bsw_thread.cuh"
+
+// PTX prmt in its default mode: a selector nibble with bit 3 set replicates the sign bit of the
+// selected byte (the __byte_perm intrinsic ignores that bit, hence the inline form)
+__device__ __forceinline__ uint32_t bsw_prmt(uint32_t a, uint32_t b, uint32_t sel)
+{
+    uint32_t d;
+    asm("prmt.b32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(sel));
+    return d;
+}
+
+template <int BITS, int STRIDE>
+__device__ BswOut bsw_lane_fast(const bwagpu_bsw_params &p, const uint8_t *__restrict__ query,
+                                int len2, const uint8_t *__restrict__ target, int len1, int w,
+                                int h0, uint32_t *__restrict__ col)
+{
+#define COL(j) col[(j) * STRIDE]
+    const int wrap = BITS == 8 ? 0xFF : 0xFFFF;
+    const int gapo_d = p.o_del + p.e_del, gapo_i = p.o_ins + p.e_ins;
+    const int e_del = p.e_del, e_ins = p.e_ins;
+    const int sc_match = p.w_match, sc_mis = -p.w_mismatch, sc_amb = -1;
+    const int nrow = len1, ncol = len2;
+    // byte tables for the PRMT score look-up: bytes 0..3 = query A,C,G,T; byte 4 = query N
+    const uint32_t mis4 = (uint32_t)(sc_mis & 0xFF) * 0x01010101u;
+    const uint32_t amb4 = (uint32_t)(sc_amb & 0xFF) * 0x01010101u;
+
+    {   // first row: seed score decaying along an insertion run; columns ncol..ncol+2 start at 0
+        int v = h0;
+        COL(0) = bsw_pack(v, 0);
+        v = h0 > gapo_i ? h0 - gapo_i : 0;
+        COL(1) = bsw_pack(v, 0);
+        for (int k = 2; k < ncol; ++k) { v = max(v - e_ins, 0); COL(k) = bsw_pack(v, 0); }
+        for (int k = max(ncol, 2); k < ncol + 3; ++k) COL(k) = 0;
+    }
+    int band;
+    {
+        int best_sub = max(max(sc_match, sc_mis), max(sc_amb, 0));
+        int qmax = (len2 * best_sub) & wrap;
+        int t = (qmax + p.end_bonus - p.o_ins) & wrap;
+        band = min(w, max(t / e_ins + 1, 1));
+        t = (qmax + p.end_bonus - p.o_del) & wrap;
+        band = min(band, max(t / e_del + 1, 1)) & wrap;
+    }
+    int head = 0, tail = len2;
+    const int mlen = min((len2 + band) & wrap, len1);
+    int best = h0, bx = 0, by = 0, gsc = -1, gi = 0, off = 0;
+    bool live = true;
+    int nlo = 0, nhi = ncol;
+
+    for (int i = 0; i < nrow; ++i) {
+        const int tc = target[i];
+        const int t = bsw_sym((uint8_t)tc, wrap);
+        uint32_t tlo, thi = amb4;
+        if (tc > 3) tlo = amb4;
+        else tlo = (mis4 & ~(0xFFu << (8 * tc))) | ((uint32_t)(sc_match & 0xFF) << (8 * tc));
+
+        const int lo = max(nlo, i - w), hi = min(min(nhi, i + w + 1), ncol);
+        int left = lo == 0 ? max(h0 - p.o_del - (i + 1) * e_del, 0) : 0;
+        int er = 0;
+        int key = 0;                              // rowmax << 16 | rowarg
+
+        const int phead = head, ptail = tail;
+        head = max(head, i - band);
+        tail = min(min(tail, i + 1 + band), len2);
+        if (head != phead || tail != ptail)
+            for (int l = lo; l < hi && head > l; ++l) COL(l) = 0;
+        if (i + 1 > mlen || head >= tail) live = false;
+
+        // general cell: exactly the body of bsw_lane_pair
+#define GENERAL_CELL(j)                                                               \
+        {                                                                             \
+            const int q = bsw_sym(query[j], wrap);                                    \
+            const uint32_t cv = COL(j);                                               \
+            const int diag = bsw_hd(cv), fc = bsw_fc(cv);                             \
+            int s = t == q ? sc_match : sc_mis;                                       \
+            if (t == wrap || q == wrap) s = sc_amb;                                   \
+            int M = diag ? diag + s : 0;                                              \
+            if (BITS == 8 && M < 0) M = 0;                                            \
+            const int h = max(max(M, er), fc);                                        \
+            er = max(max(M - gapo_i, 0), er - e_ins);                                 \
+            int fnew = max(max(M - gapo_d, 0), fc - e_del);                           \
+            const bool masked = head > (j) || (j) > tail;                             \
+            if (masked) { left = 0; fnew = 0; }                                       \
+            const bool skip = BITS == 8 ? masked : ((j) + 1 > tail);                  \
+            if (!skip) key = max(key, (h << 16) | ((j) + 1));                         \
+            COL(j) = bsw_pack(left, fnew);                                            \
+            left = h;                                                                 \
+            if ((j) + 1 == len2 && live && !((j) + 1 > tail)) {                       \
+                if (!(gsc > h)) gi = i + 1;                                           \
+                gsc = max(gsc, h);                                                    \
+            }                                                                         \
+        }
+
+        int j = lo;
+        const int ja = min(hi, max(lo, head));    // [lo, ja): before the live range
+        for (; j < ja; ++j) GENERAL_CELL(j)
+        const int jb = min(hi, tail);             // [ja, jb): live range, j >= head and j + 1 <= tail
+        if (j < jb) {
+            const uint8_t *qp = query + j;
+            uint32_t *cp = &COL(j);
+            int jp1 = j + 1;
+            for (; j < jb; ++j, ++qp, cp += STRIDE, ++jp1) {
+                const uint32_t qc = *qp;
+                const uint32_t cv = *cp;
+                const uint32_t sel = (qc & 7u) * 0x1111u + 0x8880u;       // byte qc, sign-extended
+                const int s = (int)bsw_prmt(tlo, thi, sel);
+                const int diag = (int)(cv & 0xFFFFu), fc = (int)(cv >> 16);
+                int M = diag + s;
+                M = diag ? M : 0;
+                if (BITS == 8) M = max(M, 0);
+                const int h = __vimax3_s32(M, er, fc);
+                er = __viaddmax_s32_relu(M, -gapo_i, er - e_ins);
+                const int fnew = __viaddmax_s32_relu(M, -gapo_d, fc - e_del);
+                key = max(key, (h << 16) + jp1);
+                *cp = __byte_perm((uint32_t)left, (uint32_t)fnew, 0x5410);
+                left = h;
+            }
+            if (jb == len2 && live) {             // the last query column was in the live range
+                if (!(gsc > left)) gi = i + 1;
+                gsc = max(gsc, left);
+            }
+        }
+        for (; j < hi; ++j) GENERAL_CELL(j)
+#undef GENERAL_CELL
+        COL(j) = bsw_pack(left, 0);
+
+        const int rowmax = key >> 16, rowarg = key & 0xFFFF;
+        if (rowmax == 0) break;
+        const int prev = best;
+        if (live) best = max(best, rowmax);
+        if (best > prev) { by = rowarg; bx = i + 1; off = max(off, abs(rowarg - (i + 1))); }
+        {
+            const int di = (i + 1) - bx, dj = rowarg - by;
+            const int gap = di > dj ? di - dj : dj - di;
+            if ((best - rowmax) - gap > p.zdrop) live = false;
+        }
+        for (int l = lo; l < hi; ++l) { if (COL(l) == 0) nlo = l; else break; }
+        {
+            int l;
+            for (l = hi; l >= lo; --l) if (COL(l) != 0) break;
+            nhi = min(l + 2, ncol);
+        }
+        if (live) {
+            int l;
+            for (l = lo; l < hi && COL(l) == 0; ++l) {}
+            if (l > lo) head = l;
+            int idx = tail;
+            for (l = hi; l >= lo && COL(l) == 0; --l) idx = l - 1;
+            tail = min(idx + 2, len2);
+        } else {
+            break;
+        }
+    }
+#undef COL
+    BswOut o;
+    o.score = best; o.qle = by; o.tle = bx; o.gtle = gi; o.gscore = gsc; o.max_off = off;
+    return o;
+}

@@ -9,7 +9,7 @@
 enum { SCR_BSW_PAIRS = 0, SCR_BSW_REF, SCR_BSW_QER, SCR_BSW_WORK, SCR_MISC0, SCR_MISC1, SCR_MISC2,
        SCR_MISC3, SCR_SEED_READS, SCR_SEED_OFF, SCR_SEED_LEN, SCR_SEED_SKIP, SCR_SEED_TMP,
        SCR_SEED_CNT, SCR_SEED_SCAN, SCR_SEED_PREV, SCR_SEED_OUT, SCR_SA_CNT, SCR_SA_OFF,
-       SCR_SA_COORD, SCR_CUB, SCR_STATS, SCR_SA_IN, BWAGPU_NSCRATCH };
+       SCR_SA_COORD, SCR_CUB, SCR_STATS, SCR_SA_IN, SCR_BSW_KEYS, SCR_BSW_ORDER, BWAGPU_NSCRATCH };
 
 struct bwagpu_ctx {
     int device;

@@ -45,7 +45,7 @@ int bwagpu_timer_stop(bwagpu_ctx *ctx, float *elapsed_ms);   /* records, synchro
  * kernels is bracketed by CUDA events on the context's stream (this serialises the stream, so
  * leave it off when measuring whole-step throughput).  set_profiling also clears the counters. */
 enum { BWAGPU_KERN_SEED_COLLECT = 0, BWAGPU_KERN_SEED_SORT = 1, BWAGPU_KERN_SA_WALK = 2,
-       BWAGPU_KERN_BSW = 3, BWAGPU_KERN_N = 8 };
+       BWAGPU_KERN_BSW = 3, BWAGPU_KERN_BSW_GENERIC = 4, BWAGPU_KERN_N = 8 };
 int bwagpu_set_profiling(bwagpu_ctx *ctx, int on);
 int bwagpu_kernel_time(const bwagpu_ctx *ctx, int which, double *ms, int64_t *launches);
 
