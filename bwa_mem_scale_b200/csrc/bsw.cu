@@ -18,7 +18,7 @@ template <int KIND>
 __global__ void __launch_bounds__(BSW_FAST_TPB)
 bsw_fast_kernel(bwagpu_bsw_params prm, bwagpu_seqpair *__restrict__ pairs,
                 const uint8_t *__restrict__ ref, const uint8_t *__restrict__ qer,
-                const uint32_t *__restrict__ order, int first, int n, int w)
+                const uint32_t *__restrict__ order, int first, int n, int w, int cols)
 {
     extern __shared__ uint32_t colmem[];
     const int slot = first + blockIdx.x * BSW_FAST_TPB + threadIdx.x;
@@ -26,7 +26,8 @@ bsw_fast_kernel(bwagpu_bsw_params prm, bwagpu_seqpair *__restrict__ pairs,
     const uint32_t i = order[slot];
     const bwagpu_seqpair sp = pairs[i];
     const BswOut o = bsw_lane_fast<KIND, BSW_FAST_TPB>(prm, qer + sp.idq, sp.len2, ref + sp.idr, sp.len1, w,
-                                                        sp.h0, colmem + threadIdx.x);
+                                                        sp.h0, colmem + threadIdx.x,
+                                                        colmem + cols * BSW_FAST_TPB + threadIdx.x);
     bwagpu_seqpair *d = &pairs[i];
     d->score = o.score; d->tle = o.tle; d->gtle = o.gtle; d->qle = o.qle;
     d->gscore = o.gscore; d->max_off = o.max_off;
@@ -190,11 +191,12 @@ static int bsw_launch_sorted(bwagpu_ctx *ctx, const bwagpu_bsw_params *prm, bwag
     const int n_fast = n - n_long;
     if (n_fast > 0) {
         const int cols = (max_len2 < BSW_FAST_MAX_LEN2 ? max_len2 : BSW_FAST_MAX_LEN2) + 3;
-        const size_t smem = (size_t)cols * BSW_FAST_TPB * 4;
+        const int qwords = (cols - 3 + 7) / 8 + 1;          // 4-bit query codes, 8 per word
+        const size_t smem = (size_t)(cols + qwords) * BSW_FAST_TPB * 4;
         BWAGPU_CUDA(ctx, cudaFuncSetAttribute(bsw_fast_kernel<KIND>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         BWAGPU_KERNEL_BEGIN(ctx);
         bsw_fast_kernel<KIND><<<(n_fast + BSW_FAST_TPB - 1) / BSW_FAST_TPB, BSW_FAST_TPB, smem, ctx->stream>>>(
-            *prm, d_pairs, d_ref, d_qer, order, n_long, n, w);
+            *prm, d_pairs, d_ref, d_qer, order, n_long, n, w, cols);
         BWAGPU_KERNEL_END(ctx, BWAGPU_KERN_BSW);
         BWAGPU_CUDA(ctx, cudaGetLastError());
     }

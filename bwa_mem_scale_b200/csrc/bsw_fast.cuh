@@ -27,9 +27,16 @@ __device__ __forceinline__ uint32_t bsw_prmt(uint32_t a, uint32_t b, uint32_t se
 template <int BITS, int STRIDE>
 __device__ BswOut bsw_lane_fast(const bwagpu_bsw_params &p, const uint8_t *__restrict__ query,
                                 int len2, const uint8_t *__restrict__ target, int len1, int w,
-                                int h0, uint32_t *__restrict__ col)
+                                int h0, uint32_t *__restrict__ col, uint32_t *__restrict__ qsm)
 {
 #define COL(j) col[(j) * STRIDE]
+    // stage the query once: 4-bit codes, 8 per word, word k of this thread at qsm[k * STRIDE]
+    // (a byte load per cell from global memory was the kernel's bottleneck: L1 request rate)
+    for (int k = 0; k * 8 < len2; ++k) {
+        uint32_t v = 0;
+        for (int b = 0; b < 8 && k * 8 + b < len2; ++b) v |= (uint32_t)(query[k * 8 + b] & 7u) << (4 * b);
+        qsm[k * STRIDE] = v;
+    }
     const int wrap = BITS == 8 ? 0xFF : 0xFFFF;
     const int gapo_d = p.o_del + p.e_del, gapo_i = p.o_ins + p.e_ins;
     const int e_del = p.e_del, e_ins = p.e_ins;
@@ -111,13 +118,14 @@ __device__ BswOut bsw_lane_fast(const bwagpu_bsw_params &p, const uint8_t *__res
         for (; j < ja; ++j) GENERAL_CELL(j)
         const int jb = min(hi, tail);             // [ja, jb): live range, j >= head and j + 1 <= tail
         if (j < jb) {
-            const uint8_t *qp = query + j;
             uint32_t *cp = &COL(j);
             int jp1 = j + 1;
-            for (; j < jb; ++j, ++qp, cp += STRIDE, ++jp1) {
-                const uint32_t qc = *qp;
+            uint32_t wq = qsm[(j >> 3) * STRIDE] >> (4 * (j & 7));
+            for (; j < jb; ++j, cp += STRIDE, ++jp1) {
                 const uint32_t cv = *cp;
-                const uint32_t sel = (qc & 7u) * 0x1111u + 0x8880u;       // byte qc, sign-extended
+                const uint32_t sel = (wq & 7u) * 0x1111u + 0x8880u;       // byte = query code, sign-extended
+                wq >>= 4;
+                if ((jp1 & 7) == 0) wq = qsm[(jp1 >> 3) * STRIDE];
                 const int s = (int)bsw_prmt(tlo, thi, sel);
                 const int diag = (int)(cv & 0xFFFFu), fc = (int)(cv >> 16);
                 int M = diag + s;
