@@ -249,7 +249,7 @@ def bench_seed(args, rank, world):
     n = len(reads)
     cfg = {"workload": f"FM-index seeding (SMEM rounds 1-3 + SA look-up), BASELINE config 2 shape: "
                        f"{args.ref_mbp:g} Mbp synthetic reference (10% repeats), {n} x 151 bp SE reads/GPU, "
-                       f"1% substitutions, FM-index only (no FMA tables)",
+                       f"1% substitutions, FM-index" + (" + FMA smem tables" if args.fma else " only (no FMA tables)"),
            "reads_per_gpu": n, "ref_mbp": args.ref_mbp,
            "l2_policy": "index (%.0f MB) + reads larger than L2" % (idx.nbytes() / 1e6)
            if idx.nbytes() > 126e6 else "flush between steps"}
@@ -272,6 +272,8 @@ def bench_seed(args, rank, world):
     local = int(os.environ.get("LOCAL_RANK", rank))
     ctx = Context(local)
     fmi = FMI_search(idx, ctx=ctx)
+    if args.fma:
+        fmi.build_fma()
     opt = seed_opt()
     flat, off, ln = pack_reads(reads)
     d_reads, d_off, d_len = ctx.upload(flat), ctx.upload(off), ctx.upload(ln)
@@ -379,6 +381,7 @@ def main():
     ap.add_argument("--pairs", type=int, default=1_000_000)
     ap.add_argument("--band", type=int, default=100)
     ap.add_argument("--kind", type=int, default=16, choices=[8, 16])
+    ap.add_argument("--fma", type=int, default=1, help="use the FMA smem tables (config 2)")
     ap.add_argument("--no-cpu", action="store_true")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", 0))

@@ -26,6 +26,9 @@ struct bwagpu_ctx {
     bool has_fm;
     void *d_cp_occ, *d_sa_ms, *d_sa_ls;
     int64_t fm_count[5], fm_sentinel, fm_ref_seq_len;
+    // FMA tables (all_smem_t[4^11], last_smem_t[4^13]); built on device or uploaded
+    void *d_fma_all, *d_fma_last;
+    int fma_enabled;            // bwagpu_index_use_fma: 0 = walk CP_OCC only
     int seed_read_cap;          // per-read SMEM capacity of the seeding scratch (grows on overflow)
     // optional per-kernel CUDA-event timing (bwagpu_set_profiling): bench.py's roofline numbers
     int profiling;

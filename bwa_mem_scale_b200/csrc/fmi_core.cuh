@@ -27,7 +27,39 @@ struct FmView {
     int64_t count[5];
     int64_t sentinel_index;
     int64_t ref_seq_len;
+    // FMA tables (reference all_smem_t / last_smem_t, src/FMI_search.h:99-135); NULL = not loaded
+    const uint32_t *fma_all;     // 32 words per 11-mer: last_avail, 10 x {k32,l32,s32}, pad
+    const uint32_t *fma_last;    // 4 words per 13-mer: bp|kms<<8|lms<<16|sms<<24, kls, lls, sls
 };
+
+#define FMA_ALL_BP 11
+#define FMA_LAST_BP 13
+
+// 64 bytes (16 words) of a table entry
+BWAGPU_HD void fm_load_words16(const uint32_t *p, uint32_t e[16])
+{
+#if defined(__CUDA_ARCH__)
+    uint64_t a0, a1, a2, a3, b0, b1, b2, b3;
+    asm("ld.global.nc.v4.u64 {%0,%1,%2,%3}, [%4];" : "=l"(a0), "=l"(a1), "=l"(a2), "=l"(a3) : "l"(p));
+    asm("ld.global.nc.v4.u64 {%0,%1,%2,%3}, [%4];" : "=l"(b0), "=l"(b1), "=l"(b2), "=l"(b3) : "l"(p + 8));
+    e[0] = (uint32_t)a0; e[1] = (uint32_t)(a0 >> 32); e[2] = (uint32_t)a1; e[3] = (uint32_t)(a1 >> 32);
+    e[4] = (uint32_t)a2; e[5] = (uint32_t)(a2 >> 32); e[6] = (uint32_t)a3; e[7] = (uint32_t)(a3 >> 32);
+    e[8] = (uint32_t)b0; e[9] = (uint32_t)(b0 >> 32); e[10] = (uint32_t)b1; e[11] = (uint32_t)(b1 >> 32);
+    e[12] = (uint32_t)b2; e[13] = (uint32_t)(b2 >> 32); e[14] = (uint32_t)b3; e[15] = (uint32_t)(b3 >> 32);
+#else
+    for (int i = 0; i < 16; ++i) e[i] = p[i];
+#endif
+}
+
+BWAGPU_HD void fm_load_words4(const uint32_t *p, uint32_t e[4])
+{
+#if defined(__CUDA_ARCH__)
+    const uint4 v = __ldg(reinterpret_cast<const uint4 *>(p));
+    e[0] = v.x; e[1] = v.y; e[2] = v.z; e[3] = v.w;
+#else
+    for (int i = 0; i < 4; ++i) e[i] = p[i];
+#endif
+}
 
 struct FmRec { int64_t cnt[4]; uint64_t bits[4]; };
 
@@ -112,6 +144,54 @@ BWAGPU_HD Biv fm_bext(const FmView &f, const Biv &v, int a)
     return r;
 }
 
+// ---- FMA table entries (what the reference's `smem-table` command computes) -------------------
+// idx = rank of the k-mer read as a base-4 number, first base most significant (__seq_next,
+// reference src/FMI_search.cpp:63-76); the k-mer is walked forward from its first base.
+// all_smem_t (src/FMI_search.cpp:78-120): for step i (1..10) k32 = k - previous k,
+// l32 = l - count[3 - base], s32 = s; the walk stops after storing the first step with s == 0;
+// last_avail = last step with s > 0; the rest of the 128-byte entry stays 0.
+BWAGPU_HD void fma_entry_all(const FmView &f, uint32_t idx, uint32_t e[32])
+{
+#pragma unroll
+    for (int i = 0; i < 32; ++i) e[i] = 0;
+    int a = (int)((idx >> (2 * (FMA_ALL_BP - 1))) & 3);
+    Biv cur; cur.k = fm_count(f, a); cur.l = fm_count(f, 3 - a); cur.s = fm_count(f, a + 1) - cur.k;
+    bool stop = false;
+#pragma unroll
+    for (int i = 1; i < FMA_ALL_BP; ++i) {
+        if (!stop) {
+            a = (int)((idx >> (2 * (FMA_ALL_BP - 1 - i))) & 3);
+            Biv t; t.k = cur.l; t.l = cur.k; t.s = cur.s;
+            const Biv r = fm_bext(f, t, 3 - a);
+            Biv nw; nw.k = r.l; nw.l = r.k; nw.s = r.s;
+            e[1 + 3 * (i - 1)] = (uint32_t)(nw.k - cur.k);
+            e[2 + 3 * (i - 1)] = (uint32_t)(nw.l - fm_count(f, 3 - a));
+            e[3 + 3 * (i - 1)] = (uint32_t)nw.s;
+            if (nw.s > 0) e[0] = (uint32_t)i; else stop = true;
+            cur = nw;
+        }
+    }
+}
+
+// last_smem_t (src/FMI_search.cpp:160-194): the interval after the longest prefix (bp bases, at
+// most 13) that still occurs, as 8+32-bit halves: word 0 = bp | kms<<8 | lms<<16 | sms<<24.
+BWAGPU_HD void fma_entry_last(const FmView &f, uint32_t idx, uint32_t e[4])
+{
+    int a = (int)((idx >> (2 * (FMA_LAST_BP - 1))) & 3);
+    Biv cur; cur.k = fm_count(f, a); cur.l = fm_count(f, 3 - a); cur.s = fm_count(f, a + 1) - cur.k;
+    int i = 1;
+    for (; i < FMA_LAST_BP; ++i) {
+        a = (int)((idx >> (2 * (FMA_LAST_BP - 1 - i))) & 3);
+        Biv t; t.k = cur.l; t.l = cur.k; t.s = cur.s;
+        const Biv r = fm_bext(f, t, 3 - a);
+        if (r.s == 0) break;
+        cur.k = r.l; cur.l = r.k; cur.s = r.s;
+    }
+    e[0] = (uint32_t)i | (((uint32_t)(cur.k >> 32) & 0xFF) << 8) | (((uint32_t)(cur.l >> 32) & 0xFF) << 16) |
+           (((uint32_t)(cur.s >> 32) & 0xFF) << 24);
+    e[1] = (uint32_t)cur.k; e[2] = (uint32_t)cur.l; e[3] = (uint32_t)cur.s;
+}
+
 // ---------------------------------------------------------------------------------------------
 // Per-read seeding state machine.  One bext per step() so that the threads of a warp meet at a
 // single load site; all the bookkeeping between two extensions is register/scratch work.
@@ -174,6 +254,77 @@ struct SeedMachine {
         req.k = cur.l; req.l = cur.k; req.s = cur.s; req_a = 3 - a;
     }
 
+    // One memoised forward step of the all-SMEM table (reference src/FMI_search.cpp:1435-1456):
+    // returns true when the interval fell below min_intv (the walk of this pivot is over).
+    BWAGPU_HD bool fma_step(const FmView &f, uint32_t k32, uint32_t l32, uint32_t s32, int jj)
+    {
+        const int a = q[jj];
+        next_x = jj + 1;
+        Biv nw;
+        nw.k = cur.k + (int64_t)k32; nw.l = fm_count(f, 3 - a) + (int64_t)l32; nw.s = (int64_t)s32;
+        if (nw.s != cur.s) { push_prev(); ++np; }
+        if (nw.s < min_intv) { next_x = jj; return true; }
+        cur = nw; cur_n = jj;
+        return false;
+    }
+
+    // Forward phase through the all-SMEM table: the first (up to 9) extensions of a pivot come
+    // from one 128-byte entry instead of CP_OCC.  Follows the reference literally, including what
+    // it does when an N lies inside the 11-mer (the walk then ends at the table's last usable
+    // step and next_x is set past it, src/FMI_search.cpp:1458-1461).
+    BWAGPU_HD void fma_forward(const FmView &f)
+    {
+        uint32_t idx = 0;
+        int kv = 0;
+        for (; kv < FMA_ALL_BP; ++kv) {
+            const uint32_t a = q[x + kv];
+            if (a >= 4) break;
+            idx |= a << ((FMA_ALL_BP - 1 - kv) * 2);
+        }
+        const bool with_n = kv < FMA_ALL_BP;
+        const uint32_t *ent = f.fma_all + (size_t)idx * 32;
+        uint32_t e[16];
+        fm_load_words16(ent, e);
+        const int last_avail = (int)e[0];
+        const int last_idx = (kv > last_avail ? last_avail : kv) - 1;
+        bool broke = false;
+        int kk = 0;
+#pragma unroll
+        for (int u = 0; u < 5; ++u)
+            if (!broke && kk < last_idx) { broke = fma_step(f, e[1 + 3 * u], e[2 + 3 * u], e[3 + 3 * u], x + 1 + kk); ++kk; }
+        if (!broke && kk < last_idx) {
+            fm_load_words16(ent + 16, e);
+#pragma unroll
+            for (int u = 0; u < 5; ++u)
+                if (!broke && kk < last_idx) { broke = fma_step(f, e[3 * u], e[1 + 3 * u], e[2 + 3 * u], x + 1 + kk); ++kk; }
+        }
+        j = broke ? len : x + 1 + (last_idx > 0 ? last_idx : 0);
+        if (with_n) { next_x = j + 1; j = len; }
+        if (broke) { base = len - np; j = x - 1; state = ST_BROW; }
+    }
+
+    // Round 3 through the last-SMEM table (reference src/FMI_search.cpp:1708-1752): jump over the
+    // first bp (<= 13) bases of a forward walk with one 16-byte entry.
+    BWAGPU_HD void fma_last_jump(const FmView &f, const SeedOpt &o)
+    {
+        uint32_t idx = 0, with_n = 0;
+        for (int kv = 0; kv < FMA_LAST_BP; ++kv) {
+            const uint32_t a = q[x + kv];
+            idx |= a << ((FMA_LAST_BP - 1 - kv) * 2);
+            with_n += a >> 2;
+        }
+        if (with_n) return;
+        uint32_t e[4];
+        fm_load_words4(f.fma_last + (size_t)idx * 4, e);
+        const int bp = (int)(e[0] & 0xFF);
+        j = x + bp; next_x = j;
+        cur.k = (int64_t)(((uint64_t)(int64_t)(int8_t)(e[0] >> 8) << 32) | e[1]);
+        cur.l = (int64_t)(((uint64_t)(int64_t)(int8_t)(e[0] >> 16) << 32) | e[2]);
+        cur.s = (int64_t)(((uint64_t)(int64_t)(int8_t)(e[0] >> 24) << 32) | e[3]);
+        cur_n = j - 1;
+        if (cur.s < o.max_mem_intv && cur_n - x + 1 >= o.min_seed_len + 1 && cur.s > 0) emit(x, cur_n, cur);
+    }
+
     // Runs bookkeeping until an extension is needed (returns true, request in req/req_a) or the
     // read is finished (returns false).
     BWAGPU_HD bool advance(const FmView &f, const SeedOpt &o)
@@ -186,6 +337,7 @@ struct SeedMachine {
                 if (a > 3) { state = ST_NEXT; break; }
                 single_base(f, a); cur_n = x; np = 0; j = x + 1;
                 state = ST_FWD;
+                if (f.fma_all && len - x >= FMA_ALL_BP) fma_forward(f);
                 break;
             }
             case ST_FWD: {
@@ -261,6 +413,7 @@ struct SeedMachine {
                 if (a > 3) { x = next_x; break; }
                 single_base(f, a); cur_n = x; j = x + 1;
                 state = ST_LFWD;
+                if (f.fma_last && len - x >= FMA_LAST_BP) fma_last_jump(f, o);
                 break;
             }
             case ST_LFWD: {

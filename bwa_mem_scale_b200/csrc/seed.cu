@@ -167,7 +167,99 @@ static FmView fm_view(const bwagpu_ctx *ctx)
     for (int i = 0; i < 5; ++i) f.count[i] = ctx->fm_count[i];
     f.sentinel_index = ctx->fm_sentinel;
     f.ref_seq_len = ctx->fm_ref_seq_len;
+    f.fma_all = ctx->fma_enabled ? (const uint32_t *)ctx->d_fma_all : nullptr;
+    f.fma_last = ctx->fma_enabled ? (const uint32_t *)ctx->d_fma_last : nullptr;
     return f;
+}
+
+// ---- FMA tables -------------------------------------------------------------------------------
+// One thread per k-mer (rank = the k-mer read as a base-4 number, first base most significant,
+// reference __seq_next src/FMI_search.cpp:63-76): walk it forward from its first base.
+// all_smem_t entry (src/FMI_search.cpp:78-120): for step i (base i of the k-mer, 1..10)
+// k32 = k - previous k, l32 = l - count[3 - base], s32 = s; the walk stops after storing the
+// first step with s == 0; last_avail = last step with s > 0; the rest of the entry stays 0.
+__global__ void fma_build_all_kernel(FmView f, uint32_t *__restrict__ tab)
+{
+    const uint32_t idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= (1u << (2 * FMA_ALL_BP))) return;
+    uint32_t e[32];
+    fma_entry_all(f, idx, e);
+    uint4 *dst = reinterpret_cast<uint4 *>(tab + (size_t)idx * 32);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) dst[i] = make_uint4(e[4 * i], e[4 * i + 1], e[4 * i + 2], e[4 * i + 3]);
+}
+
+__global__ void fma_build_last_kernel(FmView f, uint32_t *__restrict__ tab)
+{
+    const uint32_t idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= (1u << (2 * FMA_LAST_BP))) return;
+    uint32_t e[4];
+    fma_entry_last(f, idx, e);
+    reinterpret_cast<uint4 *>(tab)[idx] = make_uint4(e[0], e[1], e[2], e[3]);
+}
+
+static int fma_alloc(bwagpu_ctx *ctx, bool all, bool last)
+{
+    if (all && !ctx->d_fma_all) BWAGPU_CUDA(ctx, cudaMalloc(&ctx->d_fma_all, (size_t)BWAGPU_FMA_ALL_BYTES));
+    if (last && !ctx->d_fma_last) BWAGPU_CUDA(ctx, cudaMalloc(&ctx->d_fma_last, (size_t)BWAGPU_FMA_LAST_BYTES));
+    return BWAGPU_OK;
+}
+
+extern "C" int bwagpu_index_build_fma(bwagpu_ctx *ctx)
+{
+    if (!ctx) return BWAGPU_ERR_ARG;
+    if (!ctx->has_fm) BWAGPU_FAIL(ctx, BWAGPU_ERR_ARG, "index_build_fma: no FM-index loaded");
+    BWAGPU_CUDA(ctx, cudaSetDevice(ctx->device));
+    int rc = fma_alloc(ctx, true, true);
+    if (rc) return rc;
+    FmView f = fm_view(ctx);
+    BWAGPU_KERNEL_BEGIN(ctx);
+    fma_build_all_kernel<<<(1u << (2 * FMA_ALL_BP)) / 128, 128, 0, ctx->stream>>>(f, (uint32_t *)ctx->d_fma_all);
+    BWAGPU_KERNEL_END(ctx, BWAGPU_KERN_FMA_BUILD);
+    BWAGPU_KERNEL_BEGIN(ctx);
+    fma_build_last_kernel<<<(1u << (2 * FMA_LAST_BP)) / 128, 128, 0, ctx->stream>>>(f, (uint32_t *)ctx->d_fma_last);
+    BWAGPU_KERNEL_END(ctx, BWAGPU_KERN_FMA_BUILD);
+    BWAGPU_CUDA(ctx, cudaGetLastError());
+    BWAGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    ctx->fma_enabled = 1;
+    return BWAGPU_OK;
+}
+
+extern "C" int bwagpu_index_load_fma(bwagpu_ctx *ctx, const void *all_tab, const void *last_tab)
+{
+    if (!ctx) return BWAGPU_ERR_ARG;
+    BWAGPU_CUDA(ctx, cudaSetDevice(ctx->device));
+    BWAGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    if (!all_tab && ctx->d_fma_all) { cudaFree(ctx->d_fma_all); ctx->d_fma_all = nullptr; }
+    if (!last_tab && ctx->d_fma_last) { cudaFree(ctx->d_fma_last); ctx->d_fma_last = nullptr; }
+    int rc = fma_alloc(ctx, all_tab != nullptr, last_tab != nullptr);
+    if (rc) return rc;
+    if (all_tab) BWAGPU_CUDA(ctx, cudaMemcpyAsync(ctx->d_fma_all, all_tab, (size_t)BWAGPU_FMA_ALL_BYTES, cudaMemcpyHostToDevice, ctx->stream));
+    if (last_tab) BWAGPU_CUDA(ctx, cudaMemcpyAsync(ctx->d_fma_last, last_tab, (size_t)BWAGPU_FMA_LAST_BYTES, cudaMemcpyHostToDevice, ctx->stream));
+    BWAGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    ctx->fma_enabled = (all_tab || last_tab) ? 1 : 0;
+    return BWAGPU_OK;
+}
+
+extern "C" int bwagpu_index_get_fma(bwagpu_ctx *ctx, void *all_tab, void *last_tab)
+{
+    if (!ctx) return BWAGPU_ERR_ARG;
+    BWAGPU_CUDA(ctx, cudaSetDevice(ctx->device));
+    if ((all_tab && !ctx->d_fma_all) || (last_tab && !ctx->d_fma_last))
+        BWAGPU_FAIL(ctx, BWAGPU_ERR_ARG, "index_get_fma: table not resident");
+    if (all_tab) BWAGPU_CUDA(ctx, cudaMemcpyAsync(all_tab, ctx->d_fma_all, (size_t)BWAGPU_FMA_ALL_BYTES, cudaMemcpyDeviceToHost, ctx->stream));
+    if (last_tab) BWAGPU_CUDA(ctx, cudaMemcpyAsync(last_tab, ctx->d_fma_last, (size_t)BWAGPU_FMA_LAST_BYTES, cudaMemcpyDeviceToHost, ctx->stream));
+    BWAGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return BWAGPU_OK;
+}
+
+extern "C" int bwagpu_index_use_fma(bwagpu_ctx *ctx, int on)
+{
+    if (!ctx) return BWAGPU_ERR_ARG;
+    if (on && !ctx->d_fma_all && !ctx->d_fma_last)
+        BWAGPU_FAIL(ctx, BWAGPU_ERR_ARG, "index_use_fma: no FMA table resident (bwagpu_index_build_fma / _load_fma)");
+    ctx->fma_enabled = on ? 1 : 0;
+    return BWAGPU_OK;
 }
 
 extern "C" int bwagpu_index_load_fm(bwagpu_ctx *ctx, const bwagpu_fm_index_desc *d)
@@ -182,6 +274,9 @@ extern "C" int bwagpu_index_load_fm(bwagpu_ctx *ctx, const bwagpu_fm_index_desc 
     if (ctx->d_cp_occ) { cudaFree(ctx->d_cp_occ); cudaFree(ctx->d_sa_ms); cudaFree(ctx->d_sa_ls); }
     ctx->d_cp_occ = ctx->d_sa_ms = ctx->d_sa_ls = nullptr;
     ctx->has_fm = false;
+    if (ctx->d_fma_all) { cudaFree(ctx->d_fma_all); ctx->d_fma_all = nullptr; }
+    if (ctx->d_fma_last) { cudaFree(ctx->d_fma_last); ctx->d_fma_last = nullptr; }
+    ctx->fma_enabled = 0;
     const int64_t n_cp = (d->reference_seq_len >> 6) + 1, n_sa = (d->reference_seq_len >> 3) + 1;
     BWAGPU_CUDA(ctx, cudaMalloc(&ctx->d_cp_occ, (size_t)n_cp * 64));
     BWAGPU_CUDA(ctx, cudaMalloc(&ctx->d_sa_ms, (size_t)n_sa));

@@ -68,6 +68,10 @@ _SIGS = {
                                                C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p,
                                                C.c_int64, C.c_int32, C.c_int32]),
     "bwagpu_index_load_fm": (C.c_int, [C.c_void_p, C.POINTER(FmIndexDesc)]),
+    "bwagpu_index_build_fma": (C.c_int, [C.c_void_p]),
+    "bwagpu_index_load_fma": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p]),
+    "bwagpu_index_get_fma": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p]),
+    "bwagpu_index_use_fma": (C.c_int, [C.c_void_p, C.c_int]),
     "bwagpu_collect_smem": (C.c_int, [C.c_void_p, C.POINTER(SeedOpt), C.c_void_p, C.c_void_p,
                                       C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p, C.c_int64,
                                       C.POINTER(C.c_int64)]),

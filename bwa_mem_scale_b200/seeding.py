@@ -58,6 +58,34 @@ class FMI_search:
         d.sentinel_index = index.sentinel_index
         self.ctx.check(self.ctx.lib.bwagpu_index_load_fm(self.ctx.h, C.byref(d)), "bwagpu_index_load_fm")
 
+    # -- FMA "smem tables" (reference `smem-table` sub-command / FMI_search::load_smem_table,
+    #    src/FMI_search.cpp:229-277, 394-410) -------------------------------------------------
+    FMA_ALL_WORDS = (1 << 22) * 32      # all_smem_t[4^11], 128 B each
+    FMA_LAST_WORDS = (1 << 26) * 4      # last_smem_t[4^13], 16 B each
+
+    def build_fma(self) -> None:
+        """Build both tables in HBM from the resident FM-index and switch the kernels to them."""
+        self.ctx.check(self.ctx.lib.bwagpu_index_build_fma(self.ctx.h), "bwagpu_index_build_fma")
+
+    def load_fma(self, all_smem: np.ndarray | None, last_smem: np.ndarray | None) -> None:
+        """Upload tables read from <prefix>.all_smem.11 / <prefix>.last_smem.13."""
+        for a, n in ((all_smem, self.FMA_ALL_WORDS), (last_smem, self.FMA_LAST_WORDS)):
+            if a is not None and a.nbytes != n * 4:
+                raise ValueError("FMA table has the wrong size")
+        self.ctx.check(self.ctx.lib.bwagpu_index_load_fma(
+            self.ctx.h, None if all_smem is None else all_smem.ctypes.data,
+            None if last_smem is None else last_smem.ctypes.data), "bwagpu_index_load_fma")
+
+    def get_fma(self) -> tuple[np.ndarray, np.ndarray]:
+        a = np.empty(self.FMA_ALL_WORDS, np.uint32)
+        b = np.empty(self.FMA_LAST_WORDS, np.uint32)
+        self.ctx.check(self.ctx.lib.bwagpu_index_get_fma(self.ctx.h, a.ctypes.data, b.ctypes.data),
+                       "bwagpu_index_get_fma")
+        return a, b
+
+    def use_fma(self, on: bool) -> None:
+        self.ctx.check(self.ctx.lib.bwagpu_index_use_fma(self.ctx.h, 1 if on else 0), "bwagpu_index_use_fma")
+
     def close(self):
         if self._own and self.ctx is not None:
             self.ctx.close()

@@ -45,7 +45,8 @@ int bwagpu_timer_stop(bwagpu_ctx *ctx, float *elapsed_ms);   /* records, synchro
  * kernels is bracketed by CUDA events on the context's stream (this serialises the stream, so
  * leave it off when measuring whole-step throughput).  set_profiling also clears the counters. */
 enum { BWAGPU_KERN_SEED_COLLECT = 0, BWAGPU_KERN_SEED_SORT = 1, BWAGPU_KERN_SA_WALK = 2,
-       BWAGPU_KERN_BSW = 3, BWAGPU_KERN_BSW_GENERIC = 4, BWAGPU_KERN_N = 8 };
+       BWAGPU_KERN_BSW = 3, BWAGPU_KERN_BSW_GENERIC = 4, BWAGPU_KERN_FMA_BUILD = 5,
+       BWAGPU_KERN_N = 16 };
 int bwagpu_set_profiling(bwagpu_ctx *ctx, int on);
 int bwagpu_kernel_time(const bwagpu_ctx *ctx, int which, double *ms, int64_t *launches);
 
@@ -114,6 +115,23 @@ typedef struct {
 } bwagpu_fm_index_desc;
 
 int bwagpu_index_load_fm(bwagpu_ctx *ctx, const bwagpu_fm_index_desc *desc);
+
+/* FMA ("smem-table") acceleration tables: all_smem_t[4^11] (128 B each) and last_smem_t[4^13]
+ * (16 B each), reference src/FMI_search.h:99-135.  They memoise the first forward extensions of a
+ * pivot (src/FMI_search.cpp:1414-1463) and of a round-3 walk (:1708-1752).
+ *   bwagpu_index_build_fma : builds both tables in HBM from the loaded FM-index (what the
+ *                            reference's `smem-table` sub-command, build_smem_tables :229-277, does)
+ *   bwagpu_index_load_fma  : uploads tables read from <prefix>.all_smem.11 / .last_smem.13 (HOST
+ *                            pointers; either may be NULL = leave that table off)
+ *   bwagpu_index_get_fma   : copies the resident tables back (HOST buffers of 512 MiB / 1 GiB)
+ *   bwagpu_index_use_fma   : on/off switch for the seeding kernels (the planner of the reference may
+ *                            run with or without them, src/bwa_shm.cpp:1703-1717) */
+#define BWAGPU_FMA_ALL_BYTES  ((int64_t)128 << 22)
+#define BWAGPU_FMA_LAST_BYTES ((int64_t)16 << 26)
+int bwagpu_index_build_fma(bwagpu_ctx *ctx);
+int bwagpu_index_load_fma(bwagpu_ctx *ctx, const void *all_smem_table, const void *last_smem_table);
+int bwagpu_index_get_fma(bwagpu_ctx *ctx, void *all_smem_table, void *last_smem_table);
+int bwagpu_index_use_fma(bwagpu_ctx *ctx, int on);
 
 /* the mem_opt_t fields the seeding stage reads (reference src/bwamem.h:89-124) */
 typedef struct {

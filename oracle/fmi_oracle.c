@@ -8,7 +8,9 @@
  *   orc_sa_lookup     : get_sa_entries_prefetch / call_one_step          (cpp:2206-2379)
  * Written read-by-read from the algorithm (the reference sweeps all reads pivot by pivot; the
  * emission order is not observable after its final sort).
- * The FMA tables (SMEM_ACCEL) are a memoisation of backwardExt and are not modelled here.
+ * With f->fma_all / f->fma_last set, the walks go through the FMA tables exactly as the SMEM_ACCEL
+ * build does (cpp:1414-1463, 1708-1752), including what that code does when an N lies inside the
+ * table's k-mer (the tables are otherwise a pure memoisation of backwardExt).
  */
 #include <stdlib.h>
 #include <string.h>
@@ -87,8 +89,34 @@ static int pivot_search(const orc_fmi_t *f, const uint8_t *q, int len, int x, in
 {
     if (q[x] > 3) return x + 1;
     biv_t cur = single_base(f, q[x], x);
-    int np = 0, next_x = x + 1, j;
-    for (j = x + 1; j < len; ++j) {
+    int np = 0, next_x = x + 1, j = x + 1;
+    if (f->fma_all && len - x >= 11) {                  /* cpp:1414-1463 */
+        uint32_t idx = 0;
+        int k;
+        for (k = 0; k < 11; ++k) {
+            if (q[x + k] >= 4) break;
+            idx |= (uint32_t)q[x + k] << ((10 - k) * 2);
+        }
+        const uint32_t *ent = f->fma_all + (size_t)idx * 32;
+        const int with_n = k < 11;
+        const int last_avail = (int)ent[0];
+        const int last_idx = (k > last_avail ? last_avail : k) - 1;
+        for (j = x + 1, k = 0; k < last_idx; ++j, ++k) {
+            const int a = q[j];
+            next_x = j + 1;
+            biv_t nw = cur;
+            nw.k = cur.k + ent[1 + 3 * k];
+            nw.l = f->count[3 - a] + ent[2 + 3 * k];
+            nw.s = ent[3 + 3 * k];
+            nw.n = j;
+            prev[np] = cur;
+            if (nw.s != cur.s) ++np;
+            if (nw.s < min_intv) { next_x = j; j = len; break; }
+            cur = nw;
+        }
+        if (with_n) { next_x = j + 1; j = len; }
+    }
+    for (; j < len; ++j) {
         next_x = j + 1;
         if (q[j] > 3) break;
         biv_t nw = fext(f, cur, q[j], n_ext);
@@ -135,7 +163,26 @@ static void last_like_seeds(const orc_fmi_t *f, const uint8_t *q, int len, int64
         int next_x = x + 1;
         if (q[x] < 4) {
             biv_t cur = single_base(f, q[x], x);
-            for (int j = x + 1; j < len; ++j) {
+            int j = x + 1;
+            if (f->fma_last && len - x >= 13) {             /* cpp:1708-1752 */
+                uint32_t idx = 0, with_n = 0;
+                for (int k = 0; k < 13; ++k) {
+                    idx |= (uint32_t)q[x + k] << ((12 - k) * 2);
+                    with_n += q[x + k] >> 2;
+                }
+                if (!with_n) {
+                    const uint32_t *e = f->fma_last + (size_t)idx * 4;
+                    j = x + (int)(e[0] & 0xFF);
+                    next_x = j;
+                    cur.k = (int64_t)(((uint64_t)(int64_t)(int8_t)(e[0] >> 8) << 32) | e[1]);
+                    cur.l = (int64_t)(((uint64_t)(int64_t)(int8_t)(e[0] >> 16) << 32) | e[2]);
+                    cur.s = (int64_t)(((uint64_t)(int64_t)(int8_t)(e[0] >> 24) << 32) | e[3]);
+                    cur.n = j - 1;
+                    if (cur.s < max_intv && cur.n - cur.m + 1 >= min_seed_len && cur.s > 0)
+                        emit(o, rid, cur);                  /* no break here upstream */
+                }
+            }
+            for (; j < len; ++j) {
                 next_x = j + 1;
                 if (q[j] > 3) break;
                 cur = fext(f, cur, q[j], n_ext);
@@ -147,6 +194,54 @@ static void last_like_seeds(const orc_fmi_t *f, const uint8_t *q, int len, int64
             }
         }
         x = next_x;
+    }
+}
+
+/* ---- FMA table construction (SMEM_ACCEL) ------------------------------------------------------ */
+void orc_fma_entry_all(const orc_fmi_t *f, uint32_t idx, uint32_t out[32])
+{
+    memset(out, 0, 32 * sizeof(uint32_t));
+    int a = (idx >> 20) & 3;
+    biv_t cur = single_base(f, a, 0);
+    for (int i = 1; i < 11; ++i) {
+        a = (idx >> (2 * (10 - i))) & 3;
+        biv_t nw = fext(f, cur, a, NULL);
+        out[1 + 3 * (i - 1)] = (uint32_t)(nw.k - cur.k);
+        out[2 + 3 * (i - 1)] = (uint32_t)(nw.l - f->count[3 - a]);
+        out[3 + 3 * (i - 1)] = (uint32_t)nw.s;
+        if (nw.s > 0) out[0] = (uint32_t)i; else break;
+        cur = nw;
+    }
+}
+
+void orc_fma_entry_last(const orc_fmi_t *f, uint32_t idx, uint32_t out[4])
+{
+    int a = (idx >> 24) & 3, i;
+    biv_t cur = single_base(f, a, 0);
+    for (i = 1; i < 13; ++i) {
+        a = (idx >> (2 * (12 - i))) & 3;
+        biv_t nw = fext(f, cur, a, NULL);
+        if (nw.s == 0) break;
+        cur = nw;
+    }
+    out[0] = (uint32_t)i | (((uint32_t)(cur.k >> 32) & 0xFF) << 8) | (((uint32_t)(cur.l >> 32) & 0xFF) << 16) |
+             (((uint32_t)(cur.s >> 32) & 0xFF) << 24);
+    out[1] = (uint32_t)cur.k; out[2] = (uint32_t)cur.l; out[3] = (uint32_t)cur.s;
+}
+
+void orc_fma_build(const orc_fmi_t *f, uint32_t *all_tab, uint32_t *last_tab)
+{
+    if (all_tab)
+        for (uint32_t i = 0; i < (1u << 22); ++i) orc_fma_entry_all(f, i, all_tab + (size_t)i * 32);
+    if (last_tab)
+        for (uint32_t i = 0; i < (1u << 26); ++i) orc_fma_entry_last(f, i, last_tab + (size_t)i * 4);
+}
+
+void orc_fma_fill(const orc_fmi_t *f, int which_last, const uint32_t *idx, int64_t n, uint32_t *tab)
+{
+    for (int64_t i = 0; i < n; ++i) {
+        if (which_last) orc_fma_entry_last(f, idx[i], tab + (size_t)idx[i] * 4);
+        else orc_fma_entry_all(f, idx[i], tab + (size_t)idx[i] * 32);
     }
 }
 

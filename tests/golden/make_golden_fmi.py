@@ -49,6 +49,27 @@ def main():
             out[f"{name}_smem_sha256"] = digest(a[0])
             out[f"{name}_sa_sha256"] = digest(a[1])
             out[f"{name}_counts"] = np.array([len(a[0]), len(a[1])], np.int64)
+        # FMA ("accel") flavour: the reference's own smem-table output and its SMEM lists with the
+        # tables in use (they differ from the plain lists on reads with N and for short seeds)
+        import subprocess
+        subprocess.run([ol.ref_binary("accel", "sse41"), "smem-table", prefix], check=True,
+                       stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+        all_t = np.fromfile(prefix + ".all_smem.11", np.uint32)
+        last_t = np.fromfile(prefix + ".last_smem.13", np.uint32)
+        out["fma_all_sha256"] = digest(all_t)
+        out["fma_last_sha256"] = digest(last_t)
+        rng = np.random.default_rng(11)
+        ia = np.concatenate([np.arange(512), rng.integers(0, 1 << 22, 1536)])
+        il = np.concatenate([np.arange(512), rng.integers(0, 1 << 26, 1536)])
+        out["fma_all_sample_idx"], out["fma_all_sample"] = ia, all_t.reshape(-1, 32)[ia]
+        out["fma_last_sample_idx"], out["fma_last_sample"] = il, last_t.reshape(-1, 4)[il]
+        lib = ol.ref_api("accel", "sse41")
+        h = lib.ref_fmi_open(prefix.encode())
+        for name, kw, max_occ in fc.OPT_CASES:
+            sm = ol.reference_collect_smem(lib, h, ol.default_seed_opt(**kw), flat, off, ln)
+            out[f"fma_{name}_smem_sha256"] = digest(fc.smem_matrix(sm))
+            out[f"fma_{name}_count"] = np.array([len(sm)], np.int64)
+        lib.ref_fmi_close(h)
         # full vectors for the first 200 reads of the default case (small enough to commit)
         sm, sa = res[("sse41", "default")]
         keep = sm[:, 0] < 200

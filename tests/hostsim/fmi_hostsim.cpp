@@ -16,9 +16,11 @@ struct HostPrev {
 extern "C" int64_t hostsim_collect_smem(const bwagpu_fm_index_desc *d, const bwagpu_seed_opt *o,
                                         const uint8_t *reads, const int64_t *off, const int32_t *len,
                                         const uint8_t *skip, int32_t nseq, bwagpu_smem *out,
-                                        int64_t cap, int per_read_cap, int64_t *n_ext)
+                                        int64_t cap, int per_read_cap, int64_t *n_ext,
+                                        const uint32_t *fma_all, const uint32_t *fma_last)
 {
     FmView f;
+    f.fma_all = fma_all; f.fma_last = fma_last;
     f.cp_occ = (const int64_t *)d->cp_occ; f.sa_ms_byte = d->sa_ms_byte; f.sa_ls_word = d->sa_ls_word;
     memcpy(f.count, d->count, sizeof f.count);
     f.sentinel_index = d->sentinel_index; f.ref_seq_len = d->reference_seq_len;
@@ -53,6 +55,7 @@ extern "C" int64_t hostsim_sa_lookup(const bwagpu_fm_index_desc *d, const bwagpu
                                      int32_t max_occ, int64_t *coords)
 {
     FmView f;
+    f.fma_all = f.fma_last = nullptr;
     f.cp_occ = (const int64_t *)d->cp_occ; f.sa_ms_byte = d->sa_ms_byte; f.sa_ls_word = d->sa_ls_word;
     memcpy(f.count, d->count, sizeof f.count);
     f.sentinel_index = d->sentinel_index; f.ref_seq_len = d->reference_seq_len;
@@ -63,4 +66,19 @@ extern "C" int64_t hostsim_sa_lookup(const bwagpu_fm_index_desc *d, const bwagpu
         for (int r = 0; r < c; ++r) coords[w++] = fm_sa_walk(f, sm[i].k + r * step, nullptr);
     }
     return w;
+}
+
+// FMA table entries as the build kernels compute them (fma_entry_all / fma_entry_last)
+extern "C" void hostsim_fma_entries(const bwagpu_fm_index_desc *d, int which_last, const uint32_t *idx,
+                                    int64_t n, uint32_t *out)
+{
+    FmView f;
+    f.fma_all = f.fma_last = nullptr;
+    f.cp_occ = (const int64_t *)d->cp_occ; f.sa_ms_byte = d->sa_ms_byte; f.sa_ls_word = d->sa_ls_word;
+    memcpy(f.count, d->count, sizeof f.count);
+    f.sentinel_index = d->sentinel_index; f.ref_seq_len = d->reference_seq_len;
+    for (int64_t i = 0; i < n; ++i) {
+        if (which_last) fma_entry_last(f, idx[i], out + 4 * i);
+        else fma_entry_all(f, idx[i], out + 32 * i);
+    }
 }

@@ -79,7 +79,7 @@ assert SMEM_DTYPE.itemsize == 40
 class OrcFmi(C.Structure):
     _fields_ = [("ref_seq_len", C.c_int64), ("count", C.c_int64 * 5), ("cp_occ", C.c_void_p),
                 ("sa_ms_byte", C.c_void_p), ("sa_ls_word", C.c_void_p),
-                ("sentinel_index", C.c_int64)]
+                ("sentinel_index", C.c_int64), ("fma_all", C.c_void_p), ("fma_last", C.c_void_p)]
 
 
 class OrcSeedOpt(C.Structure):
@@ -93,9 +93,13 @@ def default_seed_opt(**kw) -> OrcSeedOpt:
     return OrcSeedOpt(**d)
 
 
-def orc_fmi(idx) -> OrcFmi:
-    """idx: bwa_mem_scale_b200.fmindex.FMIndex (arrays must stay alive while the struct is used)."""
+def orc_fmi(idx, fma=None) -> OrcFmi:
+    """idx: bwa_mem_scale_b200.fmindex.FMIndex (arrays must stay alive while the struct is used).
+    fma: optional (all_smem u32[4^11*32], last_smem u32[4^13*4]) tables; either may be None."""
     f = OrcFmi()
+    if fma is not None:
+        f.fma_all = fma[0].ctypes.data if fma[0] is not None else None
+        f.fma_last = fma[1].ctypes.data if fma[1] is not None else None
     f.ref_seq_len = idx.ref_seq_len
     for i, v in enumerate(idx.count_loaded()):
         f.count[i] = int(v)
@@ -122,13 +126,74 @@ def pack_reads(reads, lens=None):
     return np.ascontiguousarray(flat, dtype=np.uint8), off, ln
 
 
-def oracle_collect_smem(idx, opt: OrcSeedOpt, flat, off, ln, skip=None):
+def oracle_fma_entries(idx, which: str, indices) -> np.ndarray:
+    """Entries of the all (32 words) / last (4 words) FMA table for the given k-mer ranks."""
+    lib = oracle()
+    f = orc_fmi(idx)
+    w = 32 if which == "all" else 4
+    fn = lib.orc_fma_entry_all if which == "all" else lib.orc_fma_entry_last
+    fn.restype = None
+    fn.argtypes = [C.POINTER(OrcFmi), C.c_uint32, C.c_void_p]
+    out = np.zeros((len(indices), w), np.uint32)
+    for r, i in enumerate(indices):
+        fn(C.byref(f), int(i), out[r].ctypes.data)
+    return out
+
+
+def oracle_fma_sparse(idx, reads):
+    """(all, last) FMA tables holding only the entries `reads` (list of code arrays) can look up:
+    every 11-mer / 13-mer window prefix the seeding code indexes with (N-free part, zero-padded, as
+    src/FMI_search.cpp:1421-1427 builds the index).  Untouched entries stay zero (lazily-committed
+    pages), so this is cheap; contents of the touched entries equal the full tables'."""
+    lib = oracle()
+    lib.orc_fma_fill.restype = None
+    lib.orc_fma_fill.argtypes = [C.POINTER(OrcFmi), C.c_int, C.c_void_p, C.c_int64, C.c_void_p]
+    f = orc_fmi(idx)
+    ia, il = set(), set()
+    for r in reads:
+        r = np.asarray(r, np.int64)
+        n = len(r)
+        for x in range(n):
+            if n - x >= 11 and r[x] < 4:
+                v = 0
+                for k in range(11):
+                    if r[x + k] >= 4:
+                        break
+                    v |= int(r[x + k]) << ((10 - k) * 2)
+                ia.add(v)
+            if n - x >= 13 and r[x:x + 13].max() < 4:
+                v = 0
+                for k in range(13):
+                    v |= int(r[x + k]) << ((12 - k) * 2)
+                il.add(v)
+    a = np.zeros((1 << 22) * 32, np.uint32)
+    b = np.zeros((1 << 26) * 4, np.uint32)
+    ia = np.array(sorted(ia), np.uint32)
+    il = np.array(sorted(il), np.uint32)
+    lib.orc_fma_fill(C.byref(f), 0, ia.ctypes.data, len(ia), a.ctypes.data)
+    lib.orc_fma_fill(C.byref(f), 1, il.ctypes.data, len(il), b.ctypes.data)
+    return a, b
+
+
+def oracle_fma_build(idx, want_all=True, want_last=True):
+    """Both FMA tables from the oracle's builder (slow: ~1 minute for the pair)."""
+    lib = oracle()
+    lib.orc_fma_build.restype = None
+    lib.orc_fma_build.argtypes = [C.POINTER(OrcFmi), C.c_void_p, C.c_void_p]
+    f = orc_fmi(idx)
+    a = np.zeros((1 << 22) * 32, np.uint32) if want_all else None
+    b = np.zeros((1 << 26) * 4, np.uint32) if want_last else None
+    lib.orc_fma_build(C.byref(f), a.ctypes.data if want_all else None, b.ctypes.data if want_last else None)
+    return a, b
+
+
+def oracle_collect_smem(idx, opt: OrcSeedOpt, flat, off, ln, skip=None, fma=None):
     lib = oracle()
     lib.orc_collect_smem.restype = C.c_int64
     lib.orc_collect_smem.argtypes = [C.POINTER(OrcFmi), C.POINTER(OrcSeedOpt), C.c_void_p,
                                      C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p,
                                      C.c_int64, C.POINTER(C.c_int64)]
-    f = orc_fmi(idx)
+    f = orc_fmi(idx, fma)
     cap = max(int(ln.sum()) * 4, 1024)
     n_ext = C.c_int64(0)
     while True:

@@ -86,3 +86,34 @@ def test_skip_mask_and_empty():
     assert np.array_equal(fc.smem_matrix(part), fc.smem_matrix(full[full["rid"] % 2 == 1]))
     none, _ = ol.oracle_collect_smem(idx, opt, flat[:0], off[:0], ln[:0])
     assert len(none) == 0
+
+
+# ---- FMA tables (SMEM_ACCEL) -------------------------------------------------------------------
+def test_oracle_fma_entries_match_reference_tables():
+    """Entries of both tables against samples of the reference's own `smem-table` output."""
+    _, idx = fc.small_index()
+    assert np.array_equal(ol.oracle_fma_entries(idx, "all", GOLD["fma_all_sample_idx"]), GOLD["fma_all_sample"])
+    assert np.array_equal(ol.oracle_fma_entries(idx, "last", GOLD["fma_last_sample_idx"]), GOLD["fma_last_sample"])
+
+
+@pytest.mark.parametrize("case", fc.OPT_CASES, ids=[c[0] for c in fc.OPT_CASES])
+def test_oracle_fma_seeding_matches_golden(case):
+    """SMEM lists of the reference's accel build (tables in use): they differ from the plain lists
+    on reads with N and for seeds shorter than the table depth, and the oracle follows."""
+    name, kw, _ = case
+    ref, idx = fc.small_index()
+    reads = fc.small_reads(ref)
+    flat, off, ln = ol.pack_reads(reads)
+    fma = fma_tables(idx, reads)
+    sm, _ = ol.oracle_collect_smem(idx, ol.default_seed_opt(**kw), flat, off, ln, fma=fma)
+    assert len(sm) == int(GOLD[f"fma_{name}_count"][0])
+    assert np.array_equal(sha(fc.smem_matrix(sm)), GOLD[f"fma_{name}_smem_sha256"])
+
+
+_fma = {}
+
+
+def fma_tables(idx, reads):
+    if "t" not in _fma:
+        _fma["t"] = ol.oracle_fma_sparse(idx, reads)
+    return _fma["t"]

@@ -88,3 +88,65 @@ def test_gpu_seeding_config1_shape(gpu_ctx):
     assert np.all(np.diff(key) >= 0)
     assert np.all(got["n"] < 151) and np.all(got["m"] <= got["n"])
     assert np.all(got["s"] >= 1) and np.all(got["k"] + got["s"] <= idx.ref_seq_len)
+
+
+# ---- FMA tables (SMEM_ACCEL) -------------------------------------------------------------------
+def test_gpu_fma_tables_match_reference_bytes(gpu_ctx):
+    """Tables built on the device == the bytes the reference's `smem-table` command writes."""
+    ref, idx = fc.small_index()
+    fmi = FMI_search(idx, ctx=gpu_ctx)      # (earlier tests left another index on the shared context)
+    fmi.build_fma()
+    a, b = fmi.get_fma()
+    assert np.array_equal(a.reshape(-1, 32)[GOLD["fma_all_sample_idx"]], GOLD["fma_all_sample"])
+    assert np.array_equal(b.reshape(-1, 4)[GOLD["fma_last_sample_idx"]], GOLD["fma_last_sample"])
+    assert np.array_equal(sha(a), GOLD["fma_all_sha256"])
+    assert np.array_equal(sha(b), GOLD["fma_last_sha256"])
+    rng = np.random.default_rng(5)
+    ia, il = rng.integers(0, 1 << 22, 3000), rng.integers(0, 1 << 26, 3000)
+    assert np.array_equal(a.reshape(-1, 32)[ia], ol.oracle_fma_entries(idx, "all", ia))
+    assert np.array_equal(b.reshape(-1, 4)[il], ol.oracle_fma_entries(idx, "last", il))
+    fmi.use_fma(False)
+
+
+@pytest.mark.parametrize("mode", ["both", "all_only", "last_only", "uploaded"])
+def test_gpu_fma_seeding_matches_golden_and_oracle(gpu_ctx, mode):
+    ref, idx = fc.small_index()
+    fmi = FMI_search(idx, ctx=gpu_ctx)
+    fmi.build_fma()
+    a, b = fmi.get_fma()
+    fa, fl = a, b
+    if mode == "all_only":
+        fl = None
+    if mode == "last_only":
+        fa = None
+    if mode != "both":
+        fmi.load_fma(fa, fl)          # host tables in (what a caller holding the reference's files does)
+    flat, off, ln = ol.pack_reads(fc.small_reads(ref))
+    try:
+        for name, kw, max_occ in fc.OPT_CASES:
+            oo = ol.default_seed_opt(**kw)
+            got = fmi.collect_smem(seed_opt(oo.min_seed_len, oo.split_factor, oo.split_width, max_occ,
+                                            oo.max_mem_intv), flat, off, ln)
+            want, _ = ol.oracle_collect_smem(idx, oo, flat, off, ln, fma=(fa, fl))
+            assert np.array_equal(fc.smem_matrix(got), fc.smem_matrix(want)), (name, mode)
+            if mode in ("both", "uploaded"):
+                assert len(got) == int(GOLD[f"fma_{name}_count"][0])
+                assert np.array_equal(sha(fc.smem_matrix(got)), GOLD[f"fma_{name}_smem_sha256"])
+    finally:
+        fmi.load_fma(None, None)
+
+
+def test_gpu_fma_config1_shape(gpu_ctx):
+    """Config-1 shape with the tables on: on N-free 151-bp reads with default options the tables are
+    a pure memoisation, so the SMEM list equals the plain one."""
+    ref = synth.random_reference(1_000_000, 42)
+    idx = fmindex.build_fm_index(ref)
+    reads, _, _ = synth.simulate_reads(ref, 10000, seed=1)
+    fmi = FMI_search(idx, ctx=gpu_ctx)
+    flat, off, ln = ol.pack_reads(reads)
+    plain = fmi.collect_smem(seed_opt(), flat, off, ln)
+    fmi.build_fma()
+    got = fmi.collect_smem(seed_opt(), flat, off, ln)
+    assert np.array_equal(fc.smem_matrix(got), fc.smem_matrix(plain))
+    want, _ = ol.oracle_collect_smem(idx, ol.default_seed_opt(), flat, off, ln)
+    assert np.array_equal(fc.smem_matrix(got), fc.smem_matrix(want))
