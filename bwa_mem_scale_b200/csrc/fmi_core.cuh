@@ -223,6 +223,7 @@ struct SeedMachine {
     BWAGPU_HD void init(ReadStore q_, int len_, int rid_, PrevStore prev_, bwagpu_smem *out_, int cap_)
     {
         q = q_; len = len_; rid = rid_; prev = prev_; out = out_; cap = cap_; n_out = 0;
+        prev.reset(len_);
         round = 1; x = 0; min_intv = 1; state = len > 0 ? ST_PIVOT : ST_DONE; n_ext = 0;
         np = base = p = nc = decided = r1_count = r2_idx = 0; last_s = -1; j = next_x = 0;
         cur.k = cur.l = cur.s = 0; cur_n = 0; req = cur; req_a = 0;

@@ -13,33 +13,85 @@
 #include <cub/device/device_scan.cuh>
 #include "ctx.cuh"
 #include "fmi_core.cuh"
+#include <type_traits>
 
 #define SEED_TPB 128
 #ifndef SLOW_BATCH
 #define SLOW_BATCH 4
 #endif
 
-// prev list of one thread inside the interleaved scratch: word w of entry e of thread t lives at
-// buf[(e*3 + w) * stride + t]
+// prev list of one thread.  The first SEED_PREV_K entries pushed for a pivot live in shared memory
+// (4 words each: k, l, s low halves + a word of high bits and the span end n; word w of entry i of
+// thread t at sm[(i*4 + w) * SEED_TPB + t], bank = t: conflict-free); deeper entries spill to the
+// interleaved global scratch (word w of entry e of thread t at buf[(e*3 + w) * stride + t]).
+// Entries are addressed from the END of a len-sized array downwards (see SeedMachine), so slot
+// i = len - 1 - e is the push order.
+#ifndef SEED_PREV_K
+#define SEED_PREV_K 0
+#endif
+#define SEED_SMEM_BASES 256      // reads up to this long are staged in shared memory (4-bit codes)
+
 struct DevPrev {
+    uint32_t *sm;
     int64_t *buf;
-    int stride;
+    int stride, top;
+    __device__ __forceinline__ void reset(int len) { top = len - 1; }
     __device__ __forceinline__ void put(int e, const Biv &v, int n)
     {
-        int64_t *p = buf + (int64_t)(e * 3) * stride;
-        p[0] = v.k | ((int64_t)n << 40); p[stride] = v.l; p[2 * stride] = v.s;
+        const int i = top - e;
+        if (SEED_PREV_K > 0 && i < SEED_PREV_K) {
+            uint32_t *p = sm + i * 4 * SEED_TPB;
+            p[0] = (uint32_t)v.k; p[SEED_TPB] = (uint32_t)v.l; p[2 * SEED_TPB] = (uint32_t)v.s;
+            p[3 * SEED_TPB] = (uint32_t)(v.k >> 32) | ((uint32_t)(v.l >> 32) << 6) | ((uint32_t)(v.s >> 32) << 12) |
+                              ((uint32_t)n << 18);
+        } else {
+            int64_t *p = buf + (int64_t)(e * 3) * stride;
+            p[0] = v.k | ((int64_t)n << 40); p[stride] = v.l; p[2 * stride] = v.s;
+        }
     }
     __device__ __forceinline__ void get(int e, Biv &v, int &n) const
     {
-        const int64_t *p = buf + (int64_t)(e * 3) * stride;
-        const int64_t w0 = p[0];
-        v.k = w0 & ((1LL << 40) - 1); n = (int)(w0 >> 40); v.l = p[stride]; v.s = p[2 * stride];
+        const int i = top - e;
+        if (SEED_PREV_K > 0 && i < SEED_PREV_K) {
+            const uint32_t *p = sm + i * 4 * SEED_TPB;
+            const uint32_t hi = p[3 * SEED_TPB];
+            v.k = (int64_t)(((uint64_t)(hi & 63u) << 32) | p[0]);
+            v.l = (int64_t)(((uint64_t)((hi >> 6) & 63u) << 32) | p[SEED_TPB]);
+            v.s = (int64_t)(((uint64_t)((hi >> 12) & 63u) << 32) | p[2 * SEED_TPB]);
+            n = (int)(hi >> 18);
+        } else {
+            const int64_t *p = buf + (int64_t)(e * 3) * stride;
+            const int64_t w0 = p[0];
+            v.k = w0 & ((1LL << 40) - 1); n = (int)(w0 >> 40); v.l = p[stride]; v.s = p[2 * stride];
+        }
     }
 };
 
+// a read staged in shared memory as 4-bit codes, 8 per word (word i of thread t at w[i*SEED_TPB + t])
+struct SmemRead {
+    const uint32_t *w;
+    __device__ __forceinline__ int operator[](int j) const { return (int)((w[(j >> 3) * SEED_TPB] >> ((j & 7) * 4)) & 15u); }
+};
+
+__device__ __forceinline__ void seed_stage_read(uint32_t *w, const uint8_t *__restrict__ src, int len)
+{
+    for (int i = 0; i * 8 < len; ++i) {
+        uint32_t v = 0;
+#pragma unroll
+        for (int b = 0; b < 8; ++b)
+            if (i * 8 + b < len) { const uint32_t c = src[i * 8 + b]; v |= (c > 4u ? 4u : c) << (4 * b); }
+        w[i * SEED_TPB] = v;
+    }
+}
+
 struct SeedStats { unsigned long long n_ext, n_rec, n_lf, max_cnt; };
 
-__global__ void __launch_bounds__(SEED_TPB)
+#ifndef SEED_MIN_BLOCKS
+#define SEED_MIN_BLOCKS 1
+#endif
+// STAGED: every read of the batch is at most SEED_SMEM_BASES long and is staged in shared memory.
+template <bool STAGED>
+__global__ void __launch_bounds__(SEED_TPB, SEED_MIN_BLOCKS)
 seed_collect_kernel(FmView f, SeedOpt o, const uint8_t *__restrict__ reads,
                     const int64_t *__restrict__ off, const int32_t *__restrict__ len,
                     const uint8_t *__restrict__ skip, int nseq, bwagpu_smem *__restrict__ tmp,
@@ -48,8 +100,12 @@ seed_collect_kernel(FmView f, SeedOpt o, const uint8_t *__restrict__ reads,
 {
     const int64_t T = (int64_t)gridDim.x * blockDim.x;
     const int64_t t0 = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    DevPrev pv; pv.buf = prev_buf + t0; pv.stride = (int)T;
-    SeedMachine<DevPrev> m;
+    extern __shared__ uint32_t seed_sm[];
+    DevPrev pv; pv.buf = prev_buf + t0; pv.stride = (int)T; pv.top = 0;
+    pv.sm = seed_sm + threadIdx.x;
+    uint32_t *rd_sm = seed_sm + SEED_PREV_K * 4 * SEED_TPB + threadIdx.x;
+    using Read = typename std::conditional<STAGED, SmemRead, const uint8_t *>::type;
+    SeedMachine<DevPrev, Read> m;
     int64_t next = t0;
     bool active = false, ready = false, finished = false;
     unsigned long long n_ext = 0, n_rec = 0;
@@ -69,7 +125,13 @@ seed_collect_kernel(FmView f, SeedOpt o, const uint8_t *__restrict__ reads,
                         while (next < nseq) {
                             const int i = (int)next; next += T;
                             if (skip && skip[i]) { cnt[i] = 0; continue; }
-                            m.init(reads + off[i], len[i], i, pv, tmp + (int64_t)i * cap, cap);
+                            if constexpr (STAGED) {
+                                seed_stage_read(rd_sm, reads + off[i], len[i]);
+                                SmemRead r; r.w = rd_sm;
+                                m.init(r, len[i], i, pv, tmp + (int64_t)i * cap, cap);
+                            } else {
+                                m.init(reads + off[i], len[i], i, pv, tmp + (int64_t)i * cap, cap);
+                            }
                             got = true;
                             break;
                         }
@@ -267,8 +329,8 @@ extern "C" int bwagpu_index_load_fm(bwagpu_ctx *ctx, const bwagpu_fm_index_desc 
     if (!ctx) return BWAGPU_ERR_ARG;
     if (!d || !d->cp_occ || !d->sa_ms_byte || !d->sa_ls_word || d->reference_seq_len <= 0)
         BWAGPU_FAIL(ctx, BWAGPU_ERR_ARG, "index_load_fm: incomplete index descriptor");
-    if (d->reference_seq_len >= (1LL << 39))
-        BWAGPU_FAIL(ctx, BWAGPU_ERR_RANGE, "index_load_fm: text longer than 2^39 symbols is not supported");
+    if (d->reference_seq_len >= (1LL << 38))
+        BWAGPU_FAIL(ctx, BWAGPU_ERR_RANGE, "index_load_fm: text longer than 2^38 symbols is not supported");
     BWAGPU_CUDA(ctx, cudaSetDevice(ctx->device));
     BWAGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     if (ctx->d_cp_occ) { cudaFree(ctx->d_cp_occ); cudaFree(ctx->d_sa_ms); cudaFree(ctx->d_sa_ls); }
@@ -340,8 +402,13 @@ static int seed_collect_dev(bwagpu_ctx *ctx, const bwagpu_seed_opt *opt, const u
     so.split_len = (int)(opt->min_seed_len * opt->split_factor + .499);
     so.split_width = opt->split_width;
     so.max_mem_intv = opt->max_mem_intv;
+    const bool staged = max_len <= SEED_SMEM_BASES;
+    const size_t smem = (size_t)(SEED_PREV_K * 4 + (staged ? (max_len + 7) / 8 : 0)) * SEED_TPB * 4;
+    if (staged) BWAGPU_CUDA(ctx, cudaFuncSetAttribute(seed_collect_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    else BWAGPU_CUDA(ctx, cudaFuncSetAttribute(seed_collect_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int per_sm = 0;
-    BWAGPU_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, seed_collect_kernel, SEED_TPB, 0));
+    if (staged) BWAGPU_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, seed_collect_kernel<true>, SEED_TPB, smem));
+    else BWAGPU_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, seed_collect_kernel<false>, SEED_TPB, smem));
     if (per_sm < 1) per_sm = 1;
     int blocks = ctx->sm_count * per_sm;
     const int need = (nseq + SEED_TPB - 1) / SEED_TPB;
@@ -360,8 +427,12 @@ static int seed_collect_dev(bwagpu_ctx *ctx, const bwagpu_seed_opt *opt, const u
         BWAGPU_CUDA(ctx, cudaMemsetAsync(d_stats, 0, sizeof(SeedStats), ctx->stream));
         BWAGPU_CUDA(ctx, cudaMemsetAsync(d_cnt + nseq, 0, 4, ctx->stream));
         BWAGPU_KERNEL_BEGIN(ctx);
-        seed_collect_kernel<<<blocks, SEED_TPB, 0, ctx->stream>>>(fm_view(ctx), so, d_reads, d_off, d_len, d_skip,
-                                                                 nseq, d_tmp, cap, d_cnt, d_prev, d_stats);
+        if (staged)
+            seed_collect_kernel<true><<<blocks, SEED_TPB, smem, ctx->stream>>>(fm_view(ctx), so, d_reads, d_off, d_len, d_skip,
+                                                                              nseq, d_tmp, cap, d_cnt, d_prev, d_stats);
+        else
+            seed_collect_kernel<false><<<blocks, SEED_TPB, smem, ctx->stream>>>(fm_view(ctx), so, d_reads, d_off, d_len, d_skip,
+                                                                               nseq, d_tmp, cap, d_cnt, d_prev, d_stats);
         BWAGPU_KERNEL_END(ctx, BWAGPU_KERN_SEED_COLLECT);
         BWAGPU_CUDA(ctx, cudaGetLastError());
         BWAGPU_CUDA(ctx, cudaMemcpyAsync(h_stats, d_stats, sizeof(SeedStats), cudaMemcpyDeviceToHost, ctx->stream));

@@ -9,6 +9,7 @@
 
 struct HostPrev {
     int64_t *buf;
+    void reset(int) {}
     void put(int e, const Biv &v, int n) { buf[3 * e] = v.k | ((int64_t)n << 40); buf[3 * e + 1] = v.l; buf[3 * e + 2] = v.s; }
     void get(int e, Biv &v, int &n) const { v.k = buf[3 * e] & ((1LL << 40) - 1); n = (int)(buf[3 * e] >> 40); v.l = buf[3 * e + 1]; v.s = buf[3 * e + 2]; }
 };
