@@ -7,3 +7,4 @@ from .lib import BwaGpuError, BswParams, Context, LIB_PATH, load  # noqa: F401
 from .bsw import BandedPairWiseSW  # noqa: F401
 from .seeding import FMI_search, SMEM_DTYPE, seed_opt, pack_reads  # noqa: F401
 from .fmindex import FMIndex, build_fm_index  # noqa: F401
+from .ksw import MateSW, KSWR_DTYPE, fill_scmat  # noqa: F401

@@ -24,6 +24,12 @@ class BswParams(C.Structure):
                 ("o_del", "e_del", "o_ins", "e_ins", "zdrop", "end_bonus", "w_match", "w_mismatch")]
 
 
+class KswParams(C.Structure):
+    """bwagpu_ksw_params — the batch-constant arguments of ksw_align2 (reference src/ksw.cpp:347-350)."""
+    _fields_ = [("mat", C.c_int8 * 25), ("pad_", C.c_int8 * 3), ("o_del", C.c_int32), ("e_del", C.c_int32),
+                ("o_ins", C.c_int32), ("e_ins", C.c_int32)]
+
+
 class FmIndexDesc(C.Structure):
     """bwagpu_fm_index_desc — the arrays FMI_search::load_index leaves in memory
     (reference src/FMI_search.cpp:1251-1351); count[] in loaded form (file value + 1)."""
@@ -67,6 +73,10 @@ _SIGS = {
     "bwagpu_bsw_get_scores_device": (C.c_int, [C.c_void_p, C.POINTER(BswParams), C.c_int,
                                                C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p,
                                                C.c_int64, C.c_int32, C.c_int32]),
+    "bwagpu_ksw_align2_batch": (C.c_int, [C.c_void_p, C.POINTER(KswParams), C.c_void_p, C.c_void_p, C.c_void_p,
+                                          C.c_void_p, C.c_int32]),
+    "bwagpu_ksw_align2_batch_device": (C.c_int, [C.c_void_p, C.POINTER(KswParams), C.c_void_p, C.c_void_p,
+                                                 C.c_void_p, C.c_void_p, C.c_int32]),
     "bwagpu_index_load_fm": (C.c_int, [C.c_void_p, C.POINTER(FmIndexDesc)]),
     "bwagpu_index_build_fma": (C.c_int, [C.c_void_p]),
     "bwagpu_index_load_fma": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p]),

@@ -204,3 +204,50 @@ def ragged_reads(ref: np.ndarray, n_reads: int, seed: int, len_lo: int = 10, len
         r[rng.random(L) < n_frac] = 4
         out.append(r)
     return out
+
+
+def rescue_jobs(n_jobs: int, seed: int = 11, qlen_lo: int = 151, qlen_hi: int = 151, win_lo: int = 200,
+                win_hi: int = 900, sub_rate: float = 0.02, indel_rate: float = 0.003, n_rate: float = 0.0,
+                hit_frac: float = 0.7, xtra: int | None = None, a: int = 1, min_seed_len: int = 19,
+                repeat_frac: float = 0.2):
+    """Mate-rescue jobs shaped like those mem_matesw hands to ksw_align2 (reference
+    src/bwamem_pair.cpp:170-260): query = a whole read (len2), target = an insert-size window of the
+    reference (len1) that contains a mutated copy of the read in `hit_frac` of the jobs (and a second,
+    more diverged copy in some, so that score2/te2 are exercised).  h0 carries `xtra` as in
+    mem_sam_pe_batch_pre (KSW_XSUBO | KSW_XSTART | KSW_XBYTE when len2*a < 250 | min_seed_len*a).
+    Returns (pairs[SEQPAIR_DTYPE], ref_buf, qer_buf)."""
+    rng = np.random.default_rng(seed)
+    pairs = np.zeros(n_jobs, SEQPAIR_DTYPE)
+    refs, qers = [], []
+    ro = qo = 0
+    for i in range(n_jobs):
+        ql = int(rng.integers(qlen_lo, qlen_hi + 1))
+        wl = int(rng.integers(max(win_lo, 1), win_hi + 1))
+        win = rng.integers(0, 4, wl).astype(np.uint8)
+        q = rng.integers(0, 4, ql).astype(np.uint8)
+        if rng.random() < hit_frac and wl > 8:
+            for rep, rate in enumerate((sub_rate, 6 * sub_rate)):
+                if rep == 1 and rng.random() > repeat_frac:
+                    break
+                src = q.copy()
+                sub = rng.random(ql) < rate
+                src = np.where(sub, (src + rng.integers(1, 4, ql)) & 3, src).astype(np.uint8)
+                if rng.random() < indel_rate * ql and ql > 20:      # one indel of 1-6 bases
+                    p, g = int(rng.integers(5, ql - 5)), int(rng.integers(1, 7))
+                    src = (np.concatenate([src[:p], src[p + g:]]) if rng.random() < 0.5 else
+                           np.concatenate([src[:p], rng.integers(0, 4, g).astype(np.uint8), src[p:]]))
+                cut = int(rng.integers(0, max(len(src) // 3, 1))) if rng.random() < 0.2 else 0
+                src = src[cut:]
+                pos = int(rng.integers(0, max(wl - len(src), 0) + 1))
+                seg = src[:max(wl - pos, 0)]
+                win[pos:pos + len(seg)] = seg
+        if n_rate > 0:
+            q = np.where(rng.random(ql) < n_rate, 4, q).astype(np.uint8)
+            win = np.where(rng.random(wl) < n_rate, 4, win).astype(np.uint8)
+        x = xtra if xtra is not None else (0x40000 | 0x80000 | (0x10000 if ql * a < 250 else 0) | (min_seed_len * a))
+        pairs[i]["idr"], pairs[i]["idq"], pairs[i]["id"] = ro, qo, i
+        pairs[i]["len1"], pairs[i]["len2"], pairs[i]["h0"] = wl, ql, x
+        pairs[i]["seqid"], pairs[i]["regid"] = i, i
+        refs.append(win); qers.append(q)
+        ro += wl; qo += ql
+    return pairs, np.concatenate(refs + [np.zeros(64, np.uint8)]), np.concatenate(qers + [np.zeros(64, np.uint8)])

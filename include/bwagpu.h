@@ -45,7 +45,7 @@ int bwagpu_timer_stop(bwagpu_ctx *ctx, float *elapsed_ms);   /* records, synchro
  * kernels is bracketed by CUDA events on the context's stream (this serialises the stream, so
  * leave it off when measuring whole-step throughput).  set_profiling also clears the counters. */
 enum { BWAGPU_KERN_SEED_COLLECT = 0, BWAGPU_KERN_SEED_SORT = 1, BWAGPU_KERN_SA_WALK = 2,
-       BWAGPU_KERN_BSW = 3, BWAGPU_KERN_BSW_GENERIC = 4, BWAGPU_KERN_FMA_BUILD = 5,
+       BWAGPU_KERN_BSW = 3, BWAGPU_KERN_BSW_GENERIC = 4, BWAGPU_KERN_FMA_BUILD = 5, BWAGPU_KERN_KSW = 6,
        BWAGPU_KERN_N = 16 };
 int bwagpu_set_profiling(bwagpu_ctx *ctx, int on);
 int bwagpu_kernel_time(const bwagpu_ctx *ctx, int which, double *ms, int64_t *launches);
@@ -94,6 +94,37 @@ int bwagpu_bsw_get_scores_device(bwagpu_ctx *ctx, const bwagpu_bsw_params *prm, 
                                  bwagpu_seqpair *d_pairArray, const uint8_t *d_seqBufRef,
                                  int64_t ref_bytes, const uint8_t *d_seqBufQer, int64_t qer_bytes,
                                  int32_t numPairs, int32_t w);
+
+/* ---- S3: mate-rescue local Smith-Waterman ------------------------------------------------------
+ * bwagpu_kswr mirrors kswr_t (reference src/ksw.h), 28 bytes. */
+typedef struct {
+    int32_t score, te, qe, score2, te2, tb, qb;
+} bwagpu_kswr;
+
+/* arguments of ksw_align2 that are constant over a batch (reference src/ksw.cpp:347-350):
+ * m = 5, mat = opt->mat (5x5, row = target base, column = query base; bwa_fill_scmat
+ * src/bwa.cpp:368-378), gap penalties as mem_matesw passes them (src/bwamem_pair.cpp:217-219). */
+typedef struct {
+    int8_t mat[25];
+    int8_t pad_[3];
+    int32_t o_del, e_del, o_ins, e_ins;
+} bwagpu_ksw_params;
+
+/* Replaces the per-job ksw_align2 calls of mate rescue — the body of mem_sam_pe_batch (reference
+ * src/bwamem_pair.cpp:880-979, whose own sequential form is :891-902) and the call in mem_matesw
+ * (:217): for job i, query = seqBufQer + idq (len2 bases), target = seqBufRef + idr (len1 bases),
+ * xtra = h0 (KSW_XBYTE 0x10000 selects the 8-bit kernel, KSW_XSUBO 0x40000 | minimum score,
+ * KSW_XSTART 0x80000 = also find (tb, qb) with the reversed pass); aln[i] = the kswr_t that
+ * ksw_align2(len2, query, len1, target, 5, mat, o_del, e_del, o_ins, e_ins, xtra, 0) returns,
+ * bit-identical to the reference's striped SSE2 kernels.  Inputs are not modified (the reference
+ * reverses and restores them in place).  HOST buffers; queries up to 4096 bases. */
+int bwagpu_ksw_align2_batch(bwagpu_ctx *ctx, const bwagpu_ksw_params *prm, const bwagpu_seqpair *pairArray,
+                            const uint8_t *seqBufRef, const uint8_t *seqBufQer, bwagpu_kswr *aln,
+                            int32_t numPairs);
+/* same with every buffer resident in HBM; asynchronous on the context's stream after one scalar read-back */
+int bwagpu_ksw_align2_batch_device(bwagpu_ctx *ctx, const bwagpu_ksw_params *prm,
+                                   const bwagpu_seqpair *d_pairArray, const uint8_t *d_seqBufRef,
+                                   const uint8_t *d_seqBufQer, bwagpu_kswr *d_aln, int32_t numPairs);
 
 /* ---- S1: FM-index seeding --------------------------------------------------------------------
  * bwagpu_smem mirrors SMEM (reference src/FMI_search.h:85-93, non-DEBUG build), 40 bytes. */

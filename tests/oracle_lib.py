@@ -267,3 +267,47 @@ def reference_sa_lookup(lib, h, smems, max_occ=500):
     smems = np.ascontiguousarray(smems)
     n = lib.ref_sa_lookup(h, smems.ctypes.data, len(smems), max_occ, coords.ctypes.data)
     return coords[:n].copy()
+
+
+# ---- mate-rescue local SW (ksw_align2) -----------------------------------------------------------
+KSWR_DTYPE = np.dtype([(n, "<i4") for n in ("score", "te", "qe", "score2", "te2", "tb", "qb")])
+KSW_XBYTE, KSW_XSTOP, KSW_XSUBO, KSW_XSTART = 0x10000, 0x20000, 0x40000, 0x80000
+
+
+def score_matrix(a=1, b=4) -> np.ndarray:
+    """bwa_fill_scmat (reference src/bwa.cpp:368-378): 5x5, ambiguous = -1."""
+    m = np.full((5, 5), -1, np.int8)
+    for i in range(4):
+        for j in range(4):
+            m[i, j] = a if i == j else -b
+    return np.ascontiguousarray(m.reshape(-1))
+
+
+def oracle_ksw(pairs, ref, qer, mat=None, o_del=6, e_del=1, o_ins=6, e_ins=1):
+    lib = oracle()
+    mat = score_matrix() if mat is None else mat
+    aln = np.zeros(len(pairs), KSWR_DTYPE)
+    lib.orc_ksw_batch.restype = None
+    lib.orc_ksw_batch.argtypes = [C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int,
+                                  C.c_int, C.c_int, C.c_void_p]
+    pairs = np.ascontiguousarray(pairs)
+    lib.orc_ksw_batch(pairs.ctypes.data, len(pairs), ref.ctypes.data, qer.ctypes.data, mat.ctypes.data,
+                      o_del, e_del, o_ins, e_ins, aln.ctypes.data)
+    return aln
+
+
+def ref_ksw():
+    path = os.path.join(ORACLE_DIR, "_ref", "libref_ksw.so")
+    return C.CDLL(path) if os.path.exists(path) else None
+
+
+def reference_ksw(lib, pairs, ref, qer, mat=None, o_del=6, e_del=1, o_ins=6, e_ins=1):
+    mat = score_matrix() if mat is None else mat
+    aln = np.zeros(len(pairs), KSWR_DTYPE)
+    lib.ref_ksw_batch.restype = None
+    lib.ref_ksw_batch.argtypes = [C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int,
+                                  C.c_int, C.c_int, C.c_void_p]
+    pairs = np.ascontiguousarray(pairs)
+    lib.ref_ksw_batch(pairs.ctypes.data, len(pairs), ref.ctypes.data, qer.ctypes.data, mat.ctypes.data,
+                      o_del, e_del, o_ins, e_ins, aln.ctypes.data)
+    return aln
