@@ -12,9 +12,15 @@
 #include <cstring>
 #include "bwamem.h"
 #include "FMI_search.h"
+#include "bwa.h"
+#include <cstdio>
 
 // globals main.cpp owns upstream (src/main.cpp:48)
 uint64_t proc_freq = 1, tprof[LIM_R][LIM_C], prof[LIM_R];
+
+// the definition (src/bwamem.cpp:1209-1217) takes seedBuf/seedBufSize; the header's declaration is stale
+int mem_kernel1_core(FMI_search *fmi, const mem_opt_t *opt, bseq1_t *seq_, int nseq, mem_chain_v *chain_ar,
+                     mem_seed_t *seedBuf, int64_t seedBufSize, mem_cache *mmc, int tid);
 
 SMEM *mem_collect_smem(FMI_search *fmi, const mem_opt_t *opt, const bseq1_t *seq_, int nseq,
                        SMEM *matchArray, int32_t *min_intv_ar, int16_t *query_pos_ar,
@@ -89,6 +95,144 @@ int64_t ref_sa_lookup(void *h, SMEM *smems, int64_t n, int32_t max_occ, int64_t 
         b = e;
     }
     return cnt;
+}
+
+// ---- chaining + extension taps --------------------------------------------------------------
+// Runs the reference's own mem_kernel1_core (seeding + mem_chain_seeds + mem_chain_flt, src/bwamem.cpp:
+// 1209-1378) and mem_chain2aln_across_reads_V2 (:2810-3745) on caller-provided reads, 512 at a time
+// like worker_bwt / worker_aln (src/macro.h:63), and returns flattened copies of
+//   chains : per chain  {seqid, rid, n, w, kept, first, is_alt} + frac_rep + pos, seeds {rbeg, qbeg, len, score}
+//   regs   : per read the mem_alnreg_t records V2 leaves in av_v (including purged ones, qb = qe = -1)
+struct ref_mem_ctx {
+    FMI_search *fmi;
+    uint8_t *ref_string;
+    mem_cache mmc;
+    mem_seed_t *seedBuf;
+};
+
+void *ref_mem_open(const char *prefix)
+{
+    ref_mem_ctx *c = (ref_mem_ctx *)calloc(1, sizeof(ref_mem_ctx));
+    c->fmi = new FMI_search(prefix);
+    c->fmi->load_index();
+    char fn[4096];
+    snprintf(fn, sizeof fn, "%s.0123", prefix);
+    FILE *fp = fopen(fn, "rb");
+    fseek(fp, 0, SEEK_END); long rlen = ftell(fp); fseek(fp, 0, SEEK_SET);
+    c->ref_string = (uint8_t *)_mm_malloc(rlen + 256, 64);
+    if (fread(c->ref_string, 1, rlen, fp) != (size_t)rlen) return nullptr;
+    fclose(fp);
+    // arenas of one worker thread, sized as memoryAlloc does (src/fastmap.cpp:222-300)
+    const int64_t wsize = BATCH_SIZE * SEEDS_PER_READ;
+    const int readLen = 1024;
+    mem_cache &m = c->mmc;
+    m.seqBufLeftRef[0] = (uint8_t *)_mm_malloc(wsize * MAX_SEQ_LEN_REF + MAX_LINE_LEN, 64);
+    m.seqBufLeftQer[0] = (uint8_t *)_mm_malloc(wsize * MAX_SEQ_LEN_QER + MAX_LINE_LEN, 64);
+    m.seqBufRightRef[0] = (uint8_t *)_mm_malloc(wsize * MAX_SEQ_LEN_REF + MAX_LINE_LEN, 64);
+    m.seqBufRightQer[0] = (uint8_t *)_mm_malloc(wsize * MAX_SEQ_LEN_QER + MAX_LINE_LEN, 64);
+    m.wsize_buf_ref[0] = wsize * MAX_SEQ_LEN_REF;
+    m.wsize_buf_qer[0] = wsize * MAX_SEQ_LEN_QER;
+    m.seqPairArrayAux[0] = (SeqPair *)malloc((wsize + MAX_LINE_LEN) * sizeof(SeqPair));
+    m.seqPairArrayLeft128[0] = (SeqPair *)malloc((wsize + MAX_LINE_LEN) * sizeof(SeqPair));
+    m.seqPairArrayRight128[0] = (SeqPair *)malloc((wsize + MAX_LINE_LEN) * sizeof(SeqPair));
+    m.wsize[0] = wsize;
+    m.wsize_mem[0] = (int64_t)BATCH_MUL * BATCH_SIZE * readLen;
+    m.matchArray[0] = (SMEM *)_mm_malloc(m.wsize_mem[0] * sizeof(SMEM), 64);
+    m.min_intv_ar[0] = (int32_t *)malloc(m.wsize_mem[0] * sizeof(int32_t));
+    m.query_pos_ar[0] = (int16_t *)malloc(m.wsize_mem[0] * sizeof(int16_t));
+    m.enc_qdb[0] = (uint8_t *)malloc(m.wsize_mem[0] * sizeof(uint8_t));
+    m.rid[0] = (int32_t *)malloc(m.wsize_mem[0] * sizeof(int32_t));
+    m.lim[0] = (int32_t *)_mm_malloc((BATCH_SIZE + 32) * sizeof(int32_t), 64);
+    c->seedBuf = (mem_seed_t *)calloc(sizeof(mem_seed_t), (size_t)BATCH_SIZE * AVG_SEEDS_PER_READ);
+    return c;
+}
+
+int64_t ref_mem_l_pac(void *h) { return ((ref_mem_ctx *)h)->fmi->idx->bns->l_pac; }
+int ref_mem_n_seqs(void *h) { return ((ref_mem_ctx *)h)->fmi->idx->bns->n_seqs; }
+void ref_mem_contigs(void *h, int64_t *offset, int32_t *len)
+{
+    const bntseq_t *bns = ((ref_mem_ctx *)h)->fmi->idx->bns;
+    for (int i = 0; i < bns->n_seqs; ++i) { offset[i] = bns->anns[i].offset; len[i] = bns->anns[i].len; }
+}
+
+struct ref_chain_rec { int32_t seqid, rid, n, w, kept, first, is_alt; float frac_rep; int64_t pos; int64_t seed_off; };
+struct ref_seed_rec { int64_t rbeg; int32_t qbeg, len, score, pad_; };
+struct ref_reg_rec { int64_t rb, re; int32_t qb, qe, rid, score, truesc, w, seedcov, seedlen0, chain; float frac_rep; };
+
+// opt_i: a, b, o_del, e_del, o_ins, e_ins, pen_clip5, pen_clip3, w, zdrop, min_seed_len, max_occ, max_chain_gap,
+//        min_chain_weight, max_chain_extend, split_width (16 ints); opt_f: split_factor, mask_level, drop_ratio
+// returns 0; counts in n_out[0..2] = chains, seeds, regs.  Buffers must be large enough (caps in cap[0..2]).
+int ref_mem_core(void *h, const int32_t *opt_i, const float *opt_f, int64_t max_mem_intv,
+                 const uint8_t *reads, const int64_t *off, const int32_t *len, int nseq,
+                 ref_chain_rec *chains, ref_seed_rec *seeds, ref_reg_rec *regs, int64_t *reg_off,
+                 const int64_t *cap, int64_t *n_out)
+{
+    ref_mem_ctx *c = (ref_mem_ctx *)h;
+    mem_opt_t *opt = mem_opt_init();
+    opt->a = opt_i[0]; opt->b = opt_i[1]; opt->o_del = opt_i[2]; opt->e_del = opt_i[3]; opt->o_ins = opt_i[4];
+    opt->e_ins = opt_i[5]; opt->pen_clip5 = opt_i[6]; opt->pen_clip3 = opt_i[7]; opt->w = opt_i[8];
+    opt->zdrop = opt_i[9]; opt->min_seed_len = opt_i[10]; opt->max_occ = opt_i[11]; opt->max_chain_gap = opt_i[12];
+    opt->min_chain_weight = opt_i[13]; opt->max_chain_extend = opt_i[14]; opt->split_width = opt_i[15];
+    opt->split_factor = opt_f[0]; opt->mask_level = opt_f[1]; opt->drop_ratio = opt_f[2];
+    opt->max_mem_intv = max_mem_intv;
+    bwa_fill_scmat(opt->a, opt->b, opt->mat);
+    int64_t nc = 0, ns = 0, nr = 0;
+    for (int b0 = 0; b0 < nseq; b0 += BATCH_SIZE) {
+        const int nb = nseq - b0 < BATCH_SIZE ? nseq - b0 : BATCH_SIZE;
+        bseq1_t *seqs = (bseq1_t *)calloc(nb, sizeof(bseq1_t));
+        char name[8] = "r";
+        for (int i = 0; i < nb; ++i) {
+            seqs[i].l_seq = len[b0 + i];
+            seqs[i].id = b0 + i;
+            seqs[i].name = name;
+            seqs[i].seq = (char *)malloc(len[b0 + i] + 8);      // kernel 1 rewrites seq in place (already 2-bit here)
+            memcpy(seqs[i].seq, reads + off[b0 + i], len[b0 + i]);
+        }
+        mem_chain_v *chain_ar = (mem_chain_v *)malloc(nb * sizeof(mem_chain_v));
+        mem_alnreg_v *av = (mem_alnreg_v *)calloc(nb, sizeof(mem_alnreg_v));
+        memset(c->seedBuf, 0, sizeof(mem_seed_t) * (size_t)BATCH_SIZE * AVG_SEEDS_PER_READ);
+        mem_kernel1_core(c->fmi, opt, seqs, nb, chain_ar, c->seedBuf, (int64_t)BATCH_SIZE * AVG_SEEDS_PER_READ, &c->mmc, 0);
+        const int64_t chain_base = nc;
+        for (int i = 0; i < nb; ++i)
+            for (size_t j = 0; j < chain_ar[i].n; ++j) {
+                const mem_chain_t &ch = chain_ar[i].a[j];
+                if (nc < cap[0]) {
+                    ref_chain_rec &o = chains[nc];
+                    o.seqid = b0 + ch.seqid; o.rid = ch.rid; o.n = ch.n; o.w = ch.w; o.kept = ch.kept; o.first = ch.first;
+                    o.is_alt = ch.is_alt; o.frac_rep = ch.frac_rep; o.pos = ch.pos; o.seed_off = ns;
+                }
+                ++nc;
+                for (int k = 0; k < ch.n; ++k, ++ns)
+                    if (ns < cap[1]) { seeds[ns].rbeg = ch.seeds[k].rbeg; seeds[ns].qbeg = ch.seeds[k].qbeg;
+                                       seeds[ns].len = ch.seeds[k].len; seeds[ns].score = ch.seeds[k].score; seeds[ns].pad_ = 0; }
+            }
+        for (int i = 0; i < nb; ++i) kv_init(av[i]);
+        mem_chain2aln_across_reads_V2(opt, c->fmi->idx->bns, c->fmi->idx->pac, seqs, nb, chain_ar, av, &c->mmc, c->ref_string, 0);
+        int64_t cbase = chain_base;
+        for (int i = 0; i < nb; ++i) {
+            reg_off[b0 + i] = nr;
+            for (size_t r = 0; r < av[i].n; ++r, ++nr) {
+                const mem_alnreg_t &a = av[i].a[r];
+                if (nr < cap[2]) {
+                    ref_reg_rec &o = regs[nr];
+                    o.rb = a.rb; o.re = a.re; o.qb = a.qb; o.qe = a.qe; o.rid = a.rid; o.score = a.score; o.truesc = a.truesc;
+                    o.w = a.w; o.seedcov = a.seedcov; o.seedlen0 = a.seedlen0; o.frac_rep = a.frac_rep;
+                    o.chain = (int32_t)(cbase + (a.c - chain_ar[i].a));
+                }
+            }
+            cbase += chain_ar[i].n;
+        }
+        for (int i = 0; i < nb; ++i) {
+            for (size_t j = 0; j < chain_ar[i].n; ++j)
+                if (chain_ar[i].a[j].m > SEEDS_PER_CHAIN) free(chain_ar[i].a[j].seeds);
+            free(chain_ar[i].a); free(av[i].a); free(seqs[i].seq);
+        }
+        free(chain_ar); free(av); free(seqs);
+    }
+    reg_off[nseq] = nr;
+    n_out[0] = nc; n_out[1] = ns; n_out[2] = nr;
+    free(opt);
+    return 0;
 }
 
 }  // extern "C"

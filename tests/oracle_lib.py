@@ -311,3 +311,92 @@ def reference_ksw(lib, pairs, ref, qer, mat=None, o_del=6, e_del=1, o_ins=6, e_i
     lib.ref_ksw_batch(pairs.ctypes.data, len(pairs), ref.ctypes.data, qer.ctypes.data, mat.ctypes.data,
                       o_del, e_del, o_ins, e_ins, aln.ctypes.data)
     return aln
+
+
+# ---- chaining + extension (mem_kernel1_core / mem_chain2aln_across_reads_V2 taps) ------------------
+CHAIN_DTYPE = np.dtype([("seqid", "<i4"), ("rid", "<i4"), ("n", "<i4"), ("w", "<i4"), ("kept", "<i4"),
+                        ("first", "<i4"), ("is_alt", "<i4"), ("frac_rep", "<f4"), ("pos", "<i8"),
+                        ("seed_off", "<i8")])
+SEED_DTYPE = np.dtype([("rbeg", "<i8"), ("qbeg", "<i4"), ("len", "<i4"), ("score", "<i4"), ("pad_", "<i4")])
+REG_DTYPE = np.dtype([("rb", "<i8"), ("re", "<i8"), ("qb", "<i4"), ("qe", "<i4"), ("rid", "<i4"),
+                      ("score", "<i4"), ("truesc", "<i4"), ("w", "<i4"), ("seedcov", "<i4"),
+                      ("seedlen0", "<i4"), ("chain", "<i4"), ("frac_rep", "<f4")])
+assert CHAIN_DTYPE.itemsize == 48 and SEED_DTYPE.itemsize == 24 and REG_DTYPE.itemsize == 56
+
+
+def mem_opt(**kw):
+    """Defaults of mem_opt_init (reference src/bwamem.cpp:135-171) for the fields the taps take."""
+    d = dict(a=1, b=4, o_del=6, e_del=1, o_ins=6, e_ins=1, pen_clip5=5, pen_clip3=5, w=100, zdrop=100,
+             min_seed_len=19, max_occ=500, max_chain_gap=10000, min_chain_weight=0, max_chain_extend=1 << 30,
+             split_width=10, split_factor=1.5, mask_level=0.5, drop_ratio=0.5, max_mem_intv=20)
+    d.update(kw)
+    return d
+
+
+def opt_arrays(o):
+    oi = np.array([o[k] for k in ("a", "b", "o_del", "e_del", "o_ins", "e_ins", "pen_clip5", "pen_clip3", "w",
+                                  "zdrop", "min_seed_len", "max_occ", "max_chain_gap", "min_chain_weight",
+                                  "max_chain_extend", "split_width")], np.int32)
+    of = np.array([o["split_factor"], o["mask_level"], o["drop_ratio"]], np.float32)
+    return oi, of
+
+
+class RefMem:
+    """The reference's own seeding -> chaining -> extension core on an index written to disk."""
+
+    def __init__(self, prefix: str, flavor="plain", isa="sse41"):
+        path = os.path.join(ORACLE_DIR, "_ref", f"libref_api_{flavor}_{isa}.so")
+        self.lib = C.CDLL(path)
+        self.lib.ref_mem_open.restype = C.c_void_p
+        self.lib.ref_mem_open.argtypes = [C.c_char_p]
+        self.lib.ref_mem_l_pac.restype = C.c_int64
+        self.lib.ref_mem_l_pac.argtypes = [C.c_void_p]
+        self.lib.ref_mem_n_seqs.argtypes = [C.c_void_p]
+        self.lib.ref_mem_contigs.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+        self.lib.ref_mem_core.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p,
+                                          C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                          C.c_void_p, C.c_void_p]
+        self.h = self.lib.ref_mem_open(prefix.encode())
+        self.l_pac = self.lib.ref_mem_l_pac(self.h)
+        n = self.lib.ref_mem_n_seqs(self.h)
+        self.contig_off, self.contig_len = np.zeros(n, np.int64), np.zeros(n, np.int32)
+        self.lib.ref_mem_contigs(self.h, self.contig_off.ctypes.data, self.contig_len.ctypes.data)
+
+    def core(self, opt, flat, off, ln):
+        oi, of = opt_arrays(opt)
+        cap = np.array([len(ln) * 64 + 1024, len(ln) * 256 + 4096, len(ln) * 256 + 4096], np.int64)
+        while True:
+            chains, seeds, regs = np.zeros(cap[0], CHAIN_DTYPE), np.zeros(cap[1], SEED_DTYPE), np.zeros(cap[2], REG_DTYPE)
+            reg_off, n_out = np.zeros(len(ln) + 1, np.int64), np.zeros(3, np.int64)
+            self.lib.ref_mem_core(self.h, oi.ctypes.data, of.ctypes.data, int(opt["max_mem_intv"]), flat.ctypes.data,
+                                  off.ctypes.data, ln.ctypes.data, len(ln), chains.ctypes.data, seeds.ctypes.data,
+                                  regs.ctypes.data, reg_off.ctypes.data, cap.ctypes.data, n_out.ctypes.data)
+            if np.all(n_out <= cap):
+                return chains[:n_out[0]].copy(), seeds[:n_out[1]].copy(), regs[:n_out[2]].copy(), reg_off
+            cap = np.maximum(cap, n_out + 16)
+
+
+class OrcExtOpt(C.Structure):
+    _fields_ = [(n, C.c_int32) for n in ("a", "b", "o_del", "e_del", "o_ins", "e_ins", "pen_clip5", "pen_clip3",
+                                         "w", "zdrop")]
+
+
+def ext_opt(o) -> OrcExtOpt:
+    return OrcExtOpt(*[o[k] for k in ("a", "b", "o_del", "e_del", "o_ins", "e_ins", "pen_clip5", "pen_clip3", "w", "zdrop")])
+
+
+def oracle_chain2aln(opt, l_pac, contig_off, contig_len, ref_string, flat, off, ln, chains, seeds):
+    """mem_chain2aln_across_reads_V2 restated (oracle/c2a_oracle.c): regs[len(seeds)] in creation order."""
+    lib = oracle()
+    lib.orc_chain2aln.restype = None
+    lib.orc_chain2aln.argtypes = [C.POINTER(OrcExtOpt), C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                  C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p,
+                                  C.c_void_p]
+    regs = np.zeros(len(seeds), REG_DTYPE)
+    eo = ext_opt(opt)
+    chains, seeds = np.ascontiguousarray(chains), np.ascontiguousarray(seeds)
+    contig_off, contig_len = np.ascontiguousarray(contig_off, np.int64), np.ascontiguousarray(contig_len, np.int32)
+    lib.orc_chain2aln(C.byref(eo), int(l_pac), contig_off.ctypes.data, contig_len.ctypes.data, ref_string.ctypes.data,
+                      flat.ctypes.data, off.ctypes.data, ln.ctypes.data, len(ln), chains.ctypes.data, len(chains),
+                      seeds.ctypes.data, regs.ctypes.data, None)
+    return regs
