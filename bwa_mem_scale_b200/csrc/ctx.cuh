@@ -9,7 +9,11 @@
 enum { SCR_BSW_PAIRS = 0, SCR_BSW_REF, SCR_BSW_QER, SCR_BSW_WORK, SCR_MISC0, SCR_MISC1, SCR_MISC2,
        SCR_MISC3, SCR_SEED_READS, SCR_SEED_OFF, SCR_SEED_LEN, SCR_SEED_SKIP, SCR_SEED_TMP,
        SCR_SEED_CNT, SCR_SEED_SCAN, SCR_SEED_PREV, SCR_SEED_OUT, SCR_SA_CNT, SCR_SA_OFF,
-       SCR_SA_COORD, SCR_CUB, SCR_STATS, SCR_SA_IN, SCR_BSW_KEYS, SCR_BSW_ORDER, BWAGPU_NSCRATCH };
+       SCR_SA_COORD, SCR_CUB, SCR_STATS, SCR_SA_IN, SCR_BSW_KEYS, SCR_BSW_ORDER,
+       SCR_C2A_BK0, SCR_C2A_BK1, SCR_C2A_BK2, SCR_C2A_RETRY, SCR_C2A_CNT, SCR_C2A_RMAX, SCR_C2A_FIRST,
+       SCR_C2A_KEYS, SCR_C2A_SRT, SCR_C2A_CHAINOF, SCR_C2A_SIZES, SCR_C2A_OFFS, SCR_C2A_REGS, SCR_C2A_PURGED,
+       SCR_C2A_L, SCR_C2A_R, SCR_C2A_LQ, SCR_C2A_LR, SCR_C2A_RQ, SCR_C2A_RR, SCR_C2A_CHAINS, SCR_C2A_SEEDS,
+       BWAGPU_NSCRATCH };
 
 struct bwagpu_ctx {
     int device;
@@ -29,6 +33,9 @@ struct bwagpu_ctx {
     // FMA tables (all_smem_t[4^11], last_smem_t[4^13]); built on device or uploaded
     void *d_fma_all, *d_fma_last;
     int fma_enabled;            // bwagpu_index_use_fma: 0 = walk CP_OCC only
+    // reference text replica (.0123: forward + reverse complement, one base per byte) and contig table
+    void *d_ref_string, *d_contig_off, *d_contig_len;
+    int64_t l_pac; int n_contigs;
     int seed_read_cap;          // per-read SMEM capacity of the seeding scratch (grows on overflow)
     // optional per-kernel CUDA-event timing (bwagpu_set_profiling): bench.py's roofline numbers
     int profiling;

@@ -30,6 +30,18 @@ class KswParams(C.Structure):
                 ("o_ins", C.c_int32), ("e_ins", C.c_int32)]
 
 
+class ExtOpt(C.Structure):
+    """bwagpu_ext_opt — the mem_opt_t fields extension reads (reference src/bwamem.h:89-124)."""
+    _fields_ = [(n, C.c_int32) for n in ("a", "b", "o_del", "e_del", "o_ins", "e_ins", "pen_clip5", "pen_clip3",
+                                         "w", "zdrop")]
+
+
+class C2aResult(C.Structure):
+    _fields_ = [("d_regs", C.c_void_p)] + [(n, C.c_int64) for n in
+                ("n_regs", "n_left", "n_right", "n_retry_left", "n_retry_right", "n_pairs8", "n_pairs16",
+                 "n_pairs_scalar", "seq_bytes")]
+
+
 class FmIndexDesc(C.Structure):
     """bwagpu_fm_index_desc — the arrays FMI_search::load_index leaves in memory
     (reference src/FMI_search.cpp:1251-1351); count[] in loaded form (file value + 1)."""
@@ -73,6 +85,12 @@ _SIGS = {
     "bwagpu_bsw_get_scores_device": (C.c_int, [C.c_void_p, C.POINTER(BswParams), C.c_int,
                                                C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p,
                                                C.c_int64, C.c_int32, C.c_int32]),
+    "bwagpu_index_load_ref": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_void_p, C.c_void_p]),
+    "bwagpu_chain2aln": (C.c_int, [C.c_void_p, C.POINTER(ExtOpt), C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32,
+                                   C.c_void_p, C.c_int64, C.c_void_p, C.c_int64, C.c_void_p]),
+    "bwagpu_chain2aln_device": (C.c_int, [C.c_void_p, C.POINTER(ExtOpt), C.c_void_p, C.c_void_p, C.c_void_p,
+                                          C.c_int32, C.c_void_p, C.c_int64, C.c_void_p, C.c_int64,
+                                          C.POINTER(C2aResult)]),
     "bwagpu_ksw_align2_batch": (C.c_int, [C.c_void_p, C.POINTER(KswParams), C.c_void_p, C.c_void_p, C.c_void_p,
                                           C.c_void_p, C.c_int32]),
     "bwagpu_ksw_align2_batch_device": (C.c_int, [C.c_void_p, C.POINTER(KswParams), C.c_void_p, C.c_void_p,

@@ -45,7 +45,7 @@ int bwagpu_timer_stop(bwagpu_ctx *ctx, float *elapsed_ms);   /* records, synchro
  * kernels is bracketed by CUDA events on the context's stream (this serialises the stream, so
  * leave it off when measuring whole-step throughput).  set_profiling also clears the counters. */
 enum { BWAGPU_KERN_SEED_COLLECT = 0, BWAGPU_KERN_SEED_SORT = 1, BWAGPU_KERN_SA_WALK = 2,
-       BWAGPU_KERN_BSW = 3, BWAGPU_KERN_BSW_GENERIC = 4, BWAGPU_KERN_FMA_BUILD = 5, BWAGPU_KERN_KSW = 6,
+       BWAGPU_KERN_BSW = 3, BWAGPU_KERN_BSW_GENERIC = 4, BWAGPU_KERN_FMA_BUILD = 5, BWAGPU_KERN_KSW = 6, BWAGPU_KERN_C2A = 7,
        BWAGPU_KERN_N = 16 };
 int bwagpu_set_profiling(bwagpu_ctx *ctx, int on);
 int bwagpu_kernel_time(const bwagpu_ctx *ctx, int which, double *ms, int64_t *launches);
@@ -94,6 +94,53 @@ int bwagpu_bsw_get_scores_device(bwagpu_ctx *ctx, const bwagpu_bsw_params *prm, 
                                  bwagpu_seqpair *d_pairArray, const uint8_t *d_seqBufRef,
                                  int64_t ref_bytes, const uint8_t *d_seqBufQer, int64_t qer_bytes,
                                  int32_t numPairs, int32_t w);
+
+/* ---- S2': chains -> alignment regions ---------------------------------------------------------
+ * The whole of mem_chain2aln_across_reads_V2 (reference src/bwamem.cpp:2810-3745) on the device:
+ * extension jobs are built from the chains, the read and the HBM-resident reference text, run through
+ * the banded-SW kernels with the reference's 8/16-bit/scalar routing and two-try band doubling,
+ * applied to the regions, and the containment filter purges redundant regions.
+ *
+ * bwagpu_seed  = the payload of mem_seed_t        (reference src/bwamem.h:127-139)
+ * bwagpu_chain = mem_chain_t with seeds flattened (reference src/bwamem.h:141-148): seeds of chain c
+ *                are seeds[c.seed_off .. c.seed_off + c.n); chains come in read order (chain_ar[0],
+ *                chain_ar[1], ...) with their seeds laid out contiguously in that order
+ * bwagpu_alnreg = the mem_alnreg_t fields V2 sets (reference src/bwamem.h:152-173); `chain` is the
+ *                index of the owning chain (the reference stores the pointer a->c) */
+typedef struct { int64_t rbeg; int32_t qbeg, len, score, pad_; } bwagpu_seed;
+typedef struct {
+    int32_t seqid, rid, n, w, kept, first, is_alt; float frac_rep; int64_t pos, seed_off;
+} bwagpu_chain;
+typedef struct {
+    int64_t rb, re; int32_t qb, qe, rid, score, truesc, w, seedcov, seedlen0, chain; float frac_rep;
+} bwagpu_alnreg;
+/* the mem_opt_t fields extension reads (reference src/bwamem.h:89-124) */
+typedef struct { int32_t a, b, o_del, e_del, o_ins, e_ins, pen_clip5, pen_clip3, w, zdrop; } bwagpu_ext_opt;
+
+/* Reference text replica: ref_string = the .0123 file (2*l_pac bytes, values 0-3; reference
+ * src/fastmap.cpp:773-806) plus bns->anns[i].offset / .len for the n_seqs contigs (src/bntseq.h). */
+int bwagpu_index_load_ref(bwagpu_ctx *ctx, const uint8_t *ref_string, int64_t l_pac, int32_t n_seqs,
+                          const int64_t *contig_off, const int32_t *contig_len);
+
+/* regs[n_seeds]: the av_v records in creation order — region of the k-th best seed (descending
+ * score, ties by descending index) of chain c at regs[c.seed_off + k]; purged regions have
+ * qb = qe = -1 exactly as the reference leaves them.  HOST buffers. */
+int bwagpu_chain2aln(bwagpu_ctx *ctx, const bwagpu_ext_opt *opt, const uint8_t *enc_reads, const int64_t *off,
+                     const int32_t *len, int32_t nseq, const bwagpu_chain *chains, int64_t n_chains,
+                     const bwagpu_seed *seeds, int64_t n_seeds, bwagpu_alnreg *regs);
+
+typedef struct {
+    const bwagpu_alnreg *d_regs; int64_t n_regs;       /* context-owned, valid until the next call */
+    int64_t n_left, n_right;                           /* extension jobs built */
+    int64_t n_retry_left, n_retry_right;               /* jobs re-run with the doubled band */
+    int64_t n_pairs8, n_pairs16, n_pairs_scalar;       /* jobs per kernel kind (first try) */
+    int64_t seq_bytes;                                 /* bytes of job sequences materialised */
+} bwagpu_c2a_result;
+/* same with device-resident inputs */
+int bwagpu_chain2aln_device(bwagpu_ctx *ctx, const bwagpu_ext_opt *opt, const uint8_t *d_reads,
+                            const int64_t *d_off, const int32_t *d_len, int32_t nseq,
+                            const bwagpu_chain *d_chains, int64_t n_chains, const bwagpu_seed *d_seeds,
+                            int64_t n_seeds, bwagpu_c2a_result *res);
 
 /* ---- S3: mate-rescue local Smith-Waterman ------------------------------------------------------
  * bwagpu_kswr mirrors kswr_t (reference src/ksw.h), 28 bytes. */

@@ -1,0 +1,69 @@
+"""GPU parity tests (through the C ABI): chains -> alignment regions on CUDA vs golden reference records,
+the oracle, and (when oracle/_ref is present) the reference's own code run live on larger inputs."""
+import os
+
+import numpy as np
+import pytest
+
+import c2a_cases as cc
+import oracle_lib as ol
+from bwa_mem_scale_b200 import Extender, ext_opt, fmindex, synth
+
+pytestmark = pytest.mark.gpu
+GOLD = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "c2a_golden.npz"))
+
+
+def to_ext_opt(o):
+    return ext_opt(*[o[k] for k in ("a", "b", "o_del", "e_del", "o_ins", "e_ins", "pen_clip5", "pen_clip3", "w", "zdrop")])
+
+
+@pytest.fixture(scope="module")
+def extender(gpu_ctx):
+    ref, ref_string = cc.genome()
+    return ref, ref_string, Extender(ref_string, int(GOLD["l_pac"][0]), GOLD["contig_off"], GOLD["contig_len"], ctx=gpu_ctx)
+
+
+@pytest.mark.parametrize("case", cc.OPT_CASES, ids=[c[0] for c in cc.OPT_CASES])
+def test_gpu_chain2aln_matches_golden(extender, case):
+    name, kw = case
+    ref, ref_string, ext = extender
+    flat, off, ln = ol.pack_reads(cc.golden_reads(ref))
+    chains, seeds = GOLD[f"{name}_chains"], GOLD[f"{name}_seeds"]
+    got = ext.mem_chain2aln_across_reads_V2(to_ext_opt(ol.mem_opt(**kw)), flat, off, ln, chains, seeds)
+    assert np.array_equal(cc.reg_matrix(got), GOLD[f"{name}_regs"])
+    assert np.array_equal(got["frac_rep"], GOLD[f"{name}_frac_rep"])
+
+
+def test_gpu_chain2aln_empty_and_subset(extender):
+    ref, ref_string, ext = extender
+    flat, off, ln = ol.pack_reads(cc.golden_reads(ref))
+    chains, seeds = GOLD["default_chains"], GOLD["default_seeds"]
+    o = to_ext_opt(ol.mem_opt())
+    assert len(ext.mem_chain2aln_across_reads_V2(o, flat, off, ln, chains[:0], seeds[:0])) == 0
+    # a prefix of the chains (whole reads) gives the same regions for those reads
+    cut = int(np.searchsorted(chains["seqid"], 100))
+    ns = int(chains["seed_off"][cut])
+    got = ext.mem_chain2aln_across_reads_V2(o, flat, off, ln, chains[:cut], seeds[:ns])
+    assert np.array_equal(cc.reg_matrix(got), GOLD["default_regs"][:ns])
+
+
+def test_gpu_chain2aln_vs_reference_live(gpu_ctx, tmp_path):
+    """Reference run live (oracle/_ref travels to the GPU box): 5 k reads, 250 bp, 5 % errors."""
+    if ol.ref_api("plain", "sse41") is None or ol.ref_binary("plain", "sse41") is None:
+        pytest.skip("oracle/_ref not present")
+    ref = synth.repeat_reference(2_000_000, 9, n_families=30, repeat_frac=0.2, divergence=0.03)
+    prefix = str(tmp_path / "ref")
+    fmindex.write_fasta(prefix + ".fa", ref)
+    ol.ref_index(prefix, prefix + ".fa")
+    rm = ol.RefMem(prefix)
+    ref_string = fmindex.text_with_revcomp(ref)
+    ext = Extender(ref_string, rm.l_pac, rm.contig_off, rm.contig_len, ctx=gpu_ctx)
+    for seed, kw in ((1, dict(read_len=151, err=0.01)), (2, dict(read_len=250, err=0.05))):
+        reads, _, _ = synth.simulate_reads(ref, 5000, seed=seed, **kw)
+        flat, off, ln = ol.pack_reads(reads)
+        o = ol.mem_opt()
+        chains, seeds, regs, _ = rm.core(o, flat, off, ln)
+        got = ext.mem_chain2aln_across_reads_V2(to_ext_opt(o), flat, off, ln, chains, seeds)
+        assert np.array_equal(cc.reg_matrix(got), cc.reg_matrix(regs)), kw
+    ref0, rs0 = cc.genome()     # restore the module fixture's reference replica on the shared context
+    Extender(rs0, int(GOLD["l_pac"][0]), GOLD["contig_off"], GOLD["contig_len"], ctx=gpu_ctx)
