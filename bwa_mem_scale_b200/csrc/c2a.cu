@@ -339,18 +339,21 @@ __global__ void c2a_filter_kernel(C2aOpt o, const int32_t *__restrict__ len, int
 
 // ---- host side ------------------------------------------------------------------------------
 extern "C" int bwagpu_index_load_ref(bwagpu_ctx *ctx, const uint8_t *ref_string, int64_t l_pac, int32_t n_seqs,
-                                     const int64_t *contig_off, const int32_t *contig_len)
+                                     const int64_t *contig_off, const int32_t *contig_len, const uint8_t *contig_is_alt)
 {
     if (!ctx) return BWAGPU_ERR_ARG;
     if (!ref_string || l_pac <= 0 || n_seqs <= 0 || !contig_off || !contig_len)
         BWAGPU_FAIL(ctx, BWAGPU_ERR_ARG, "index_load_ref: incomplete reference descriptor");
     BWAGPU_CUDA(ctx, cudaSetDevice(ctx->device));
     BWAGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-    if (ctx->d_ref_string) { cudaFree(ctx->d_ref_string); cudaFree(ctx->d_contig_off); cudaFree(ctx->d_contig_len); }
-    ctx->d_ref_string = ctx->d_contig_off = ctx->d_contig_len = nullptr;
+    if (ctx->d_ref_string) { cudaFree(ctx->d_ref_string); cudaFree(ctx->d_contig_off); cudaFree(ctx->d_contig_len); cudaFree(ctx->d_contig_alt); }
+    ctx->d_ref_string = ctx->d_contig_off = ctx->d_contig_len = ctx->d_contig_alt = nullptr;
     BWAGPU_CUDA(ctx, cudaMalloc(&ctx->d_ref_string, (size_t)(2 * l_pac) + 64));
     BWAGPU_CUDA(ctx, cudaMalloc(&ctx->d_contig_off, (size_t)n_seqs * 8));
     BWAGPU_CUDA(ctx, cudaMalloc(&ctx->d_contig_len, (size_t)n_seqs * 4));
+    BWAGPU_CUDA(ctx, cudaMalloc(&ctx->d_contig_alt, (size_t)n_seqs));
+    if (contig_is_alt) BWAGPU_CUDA(ctx, cudaMemcpyAsync(ctx->d_contig_alt, contig_is_alt, (size_t)n_seqs, cudaMemcpyHostToDevice, ctx->stream));
+    else BWAGPU_CUDA(ctx, cudaMemsetAsync(ctx->d_contig_alt, 0, (size_t)n_seqs, ctx->stream));
     BWAGPU_CUDA(ctx, cudaMemcpyAsync(ctx->d_ref_string, ref_string, (size_t)(2 * l_pac), cudaMemcpyHostToDevice, ctx->stream));
     BWAGPU_CUDA(ctx, cudaMemcpyAsync(ctx->d_contig_off, contig_off, (size_t)n_seqs * 8, cudaMemcpyHostToDevice, ctx->stream));
     BWAGPU_CUDA(ctx, cudaMemcpyAsync(ctx->d_contig_len, contig_len, (size_t)n_seqs * 4, cudaMemcpyHostToDevice, ctx->stream));

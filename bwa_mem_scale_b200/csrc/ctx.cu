@@ -62,7 +62,7 @@ extern "C" void bwagpu_destroy(bwagpu_ctx *ctx)
     if (ctx->d_cp_occ) cudaFree(ctx->d_cp_occ);
     if (ctx->d_sa_ms) cudaFree(ctx->d_sa_ms);
     if (ctx->d_sa_ls) cudaFree(ctx->d_sa_ls);
-    if (ctx->d_ref_string) { cudaFree(ctx->d_ref_string); cudaFree(ctx->d_contig_off); cudaFree(ctx->d_contig_len); }
+    if (ctx->d_ref_string) { cudaFree(ctx->d_ref_string); cudaFree(ctx->d_contig_off); cudaFree(ctx->d_contig_len); cudaFree(ctx->d_contig_alt); }
     if (ctx->d_fma_all) cudaFree(ctx->d_fma_all);
     if (ctx->d_fma_last) cudaFree(ctx->d_fma_last);
     cudaEventDestroy(ctx->ev_start);

@@ -13,6 +13,7 @@ enum { SCR_BSW_PAIRS = 0, SCR_BSW_REF, SCR_BSW_QER, SCR_BSW_WORK, SCR_MISC0, SCR
        SCR_C2A_BK0, SCR_C2A_BK1, SCR_C2A_BK2, SCR_C2A_RETRY, SCR_C2A_CNT, SCR_C2A_RMAX, SCR_C2A_FIRST,
        SCR_C2A_KEYS, SCR_C2A_SRT, SCR_C2A_CHAINOF, SCR_C2A_SIZES, SCR_C2A_OFFS, SCR_C2A_REGS, SCR_C2A_PURGED,
        SCR_C2A_L, SCR_C2A_R, SCR_C2A_LQ, SCR_C2A_LR, SCR_C2A_RQ, SCR_C2A_RR, SCR_C2A_CHAINS, SCR_C2A_SEEDS,
+       SCR_CH_SD, SCR_CH_CH, SCR_CH_NODES, SCR_CH_ORD, SCR_CH_CNT, SCR_CH_OFFS, SCR_CH_FRAC,
        BWAGPU_NSCRATCH };
 
 struct bwagpu_ctx {
@@ -34,7 +35,7 @@ struct bwagpu_ctx {
     void *d_fma_all, *d_fma_last;
     int fma_enabled;            // bwagpu_index_use_fma: 0 = walk CP_OCC only
     // reference text replica (.0123: forward + reverse complement, one base per byte) and contig table
-    void *d_ref_string, *d_contig_off, *d_contig_len;
+    void *d_ref_string, *d_contig_off, *d_contig_len, *d_contig_alt;
     int64_t l_pac; int n_contigs;
     int seed_read_cap;          // per-read SMEM capacity of the seeding scratch (grows on overflow)
     // optional per-kernel CUDA-event timing (bwagpu_set_profiling): bench.py's roofline numbers

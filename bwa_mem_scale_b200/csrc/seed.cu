@@ -513,6 +513,7 @@ extern "C" int bwagpu_seed_fm_device(bwagpu_ctx *ctx, const bwagpu_seed_opt *opt
         res->d_coords = d_coords; res->n_coords = nc; res->d_coord_off = d_coff;
     }
     res->d_smems = d_sm; res->n_smem = tot;
+    res->d_smem_off = (const int64_t *)ctx->scratch[SCR_SEED_SCAN];
     res->n_ext = (int64_t)st.n_ext; res->n_cp_records = (int64_t)st.n_rec; res->n_lf_steps = (int64_t)st2.n_lf;
     return BWAGPU_OK;
 }

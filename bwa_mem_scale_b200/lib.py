@@ -58,7 +58,17 @@ class SeedOpt(C.Structure):
 class SeedResult(C.Structure):
     _fields_ = [("d_smems", C.c_void_p), ("n_smem", C.c_int64), ("d_coords", C.c_void_p),
                 ("n_coords", C.c_int64), ("d_coord_off", C.c_void_p), ("n_ext", C.c_int64),
-                ("n_cp_records", C.c_int64), ("n_lf_steps", C.c_int64)]
+                ("n_cp_records", C.c_int64), ("n_lf_steps", C.c_int64), ("d_smem_off", C.c_void_p)]
+
+
+class ChainOpt(C.Structure):
+    """bwagpu_chain_opt — the mem_opt_t fields chaining reads (reference src/bwamem.h:89-124)."""
+    _fields_ = [(n, C.c_int32) for n in ("w", "max_chain_gap", "max_occ", "min_seed_len", "min_chain_weight",
+                                         "max_chain_extend")] + [("mask_level", C.c_float), ("drop_ratio", C.c_float)]
+
+
+class ChainResult(C.Structure):
+    _fields_ = [("d_chains", C.c_void_p), ("n_chains", C.c_int64), ("d_seeds", C.c_void_p), ("n_seeds", C.c_int64)]
 
 
 _lib = None
@@ -85,7 +95,14 @@ _SIGS = {
     "bwagpu_bsw_get_scores_device": (C.c_int, [C.c_void_p, C.POINTER(BswParams), C.c_int,
                                                C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p,
                                                C.c_int64, C.c_int32, C.c_int32]),
-    "bwagpu_index_load_ref": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_void_p, C.c_void_p]),
+    "bwagpu_index_load_ref": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_void_p, C.c_void_p,
+                                        C.c_void_p]),
+    "bwagpu_chain_seeds": (C.c_int, [C.c_void_p, C.POINTER(ChainOpt), C.c_void_p, C.c_int64, C.c_void_p, C.c_int64,
+                                     C.c_void_p, C.c_int32, C.c_void_p, C.c_int64, C.c_void_p, C.c_int64,
+                                     C.POINTER(C.c_int64), C.POINTER(C.c_int64)]),
+    "bwagpu_chain_seeds_device": (C.c_int, [C.c_void_p, C.POINTER(ChainOpt), C.c_void_p, C.c_int64, C.c_void_p,
+                                            C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32,
+                                            C.POINTER(ChainResult)]),
     "bwagpu_chain2aln": (C.c_int, [C.c_void_p, C.POINTER(ExtOpt), C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32,
                                    C.c_void_p, C.c_int64, C.c_void_p, C.c_int64, C.c_void_p]),
     "bwagpu_chain2aln_device": (C.c_int, [C.c_void_p, C.POINTER(ExtOpt), C.c_void_p, C.c_void_p, C.c_void_p,

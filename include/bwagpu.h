@@ -45,7 +45,7 @@ int bwagpu_timer_stop(bwagpu_ctx *ctx, float *elapsed_ms);   /* records, synchro
  * kernels is bracketed by CUDA events on the context's stream (this serialises the stream, so
  * leave it off when measuring whole-step throughput).  set_profiling also clears the counters. */
 enum { BWAGPU_KERN_SEED_COLLECT = 0, BWAGPU_KERN_SEED_SORT = 1, BWAGPU_KERN_SA_WALK = 2,
-       BWAGPU_KERN_BSW = 3, BWAGPU_KERN_BSW_GENERIC = 4, BWAGPU_KERN_FMA_BUILD = 5, BWAGPU_KERN_KSW = 6, BWAGPU_KERN_C2A = 7,
+       BWAGPU_KERN_BSW = 3, BWAGPU_KERN_BSW_GENERIC = 4, BWAGPU_KERN_FMA_BUILD = 5, BWAGPU_KERN_KSW = 6, BWAGPU_KERN_C2A = 7, BWAGPU_KERN_CHAIN = 8,
        BWAGPU_KERN_N = 16 };
 int bwagpu_set_profiling(bwagpu_ctx *ctx, int on);
 int bwagpu_kernel_time(const bwagpu_ctx *ctx, int which, double *ms, int64_t *launches);
@@ -67,6 +67,12 @@ typedef struct {
     int32_t score, tle, gtle, qle;
     int32_t gscore, max_off;
 } bwagpu_seqpair;
+
+/* bwagpu_smem mirrors SMEM (reference src/FMI_search.h:85-93, non-DEBUG build), 40 bytes */
+typedef struct {
+    uint32_t rid, m, n, pad_;
+    int64_t k, l, s;
+} bwagpu_smem;
 
 /* constructor arguments of BandedPairWiseSW (reference src/bandedSWA.cpp:51-98 as called from
  * src/bwamem.cpp:3210-3216): w_match = opt->a, w_mismatch = opt->b (positive), end_bonus =
@@ -120,7 +126,35 @@ typedef struct { int32_t a, b, o_del, e_del, o_ins, e_ins, pen_clip5, pen_clip3,
 /* Reference text replica: ref_string = the .0123 file (2*l_pac bytes, values 0-3; reference
  * src/fastmap.cpp:773-806) plus bns->anns[i].offset / .len for the n_seqs contigs (src/bntseq.h). */
 int bwagpu_index_load_ref(bwagpu_ctx *ctx, const uint8_t *ref_string, int64_t l_pac, int32_t n_seqs,
-                          const int64_t *contig_off, const int32_t *contig_len);
+                          const int64_t *contig_off, const int32_t *contig_len,
+                          const uint8_t *contig_is_alt /* bns->anns[i].is_alt; NULL = none */);
+
+/* ---- S1'': seeds -> chains --------------------------------------------------------------------
+ * Replaces mem_chain_seeds + mem_chain_flt as worker_bwt runs them (reference src/bwamem.cpp:1341-1363;
+ * :789-936, :528-646): the SMEMs (sorted as bwagpu_collect_smem returns them) and their SA
+ * coordinates (as bwagpu_get_sa_entries returns them) become, per read, the filtered chain list in
+ * the reference's final order — weight-descending as its ks_introsort leaves it — with every field
+ * the reference sets (w, kept, first, frac_rep, pos, rid, is_alt).  Output layout = the input layout
+ * of bwagpu_chain2aln.  The chain B-tree (kbtree.h) and the unstable sort (ksort.h) are replayed
+ * step for step because their tie behaviour is observable. */
+typedef struct {
+    int32_t w, max_chain_gap, max_occ, min_seed_len, min_chain_weight, max_chain_extend;   /* mem_opt_t */
+    float mask_level, drop_ratio;
+} bwagpu_chain_opt;
+int bwagpu_chain_seeds(bwagpu_ctx *ctx, const bwagpu_chain_opt *opt, const bwagpu_smem *smems, int64_t n_smem,
+                       const int64_t *coords, int64_t n_coords, const int32_t *len, int32_t nseq,
+                       bwagpu_chain *chains, int64_t chains_cap, bwagpu_seed *seeds, int64_t seeds_cap,
+                       int64_t *n_chains, int64_t *n_seeds);                 /* HOST buffers */
+typedef struct {
+    const bwagpu_chain *d_chains; int64_t n_chains;     /* context-owned, valid until the next chaining call */
+    const bwagpu_seed *d_seeds;   int64_t n_seeds;
+} bwagpu_chain_result;
+/* device-resident inputs: d_smem_off[nseq+1] = SMEM range of each read, d_coord_off[n_smem+1] =
+ * coordinate range of each SMEM (both are outputs of bwagpu_seed_fm_device) */
+int bwagpu_chain_seeds_device(bwagpu_ctx *ctx, const bwagpu_chain_opt *opt, const bwagpu_smem *d_smems,
+                              int64_t n_smem, const int64_t *d_smem_off, const int64_t *d_coords,
+                              int64_t n_coords, const int64_t *d_coord_off, const int32_t *d_len,
+                              int32_t nseq, int32_t max_len, bwagpu_chain_result *res);
 
 /* regs[n_seeds]: the av_v records in creation order — region of the k-th best seed (descending
  * score, ties by descending index) of chain c at regs[c.seed_off + k]; purged regions have
@@ -175,10 +209,6 @@ int bwagpu_ksw_align2_batch_device(bwagpu_ctx *ctx, const bwagpu_ksw_params *prm
 
 /* ---- S1: FM-index seeding --------------------------------------------------------------------
  * bwagpu_smem mirrors SMEM (reference src/FMI_search.h:85-93, non-DEBUG build), 40 bytes. */
-typedef struct {
-    uint32_t rid, m, n, pad_;
-    int64_t k, l, s;
-} bwagpu_smem;
 
 /* The arrays FMI_search::load_index leaves in host memory (reference src/FMI_search.cpp:1251-1351,
  * members at src/FMI_search.h:230-254).  count[] is the LOADED form (file value + 1,
@@ -246,6 +276,7 @@ typedef struct {
     const int64_t *d_coord_off;          /* [n_smem + 1] first coordinate of each SMEM */
     int64_t n_ext, n_cp_records;         /* backward extensions done, CP_OCC records fetched */
     int64_t n_lf_steps;                  /* LF steps of the SA stage */
+    const int64_t *d_smem_off;           /* [nseq + 1] first SMEM of each read */
 } bwagpu_seed_result;
 int bwagpu_seed_fm_device(bwagpu_ctx *ctx, const bwagpu_seed_opt *opt, const uint8_t *d_reads,
                           const int64_t *d_off, const int32_t *d_len, const uint8_t *d_skip,
