@@ -341,6 +341,156 @@ def bench_seed(args, rank, world):
     return out
 
 # ------------------------------------------------------------------------------------------------
+KERNELS = {0: "seed_collect", 1: "seed_sort", 2: "sa_walk", 3: "bsw", 4: "bsw_generic", 7: "chain2aln", 8: "chain_seeds"}
+
+
+def cpu_mem_core(prefix, reads, threads):
+    """CPU baseline for seed+extend: the REFERENCE's own mem_kernel1_core + mem_chain2aln_across_reads_V2
+    (oracle/_ref tap library) over `reads`, one worker per host thread on a shared index.  Returns
+    (seconds, kind) — timing excludes loading the index."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import oracle_lib as ol
+    isa = "avx2" if os.path.exists(os.path.join(ol.ORACLE_DIR, "_ref", "libref_api_plain_avx2.so")) else "sse41"
+    rm0 = ol.RefMem(prefix, "plain", isa)
+    workers = [rm0] + [rm0.clone() for _ in range(threads - 1)]
+    chunks = [c for c in np.array_split(np.arange(len(reads)), threads) if len(c)]
+    o = ol.mem_opt()
+
+    def work(a):
+        w, c = a
+        flat, off, ln = ol.pack_reads(reads[c])
+        w.core(o, flat, off, ln)
+
+    from concurrent.futures import ThreadPoolExecutor
+    t0 = time.perf_counter()
+    with ThreadPoolExecutor(threads) as ex:
+        list(ex.map(work, zip(workers, chunks)))
+    return time.perf_counter() - t0, f"reference ({isa} build)"
+
+
+def bench_mem(args, rank, world):
+    """Seed + extend for 151-bp SE reads (BASELINE config 2 shape): reads -> SMEMs -> SA -> chains ->
+    banded-SW extension -> alignment regions, everything on the device."""
+    from bwa_mem_scale_b200 import (Context, Extender, FMI_search, REG_DTYPE, chain_opt, ext_opt, fmindex,
+                                    mem_core_device, pack_reads, seed_opt)
+    ref, idx, reads = seed_inputs(args, rank)
+    n = len(reads)
+    cfg = {"workload": f"seed+extend, BASELINE config 2 shape: {args.ref_mbp:g} Mbp synthetic reference (10% repeats), "
+                       f"{n} x 151 bp SE reads/GPU, 1% substitutions, FM-index" + (" + FMA smem tables" if args.fma else "")
+                       + "; reads -> SMEMs -> SA -> chains -> banded SW (both band tries) -> alignment regions",
+           "reads_per_gpu": n, "ref_mbp": args.ref_mbp,
+           "l2_policy": "index (%.0f MB) + reference text + reads larger than L2" % (idx.nbytes() / 1e6)
+           if idx.nbytes() > 126e6 else "flush between steps"}
+    if args.impl == "reference":
+        if rank != 0:
+            return None
+        import tempfile
+        thr = cpu_threads()
+        sample = reads[: min(n, 4000 * thr)]
+        with tempfile.TemporaryDirectory() as td:
+            prefix = os.path.join(td, "ref")
+            fmindex.write_index_files(prefix, ref, idx)
+            for _ in range(min(args.warmup, 1)):
+                cpu_mem_core(prefix, sample[: 200 * thr], thr)
+            t, kind = 0.0, ""
+            for _ in range(args.steps):
+                dt, kind = cpu_mem_core(prefix, sample, thr)
+                t += dt
+        v = len(sample) * args.steps / t
+        return {"impl": "reference", "metric": "aligned reads/s (151bp SE, seed+extend)", "value": v, "unit": "reads/s",
+                "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * t / args.steps,
+                "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "int64/int16", "data": "synthetic",
+                "config": cfg,
+                "cpu_baseline": {"value": v, "unit": "reads/s", "cores": thr, "kind": "reference",
+                                 "sample": f"{len(sample)} reads of the same set per step, {kind}, "
+                                           "mem_kernel1_core + mem_chain2aln_across_reads_V2"},
+                "e2e": {"value": v, "unit": "reads/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    local = int(os.environ.get("LOCAL_RANK", rank))
+    ctx = Context(local)
+    fmi = FMI_search(idx, ctx=ctx)
+    if args.fma:
+        fmi.build_fma()
+    ext = Extender(fmindex.text_with_revcomp(ref), len(ref), [0], [len(ref)], ctx=ctx)
+    so, co, eo = seed_opt(), chain_opt(), ext_opt()
+    flat, off, ln = pack_reads(reads)
+    d_reads, d_off, d_len = ctx.upload(flat), ctx.upload(off), ctx.upload(ln)
+    flush = ctx.malloc(256 << 20) if "flush" in cfg["l2_policy"] else None
+
+    def step():
+        return mem_core_device(fmi, ext, so, co, eo, d_reads, d_off, d_len, n, 151)
+
+    for _ in range(args.warmup):
+        sres, cres, ares = step()
+    ctx.synchronize()
+    barrier()
+    sampler = ClockSampler(local)
+    sampler.start()
+    l0 = ctx.launch_count()
+    ms = 0.0
+    for _ in range(args.steps):
+        if flush:
+            ctx.memset(flush, 1, 256 << 20)
+        ctx.timer_start()
+        sres, cres, ares = step()
+        ms += ctx.timer_stop()
+    ms = allreduce_max(ms)
+    launches = ctx.launch_count() - l0
+    # e2e: host reads in (H2D), regions out (D2H), through the same calls
+    regs = np.zeros(ares.n_regs + 1024, REG_DTYPE)
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        ctx.h2d(d_reads, flat); ctx.h2d(d_off, off); ctx.h2d(d_len, ln)
+        sres, cres, ares = step()
+        out = regs[:ares.n_regs] if ares.n_regs <= len(regs) else np.zeros(ares.n_regs, REG_DTYPE)
+        ctx.d2h(out, ares.d_regs)
+    e2e_s = allreduce_max(time.perf_counter() - t0)
+    clocks = sampler.stop()
+    ctx.set_profiling(True)
+    for _ in range(min(args.steps, 2)):
+        sres, cres, ares = step()
+    ktimes = {name: ctx.kernel_time(k) for k, name in KERNELS.items()}
+    ctx.set_profiling(False)
+    if rank != 0:
+        return None
+    pk, pk_kind = peaks()
+    k_ms, k_n = ktimes["seed_collect"]
+    alg_bytes = sres.n_cp_records * 64
+    ach = alg_bytes / (k_ms / max(k_n, 1) * 1e-3) / 1e9
+    nprof = max(min(args.steps, 2), 1)
+    purged = int(((out["qb"] == -1) & (out["qe"] == -1)).sum())
+    res = {"metric": "aligned reads/s (151bp SE, seed+extend)", "value": n * world * args.steps / (ms * 1e-3),
+           "unit": "reads/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+           "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+           "dtype": "int64/int16", "data": "synthetic", "config": cfg, "clocks": clocks,
+           "gpu_launches": int(launches),
+           "e2e": {"value": n * world * args.steps / e2e_s, "unit": "reads/s",
+                   "h2d_bytes_per_step": int(flat.nbytes + off.nbytes + ln.nbytes),
+                   "d2h_bytes_per_step": int(ares.n_regs * REG_DTYPE.itemsize)},
+           "roofline": {"bound": "hbm", "kernel": "seed_collect_kernel", "achieved": ach, "peak": pk["hbm_gbs"],
+                        "unit": "GB/s", "frac": ach / pk["hbm_gbs"], "traffic": None, "peak_kind": pk_kind,
+                        "kernel_ms": k_ms / max(k_n, 1),
+                        "kernel_ms_per_step": {name: t / nprof for name, (t, c) in ktimes.items()},
+                        "bext_per_read": sres.n_ext / n, "cp_records_per_read": sres.n_cp_records / n},
+           "work": {"smem_per_read": sres.n_smem / n, "sa_rows_per_read": sres.n_coords / n,
+                    "chains_per_read": cres.n_chains / n, "regions_per_read": ares.n_regs / n,
+                    "regions_purged_per_read": purged / n, "sw_jobs_per_read": (ares.n_left + ares.n_right) / n,
+                    "sw_jobs_retried_per_read": (ares.n_retry_left + ares.n_retry_right) / n,
+                    "sw_jobs_8bit_frac": ares.n_pairs8 / max(ares.n_left + ares.n_right, 1)}}
+    if not args.no_cpu:
+        import tempfile
+        thr = cpu_threads()
+        sample = reads[: min(n, 4000 * thr)]
+        with tempfile.TemporaryDirectory() as td:
+            prefix = os.path.join(td, "ref")
+            fmindex.write_index_files(prefix, ref, idx)
+            dt, kind = cpu_mem_core(prefix, sample, thr)
+        res["cpu_baseline"] = {"value": len(sample) / dt, "unit": "reads/s", "cores": thr, "kind": "reference",
+                               "sample": f"{len(sample)} reads of the same set, {kind}, mem_kernel1_core + "
+                                         f"mem_chain2aln_across_reads_V2, {dt:.1f}s"}
+    return res
+
+# ------------------------------------------------------------------------------------------------
 _dist = None
 
 
@@ -375,7 +525,7 @@ def main():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="bsw", choices=["bsw", "seed"])
+    ap.add_argument("--workload", default="mem", choices=["mem", "bsw", "seed"])
     ap.add_argument("--ref-mbp", type=float, default=100.0)
     ap.add_argument("--reads", type=int, default=1_000_000)
     ap.add_argument("--pairs", type=int, default=1_000_000)
@@ -386,7 +536,7 @@ def main():
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", 0))
     world = int(os.environ.get("WORLD_SIZE", 1))
-    fn = {"bsw": bench_bsw, "seed": bench_seed}[args.workload]
+    fn = {"mem": bench_mem, "bsw": bench_bsw, "seed": bench_seed}[args.workload]
     if args.impl == "reference":
         if rank == 0:
             print(json.dumps(fn(args, 0, world)))

@@ -180,6 +180,31 @@ def build_fm_index(ref_fwd: np.ndarray, device=None) -> FMIndex:
     return FMIndex(n, count, cp.cpu().numpy(), ms, ls, sentinel_index)
 
 
+def write_bns_files(prefix: str, ref_fwd: np.ndarray, name: str = "chr1") -> None:
+    """<prefix>.ann / .amb / .pac for a single N-free contig, byte-identical to what the reference's
+    `index` sub-command writes (bns_fasta2bntseq + bns_dump, reference src/bntseq.cpp:256-381, 81-131):
+    .ann/.amb are text, .pac packs 4 bases per byte (first base in the top bits) followed by an extra
+    zero byte when l_pac is a multiple of 4 and a final byte holding l_pac % 4."""
+    ref_fwd = np.asarray(ref_fwd, dtype=np.uint8)
+    n = len(ref_fwd)
+    with open(prefix + ".ann", "w") as f:
+        f.write(f"{n} 1 11\n0 {name} (null)\n0 {n} 0\n")
+    with open(prefix + ".amb", "w") as f:
+        f.write(f"{n} 1 0\n")
+    pad = (-n) % 4
+    v = np.concatenate([ref_fwd, np.zeros(pad, np.uint8)]).reshape(-1, 4)
+    packed = ((v[:, 0] << 6) | (v[:, 1] << 4) | (v[:, 2] << 2) | v[:, 3]).astype(np.uint8)
+    tail = [0, 0] if n % 4 == 0 else [n % 4]
+    np.concatenate([packed, np.array(tail, np.uint8)]).tofile(prefix + ".pac")
+
+
+def write_index_files(prefix: str, ref_fwd: np.ndarray, idx: "FMIndex") -> None:
+    """Everything FMI_search::load_index + bwa_idx_load_ele read for a plain FM-index run."""
+    idx.save(prefix)
+    write_0123(prefix, ref_fwd)
+    write_bns_files(prefix, ref_fwd)
+
+
 def write_fasta(path: str, ref_fwd: np.ndarray, name: str = "chr1", width: int = 80) -> None:
     letters = np.frombuffer(b"ACGTN", dtype=np.uint8)[np.asarray(ref_fwd, dtype=np.uint8)]
     with open(path, "wb") as f:

@@ -147,6 +147,37 @@ void *ref_mem_open(const char *prefix)
     return c;
 }
 
+// a second worker on the same (read-only) index: own arenas, shared FMI_search / reference text,
+// like the reference's threads sharing w.fmi (src/bwamem.h:228-253)
+void *ref_mem_clone(void *h0)
+{
+    ref_mem_ctx *p = (ref_mem_ctx *)h0;
+    ref_mem_ctx *c = (ref_mem_ctx *)calloc(1, sizeof(ref_mem_ctx));
+    c->fmi = p->fmi; c->ref_string = p->ref_string;
+    const int64_t wsize = BATCH_SIZE * SEEDS_PER_READ;
+    const int readLen = 1024;
+    mem_cache &m = c->mmc;
+    m.seqBufLeftRef[0] = (uint8_t *)_mm_malloc(wsize * MAX_SEQ_LEN_REF + MAX_LINE_LEN, 64);
+    m.seqBufLeftQer[0] = (uint8_t *)_mm_malloc(wsize * MAX_SEQ_LEN_QER + MAX_LINE_LEN, 64);
+    m.seqBufRightRef[0] = (uint8_t *)_mm_malloc(wsize * MAX_SEQ_LEN_REF + MAX_LINE_LEN, 64);
+    m.seqBufRightQer[0] = (uint8_t *)_mm_malloc(wsize * MAX_SEQ_LEN_QER + MAX_LINE_LEN, 64);
+    m.wsize_buf_ref[0] = wsize * MAX_SEQ_LEN_REF;
+    m.wsize_buf_qer[0] = wsize * MAX_SEQ_LEN_QER;
+    m.seqPairArrayAux[0] = (SeqPair *)malloc((wsize + MAX_LINE_LEN) * sizeof(SeqPair));
+    m.seqPairArrayLeft128[0] = (SeqPair *)malloc((wsize + MAX_LINE_LEN) * sizeof(SeqPair));
+    m.seqPairArrayRight128[0] = (SeqPair *)malloc((wsize + MAX_LINE_LEN) * sizeof(SeqPair));
+    m.wsize[0] = wsize;
+    m.wsize_mem[0] = (int64_t)BATCH_MUL * BATCH_SIZE * readLen;
+    m.matchArray[0] = (SMEM *)_mm_malloc(m.wsize_mem[0] * sizeof(SMEM), 64);
+    m.min_intv_ar[0] = (int32_t *)malloc(m.wsize_mem[0] * sizeof(int32_t));
+    m.query_pos_ar[0] = (int16_t *)malloc(m.wsize_mem[0] * sizeof(int16_t));
+    m.enc_qdb[0] = (uint8_t *)malloc(m.wsize_mem[0] * sizeof(uint8_t));
+    m.rid[0] = (int32_t *)malloc(m.wsize_mem[0] * sizeof(int32_t));
+    m.lim[0] = (int32_t *)_mm_malloc((BATCH_SIZE + 32) * sizeof(int32_t), 64);
+    c->seedBuf = (mem_seed_t *)calloc(sizeof(mem_seed_t), (size_t)BATCH_SIZE * AVG_SEEDS_PER_READ);
+    return c;
+}
+
 int64_t ref_mem_l_pac(void *h) { return ((ref_mem_ctx *)h)->fmi->idx->bns->l_pac; }
 int ref_mem_n_seqs(void *h) { return ((ref_mem_ctx *)h)->fmi->idx->bns->n_seqs; }
 void ref_mem_contigs(void *h, int64_t *offset, int32_t *len)

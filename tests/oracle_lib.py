@@ -344,9 +344,11 @@ def opt_arrays(o):
 class RefMem:
     """The reference's own seeding -> chaining -> extension core on an index written to disk."""
 
-    def __init__(self, prefix: str, flavor="plain", isa="sse41"):
+    def __init__(self, prefix: str, flavor="plain", isa="sse41", _parent=None):
         path = os.path.join(ORACLE_DIR, "_ref", f"libref_api_{flavor}_{isa}.so")
         self.lib = C.CDLL(path)
+        self.lib.ref_mem_clone.restype = C.c_void_p
+        self.lib.ref_mem_clone.argtypes = [C.c_void_p]
         self.lib.ref_mem_open.restype = C.c_void_p
         self.lib.ref_mem_open.argtypes = [C.c_char_p]
         self.lib.ref_mem_l_pac.restype = C.c_int64
@@ -356,11 +358,16 @@ class RefMem:
         self.lib.ref_mem_core.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p,
                                           C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                                           C.c_void_p, C.c_void_p]
-        self.h = self.lib.ref_mem_open(prefix.encode())
+        self.h = self.lib.ref_mem_open(prefix.encode()) if _parent is None else self.lib.ref_mem_clone(_parent.h)
+        self._args = (prefix, flavor, isa)
         self.l_pac = self.lib.ref_mem_l_pac(self.h)
         n = self.lib.ref_mem_n_seqs(self.h)
         self.contig_off, self.contig_len = np.zeros(n, np.int64), np.zeros(n, np.int32)
         self.lib.ref_mem_contigs(self.h, self.contig_off.ctypes.data, self.contig_len.ctypes.data)
+
+    def clone(self):
+        """Another worker on the same loaded index (own scratch arenas), for multi-threaded baselines."""
+        return RefMem(*self._args, _parent=self)
 
     def core(self, opt, flat, off, ln):
         oi, of = opt_arrays(opt)
