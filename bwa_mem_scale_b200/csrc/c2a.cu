@@ -152,7 +152,10 @@ __global__ void c2a_fill_kernel(C2aOpt o, const uint8_t *__restrict__ ref_string
                                 bwagpu_seqpair *__restrict__ R, uint8_t *__restrict__ LQ, uint8_t *__restrict__ LR,
                                 uint8_t *__restrict__ RQ, uint8_t *__restrict__ RR)
 {
-    const int64_t ri = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    // one warp per region: every lane derives the same scalars, lane 0 stores the records, all 32
+    // lanes copy the sequence bytes (coalesced instead of one serial byte loop per region)
+    const int64_t ri = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
     if (ri >= n_regs) return;
     const int ci = chain_of[ri];
     const bwagpu_chain c = chains[ci];
@@ -171,11 +174,11 @@ __global__ void c2a_fill_kernel(C2aOpt o, const uint8_t *__restrict__ ref_string
         sp.id = (int32_t)ri;
         const int64_t qo = offs[2 * stride + ri], ro = offs[3 * stride + ri], tmp = s.rbeg - r0;
         sp.idq = (int32_t)qo; sp.idr = (int32_t)ro;
-        for (int i = 0; i < s.qbeg; ++i) LQ[qo + i] = query[s.qbeg - 1 - i];
-        for (int64_t i = 0; i < tmp; ++i) LR[ro + i] = rseq[tmp - 1 - i];
+        for (int i = lane; i < s.qbeg; i += 32) LQ[qo + i] = query[s.qbeg - 1 - i];
+        for (int64_t i = lane; i < tmp; i += 32) LR[ro + i] = rseq[tmp - 1 - i];
         sp.len2 = s.qbeg; sp.len1 = (int32_t)tmp;
         sp.score = sp.tle = sp.gtle = sp.qle = sp.gscore = sp.max_off = 0;
-        L[offs[ri]] = sp;
+        if (lane == 0) L[offs[ri]] = sp;
         a.qb = s.qbeg; a.rb = s.rbeg;
     } else {
         a.score = a.truesc = s.len * o.a; a.qb = 0; a.rb = s.rbeg;
@@ -187,10 +190,10 @@ __global__ void c2a_fill_kernel(C2aOpt o, const uint8_t *__restrict__ ref_string
         sp.len2 = (int32_t)(l_query - qe); sp.len1 = (int32_t)(r1 - r0 - re);
         const int64_t qo = offs[4 * stride + ri], ro = offs[5 * stride + ri];
         sp.idq = (int32_t)qo; sp.idr = (int32_t)ro;
-        for (int i = 0; i < sp.len2; ++i) RQ[qo + i] = query[qe + i];
-        for (int i = 0; i < sp.len1; ++i) RR[ro + i] = rseq[re + i];
+        for (int i = lane; i < sp.len2; i += 32) RQ[qo + i] = query[qe + i];
+        for (int i = lane; i < sp.len1; i += 32) RR[ro + i] = rseq[re + i];
         sp.score = sp.tle = sp.gtle = sp.qle = sp.gscore = sp.max_off = 0;
-        R[offs[stride + ri]] = sp;
+        if (lane == 0) R[offs[stride + ri]] = sp;
         a.qe = (int32_t)qe; a.re = r0 + re;
     } else {
         a.qe = l_query; a.re = s.rbeg + s.len;
@@ -204,7 +207,7 @@ __global__ void c2a_fill_kernel(C2aOpt o, const uint8_t *__restrict__ ref_string
             a.seedcov = cov;
         }
     }
-    regs[ri] = a;
+    if (lane == 0) regs[ri] = a;
 }
 
 // right jobs start from the score the left extension reached (:3423-3428)
@@ -474,7 +477,7 @@ extern "C" int bwagpu_chain2aln_device(bwagpu_ctx *ctx, const bwagpu_ext_opt *eo
     if ((rc = bwagpu_scratch(ctx, SCR_C2A_RQ, tot[4] + 64, (void **)&RQ))) return rc;
     if ((rc = bwagpu_scratch(ctx, SCR_C2A_RR, tot[5] + 64, (void **)&RR))) return rc;
     BWAGPU_KERNEL_BEGIN(ctx);
-    c2a_fill_kernel<<<C2A_GRID(n_seeds)>>>(o, (const uint8_t *)ctx->d_ref_string, d_reads, d_off, d_len, d_chains, d_seeds, srt,
+    c2a_fill_kernel<<<C2A_GRID(n_seeds * 32)>>>(o, (const uint8_t *)ctx->d_ref_string, d_reads, d_off, d_len, d_chains, d_seeds, srt,
                                            chain_of, rmax, n_seeds, offs, stride, regs, L, R, LQ, LR, RQ, RR);
     BWAGPU_KERNEL_END(ctx, BWAGPU_KERN_C2A);
     BWAGPU_CUDA(ctx, cudaGetLastError());
