@@ -218,7 +218,10 @@ def seed_inputs(args, rank):
     n_bp = int(args.ref_mbp * 1e6)
     ref = synth.repeat_reference(n_bp, 43, n_families=50, repeat_frac=0.10, divergence=0.02)
     idx = fmindex.build_fm_index(ref)
-    reads, _, _ = synth.simulate_reads(ref, args.reads, seed=500 + rank)
+    err = 0.01
+    if getattr(args, "exact_frac", None) is not None:      # P(no substitution in 151 bp) = (1-err)^151
+        err = 1.0 - float(args.exact_frac) ** (1.0 / 151)
+    reads, _, _ = synth.simulate_reads(ref, args.reads, seed=500 + rank, err=err)
     return ref, idx, reads
 
 
@@ -341,7 +344,8 @@ def bench_seed(args, rank, world):
     return out
 
 # ------------------------------------------------------------------------------------------------
-KERNELS = {0: "seed_collect", 1: "seed_sort", 2: "sa_walk", 3: "bsw", 4: "bsw_generic", 7: "chain2aln", 8: "chain_seeds"}
+KERNELS = {0: "seed_collect", 1: "seed_sort", 2: "sa_walk", 3: "bsw", 4: "bsw_generic", 7: "chain2aln", 8: "chain_seeds",
+           9: "emf_probe"}
 
 
 def cpu_mem_core(prefix, reads, threads):
@@ -490,9 +494,18 @@ def bench_mem(args, rank, world):
     flat, off, ln = pack_reads(reads)
     d_reads, d_off, d_len = ctx.upload(flat), ctx.upload(off), ctx.upload(ln)
     flush = ctx.malloc(256 << 20) if "flush" in cfg["l2_policy"] else None
+    emf = d_emf = None
+    if args.emf:
+        from bwa_mem_scale_b200 import PerfectMatch, PerfectTable
+        t0 = time.perf_counter()
+        table = PerfectTable.build(ref, 151, 1.1)
+        cfg["emf"] = {"seed_len": 151, "slack": 1.1, "table_mb": table.seed_table.nbytes / 1e6,
+                      "host_build_s": time.perf_counter() - t0}
+        emf = PerfectMatch(table, ctx)
+        d_emf = (ctx.malloc(4 * n), ctx.malloc(8 * n), ctx.malloc(n))
 
     def step():
-        return mem_core_device(fmi, ext, so, co, eo, d_reads, d_off, d_len, n, 151)
+        return mem_core_device(fmi, ext, so, co, eo, d_reads, d_off, d_len, n, 151, emf, d_emf)
 
     for _ in range(args.warmup):
         sres, cres, ares = step()
@@ -552,6 +565,10 @@ def bench_mem(args, rank, world):
                     "regions_purged_per_read": purged / n, "sw_jobs_per_read": (ares.n_left + ares.n_right) / n,
                     "sw_jobs_retried_per_read": (ares.n_retry_left + ares.n_retry_right) / n,
                     "sw_jobs_8bit_frac": ares.n_pairs8 / max(ares.n_left + ares.n_right, 1)}}
+    if emf is not None:
+        skip = np.zeros(n, np.uint8)
+        ctx.d2h(skip, d_emf[2])
+        res["work"]["emf_answered_frac"] = float(skip.mean())
     if not args.no_cpu:
         import tempfile
         thr = cpu_threads()
@@ -607,6 +624,8 @@ def main():
     ap.add_argument("--band", type=int, default=100)
     ap.add_argument("--kind", type=int, default=16, choices=[8, 16])
     ap.add_argument("--fma", type=int, default=1, help="use the FMA smem tables (config 2)")
+    ap.add_argument("--emf", type=int, default=0, help="mem workload: exact-match filter in front (table built on the host)")
+    ap.add_argument("--exact-frac", type=float, default=None, help="fraction of error-free reads (default: what 1%% substitutions give)")
     ap.add_argument("--contexts", type=int, default=1, help="mem workload: contexts (streams) per GPU")
     ap.add_argument("--no-cpu", action="store_true")
     args = ap.parse_args()

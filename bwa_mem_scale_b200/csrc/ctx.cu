@@ -65,6 +65,8 @@ extern "C" void bwagpu_destroy(bwagpu_ctx *ctx)
     if (ctx->d_ref_string) { cudaFree(ctx->d_ref_string); cudaFree(ctx->d_contig_off); cudaFree(ctx->d_contig_len); cudaFree(ctx->d_contig_alt); }
     if (ctx->d_fma_all) cudaFree(ctx->d_fma_all);
     if (ctx->d_fma_last) cudaFree(ctx->d_fma_last);
+    if (ctx->d_emf_loc) cudaFree(ctx->d_emf_loc);
+    if (ctx->d_emf_seed) cudaFree(ctx->d_emf_seed);
     cudaEventDestroy(ctx->ev_start);
     cudaEventDestroy(ctx->ev_stop);
     cudaEventDestroy(ctx->kev0);

@@ -37,6 +37,9 @@ struct bwagpu_ctx {
     // reference text replica (.0123: forward + reverse complement, one base per byte) and contig table
     void *d_ref_string, *d_contig_off, *d_contig_len, *d_contig_alt;
     int64_t l_pac; int n_contigs;
+    // EMF table replica (bwagpu_emf_load)
+    void *d_emf_loc, *d_emf_seed;
+    bwagpu_emf_desc emf;
     int seed_read_cap;          // per-read SMEM capacity of the seeding scratch (grows on overflow)
     // optional per-kernel CUDA-event timing (bwagpu_set_profiling): bench.py's roofline numbers
     int profiling;

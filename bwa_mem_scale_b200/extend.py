@@ -91,12 +91,20 @@ class Extender:
         return res
 
 
-def mem_core_device(fmi, ext: Extender, sopt, copt: ChainOpt, eopt: ExtOpt, d_reads, d_off, d_len, nseq, max_len):
-    """reads -> alignment regions entirely on the device: seeding (bwagpu_seed_fm_device), chaining
-    (bwagpu_chain_seeds_device) and extension (bwagpu_chain2aln_device) back to back on one context —
-    the compute of worker_bwt + worker_aln (reference src/bwamem.cpp:1489-1543) up to the regions
-    mem_chain2aln_across_reads_V2 leaves.  Returns (seed_result, chain_result, c2a_result)."""
-    sres = fmi.seed_device(sopt, d_reads, d_off, d_len, None, nseq, max_len)
+def mem_core_device(fmi, ext: Extender, sopt, copt: ChainOpt, eopt: ExtOpt, d_reads, d_off, d_len, nseq, max_len,
+                    emf=None, d_emf=None):
+    """reads -> alignment regions entirely on the device: [EMF probe (bwagpu_emf_probe_device),] seeding
+    (bwagpu_seed_fm_device), chaining (bwagpu_chain_seeds_device) and extension (bwagpu_chain2aln_device)
+    back to back on one context — the compute of worker_bwt + worker_aln (reference src/bwamem.cpp:
+    1489-1543) up to the regions mem_chain2aln_across_reads_V2 leaves.  With `emf` (a PerfectMatch) and
+    `d_emf` = (d_ret, d_perfect, d_skip) device buffers of nseq records, reads the filter answers are
+    left out of everything downstream (bwamem.cpp:1245-1272).  Returns (seed_result, chain_result,
+    c2a_result)."""
+    d_skip = None
+    if emf is not None:
+        d_ret, d_perfect, d_skip = d_emf
+        emf.probe_device(d_reads, d_off, d_len, nseq, d_ret, d_perfect, d_skip)
+    sres = fmi.seed_device(sopt, d_reads, d_off, d_len, d_skip, nseq, max_len)
     cres = ext.chain_seeds_device(copt, sres, d_len, nseq, max_len)
     ares = ext.chain2aln_device(eopt, d_reads, d_off, d_len, nseq, cres.d_chains, cres.n_chains, cres.d_seeds, cres.n_seeds)
     return sres, cres, ares

@@ -30,6 +30,13 @@ class KswParams(C.Structure):
                 ("o_ins", C.c_int32), ("e_ins", C.c_int32)]
 
 
+class EmfDesc(C.Structure):
+    """bwagpu_emf_desc — header fields of perfect_table_t (reference src/perfect.h:175-199)."""
+    _fields_ = [("seed_len", C.c_int32), ("num_loc_entry", C.c_uint32), ("num_seed_entry", C.c_uint32),
+                ("num_seed_load", C.c_uint32), ("seq_len", C.c_uint32), ("num_seed_used", C.c_uint32),
+                ("num_seed_key", C.c_uint32)]
+
+
 class ExtOpt(C.Structure):
     """bwagpu_ext_opt — the mem_opt_t fields extension reads (reference src/bwamem.h:89-124)."""
     _fields_ = [(n, C.c_int32) for n in ("a", "b", "o_del", "e_del", "o_ins", "e_ins", "pen_clip5", "pen_clip3",
@@ -112,6 +119,16 @@ _SIGS = {
                                           C.c_void_p, C.c_int32]),
     "bwagpu_ksw_align2_batch_device": (C.c_int, [C.c_void_p, C.POINTER(KswParams), C.c_void_p, C.c_void_p,
                                                  C.c_void_p, C.c_void_p, C.c_int32]),
+    "bwagpu_emf_load": (C.c_int, [C.c_void_p, C.POINTER(EmfDesc), C.c_void_p, C.c_void_p]),
+    "bwagpu_emf_unload": (C.c_int, [C.c_void_p]),
+    "bwagpu_emf_probe": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p,
+                                   C.c_void_p]),
+    "bwagpu_emf_probe_device": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p,
+                                          C.c_void_p, C.c_void_p]),
+    "bwagpu_emf_build": (C.c_int, [C.c_void_p, C.c_int64, C.c_int32, C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p,
+                                   C.c_void_p, C.c_int32, C.c_double, C.c_int32, C.POINTER(EmfDesc),
+                                   C.POINTER(C.c_void_p), C.POINTER(C.c_void_p)]),
+    "bwagpu_emf_free_tables": (None, [C.c_void_p, C.c_void_p]),
     "bwagpu_index_load_fm": (C.c_int, [C.c_void_p, C.POINTER(FmIndexDesc)]),
     "bwagpu_index_build_fma": (C.c_int, [C.c_void_p]),
     "bwagpu_index_load_fma": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p]),

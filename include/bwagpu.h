@@ -45,7 +45,7 @@ int bwagpu_timer_stop(bwagpu_ctx *ctx, float *elapsed_ms);   /* records, synchro
  * kernels is bracketed by CUDA events on the context's stream (this serialises the stream, so
  * leave it off when measuring whole-step throughput).  set_profiling also clears the counters. */
 enum { BWAGPU_KERN_SEED_COLLECT = 0, BWAGPU_KERN_SEED_SORT = 1, BWAGPU_KERN_SA_WALK = 2,
-       BWAGPU_KERN_BSW = 3, BWAGPU_KERN_BSW_GENERIC = 4, BWAGPU_KERN_FMA_BUILD = 5, BWAGPU_KERN_KSW = 6, BWAGPU_KERN_C2A = 7, BWAGPU_KERN_CHAIN = 8,
+       BWAGPU_KERN_BSW = 3, BWAGPU_KERN_BSW_GENERIC = 4, BWAGPU_KERN_FMA_BUILD = 5, BWAGPU_KERN_KSW = 6, BWAGPU_KERN_C2A = 7, BWAGPU_KERN_CHAIN = 8, BWAGPU_KERN_EMF = 9,
        BWAGPU_KERN_N = 16 };
 int bwagpu_set_profiling(bwagpu_ctx *ctx, int on);
 int bwagpu_kernel_time(const bwagpu_ctx *ctx, int which, double *ms, int64_t *launches);
@@ -281,6 +281,52 @@ typedef struct {
 int bwagpu_seed_fm_device(bwagpu_ctx *ctx, const bwagpu_seed_opt *opt, const uint8_t *d_reads,
                           const int64_t *d_off, const int32_t *d_len, const uint8_t *d_skip,
                           int32_t nseq, int32_t max_len, bwagpu_seed_result *res);
+
+/* ---- S0: EMF, the exact-match filter -----------------------------------------------------------
+ * Replaces the per-read loop around find_perfect_match_entry in worker_bwt / mem_kernel1_core
+ * (reference src/bwamem.cpp:1083-1119, 1245-1272; src/perfect_map.cpp:638-659 with
+ * __find_perfect_match_entry :583-629 and seedmatch_further :528-581).  The table is the one the
+ * reference's `perfect-index` sub-command writes to <prefix>.perfect.<seed_len>: a 64-byte header,
+ * loc_table[num_loc_entry], seed_table[num_seed_entry] (src/perfect_index.cpp:1418-1424).
+ * bwagpu_seed_entry mirrors seed_entry_t (src/perfect.h:81-97); bwagpu_perfect mirrors
+ * bseq1_perfect_t (:131-138); bwagpu_emf_desc carries the header fields of perfect_table_t
+ * (:175-199) the probe reads. */
+typedef struct { uint32_t flags, location, left, right; } bwagpu_seed_entry;
+typedef struct { uint32_t flags, location; } bwagpu_perfect;
+typedef struct {
+    int32_t  seed_len;          /* pt->seed_len */
+    uint32_t num_loc_entry;     /* pt->num_loc_entry */
+    uint32_t num_seed_entry;    /* pt->num_seed_entry: the hash modulus */
+    uint32_t num_seed_load;     /* MEMSCALE partial load (perfect.h:752-758): entries >= this are absent; 0 = all */
+    uint32_t seq_len;           /* pt->seq_len = l_pac */
+    uint32_t num_seed_used, num_seed_key;   /* statistics kept in the header */
+} bwagpu_emf_desc;
+enum { BWAGPU_EMF_NO_TABLE = 0, BWAGPU_EMF_WITH_N = 1, BWAGPU_EMF_NOT_MATCHED = 2, BWAGPU_EMF_FW_MATCHED = 3,
+       BWAGPU_EMF_RC_MATCHED = 4, BWAGPU_EMF_SEED_ONLY_MATCHED = 5 };   /* FIND_PERFECT_*, perfect.h:902-907 */
+
+/* Copies the table into this GPU's HBM (load_perfect_table, reference src/perfect_map.cpp:204-291).
+ * Needs the reference text (bwagpu_index_load_ref) resident first.  HOST pointers. */
+int bwagpu_emf_load(bwagpu_ctx *ctx, const bwagpu_emf_desc *desc, const uint32_t *loc_table,
+                    const bwagpu_seed_entry *seed_table);
+int bwagpu_emf_unload(bwagpu_ctx *ctx);
+/* One probe per read.  enc_reads as in bwagpu_collect_smem.  ret[i] = FIND_PERFECT_* code,
+ * perfect[i] = seqs[i].perfect ({0,0} unless ret is FW/RC_MATCHED), skip[i] (may be NULL) = 1 when
+ * the read is answered here and must be left out of seeding.  With no table loaded every ret is
+ * NO_TABLE (bwamem.cpp:1094-1097).  HOST buffers. */
+int bwagpu_emf_probe(bwagpu_ctx *ctx, const uint8_t *enc_reads, const int64_t *off, const int32_t *len,
+                     int32_t nseq, int32_t *ret, bwagpu_perfect *perfect, uint8_t *skip);
+/* same with every buffer resident in HBM; asynchronous on the context's stream */
+int bwagpu_emf_probe_device(bwagpu_ctx *ctx, const uint8_t *d_reads, const int64_t *d_off, const int32_t *d_len,
+                            int32_t nseq, int32_t *d_ret, bwagpu_perfect *d_perfect, uint8_t *d_skip);
+/* Offline table builder on the HOST (no context needed): what `bwa-mem2 perfect-index -l seed_len
+ * -s slack` does (reference src/perfect_index.cpp:614-757, 926-990, 1317-1435), same table bytes.
+ * ref_string: forward .0123 text, l_pac bases; contigs as in .ann, holes as in .amb.  The two
+ * tables are malloc'ed here; release them with bwagpu_emf_free_tables. */
+int bwagpu_emf_build(const uint8_t *ref_string, int64_t l_pac, int32_t n_seqs, const int64_t *contig_off,
+                     const int32_t *contig_len, int32_t n_holes, const int64_t *hole_off, const int32_t *hole_len,
+                     int32_t seed_len, double slack, int32_t n_threads, bwagpu_emf_desc *desc,
+                     uint32_t **loc_table, bwagpu_seed_entry **seed_table);
+void bwagpu_emf_free_tables(uint32_t *loc_table, bwagpu_seed_entry *seed_table);
 
 #ifdef __cplusplus
 }

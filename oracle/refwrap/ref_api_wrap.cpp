@@ -26,6 +26,10 @@ SMEM *mem_collect_smem(FMI_search *fmi, const mem_opt_t *opt, const bseq1_t *seq
                        SMEM *matchArray, int32_t *min_intv_ar, int16_t *query_pos_ar,
                        uint8_t *enc_qdb, int32_t *rid, int64_t &tot_smem);
 
+#ifdef PERFECT_MATCH
+int find_perfect_match_entry(perfect_table_t *pt, bseq1_t *seq, int len);   // src/perfect_map.cpp:638
+#endif
+
 extern "C" {
 
 int ref_sizeof_smem(void) { return (int)sizeof(SMEM); }
@@ -42,9 +46,9 @@ void ref_fmi_close(void *h) { delete (FMI_search *)h; }
 // reads: concatenated 2-bit codes (0-3, >=4 = N); off[i] = start of read i; len[i] its length.
 // opt: min_seed_len, split_width, max_mem_intv; split_factor as float.  Returns tot_smem, writes
 // the sorted SMEM array exactly as mem_collect_smem leaves it in matchArray.
-int64_t ref_collect_smem(void *h, int min_seed_len, float split_factor, int split_width,
-                         int64_t max_mem_intv, const uint8_t *reads, const int64_t *off,
-                         const int32_t *len, int nseq, SMEM *out, int64_t out_cap)
+static int64_t collect_smem_impl(void *h, int min_seed_len, float split_factor, int split_width,
+                                 int64_t max_mem_intv, const uint8_t *reads, const int64_t *off,
+                                 const int32_t *len, int nseq, SMEM *out, int64_t out_cap, const uint8_t *skip)
 {
     FMI_search *fmi = (FMI_search *)h;
     mem_opt_t *opt = mem_opt_init();
@@ -61,6 +65,9 @@ int64_t ref_collect_smem(void *h, int min_seed_len, float split_factor, int spli
         seqs[i].seq = (char *)(reads + off[i]);
         tot_len += len[i];
         if (len[i] > maxlen) maxlen = len[i];
+#ifdef PERFECT_MATCH
+        if (skip && skip[i]) { seqs[i].perfect.flags = FLAG_VALID; seqs[i].perfect.location = 0; }   // an EMF answer
+#endif
     }
     // arenas sized like memoryAlloc does per thread (src/fastmap.cpp:280-300) but for this batch
     int64_t cap = (int64_t)20 * nseq * maxlen + 1024;
@@ -77,6 +84,22 @@ int64_t ref_collect_smem(void *h, int min_seed_len, float split_factor, int spli
     _mm_free(enc_qdb);
     free(seqs); free(opt);
     return tot;
+}
+
+int64_t ref_collect_smem(void *h, int min_seed_len, float split_factor, int split_width,
+                         int64_t max_mem_intv, const uint8_t *reads, const int64_t *off,
+                         const int32_t *len, int nseq, SMEM *out, int64_t out_cap)
+{
+    return collect_smem_impl(h, min_seed_len, split_factor, split_width, max_mem_intv, reads, off, len, nseq, out, out_cap, nullptr);
+}
+
+// same with reads marked as answered by the EMF (seq_[i].perfect.exist != 0, src/bwamem.cpp:672-689);
+// only meaningful in the PERFECT_MATCH flavours
+int64_t ref_collect_smem_skip(void *h, int min_seed_len, float split_factor, int split_width,
+                              int64_t max_mem_intv, const uint8_t *reads, const int64_t *off,
+                              const int32_t *len, int nseq, SMEM *out, int64_t out_cap, const uint8_t *skip)
+{
+    return collect_smem_impl(h, min_seed_len, split_factor, split_width, max_mem_intv, reads, off, len, nseq, out, out_cap, skip);
 }
 
 // coords[] receives the SA coordinates in SMEM order then row order (k, k+step, ...), as
@@ -265,5 +288,57 @@ int ref_mem_core(void *h, const int32_t *opt_i, const float *opt_f, int64_t max_
     free(opt);
     return 0;
 }
+
+#ifdef PERFECT_MATCH
+// ---- EMF tap: the reference's own find_perfect_match_entry (src/perfect_map.cpp:638-659) over a table
+// file written by its `perfect-index` sub-command.  The file is read here (header, loc_table,
+// seed_table back to back, src/perfect_index.cpp:1418-1424) instead of through load_perfect_table,
+// which insists on the shm store in the scale flavour.
+struct ref_emf_ctx { perfect_table_t pt; uint8_t *blob; uint8_t *ref; };
+
+void *ref_emf_open(const char *table_path, const char *ref0123_path, uint32_t num_seed_load)
+{
+    ref_emf_ctx *c = new ref_emf_ctx();
+    FILE *fp = fopen(table_path, "rb");
+    if (!fp) { delete c; return nullptr; }
+    fseek(fp, 0, SEEK_END); long sz = ftell(fp); fseek(fp, 0, SEEK_SET);
+    c->blob = (uint8_t *)malloc(sz);
+    if (fread(c->blob, 1, sz, fp) != (size_t)sz) { fclose(fp); free(c->blob); delete c; return nullptr; }
+    fclose(fp);
+    memcpy(&c->pt, c->blob, sizeof(perfect_table_t));
+    c->pt.loc_table = (uint32_t *)(c->blob + sizeof(perfect_table_t));
+    c->pt.seed_table = (seed_entry_t *)(c->blob + sizeof(perfect_table_t) + sizeof(uint32_t) * (size_t)c->pt.num_loc_entry);
+#ifdef MEMSCALE
+    c->pt.num_seed_load = (num_seed_load > 0 && num_seed_load < c->pt.num_seed_entry) ? num_seed_load : c->pt.num_seed_entry;
+#endif
+    fp = fopen(ref0123_path, "rb");
+    if (!fp) { free(c->blob); delete c; return nullptr; }
+    fseek(fp, 0, SEEK_END); sz = ftell(fp); fseek(fp, 0, SEEK_SET);
+    c->ref = (uint8_t *)malloc(sz + 64);
+    if (fread(c->ref, 1, sz, fp) != (size_t)sz) { fclose(fp); free(c->blob); free(c->ref); delete c; return nullptr; }
+    fclose(fp);
+    c->pt.ref_string = c->ref;
+    perfect_table_seed_len = c->pt.seed_len;
+    return c;
+}
+
+void ref_emf_close(void *h) { ref_emf_ctx *c = (ref_emf_ctx *)h; free(c->blob); free(c->ref); delete c; }
+
+void ref_emf_probe(void *h, uint8_t *reads, const int64_t *off, const int32_t *len, int32_t nseq,
+                   int32_t *ret, uint32_t *perfect)
+{
+    ref_emf_ctx *c = (ref_emf_ctx *)h;
+    perfect_table_seed_len = c->pt.seed_len;
+    for (int32_t i = 0; i < nseq; ++i) {
+        bseq1_t s;
+        memset(&s, 0, sizeof(s));
+        s.seq = (char *)(reads + off[i]);
+        s.l_seq = len[i];
+        ret[i] = find_perfect_match_entry(&c->pt, &s, len[i]);
+        perfect[2 * i] = s.perfect.flags;
+        perfect[2 * i + 1] = s.perfect.location;
+    }
+}
+#endif  // PERFECT_MATCH
 
 }  // extern "C"

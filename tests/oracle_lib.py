@@ -407,3 +407,80 @@ def oracle_chain2aln(opt, l_pac, contig_off, contig_len, ref_string, flat, off, 
                       flat.ctypes.data, off.ctypes.data, ln.ctypes.data, len(ln), chains.ctypes.data, len(chains),
                       seeds.ctypes.data, regs.ctypes.data, None)
     return regs
+
+
+# ---- EMF (exact-match filter) ----------------------------------------------------------------
+class OrcEmfTable(C.Structure):
+    _fields_ = [("seed_len", C.c_int32), ("num_loc_entry", C.c_uint32), ("num_seed_entry", C.c_uint32),
+                ("num_seed_load", C.c_uint32), ("seq_len", C.c_uint32), ("ref_string", C.c_void_p),
+                ("loc_table", C.c_void_p), ("seed_table", C.c_void_p)]
+
+
+def oracle_emf_probe(table, ref_string, flat, off, ln, num_seed_load=0):
+    """find_perfect_match_entry restated (oracle/emf_oracle.c) over a bwa_mem_scale_b200.PerfectTable
+    (or None = no table): (ret codes, perfect[n][2] = flags, location)."""
+    lib = oracle()
+    lib.orc_emf_probe.restype = None
+    lib.orc_emf_probe.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p]
+    ret, perfect = np.zeros(len(ln), np.int32), np.zeros((len(ln), 2), np.uint32)
+    flat = np.ascontiguousarray(flat, np.uint8)
+    ref_string = np.ascontiguousarray(ref_string, np.uint8)
+    if table is None:
+        tp = None
+    else:
+        ns = len(table.seed_table)
+        t = OrcEmfTable(table.seed_len, len(table.loc_table), ns, num_seed_load if 0 < num_seed_load < ns else ns,
+                        table.seq_len, ref_string.ctypes.data, table.loc_table.ctypes.data, table.seed_table.ctypes.data)
+        tp = C.addressof(t)
+    lib.orc_emf_probe(tp, flat.ctypes.data, off.ctypes.data, ln.ctypes.data, len(ln), ret.ctypes.data, perfect.ctypes.data)
+    return ret, perfect
+
+
+def write_emf_inputs(prefix, ref_fwd, contig_off, contig_len, hole_off, hole_len):
+    """The three files the reference's `perfect-index` reads (src/perfect_index.cpp:113-213, 1439-1462):
+    <prefix>.ann, <prefix>.amb (text, bns_dump format src/bntseq.cpp:81-131) and <prefix>.0123."""
+    n = len(ref_fwd)
+    with open(prefix + ".ann", "w") as f:
+        f.write(f"{n} {len(contig_off)} 11\n")
+        for i, (o, l) in enumerate(zip(contig_off, contig_len)):
+            na = sum(1 for h in hole_off if o <= h < o + l)
+            f.write(f"0 chr{i + 1} (null)\n{int(o)} {int(l)} {na}\n")
+    with open(prefix + ".amb", "w") as f:
+        f.write(f"{n} {len(contig_off)} {len(hole_off)}\n")
+        for o, l in zip(hole_off, hole_len):
+            f.write(f"{int(o)} {int(l)} N\n")
+    t = np.concatenate([ref_fwd, (3 - ref_fwd[::-1])]).astype(np.uint8)
+    t.tofile(prefix + ".0123")
+    return t
+
+
+def ref_perfect_index(prefix, seed_len, slack=1.1, flavor="emf", isa="sse41"):
+    """Run the reference's own `perfect-index` sub-command: writes <prefix>.perfect.<seed_len>."""
+    subprocess.run([ref_binary(flavor, isa), "perfect-index", "-l", str(seed_len), "-s", str(slack), prefix],
+                   check=True, stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+    return f"{prefix}.perfect.{seed_len}"
+
+
+class RefEmf:
+    """The reference's own find_perfect_match_entry over a table file (oracle/refwrap/ref_api_wrap.cpp)."""
+
+    def __init__(self, table_path, ref0123_path, flavor="emf", isa="sse41", num_seed_load=0):
+        self.lib = C.CDLL(os.path.join(ORACLE_DIR, "_ref", f"libref_api_{flavor}_{isa}.so"))
+        self.lib.ref_emf_open.restype = C.c_void_p
+        self.lib.ref_emf_open.argtypes = [C.c_char_p, C.c_char_p, C.c_uint32]
+        self.lib.ref_emf_close.argtypes = [C.c_void_p]
+        self.lib.ref_emf_probe.argtypes = [C.c_void_p] * 4 + [C.c_int32, C.c_void_p, C.c_void_p]
+        self.h = self.lib.ref_emf_open(table_path.encode(), ref0123_path.encode(), num_seed_load)
+        if not self.h:
+            raise OSError(f"cannot open {table_path}")
+
+    def probe(self, flat, off, ln):
+        ret, perfect = np.zeros(len(ln), np.int32), np.zeros((len(ln), 2), np.uint32)
+        flat = np.ascontiguousarray(flat, np.uint8).copy()
+        self.lib.ref_emf_probe(self.h, flat.ctypes.data, off.ctypes.data, ln.ctypes.data, len(ln), ret.ctypes.data,
+                               perfect.ctypes.data)
+        return ret, perfect
+
+    def close(self):
+        self.lib.ref_emf_close(self.h)
+        self.h = None

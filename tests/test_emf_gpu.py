@@ -1,0 +1,81 @@
+"""GPU parity tests (through the C ABI): the EMF probe kernel vs golden data from the reference's
+find_perfect_match_entry and vs the oracle."""
+import os
+
+import numpy as np
+import pytest
+
+import emf_cases as ec
+import oracle_lib as ol
+from bwa_mem_scale_b200 import Extender, PerfectMatch, PerfectTable, synth
+from test_oracle_emf import CASES, GOLD, table, workload
+
+pytestmark = pytest.mark.gpu
+
+
+def resident_text(gpu_ctx, g, text):
+    return Extender(text, len(g[0]), g[1], g[2], ctx=gpu_ctx)
+
+
+@pytest.mark.parametrize("case", CASES, ids=[c[0] for c in CASES])
+def test_gpu_probe_matches_golden_and_oracle(gpu_ctx, case):
+    name, L, slack = case
+    g, text, (flat, off, ln) = workload()
+    resident_text(gpu_ctx, g, text)
+    t = table(*case)
+    pm = PerfectMatch(t, gpu_ctx)
+    ret, perfect, skip = pm.find_perfect_match_entry(flat, off, ln)
+    pf = np.stack([perfect["flags"], perfect["location"]], axis=1)
+    assert np.array_equal(ret, GOLD[f"{name}_ret"]) and np.array_equal(pf, GOLD[f"{name}_perfect"])
+    assert np.array_equal(skip, ((ret == 3) | (ret == 4)).astype(np.uint8))
+    want = ol.oracle_emf_probe(t, text, flat, off, ln)
+    assert np.array_equal(ret, want[0]) and np.array_equal(pf, want[1])
+    # MEMSCALE partial load (perfect.h:752-758): entries past num_seed_load are absent
+    pm = PerfectMatch(t, gpu_ctx, num_seed_load=t.num_seed_entry // 2)
+    ret, perfect, _ = pm.find_perfect_match_entry(flat, off, ln)
+    pf = np.stack([perfect["flags"], perfect["location"]], axis=1)
+    assert np.array_equal(ret, GOLD[f"{name}_half_ret"]) and np.array_equal(pf, GOLD[f"{name}_half_perfect"])
+    pm.unload()
+
+
+def test_gpu_probe_without_table_and_empty_batch(gpu_ctx):
+    g, text, (flat, off, ln) = workload()
+    resident_text(gpu_ctx, g, text)
+    pm = PerfectMatch(None, gpu_ctx)
+    ret, perfect, skip = pm.find_perfect_match_entry(flat, off, ln)
+    assert np.all(ret == 0) and np.all(perfect["flags"] == 0) and np.all(skip == 0)
+    pm = PerfectMatch(table(*CASES[0]), gpu_ctx)
+    ret, _, _ = pm.find_perfect_match_entry(flat[:0], off[:0], ln[:0])
+    assert len(ret) == 0
+    pm.unload()
+
+
+def test_gpu_probe_config1_shape_and_seeding_skip(gpu_ctx):
+    """1 Mbp random reference, 10 k x 151 bp reads, a third of them error-free: probe == oracle, and
+    the reads it answers drop out of seeding exactly as the reference's skip does (bwamem.cpp:672-689)."""
+    from bwa_mem_scale_b200 import FMI_search, fmindex, seed_opt
+    import fmi_cases as fc
+    ref = synth.random_reference(1_000_000, 42)
+    text = np.concatenate([ref, 3 - ref[::-1]]).astype(np.uint8)
+    reads, _, _ = synth.simulate_reads(ref, 10000, seed=1, err=0.007)
+    flat, off, ln = ol.pack_reads(reads)
+    t = PerfectTable.build(ref, 151, 1.1)
+    Extender(text, len(ref), [0], [len(ref)], ctx=gpu_ctx)
+    pm = PerfectMatch(t, gpu_ctx)
+    ret, perfect, skip = pm.find_perfect_match_entry(flat, off, ln)
+    want = ol.oracle_emf_probe(t, text, flat, off, ln)
+    assert np.array_equal(ret, want[0])
+    assert np.array_equal(np.stack([perfect["flags"], perfect["location"]], axis=1), want[1])
+    assert 2000 < skip.sum() < 5000
+    # every answered read really is a verbatim copy of the text at the reported place
+    for i in np.nonzero(skip)[0][:200]:
+        loc = int(perfect["location"][i])
+        w = ref[loc:loc + 151]
+        assert np.array_equal(reads[i], w if ret[i] == 3 else 3 - w[::-1])
+    idx = fmindex.build_fm_index(ref)
+    fmi = FMI_search(idx, ctx=gpu_ctx)
+    got = fmi.collect_smem(seed_opt(), flat, off, ln, skip)
+    exp, _ = ol.oracle_collect_smem(idx, ol.default_seed_opt(), flat, off, ln, skip)
+    assert np.array_equal(fc.smem_matrix(got), fc.smem_matrix(exp))
+    assert not np.any(skip[got["rid"]])
+    pm.unload()
