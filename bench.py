@@ -260,7 +260,7 @@ def bench_seed(args, rank, world):
         if rank != 0:
             return None
         thr = cpu_threads()
-        sample = reads[: min(n, 4000 * thr)]
+        sample = reads[: min(n, 32000 * thr)]
         for _ in range(args.warmup):
             cpu_seed(idx, sample[:200 * thr], thr)
         t = sum(cpu_seed(idx, sample, thr) for _ in range(args.steps))
@@ -463,7 +463,7 @@ def bench_mem(args, rank, world):
             return None
         import tempfile
         thr = cpu_threads()
-        sample = reads[: min(n, 4000 * thr)]
+        sample = reads[: min(n, 32000 * thr)]
         with tempfile.TemporaryDirectory() as td:
             prefix = os.path.join(td, "ref")
             fmindex.write_index_files(prefix, ref, idx)
@@ -523,12 +523,14 @@ def bench_mem(args, rank, world):
         ms += ctx.timer_stop()
     ms = allreduce_max(ms)
     launches = ctx.launch_count() - l0
-    # e2e: host reads in (H2D), regions out (D2H), through the same calls
-    regs = np.zeros(ares.n_regs + 1024, REG_DTYPE)
+    # e2e: reads in from pinned host memory (H2D), regions out to pinned host memory (D2H), same calls
+    p_flat, p_off, p_ln = ctx.pinned(flat.shape, flat.dtype), ctx.pinned(off.shape, off.dtype), ctx.pinned(ln.shape, ln.dtype)
+    p_flat[:], p_off[:], p_ln[:] = flat, off, ln
+    regs = ctx.pinned(int(ares.n_regs * 1.25) + 1024, REG_DTYPE)
     barrier()
     t0 = time.perf_counter()
     for _ in range(args.steps):
-        ctx.h2d(d_reads, flat); ctx.h2d(d_off, off); ctx.h2d(d_len, ln)
+        ctx.h2d_async(d_reads, p_flat); ctx.h2d_async(d_off, p_off); ctx.h2d_async(d_len, p_ln)
         sres, cres, ares = step()
         out = regs[:ares.n_regs] if ares.n_regs <= len(regs) else np.zeros(ares.n_regs, REG_DTYPE)
         ctx.d2h(out, ares.d_regs)
@@ -572,7 +574,7 @@ def bench_mem(args, rank, world):
     if not args.no_cpu:
         import tempfile
         thr = cpu_threads()
-        sample = reads[: min(n, 4000 * thr)]
+        sample = reads[: min(n, 32000 * thr)]
         with tempfile.TemporaryDirectory() as td:
             prefix = os.path.join(td, "ref")
             fmindex.write_index_files(prefix, ref, idx)

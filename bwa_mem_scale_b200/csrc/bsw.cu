@@ -90,6 +90,26 @@ bsw_thread_kernel(bwagpu_bsw_params prm, bwagpu_seqpair *__restrict__ pairs,
     }
 }
 
+// Shared memory per thread follows the query length, so the sorted order is cut into length tiers
+// and each tier is launched with the column count it needs: short tiers get several times the
+// resident warps of the longest one.  out[t] = first slot of the descending order whose len2 is
+// <= BSW_TIERS[t].
+#define BSW_NTIER 4
+__constant__ int BSW_TIERS[BSW_NTIER] = {112, 80, 56, 40};
+static const int BSW_TIERS_H[BSW_NTIER] = {112, 80, 56, 40};
+__global__ void bsw_tier_kernel(const uint32_t *__restrict__ keys_desc, int n, int *__restrict__ out)
+{
+    const int t = threadIdx.x;
+    if (t >= BSW_NTIER) return;
+    const uint32_t thr = (uint32_t)BSW_TIERS[t];
+    int lo = 0, hi = n;                       // first index with (key >> 16) <= thr
+    while (lo < hi) {
+        const int mid = (lo + hi) >> 1;
+        if ((keys_desc[mid] >> 16) <= thr) hi = mid; else lo = mid + 1;
+    }
+    out[t] = lo;
+}
+
 // max len2 over the batch (device reduction; result read back by the launcher)
 __global__ void bsw_maxlen_kernel(const bwagpu_seqpair *__restrict__ pairs, int n, int *out)
 {
@@ -169,8 +189,10 @@ static int bsw_launch_sorted(bwagpu_ctx *ctx, const bwagpu_bsw_params *prm, bwag
     if ((rc = bwagpu_scratch(ctx, SCR_CUB, (int64_t)bytes + 256, &tmp))) return rc;
     BWAGPU_CUDA(ctx, cub::DeviceRadixSort::SortPairsDescending(tmp, bytes, keys, keys_out, idx_in, order, n, 0, 32, ctx->stream));
     ctx->launches += 5;      // CUB onesweep: histogram + 4 digit passes
-    int h_m[4];
-    BWAGPU_CUDA(ctx, cudaMemcpyAsync(h_m, d_m, 16, cudaMemcpyDeviceToHost, ctx->stream));
+    bsw_tier_kernel<<<1, 32, 0, ctx->stream>>>(keys_out, n, d_m + 4);
+    ctx->launches += 1;
+    int h_m[8];
+    BWAGPU_CUDA(ctx, cudaMemcpyAsync(h_m, d_m, 32, cudaMemcpyDeviceToHost, ctx->stream));
     BWAGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     const int max_len2 = h_m[1], n_long = h_m[2];
     // 2. the few long pairs (front of the order) take the generic global-scratch kernel
@@ -187,18 +209,29 @@ static int bsw_launch_sorted(bwagpu_ctx *ctx, const bwagpu_bsw_params *prm, bwag
         BWAGPU_KERNEL_END(ctx, BWAGPU_KERN_BSW_GENERIC);
         BWAGPU_CUDA(ctx, cudaGetLastError());
     }
-    // 3. everything else: shared-memory kernel
-    const int n_fast = n - n_long;
-    if (n_fast > 0) {
-        const int cols = (max_len2 < BSW_FAST_MAX_LEN2 ? max_len2 : BSW_FAST_MAX_LEN2) + 3;
-        const int qwords = (cols - 3 + 7) / 8 + 1;          // 4-bit query codes, 8 per word
-        const size_t smem = (size_t)(cols + qwords) * BSW_FAST_TPB * 4;
-        BWAGPU_CUDA(ctx, cudaFuncSetAttribute(bsw_fast_kernel<KIND>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        BWAGPU_KERNEL_BEGIN(ctx);
-        bsw_fast_kernel<KIND><<<(n_fast + BSW_FAST_TPB - 1) / BSW_FAST_TPB, BSW_FAST_TPB, smem, ctx->stream>>>(
-            *prm, d_pairs, d_ref, d_qer, order, n_long, n, w, cols);
-        BWAGPU_KERNEL_END(ctx, BWAGPU_KERN_BSW);
-        BWAGPU_CUDA(ctx, cudaGetLastError());
+    // 3. everything else: shared-memory kernel, one launch per length tier
+    if (n - n_long > 0) {
+        static const bool one_tier = getenv("BWAGPU_BSW_TIERS") && !strcmp(getenv("BWAGPU_BSW_TIERS"), "0");
+        const int cap2 = max_len2 < BSW_FAST_MAX_LEN2 ? max_len2 : BSW_FAST_MAX_LEN2;
+        auto smem_of = [](int len2) { const int cols = len2 + 3, qwords = (len2 + 7) / 8 + 1; return (size_t)(cols + qwords) * BSW_FAST_TPB * 4; };
+        BWAGPU_CUDA(ctx, cudaFuncSetAttribute(bsw_fast_kernel<KIND>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_of(cap2)));
+        int lo = n_long;
+        for (int t = 0; t <= BSW_NTIER; ++t) {
+            int hi = t < BSW_NTIER ? h_m[4 + t] : n;           // slots [lo, hi) hold len2 in (TIERS[t], TIERS[t-1]]
+            if (one_tier) hi = n;
+            if (hi < lo) hi = lo;
+            if (hi > lo) {
+                int len2 = t == 0 ? cap2 : BSW_TIERS_H[t - 1];
+                if (len2 > cap2) len2 = cap2;
+                BWAGPU_KERNEL_BEGIN(ctx);
+                bsw_fast_kernel<KIND><<<(hi - lo + BSW_FAST_TPB - 1) / BSW_FAST_TPB, BSW_FAST_TPB, smem_of(len2), ctx->stream>>>(
+                    *prm, d_pairs, d_ref, d_qer, order, lo, hi, w, len2 + 3);
+                BWAGPU_KERNEL_END(ctx, BWAGPU_KERN_BSW);
+                BWAGPU_CUDA(ctx, cudaGetLastError());
+            }
+            lo = hi;
+            if (one_tier) break;
+        }
     }
     return BWAGPU_OK;
 }

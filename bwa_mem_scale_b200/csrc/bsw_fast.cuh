@@ -24,6 +24,11 @@ __device__ __forceinline__ uint32_t bsw_prmt(uint32_t a, uint32_t b, uint32_t se
     return d;
 }
 
+#ifndef BSW_UNROLL
+#define BSW_UNROLL 4
+#endif
+constexpr int kBswUnroll = BSW_UNROLL;
+
 template <int BITS, int STRIDE>
 __device__ BswOut bsw_lane_fast(const bwagpu_bsw_params &p, const uint8_t *__restrict__ query,
                                 int len2, const uint8_t *__restrict__ target, int len1, int w,
@@ -69,8 +74,10 @@ __device__ BswOut bsw_lane_fast(const bwagpu_bsw_params &p, const uint8_t *__res
     bool live = true;
     int nlo = 0, nhi = ncol;
 
+    int tc_next = nrow > 0 ? target[0] : 0;       // one row ahead: keeps the byte load off the row's critical path
     for (int i = 0; i < nrow; ++i) {
-        const int tc = target[i];
+        const int tc = tc_next;
+        if (i + 1 < nrow) tc_next = target[i + 1];
         const int t = bsw_sym((uint8_t)tc, wrap);
         uint32_t tlo, thi = amb4;
         if (tc > 3) tlo = amb4;
@@ -121,6 +128,7 @@ __device__ BswOut bsw_lane_fast(const bwagpu_bsw_params &p, const uint8_t *__res
             uint32_t *cp = &COL(j);
             int jp1 = j + 1;
             uint32_t wq = qsm[(j >> 3) * STRIDE] >> (4 * (j & 7));
+#pragma unroll kBswUnroll
             for (; j < jb; ++j, cp += STRIDE, ++jp1) {
                 const uint32_t cv = *cp;
                 const uint32_t sel = (wq & 7u) * 0x1111u + 0x8880u;       // byte = query code, sign-extended

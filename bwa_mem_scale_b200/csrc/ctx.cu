@@ -156,6 +156,37 @@ extern "C" int bwagpu_d2h(bwagpu_ctx *ctx, void *dst, const void *src, int64_t b
     return BWAGPU_OK;
 }
 
+extern "C" int bwagpu_host_alloc(bwagpu_ctx *ctx, int64_t bytes, void **hptr)
+{
+    if (!ctx || !hptr || bytes < 0) return BWAGPU_ERR_ARG;
+    BWAGPU_CUDA(ctx, cudaSetDevice(ctx->device));
+    BWAGPU_CUDA(ctx, cudaHostAlloc(hptr, (size_t)(bytes ? bytes : 1), cudaHostAllocPortable));
+    return BWAGPU_OK;
+}
+
+extern "C" int bwagpu_host_free(bwagpu_ctx *ctx, void *hptr)
+{
+    if (!ctx) return BWAGPU_ERR_ARG;
+    if (hptr) BWAGPU_CUDA(ctx, cudaFreeHost(hptr));
+    return BWAGPU_OK;
+}
+
+extern "C" int bwagpu_h2d_async(bwagpu_ctx *ctx, void *dst, const void *src, int64_t bytes)
+{
+    if (!ctx || bytes < 0) return BWAGPU_ERR_ARG;
+    BWAGPU_CUDA(ctx, cudaSetDevice(ctx->device));
+    BWAGPU_CUDA(ctx, cudaMemcpyAsync(dst, src, (size_t)bytes, cudaMemcpyHostToDevice, ctx->stream));
+    return BWAGPU_OK;
+}
+
+extern "C" int bwagpu_d2h_async(bwagpu_ctx *ctx, void *dst, const void *src, int64_t bytes)
+{
+    if (!ctx || bytes < 0) return BWAGPU_ERR_ARG;
+    BWAGPU_CUDA(ctx, cudaSetDevice(ctx->device));
+    BWAGPU_CUDA(ctx, cudaMemcpyAsync(dst, src, (size_t)bytes, cudaMemcpyDeviceToHost, ctx->stream));
+    return BWAGPU_OK;
+}
+
 extern "C" int bwagpu_memset(bwagpu_ctx *ctx, void *dst, int value, int64_t bytes)
 {
     if (!ctx || bytes < 0) return BWAGPU_ERR_ARG;

@@ -119,6 +119,10 @@ _SIGS = {
                                           C.c_void_p, C.c_int32]),
     "bwagpu_ksw_align2_batch_device": (C.c_int, [C.c_void_p, C.POINTER(KswParams), C.c_void_p, C.c_void_p,
                                                  C.c_void_p, C.c_void_p, C.c_int32]),
+    "bwagpu_host_alloc": (C.c_int, [C.c_void_p, C.c_int64, C.POINTER(C.c_void_p)]),
+    "bwagpu_host_free": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "bwagpu_h2d_async": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64]),
+    "bwagpu_d2h_async": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64]),
     "bwagpu_emf_load": (C.c_int, [C.c_void_p, C.POINTER(EmfDesc), C.c_void_p, C.c_void_p]),
     "bwagpu_emf_unload": (C.c_int, [C.c_void_p]),
     "bwagpu_emf_probe": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p,
@@ -184,6 +188,9 @@ class Context:
 
     def close(self) -> None:
         if getattr(self, "h", None):
+            for p in getattr(self, "_pinned", []):
+                self.lib.bwagpu_host_free(self.h, p)
+            self._pinned = []
             self.lib.bwagpu_destroy(self.h)
             self.h = None
 
@@ -235,6 +242,23 @@ class Context:
 
     def d2h(self, arr, dptr: int) -> None:
         self.check(self.lib.bwagpu_d2h(self.h, arr.ctypes.data, C.c_void_p(dptr), arr.nbytes), "d2h")
+
+    def h2d_async(self, dptr: int, arr) -> None:
+        self.check(self.lib.bwagpu_h2d_async(self.h, C.c_void_p(dptr), arr.ctypes.data, arr.nbytes), "h2d_async")
+
+    def d2h_async(self, arr, dptr: int) -> None:
+        self.check(self.lib.bwagpu_d2h_async(self.h, arr.ctypes.data, C.c_void_p(dptr), arr.nbytes), "d2h_async")
+
+    def pinned(self, shape, dtype):
+        """A numpy array over page-locked host memory (bwagpu_host_alloc); lives until the context closes."""
+        import numpy as np
+        dtype = np.dtype(dtype)
+        n = int(np.prod(shape))
+        p = C.c_void_p()
+        self.check(self.lib.bwagpu_host_alloc(self.h, n * dtype.itemsize, C.byref(p)), "host_alloc")
+        buf = (C.c_uint8 * max(n * dtype.itemsize, 1)).from_address(p.value)
+        self._pinned = getattr(self, "_pinned", []) + [p]
+        return np.frombuffer(buf, dtype=dtype, count=n).reshape(shape)
 
     def memset(self, dptr: int, value: int, nbytes: int) -> None:
         self.check(self.lib.bwagpu_memset(self.h, C.c_void_p(dptr), value, int(nbytes)), "memset")

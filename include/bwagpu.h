@@ -56,6 +56,13 @@ int bwagpu_free(bwagpu_ctx *ctx, void *dptr);
 int bwagpu_h2d(bwagpu_ctx *ctx, void *dst_dev, const void *src_host, int64_t bytes);
 int bwagpu_d2h(bwagpu_ctx *ctx, void *dst_host, const void *src_dev, int64_t bytes);
 int bwagpu_memset(bwagpu_ctx *ctx, void *dst_dev, int value, int64_t bytes);   /* async on ctx's stream */
+/* Page-locked host memory for the caller's batch buffers (the reference keeps its per-thread arenas
+ * for the whole run, src/fastmap.cpp:280-300; pinning them once makes every copy a DMA at PCIe speed),
+ * and copies that only enqueue on the context's stream (pair with bwagpu_synchronize). */
+int bwagpu_host_alloc(bwagpu_ctx *ctx, int64_t bytes, void **hptr);
+int bwagpu_host_free(bwagpu_ctx *ctx, void *hptr);
+int bwagpu_h2d_async(bwagpu_ctx *ctx, void *dst_dev, const void *src_host, int64_t bytes);
+int bwagpu_d2h_async(bwagpu_ctx *ctx, void *dst_host, const void *src_dev, int64_t bytes);
 
 /* ---- S2: banded Smith-Waterman extension ------------------------------------------------------
  * bwagpu_seqpair mirrors SeqPair (reference src/bandedSWA.h:90-99), 56 bytes. */
