@@ -593,7 +593,8 @@ def init_dist(world):
     if world > 1:
         import torch
         import torch.distributed as dist
-        torch.cuda.set_device(int(os.environ.get("LOCAL_RANK", 0)))
+        if torch.cuda.is_available():
+            torch.cuda.set_device(int(os.environ.get("LOCAL_RANK", 0)))
         dist.init_process_group("nccl" if torch.cuda.is_available() else "gloo")
         _dist = dist
 
