@@ -344,6 +344,9 @@ def bench_seed(args, rank, world):
     return out
 
 # ------------------------------------------------------------------------------------------------
+# dram__bytes_read.sum + dram__bytes_write.sum of seed_collect_kernel<true>, one launch of the default
+# configuration (100 Mbp, 1 M reads, FMA on): profiles/r01_ncu_mem_kernels_summary.txt
+NCU_SEED_COLLECT_TRAFFIC = int(61.099131e9 + 10.094755e9)
 KERNELS = {0: "seed_collect", 1: "seed_sort", 2: "sa_walk", 3: "bsw", 4: "bsw_generic", 7: "chain2aln", 8: "chain_seeds",
            9: "emf_probe"}
 
@@ -548,6 +551,9 @@ def bench_mem(args, rank, world):
     alg_bytes = sres.n_cp_records * 64
     ach = alg_bytes / (k_ms / max(k_n, 1) * 1e-3) / 1e9
     nprof = max(min(args.steps, 2), 1)
+    traffic = None
+    if args.ref_mbp == 100.0 and n == 1_000_000 and args.fma and not args.emf and args.exact_frac is None:
+        traffic = NCU_SEED_COLLECT_TRAFFIC     # same configuration as the committed capture
     purged = int(((out["qb"] == -1) & (out["qe"] == -1)).sum())
     res = {"metric": "aligned reads/s (151bp SE, seed+extend)", "value": n * world * args.steps / (ms * 1e-3),
            "unit": "reads/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
@@ -558,8 +564,8 @@ def bench_mem(args, rank, world):
                    "h2d_bytes_per_step": int(flat.nbytes + off.nbytes + ln.nbytes),
                    "d2h_bytes_per_step": int(ares.n_regs * REG_DTYPE.itemsize)},
            "roofline": {"bound": "hbm", "kernel": "seed_collect_kernel", "achieved": ach, "peak": pk["hbm_gbs"],
-                        "unit": "GB/s", "frac": ach / pk["hbm_gbs"], "traffic": None, "peak_kind": pk_kind,
-                        "kernel_ms": k_ms / max(k_n, 1),
+                        "unit": "GB/s", "frac": ach / pk["hbm_gbs"], "traffic": traffic, "algorithmic_bytes": int(alg_bytes),
+                        "peak_kind": pk_kind, "kernel_ms": k_ms / max(k_n, 1),
                         "kernel_ms_per_step": {name: t / nprof for name, (t, c) in ktimes.items()},
                         "bext_per_read": sres.n_ext / n, "cp_records_per_read": sres.n_cp_records / n},
            "work": {"smem_per_read": sres.n_smem / n, "sa_rows_per_read": sres.n_coords / n,
@@ -593,6 +599,7 @@ def init_dist(world):
     if world > 1:
         import torch
         import torch.distributed as dist
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")   # keep stdout to the one JSON line
         if torch.cuda.is_available():
             torch.cuda.set_device(int(os.environ.get("LOCAL_RANK", 0)))
         dist.init_process_group("nccl" if torch.cuda.is_available() else "gloo")
