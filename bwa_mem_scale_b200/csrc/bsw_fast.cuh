@@ -126,26 +126,53 @@ __device__ BswOut bsw_lane_fast(const bwagpu_bsw_params &p, const uint8_t *__res
         const int jb = min(hi, tail);             // [ja, jb): live range, j >= head and j + 1 <= tail
         if (j < jb) {
             uint32_t *cp = &COL(j);
-            int jp1 = j + 1;
-            uint32_t wq = qsm[(j >> 3) * STRIDE] >> (4 * (j & 7));
-#pragma unroll kBswUnroll
-            for (; j < jb; ++j, cp += STRIDE, ++jp1) {
-                const uint32_t cv = *cp;
-                const uint32_t sel = (wq & 7u) * 0x1111u + 0x8880u;       // byte = query code, sign-extended
-                wq >>= 4;
-                if ((jp1 & 7) == 0) wq = qsm[(jp1 >> 3) * STRIDE];
-                const int s = (int)bsw_prmt(tlo, thi, sel);
-                const int diag = (int)(cv & 0xFFFFu), fc = (int)(cv >> 16);
-                int M = diag + s;
-                M = diag ? M : 0;
-                if (BITS == 8) M = max(M, 0);
-                const int h = __vimax3_s32(M, er, fc);
-                er = __viaddmax_s32_relu(M, -gapo_i, er - e_ins);
-                const int fnew = __viaddmax_s32_relu(M, -gapo_d, fc - e_del);
-                key = max(key, (h << 16) + jp1);
-                *cp = __byte_perm((uint32_t)left, (uint32_t)fnew, 0x5410);
-                left = h;
+            // one live cell: NIB = query code of column J, KEY receives (h << 16) + (J + 1)
+#define LIVE_CELL(NIB, J, KEY)                                                        \
+            {                                                                         \
+                const uint32_t cv = *cp;                                              \
+                const uint32_t sel = (NIB) * 0x1111u + 0x8880u;   /* byte = query code, sign-extended */ \
+                const int s = (int)bsw_prmt(tlo, thi, sel);                           \
+                const int diag = (int)(cv & 0xFFFFu), fc = (int)(cv >> 16);           \
+                int M = diag + s;                                                     \
+                M = diag ? M : 0;                                                     \
+                if (BITS == 8) M = max(M, 0);                                         \
+                const int h = __vimax3_s32(M, er, fc);                                \
+                er = __viaddmax_s32_relu(M, -gapo_i, er - e_ins);                     \
+                const int fnew = __viaddmax_s32_relu(M, -gapo_d, fc - e_del);         \
+                KEY = (h << 16) + ((J) + 1);                                          \
+                *cp = __byte_perm((uint32_t)left, (uint32_t)fnew, 0x5410);            \
+                left = h;                                                             \
+                cp += STRIDE;                                                         \
             }
+            // columns up to the next multiple of 8 (the query is staged 8 codes per word)
+            const int jpro = min(jb, (j + 7) & ~7);
+            if (j < jpro) {
+                uint32_t wq = qsm[(j >> 3) * STRIDE] >> (4 * (j & 7));
+                for (; j < jpro; ++j) { int k1; LIVE_CELL(wq & 7u, j, k1) key = max(key, k1); wq >>= 4; }
+            }
+            // whole words: 8 cells straight-line, shifts known at compile time
+            const uint32_t *qp = qsm + (j >> 3) * STRIDE;
+            for (; j + 8 <= jb; j += 8, qp += STRIDE) {
+                const uint32_t wq = *qp;
+                int k0, k1, k2, k3, k4, k5, k6, k7;
+                LIVE_CELL(wq & 7u, j, k0)
+                LIVE_CELL((wq >> 4) & 7u, j + 1, k1)
+                LIVE_CELL((wq >> 8) & 7u, j + 2, k2)
+                LIVE_CELL((wq >> 12) & 7u, j + 3, k3)
+                LIVE_CELL((wq >> 16) & 7u, j + 4, k4)
+                LIVE_CELL((wq >> 20) & 7u, j + 5, k5)
+                LIVE_CELL((wq >> 24) & 7u, j + 6, k6)
+                LIVE_CELL((wq >> 28) & 7u, j + 7, k7)
+                key = __vimax3_s32(key, k0, k1);
+                key = __vimax3_s32(key, k2, k3);
+                key = __vimax3_s32(key, k4, k5);
+                key = __vimax3_s32(key, k6, k7);
+            }
+            if (j < jb) {
+                uint32_t wq = *qp;
+                for (; j < jb; ++j) { int k1; LIVE_CELL(wq & 7u, j, k1) key = max(key, k1); wq >>= 4; }
+            }
+#undef LIVE_CELL
             if (jb == len2 && live) {             // the last query column was in the live range
                 if (!(gsc > left)) gi = i + 1;
                 gsc = max(gsc, left);

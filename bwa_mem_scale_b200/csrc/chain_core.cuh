@@ -49,7 +49,8 @@ struct WChain {
     int32_t w, kept, first, is_alt;
 };
 
-struct BtNode { int32_t n, is_internal; int32_t key[CHAIN_BT_MAXKEYS]; int32_t ptr[CHAIN_BT_MAXKEYS + 1]; };
+// kpos[a] mirrors ch[key[a]].pos so that a search reads one node instead of chasing every key
+struct BtNode { int32_t n, is_internal; int32_t key[CHAIN_BT_MAXKEYS]; int32_t ptr[CHAIN_BT_MAXKEYS + 1]; int64_t kpos[CHAIN_BT_MAXKEYS]; };
 
 CHAIN_HD int chain_pos2rid(const RefView &r, int64_t pos_f)          // bns_pos2rid, src/bntseq.cpp:397-411
 {
@@ -88,17 +89,25 @@ struct ChainBuilder {
 
     CHAIN_HD int cmp_pos(int64_t a, int64_t b) const { return (b < a) - (a < b); }
 
-    CHAIN_HD int getp_aux(const BtNode &x, int64_t k, int *r) const      // __kb_getp_aux
+    // __kb_getp_aux: the binary search's answer is the lower bound, i.e. the number of keys whose pos
+    // is < k (a node's keys are sorted by pos); counted over the node's own copy of the positions,
+    // nine independent loads instead of a chain of dependent ones
+    CHAIN_HD int getp_aux(const BtNode &x, int64_t k, int *r) const
     {
-        if (x.n == 0) return -1;
-        int begin = 0, end = x.n;
-        while (begin < end) {
-            const int mid = (begin + end) >> 1;
-            if (cmp_pos(s.ch[x.key[mid]].pos, k) < 0) begin = mid + 1; else end = mid;
+        const int n = x.n;
+        if (n == 0) return -1;
+        int begin = 0, eq = 0;
+#if defined(__CUDA_ARCH__)
+#pragma unroll
+#endif
+        for (int a = 0; a < CHAIN_BT_MAXKEYS; ++a) {
+            const int64_t p = a < n ? x.kpos[a] : k + 1;
+            begin += p < k;
+            eq |= p == k;
         }
-        if (begin == x.n) { *r = 1; return x.n - 1; }
-        if ((*r = cmp_pos(k, s.ch[x.key[begin]].pos)) < 0) --begin;
-        return begin;
+        if (begin == n) { *r = 1; return n - 1; }
+        *r = eq ? 0 : -1;
+        return eq ? begin : begin - 1;
     }
 
     CHAIN_HD int interval_lower(int64_t k) const                           // kb_intervalp: lower only
@@ -126,13 +135,13 @@ struct ChainBuilder {
         const int zi = new_node(s.nodes[yi].is_internal);
         BtNode &x = s.nodes[xi], &y = s.nodes[yi], &z = s.nodes[zi];
         z.n = CHAIN_BT_T - 1;
-        for (int a = 0; a < CHAIN_BT_T - 1; ++a) z.key[a] = y.key[CHAIN_BT_T + a];
+        for (int a = 0; a < CHAIN_BT_T - 1; ++a) { z.key[a] = y.key[CHAIN_BT_T + a]; z.kpos[a] = y.kpos[CHAIN_BT_T + a]; }
         if (y.is_internal) for (int a = 0; a < CHAIN_BT_T; ++a) z.ptr[a] = y.ptr[CHAIN_BT_T + a];
         y.n = CHAIN_BT_T - 1;
         for (int a = x.n; a > i; --a) x.ptr[a + 1] = x.ptr[a];
         x.ptr[i + 1] = zi;
-        for (int a = x.n - 1; a >= i; --a) x.key[a + 1] = x.key[a];
-        x.key[i] = y.key[CHAIN_BT_T - 1];
+        for (int a = x.n - 1; a >= i; --a) { x.key[a + 1] = x.key[a]; x.kpos[a + 1] = x.kpos[a]; }
+        x.key[i] = y.key[CHAIN_BT_T - 1]; x.kpos[i] = y.kpos[CHAIN_BT_T - 1];
         ++x.n;
     }
 
@@ -151,15 +160,15 @@ struct ChainBuilder {
             int r;
             if (!x.is_internal) {
                 const int i = getp_aux(x, k, &r);
-                for (int a = x.n - 1; a > i; --a) x.key[a + 1] = x.key[a];
-                x.key[i + 1] = ci;
+                for (int a = x.n - 1; a > i; --a) { x.key[a + 1] = x.key[a]; x.kpos[a + 1] = x.kpos[a]; }
+                x.key[i + 1] = ci; x.kpos[i + 1] = k;
                 ++x.n;
                 return;
             }
             int i = getp_aux(x, k, &r) + 1;
             if (s.nodes[x.ptr[i]].n == CHAIN_BT_MAXKEYS) {
                 split(xi, i, x.ptr[i]);
-                if (cmp_pos(k, s.ch[s.nodes[xi].key[i]].pos) > 0) ++i;
+                if (cmp_pos(k, s.nodes[xi].kpos[i]) > 0) ++i;
             }
             xi = s.nodes[xi].ptr[i];
         }
@@ -235,6 +244,7 @@ struct ChainBuilder {
 
     CHAIN_HD int weight(const WChain &c) const                              // mem_chain_weight :455-474
     {
+        if (c.n == 1) return c.last_len < (1 << 30) ? c.last_len : (1 << 30) - 1;   // one seed: both covers = its length
         int64_t end = 0; int w = 0;
         for (int si = c.head; si >= 0; si = s.sd[si].pad_) {
             const bwagpu_seed &e = s.sd[si];
@@ -330,28 +340,41 @@ struct ChainBuilder {
         if (n == 0) return 0;
         int32_t *a = s.ord;
         introsort(a, n);
+        // the kept list is scanned once per chain: keep the fields the scan reads (query span, weight,
+        // is_alt, "first already set") side by side in the tree's node storage, which is dead after
+        // traverse(), instead of chasing lst -> ord -> chain for every test
+        struct Kept { int32_t beg, end, w, flags; };
+        Kept *lv = reinterpret_cast<Kept *>(s.nodes);
         int nl = 0;
-        s.ch[a[0]].kept = 3;
-        s.lst[nl++] = 0;
+        {
+            WChain &c0 = s.ch[a[0]];
+            c0.kept = 3;
+            lv[0].beg = chn_beg(c0); lv[0].end = chn_end(c0); lv[0].w = c0.w; lv[0].flags = c0.is_alt ? 1 : 0;
+            s.lst[nl++] = 0;
+        }
+        const int msl2 = o.min_seed_len << 1;
         for (int i = 1; i < n; ++i) {
             int large_ovlp = 0, k;
             WChain &ci = s.ch[a[i]];
+            const int bi = chn_beg(ci), ei = chn_end(ci), wi = ci.w, alt_i = ci.is_alt;
             for (k = 0; k < nl; ++k) {
-                const int j = s.lst[k];
-                WChain &cj = s.ch[a[j]];
-                const int b_max = chn_beg(cj) > chn_beg(ci) ? chn_beg(cj) : chn_beg(ci);
-                const int e_min = chn_end(cj) < chn_end(ci) ? chn_end(cj) : chn_end(ci);
-                if (e_min > b_max && (!cj.is_alt || ci.is_alt)) {
-                    const int li = chn_end(ci) - chn_beg(ci), lj = chn_end(cj) - chn_beg(cj);
+                const Kept kv = lv[k];
+                const int b_max = kv.beg > bi ? kv.beg : bi;
+                const int e_min = kv.end < ei ? kv.end : ei;
+                if (e_min > b_max && (!(kv.flags & 1) || alt_i)) {
+                    const int li = ei - bi, lj = kv.end - kv.beg;
                     const int min_l = li < lj ? li : lj;
                     if ((float)(e_min - b_max) >= (float)min_l * o.mask_level && min_l < o.max_chain_gap) {
                         large_ovlp = 1;
-                        if (cj.first < 0) cj.first = i;
-                        if ((float)ci.w < (float)cj.w * o.drop_ratio && cj.w - ci.w >= o.min_seed_len << 1) break;
+                        if (!(kv.flags & 2)) { s.ch[a[s.lst[k]]].first = i; lv[k].flags = kv.flags | 2; }
+                        if ((float)wi < (float)kv.w * o.drop_ratio && kv.w - wi >= msl2) break;
                     }
                 }
             }
-            if (k == nl) { s.lst[nl++] = i; ci.kept = large_ovlp ? 2 : 3; }
+            if (k == nl) {
+                lv[nl].beg = bi; lv[nl].end = ei; lv[nl].w = wi; lv[nl].flags = alt_i ? 1 : 0;
+                s.lst[nl++] = i; ci.kept = large_ovlp ? 2 : 3;
+            }
         }
         for (int i = 0; i < nl; ++i) {
             const WChain &c = s.ch[a[s.lst[i]]];
