@@ -47,6 +47,11 @@ extern "C" int bwagpu_create(int device, bwagpu_ctx **out)
     CK(cudaEventCreate(&ctx->ev_stop));
     CK(cudaEventCreate(&ctx->kev0));
     CK(cudaEventCreate(&ctx->kev1));
+    CK(cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking));
+    CK(cudaEventCreateWithFlags(&ctx->ev_main_done, cudaEventDisableTiming));
+    CK(cudaEventCreateWithFlags(&ctx->ev_h2d_done, cudaEventDisableTiming));
+    CK(cudaEventCreateWithFlags(&ctx->ev_d2h_done, cudaEventDisableTiming));
+    ctx->d2h_pending_slot = -1;
 #undef CK
     *out = ctx;
     return BWAGPU_OK;
@@ -71,6 +76,9 @@ extern "C" void bwagpu_destroy(bwagpu_ctx *ctx)
     cudaEventDestroy(ctx->ev_stop);
     cudaEventDestroy(ctx->kev0);
     cudaEventDestroy(ctx->kev1);
+    cudaStreamSynchronize(ctx->copy_stream);
+    cudaEventDestroy(ctx->ev_main_done); cudaEventDestroy(ctx->ev_h2d_done); cudaEventDestroy(ctx->ev_d2h_done);
+    cudaStreamDestroy(ctx->copy_stream);
     cudaStreamDestroy(ctx->stream);
     free(ctx);
 }
@@ -187,6 +195,57 @@ extern "C" int bwagpu_d2h_async(bwagpu_ctx *ctx, void *dst, const void *src, int
     return BWAGPU_OK;
 }
 
+// ---- copies on the second stream ----
+extern "C" int bwagpu_h2d_overlap(bwagpu_ctx *ctx, void *dst, const void *src, int64_t bytes)
+{
+    if (!ctx || bytes < 0) return BWAGPU_ERR_ARG;
+    BWAGPU_CUDA(ctx, cudaSetDevice(ctx->device));
+    // after everything already enqueued on the main stream (the batch that last used dst), before what comes next
+    BWAGPU_CUDA(ctx, cudaEventRecord(ctx->ev_main_done, ctx->stream));
+    BWAGPU_CUDA(ctx, cudaStreamWaitEvent(ctx->copy_stream, ctx->ev_main_done, 0));
+    BWAGPU_CUDA(ctx, cudaMemcpyAsync(dst, src, (size_t)bytes, cudaMemcpyHostToDevice, ctx->copy_stream));
+    BWAGPU_CUDA(ctx, cudaEventRecord(ctx->ev_h2d_done, ctx->copy_stream));
+    ctx->h2d_pending = 1;
+    return BWAGPU_OK;
+}
+
+extern "C" int bwagpu_h2d_fence(bwagpu_ctx *ctx)
+{
+    if (!ctx) return BWAGPU_ERR_ARG;
+    if (ctx->h2d_pending) {
+        BWAGPU_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, ctx->ev_h2d_done, 0));
+        ctx->h2d_pending = 0;
+    }
+    return BWAGPU_OK;
+}
+
+extern "C" int bwagpu_d2h_overlap(bwagpu_ctx *ctx, void *dst, const void *src, int64_t bytes)
+{
+    if (!ctx || bytes < 0) return BWAGPU_ERR_ARG;
+    BWAGPU_CUDA(ctx, cudaSetDevice(ctx->device));
+    if (ctx->d2h_pending_slot >= 0) {          // one result buffer in flight at a time
+        BWAGPU_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, ctx->ev_d2h_done, 0));
+        ctx->d2h_pending_slot = -1;
+    }
+    BWAGPU_CUDA(ctx, cudaEventRecord(ctx->ev_main_done, ctx->stream));
+    BWAGPU_CUDA(ctx, cudaStreamWaitEvent(ctx->copy_stream, ctx->ev_main_done, 0));
+    BWAGPU_CUDA(ctx, cudaMemcpyAsync(dst, src, (size_t)bytes, cudaMemcpyDeviceToHost, ctx->copy_stream));
+    BWAGPU_CUDA(ctx, cudaEventRecord(ctx->ev_d2h_done, ctx->copy_stream));
+    for (int i = 0; i < BWAGPU_NSCRATCH; ++i) {
+        const char *b = (const char *)ctx->scratch[i];
+        if (b && (const char *)src >= b && (const char *)src < b + ctx->scratch_bytes[i]) { ctx->d2h_pending_slot = i; break; }
+    }
+    return BWAGPU_OK;
+}
+
+extern "C" int bwagpu_copy_synchronize(bwagpu_ctx *ctx)
+{
+    if (!ctx) return BWAGPU_ERR_ARG;
+    BWAGPU_CUDA(ctx, cudaSetDevice(ctx->device));
+    BWAGPU_CUDA(ctx, cudaStreamSynchronize(ctx->copy_stream));
+    return BWAGPU_OK;
+}
+
 extern "C" int bwagpu_memset(bwagpu_ctx *ctx, void *dst, int value, int64_t bytes)
 {
     if (!ctx || bytes < 0) return BWAGPU_ERR_ARG;
@@ -197,6 +256,10 @@ extern "C" int bwagpu_memset(bwagpu_ctx *ctx, void *dst, int value, int64_t byte
 
 int bwagpu_scratch(bwagpu_ctx *ctx, int slot, int64_t bytes, void **out)
 {
+    if (slot == ctx->d2h_pending_slot) {      // an overlapped D2H still reads this buffer: order the stream after it
+        BWAGPU_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, ctx->ev_d2h_done, 0));
+        ctx->d2h_pending_slot = -1;
+    }
     if (bytes > ctx->scratch_bytes[slot]) {
         if (ctx->scratch[slot]) {
             BWAGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));

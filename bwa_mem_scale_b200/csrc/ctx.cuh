@@ -21,6 +21,11 @@ struct bwagpu_ctx {
     int sm_count;
     cudaStream_t stream;
     cudaEvent_t ev_start, ev_stop;
+    // second stream for copies that overlap the kernels of the next batch (bwagpu_*_overlap)
+    cudaStream_t copy_stream;
+    cudaEvent_t ev_main_done, ev_h2d_done, ev_d2h_done;
+    int d2h_pending_slot;        // scratch slot an overlapped D2H is still reading (-1: none)
+    int h2d_pending;
     int64_t launches;
     char err[512];
     // grow-only device scratch owned by the context (one chunk of reads at a time is in flight,

@@ -123,6 +123,10 @@ _SIGS = {
     "bwagpu_host_free": (C.c_int, [C.c_void_p, C.c_void_p]),
     "bwagpu_h2d_async": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64]),
     "bwagpu_d2h_async": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64]),
+    "bwagpu_h2d_overlap": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64]),
+    "bwagpu_h2d_fence": (C.c_int, [C.c_void_p]),
+    "bwagpu_d2h_overlap": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64]),
+    "bwagpu_copy_synchronize": (C.c_int, [C.c_void_p]),
     "bwagpu_emf_load": (C.c_int, [C.c_void_p, C.POINTER(EmfDesc), C.c_void_p, C.c_void_p]),
     "bwagpu_emf_unload": (C.c_int, [C.c_void_p]),
     "bwagpu_emf_probe": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p,
@@ -248,6 +252,18 @@ class Context:
 
     def d2h_async(self, arr, dptr: int) -> None:
         self.check(self.lib.bwagpu_d2h_async(self.h, arr.ctypes.data, C.c_void_p(dptr), arr.nbytes), "d2h_async")
+
+    def h2d_overlap(self, dptr: int, arr) -> None:
+        self.check(self.lib.bwagpu_h2d_overlap(self.h, C.c_void_p(dptr), arr.ctypes.data, arr.nbytes), "h2d_overlap")
+
+    def h2d_fence(self) -> None:
+        self.check(self.lib.bwagpu_h2d_fence(self.h), "h2d_fence")
+
+    def d2h_overlap(self, arr, dptr: int) -> None:
+        self.check(self.lib.bwagpu_d2h_overlap(self.h, arr.ctypes.data, C.c_void_p(dptr), arr.nbytes), "d2h_overlap")
+
+    def copy_synchronize(self) -> None:
+        self.check(self.lib.bwagpu_copy_synchronize(self.h), "copy_synchronize")
 
     def pinned(self, shape, dtype):
         """A numpy array over page-locked host memory (bwagpu_host_alloc); lives until the context closes."""

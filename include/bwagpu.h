@@ -63,6 +63,17 @@ int bwagpu_host_alloc(bwagpu_ctx *ctx, int64_t bytes, void **hptr);
 int bwagpu_host_free(bwagpu_ctx *ctx, void *hptr);
 int bwagpu_h2d_async(bwagpu_ctx *ctx, void *dst_dev, const void *src_host, int64_t bytes);
 int bwagpu_d2h_async(bwagpu_ctx *ctx, void *dst_host, const void *src_dev, int64_t bytes);
+/* Copies on the context's SECOND stream, for a double-buffered batch loop (what the reference's
+ * kt_pipeline does with its read / compute / write steps, src/fastmap.cpp:430-640):
+ *   bwagpu_h2d_overlap : starts copying the NEXT batch into a buffer the running batch does not use
+ *   bwagpu_h2d_fence   : later work on the main stream waits for that copy (call before using the buffer)
+ *   bwagpu_d2h_overlap : copies a finished result out, ordered after everything enqueued so far; the
+ *                        stage that next rewrites the source buffer waits for the copy by itself
+ *   bwagpu_copy_synchronize : host waits for the second stream (the copied-out result is then valid) */
+int bwagpu_h2d_overlap(bwagpu_ctx *ctx, void *dst_dev, const void *src_host, int64_t bytes);
+int bwagpu_h2d_fence(bwagpu_ctx *ctx);
+int bwagpu_d2h_overlap(bwagpu_ctx *ctx, void *dst_host, const void *src_dev, int64_t bytes);
+int bwagpu_copy_synchronize(bwagpu_ctx *ctx);
 
 /* ---- S2: banded Smith-Waterman extension ------------------------------------------------------
  * bwagpu_seqpair mirrors SeqPair (reference src/bandedSWA.h:90-99), 56 bytes. */
