@@ -606,6 +606,103 @@ def bench_mem(args, rank, world):
     return res
 
 # ------------------------------------------------------------------------------------------------
+def ref_ksw_cpu(pairs, ref, qer, threads):
+    """The reference's own ksw_align2 (oracle/_ref/libref_ksw.so = src/ksw.cpp, SSE) over `pairs`,
+    chunked across host threads.  Returns seconds."""
+    from concurrent.futures import ThreadPoolExecutor
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import oracle_lib as ol
+    lib = ol.ref_ksw()
+    if lib is None:
+        raise RuntimeError("oracle/_ref/libref_ksw.so is missing")
+    chunks = [c for c in np.array_split(np.arange(len(pairs)), max(threads * 4, 1)) if len(c)]
+    t0 = time.perf_counter()
+    with ThreadPoolExecutor(max_workers=threads) as ex:
+        list(ex.map(lambda c: ol.reference_ksw(lib, pairs[c], ref, qer), chunks))
+    return time.perf_counter() - t0
+
+
+def bench_ksw(args, rank, world):
+    """Mate-rescue SW (BASELINE config 4's kernel): ksw_align2 jobs shaped like mem_matesw's, 151-bp query
+    against an insert-size window, xtra = SUBO | START | BYTE | min_seed_len."""
+    from bwa_mem_scale_b200 import Context, KSWR_DTYPE, MateSW, synth
+    uniq = min(args.pairs, 20000)
+    pairs, ref, qer = synth.rescue_jobs(uniq, seed=2000 + rank)
+    reps = max(args.pairs // uniq, 1)
+    pairs = np.tile(pairs, reps)                     # the same windows again: the kernel is compute bound
+    pairs["id"] = np.arange(len(pairs))
+    n = len(pairs)
+    cells = float((pairs["len1"].astype(np.int64) * pairs["len2"]).sum())
+    cfg = {"workload": f"mate-rescue SW (BASELINE config 4 kernel): {n} ksw_align2 jobs/GPU ({uniq} distinct), 151 bp query x "
+                       "200-900 bp window, xtra = SUBO|START|BYTE|19; cell updates = len1 x len2 of the forward pass",
+           "jobs_per_gpu": n, "l2_policy": "flush between steps"}
+    if args.impl == "reference":
+        if rank != 0:
+            return None
+        thr = cpu_threads()
+        sample = pairs[: min(n, 4000 * thr)]
+        sc = float((sample["len1"].astype(np.int64) * sample["len2"]).sum())
+        ref_ksw_cpu(sample[:200 * thr], ref, qer, thr)
+        t = sum(ref_ksw_cpu(sample, ref, qer, thr) for _ in range(args.steps))
+        v = sc * args.steps / t / 1e9
+        return {"impl": "reference", "metric": "mate-rescue SW GCUPS", "value": v, "unit": "GCUPS", "n_gpus": args.gpus,
+                "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * t / args.steps, "higher_is_better": True,
+                "scaling": "weak", "vs_baseline": None, "dtype": "u8/int16", "data": "synthetic", "config": cfg,
+                "cpu_baseline": {"value": v, "unit": "GCUPS", "cores": thr, "kind": "reference",
+                                 "sample": f"{len(sample)} jobs of the same set, ksw_align2 (SSE build)"},
+                "e2e": {"value": v, "unit": "GCUPS", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    local = int(os.environ.get("LOCAL_RANK", rank))
+    ctx = Context(local)
+    sw = MateSW(ctx=ctx)
+    dp, dr, dq, da = ctx.upload(pairs), ctx.upload(ref), ctx.upload(qer), ctx.malloc(n * KSWR_DTYPE.itemsize)
+    flush = ctx.malloc(256 << 20)
+    for _ in range(args.warmup):
+        sw.batch_device(dp, dr, dq, da, n)
+    ctx.synchronize()
+    barrier()
+    sampler = ClockSampler(local)
+    sampler.start()
+    l0 = ctx.launch_count()
+    ms = 0.0
+    for _ in range(args.steps):
+        ctx.memset(flush, 1, 256 << 20)
+        ctx.timer_start()
+        sw.batch_device(dp, dr, dq, da, n)
+        ms += ctx.timer_stop()
+    launches = ctx.launch_count() - l0
+    ms = allreduce_max(ms)
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        aln = sw.mem_sam_pe_batch(pairs, ref, qer)
+    e2e_s = allreduce_max(time.perf_counter() - t0)
+    clocks = sampler.stop()
+    if rank != 0:
+        return None
+    pk, pk_kind = peaks()
+    alg_bytes = pairs.nbytes + float((pairs["len1"] + pairs["len2"]).sum()) + n * KSWR_DTYPE.itemsize
+    ach = alg_bytes * args.steps / (ms * 1e-3) / 1e9
+    out = {"metric": "mate-rescue SW GCUPS", "value": cells * world * args.steps / (ms * 1e-3) / 1e9, "unit": "GCUPS",
+           "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps,
+           "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8/int16", "data": "synthetic",
+           "config": cfg, "clocks": clocks, "gpu_launches": int(launches),
+           "e2e": {"value": cells * world * args.steps / e2e_s / 1e9, "unit": "GCUPS",
+                   "h2d_bytes_per_step": int(pairs.nbytes + ref.nbytes + qer.nbytes), "d2h_bytes_per_step": int(aln.nbytes)},
+           "roofline": {"bound": "hbm", "achieved": ach, "peak": pk["hbm_gbs"], "unit": "GB/s", "frac": ach / pk["hbm_gbs"],
+                        "traffic": None, "peak_kind": pk_kind, "note": "SW is integer-issue bound, not HBM bound; see DESIGN.md"},
+           "work": {"u8_jobs_frac": float(((pairs["h0"] & 0x10000) != 0).mean()),
+                    "jobs_with_hit_frac": float((aln["score"] >= 19).mean())}}
+    if not args.no_cpu:
+        thr = cpu_threads()
+        sample = pairs[: min(n, 4000 * thr)]
+        sc = float((sample["len1"].astype(np.int64) * sample["len2"]).sum())
+        dt = ref_ksw_cpu(sample, ref, qer, thr)
+        out["cpu_baseline"] = {"value": sc / dt / 1e9, "unit": "GCUPS", "cores": thr, "kind": "reference",
+                               "sample": f"{len(sample)} jobs of the same set, ksw_align2 (SSE build), {dt:.1f}s"}
+    return out
+
+
+# ------------------------------------------------------------------------------------------------
 _dist = None
 
 
@@ -642,7 +739,7 @@ def main():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="mem", choices=["mem", "bsw", "seed"])
+    ap.add_argument("--workload", default="mem", choices=["mem", "bsw", "seed", "ksw"])
     ap.add_argument("--ref-mbp", type=float, default=100.0)
     ap.add_argument("--reads", type=int, default=1_000_000)
     ap.add_argument("--pairs", type=int, default=1_000_000)
@@ -656,7 +753,7 @@ def main():
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", 0))
     world = int(os.environ.get("WORLD_SIZE", 1))
-    fn = {"mem": bench_mem, "bsw": bench_bsw, "seed": bench_seed}[args.workload]
+    fn = {"mem": bench_mem, "bsw": bench_bsw, "seed": bench_seed, "ksw": bench_ksw}[args.workload]
     if args.impl == "reference":
         if rank == 0:
             print(json.dumps(fn(args, 0, world)))
