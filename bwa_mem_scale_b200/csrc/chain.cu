@@ -26,7 +26,13 @@ __device__ __forceinline__ ChainScratch chain_scratch(bwagpu_seed *sd, WChain *c
 
 // per read: build + filter; leaves the surviving chains in ord[] and their counts in cnt[0][r] (chains),
 // cnt[1][r] (seeds)
-__global__ void chain_build_kernel(ChainOpt o, RefView rv, ChainIn in, bwagpu_seed *sd, WChain *ch, BtNode *nodes,
+#ifndef CHAIN_TPB
+#define CHAIN_TPB 64
+#endif
+#ifndef CHAIN_MINB
+#define CHAIN_MINB 16
+#endif
+__global__ void __launch_bounds__(CHAIN_TPB, CHAIN_MINB) chain_build_kernel(ChainOpt o, RefView rv, ChainIn in, bwagpu_seed *sd, WChain *ch, BtNode *nodes,
                                    int32_t *ord, int32_t *lst, int64_t *cnt_chains, int64_t *cnt_seeds,
                                    float *frac_rep)
 {
@@ -159,7 +165,7 @@ extern "C" int bwagpu_chain_seeds_device(bwagpu_ctx *ctx, const bwagpu_chain_opt
     if ((rc = bwagpu_scratch(ctx, SCR_CH_FRAC, (int64_t)(nseq + 1) * 4, (void **)&frac))) return rc;
     BWAGPU_CUDA(ctx, cudaMemsetAsync(cnt, 0, (size_t)(nseq + 1) * 16, ctx->stream));
     BWAGPU_KERNEL_BEGIN(ctx);
-    chain_build_kernel<<<(nseq + 63) / 64, 64, 0, ctx->stream>>>(o, rv, in, sd, ch, nodes, ord, lst, cnt, cnt + nseq + 1, frac);
+    chain_build_kernel<<<(nseq + CHAIN_TPB - 1) / CHAIN_TPB, CHAIN_TPB, 0, ctx->stream>>>(o, rv, in, sd, ch, nodes, ord, lst, cnt, cnt + nseq + 1, frac);
     BWAGPU_KERNEL_END(ctx, BWAGPU_KERN_CHAIN);
     BWAGPU_CUDA(ctx, cudaGetLastError());
     if ((rc = chain_scan(ctx, cnt, offs, nseq + 1))) return rc;

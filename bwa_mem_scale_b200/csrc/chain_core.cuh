@@ -263,14 +263,17 @@ struct ChainBuilder {
         return w < (1 << 30) ? w : (1 << 30) - 1;
     }
 
-    // ---- ks_introsort(mem_flt) replayed on ord[] with flt_lt(a,b) = a.w > b.w --------------------
-    CHAIN_HD bool lt(int a, int b) const { return s.ch[a].w > s.ch[b].w; }
-    CHAIN_HD void insertsort(int32_t *a, int lo, int hi)                     // [lo, hi)
+    // ---- ks_introsort(mem_flt) replayed with flt_lt(a,b) = a.w > b.w ---------------------------------
+    // The elements are (weight << 32 | chain index): every comparison reads the weight from the element
+    // itself instead of chasing the index into the chain array; the moves are those of the reference.
+    typedef uint64_t SortKey;
+    CHAIN_HD bool lt(SortKey a, SortKey b) const { return (uint32_t)(a >> 32) > (uint32_t)(b >> 32); }
+    CHAIN_HD void insertsort(SortKey *a, int lo, int hi)                     // [lo, hi)
     {
         for (int i = lo + 1; i < hi; ++i)
-            for (int j = i; j > lo && lt(a[j], a[j - 1]); --j) { const int t = a[j]; a[j] = a[j - 1]; a[j - 1] = t; }
+            for (int j = i; j > lo && lt(a[j], a[j - 1]); --j) { const SortKey t = a[j]; a[j] = a[j - 1]; a[j - 1] = t; }
     }
-    CHAIN_HD void combsort(int32_t *a, int n)
+    CHAIN_HD void combsort(SortKey *a, int n)
     {
         const double shrink = 1.2473309501039786540366528676643;
         int do_swap; size_t gap = (size_t)n;
@@ -279,15 +282,15 @@ struct ChainBuilder {
             do_swap = 0;
             for (size_t i = 0; i + gap < (size_t)n; ++i) {
                 const size_t j = i + gap;
-                if (lt(a[j], a[i])) { const int t = a[i]; a[i] = a[j]; a[j] = t; do_swap = 1; }
+                if (lt(a[j], a[i])) { const SortKey t = a[i]; a[i] = a[j]; a[j] = t; do_swap = 1; }
             }
         } while (do_swap || gap > 2);
         if (gap != 1) insertsort(a, 0, n);
     }
-    CHAIN_HD void introsort(int32_t *a, int n)
+    CHAIN_HD void introsort(SortKey *a, int n)
     {
         if (n < 1) return;
-        if (n == 2) { if (lt(a[1], a[0])) { const int t = a[0]; a[0] = a[1]; a[1] = t; } return; }
+        if (n == 2) { if (lt(a[1], a[0])) { const SortKey t = a[0]; a[0] = a[1]; a[1] = t; } return; }
         int d;
         for (d = 2; (1ul << d) < (unsigned long)n; ++d) {}
         int st_l[72], st_r[72], st_d[72], top = 0;
@@ -299,15 +302,15 @@ struct ChainBuilder {
                 int i = sl, j = tr, k = i + ((j - i) >> 1) + 1;
                 if (lt(a[k], a[i])) { if (lt(a[k], a[j])) k = j; }
                 else k = lt(a[j], a[i]) ? i : j;
-                const int rp = a[k];
-                if (k != tr) { const int t = a[k]; a[k] = a[tr]; a[tr] = t; }
+                const SortKey rp = a[k];
+                if (k != tr) { const SortKey t = a[k]; a[k] = a[tr]; a[tr] = t; }
                 for (;;) {
                     do ++i; while (lt(a[i], rp));
                     do --j; while (i <= j && lt(rp, a[j]));
                     if (j <= i) break;
-                    const int t = a[i]; a[i] = a[j]; a[j] = t;
+                    const SortKey t = a[i]; a[i] = a[j]; a[j] = t;
                 }
-                { const int t = a[i]; a[i] = a[tr]; a[tr] = t; }
+                { const SortKey t = a[i]; a[i] = a[tr]; a[tr] = t; }
                 if (i - sl > tr - i) {
                     if (i - sl > 16) { st_l[top] = sl; st_r[top] = i - 1; st_d[top] = d; ++top; }
                     sl = tr - i > 16 ? i + 1 : tr;
@@ -339,7 +342,12 @@ struct ChainBuilder {
         }
         if (n == 0) return 0;
         int32_t *a = s.ord;
-        introsort(a, n);
+        {
+            SortKey *sk = reinterpret_cast<SortKey *>(s.nodes);       // node storage is dead after traverse()
+            for (int i = 0; i < n; ++i) sk[i] = ((SortKey)(uint32_t)s.ch[a[i]].w << 32) | (uint32_t)a[i];
+            introsort(sk, n);
+            for (int i = 0; i < n; ++i) a[i] = (int32_t)(uint32_t)sk[i];
+        }
         // the kept list is scanned once per chain: keep the fields the scan reads (query span, weight,
         // is_alt, "first already set") side by side in the tree's node storage, which is dead after
         // traverse(), instead of chasing lst -> ord -> chain for every test
