@@ -279,6 +279,104 @@ __global__ void c2a_apply_kernel(C2aOpt o, int left, int w, int last_try, const 
     }
 }
 
+// reads with more regions than this are filtered by a whole warp (c2a_filter_warp_kernel)
+#define C2A_FILTER_WARP_MIN 48
+
+// The containment filter for reads with many regions (repeats): one read per warp.  The scan over
+// the regions created so far (:3652-3690) is the quadratic part; 32 of them are classified at a time
+// (purged / not containing -> counts / close to the seed's diagonal -> stop) and the reference's
+// sequential rules -- stop at the first "close" region, or once `lim` live regions have been seen --
+// are resolved with ballots and a prefix population count.
+__global__ void __launch_bounds__(128)
+c2a_filter_warp_kernel(C2aOpt o, const int32_t *__restrict__ len, int32_t nseq,
+                       const bwagpu_chain *__restrict__ chains, const bwagpu_seed *__restrict__ seeds,
+                       const uint32_t *__restrict__ srt, const int64_t *__restrict__ first_chain,
+                       const int64_t *__restrict__ last_chain, bwagpu_alnreg *__restrict__ regs,
+                       uint8_t *__restrict__ purged)
+{
+    const int l = (int)(((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5);
+    const int lane = threadIdx.x & 31;
+    if (l >= nseq) return;
+    const int64_t c0 = first_chain[l], c1 = last_chain[l];
+    if (c0 < 0) return;
+    const int64_t rbase = chains[c0].seed_off;
+    const int64_t n_regs = chains[c1].seed_off + chains[c1].n - rbase;
+    if (n_regs <= C2A_FILTER_WARP_MIN) return;
+    const int l_query = len[l];
+    bwagpu_alnreg *av = regs + rbase;
+    int lim = 0;
+    for (int64_t ci = c0; ci <= c1; ++ci) {
+        const bwagpu_chain c = chains[ci];
+        const bwagpu_seed *cs = seeds + c.seed_off;
+        const uint32_t *srt2 = srt + c.seed_off;
+        uint8_t *pg = purged + c.seed_off;
+        for (int k = c.n - 1; k >= 0; --k) {
+            const bwagpu_seed s = cs[srt2[k]];
+            int v = 0;
+            bool hit = false;                                   // left the scan through a `break`
+            for (int64_t base = 0; base < n_regs && v < lim && !hit; base += 32) {
+                const int64_t i = base + lane;
+                int cls = 0;                                    // 0 = skipped (purged / past the end), 1 = counts, 2 = stop
+                if (i < n_regs) {
+                    const bwagpu_alnreg a = av[i];
+                    if (!(a.qb == -1 && a.qe == -1)) {
+                        cls = 1;
+                        if (!(s.rbeg < a.rb || s.rbeg + s.len > a.re || s.qbeg < a.qb || s.qbeg + s.len > a.qe) &&
+                            !(s.len - a.seedlen0 > .1 * l_query)) {
+                            int qd = s.qbeg - a.qb; int64_t rd = s.rbeg - a.rb;
+                            int max_gap = c2a_max_gap(o, qd < rd ? qd : (int)rd);
+                            int w = max_gap < a.w ? max_gap : a.w;
+                            if (qd - rd < w && rd - qd < w) cls = 2;
+                            else {
+                                qd = a.qe - (s.qbeg + s.len); rd = a.re - (s.rbeg + s.len);
+                                max_gap = c2a_max_gap(o, qd < rd ? qd : (int)rd);
+                                w = max_gap < a.w ? max_gap : a.w;
+                                if (qd - rd < w && rd - qd < w) cls = 2;
+                            }
+                        }
+                    }
+                }
+                const unsigned m_cnt = __ballot_sync(0xffffffffu, cls == 1);
+                const unsigned m_stop = __ballot_sync(0xffffffffu, cls == 2);
+                // entry `lane` is examined only while the count of live regions seen before it is < lim
+                const int before = v + __popc(m_cnt & ((1u << lane) - 1u));
+                const unsigned m_seen = __ballot_sync(0xffffffffu, before < lim);     // a prefix of the lanes
+                const unsigned m_hit = m_stop & m_seen;
+                if (m_hit) {
+                    const int at = __ffs(m_hit) - 1;
+                    v += __popc(m_cnt & ((1u << at) - 1u));
+                    hit = true;
+                } else {
+                    v += __popc(m_cnt & m_seen);
+                }
+            }
+            if (v < lim) {          // (also when the scan ran off the end of the list, as in the reference)
+                int vv = c.n;
+                if (lane == 0) {
+                    for (vv = k + 1; vv < c.n; ++vv) {
+                        if (pg[vv]) continue;
+                        const bwagpu_seed t = cs[srt2[vv]];
+                        if (t.len < s.len * .95) continue;
+                        if (s.qbeg <= t.qbeg && s.qbeg + s.len - t.qbeg >= s.len >> 2 && t.qbeg - s.qbeg != t.rbeg - s.rbeg) break;
+                        if (t.qbeg <= s.qbeg && t.qbeg + t.len - s.qbeg >= s.len >> 2 && s.qbeg - t.qbeg != s.rbeg - t.rbeg) break;
+                    }
+                }
+                vv = __shfl_sync(0xffffffffu, vv, 0);
+                if (vv == c.n) {
+                    if (lane == 0) {
+                        bwagpu_alnreg *ar = &regs[c.seed_off + (c.n - 1 - k)];
+                        ar->qb = -1; ar->qe = -1;
+                        pg[k] = 1;
+                    }
+                    __syncwarp();
+                    continue;
+                }
+            }
+            lim++;
+        }
+    }
+}
+
 // the containment filter, one read per thread (:3634-3745)
 __global__ void c2a_filter_kernel(C2aOpt o, const int32_t *__restrict__ len, int32_t nseq,
                                   const bwagpu_chain *__restrict__ chains, const bwagpu_seed *__restrict__ seeds,
@@ -293,6 +391,7 @@ __global__ void c2a_filter_kernel(C2aOpt o, const int32_t *__restrict__ len, int
     const int l_query = len[l];
     const int64_t rbase = chains[c0].seed_off;
     const int64_t n_regs = chains[c1].seed_off + chains[c1].n - rbase;
+    if (n_regs > C2A_FILTER_WARP_MIN) return;            // c2a_filter_warp_kernel takes this read
     bwagpu_alnreg *av = regs + rbase;
     int lim = 0;
     for (int64_t ci = c0; ci <= c1; ++ci) {
@@ -488,6 +587,9 @@ extern "C" int bwagpu_chain2aln_device(bwagpu_ctx *ctx, const bwagpu_ext_opt *eo
     if ((rc = c2a_side(ctx, o, eo, 0, R, tot[1], RR, tot[5], RQ, tot[4], regs, d_chains, d_seeds, d_len, res))) return rc;
     BWAGPU_KERNEL_BEGIN(ctx);
     c2a_filter_kernel<<<C2A_GRID(nseq)>>>(o, d_len, nseq, d_chains, d_seeds, srt, first_chain, last_chain, regs, purged);
+    c2a_filter_warp_kernel<<<(unsigned)(((int64_t)nseq * 32 + 127) / 128), 128, 0, ctx->stream>>>(
+        o, d_len, nseq, d_chains, d_seeds, srt, first_chain, last_chain, regs, purged);
+    ctx->launches++;
     BWAGPU_KERNEL_END(ctx, BWAGPU_KERN_C2A);
     BWAGPU_CUDA(ctx, cudaGetLastError());
     res->d_regs = regs; res->n_regs = n_seeds;
