@@ -484,3 +484,61 @@ class RefEmf:
     def close(self):
         self.lib.ref_emf_close(self.h)
         self.h = None
+
+
+# ---- ERT seeding (reference src/ertseeding.cpp through oracle/refwrap/ref_ert_wrap.cpp) ------------------
+ERT_MEM_DTYPE = np.dtype([("rid", "<i4"), ("start", "<i4"), ("end", "<i4"), ("hitcount", "<i4"), ("hit_off", "<i8")])
+
+
+class RefErt:
+    """The reference's own ERT seeding on an index written by its `index -a ert` (files mmap'ed)."""
+
+    def __init__(self, prefix: str, flavor="plain", isa="sse41"):
+        self.lib = C.CDLL(os.path.join(ORACLE_DIR, "_ref", f"libref_api_{flavor}_{isa}.so"))
+        self.lib.ref_ert_open.restype = C.c_void_p
+        self.lib.ref_ert_open.argtypes = [C.c_char_p]
+        self.lib.ref_ert_close.argtypes = [C.c_void_p]
+        self.lib.ref_ert_kmer.restype = C.c_void_p
+        self.lib.ref_ert_kmer.argtypes = [C.c_void_p]
+        self.lib.ref_ert_mlt.restype = C.c_void_p
+        self.lib.ref_ert_mlt.argtypes = [C.c_void_p, C.c_void_p]
+        self.lib.ref_ert_tables.restype = C.c_void_p
+        self.lib.ref_ert_seed.argtypes = [C.c_void_p, C.c_int, C.c_float, C.c_int, C.c_int, C.c_void_p, C.c_void_p,
+                                          C.c_void_p, C.c_int, C.c_void_p, C.c_int64, C.c_void_p, C.c_int64,
+                                          C.c_void_p, C.c_void_p]
+        self.h = self.lib.ref_ert_open(prefix.encode())
+        assert self.h, f"cannot map the ERT index {prefix}"
+
+    def kmer_table(self) -> np.ndarray:
+        """The 2^30-entry k-mer table as a (lazy, mmap-backed) array."""
+        p = self.lib.ref_ert_kmer(self.h)
+        return np.ctypeslib.as_array(C.cast(p, C.POINTER(C.c_uint64)), shape=(1 << 30,))
+
+    def mlt_table(self) -> np.ndarray:
+        n = C.c_int64(0)
+        p = self.lib.ref_ert_mlt(self.h, C.byref(n))
+        return np.ctypeslib.as_array(C.cast(p, C.POINTER(C.c_uint8)), shape=(n.value,))
+
+    def tables(self):
+        """(leaf_table, code_table) of src/ertseeding.cpp:25-430 as [3][256][4] arrays."""
+        out = []
+        for which in (0, 1):
+            p = self.lib.ref_ert_tables(which)
+            out.append(np.ctypeslib.as_array(C.cast(p, C.POINTER(C.c_uint8)), shape=(3, 256, 4)).copy())
+        return out
+
+    def seed(self, flat, off, ln, min_seed_len=19, split_factor=1.5, split_width=10, max_mem_intv=20):
+        mem_cap, hit_cap = len(ln) * 16 + 64, len(ln) * 256 + 1024
+        while True:
+            mems, hits = np.zeros(mem_cap, ERT_MEM_DTYPE), np.zeros(hit_cap, np.int64)
+            mem_off, n_out = np.zeros(len(ln) + 1, np.int64), np.zeros(3, np.int64)
+            self.lib.ref_ert_seed(self.h, min_seed_len, split_factor, split_width, max_mem_intv, flat.ctypes.data,
+                                  off.ctypes.data, ln.ctypes.data, len(ln), mems.ctypes.data, mem_cap,
+                                  hits.ctypes.data, hit_cap, mem_off.ctypes.data, n_out.ctypes.data)
+            if n_out[0] <= mem_cap and n_out[1] <= hit_cap:
+                return mems[:n_out[0]].copy(), hits[:n_out[1]].copy(), mem_off
+            mem_cap, hit_cap = int(n_out[0]) + 16, int(n_out[1]) + 16
+
+    def close(self):
+        self.lib.ref_ert_close(self.h)
+        self.h = None
