@@ -11,3 +11,4 @@ from .ksw import MateSW, KSWR_DTYPE, fill_scmat  # noqa: F401
 from .extend import Extender, ext_opt, chain_opt, mem_core_device, CHAIN_DTYPE, SEED_DTYPE, REG_DTYPE  # noqa: F401
 from .emf import PerfectTable, PerfectMatch, SEED_ENTRY_DTYPE, PERFECT_DTYPE  # noqa: F401
 from .shard import shard_bounds, shard_reads, merge_smems, merge_regions  # noqa: F401
+from .ert import ErtIndex, ErtSeeding, ERT_MEM_DTYPE, mem_core_ert_device  # noqa: F401

@@ -14,6 +14,7 @@ struct ChainIn {
     const bwagpu_smem *smems; const int64_t *smem_off;      // SMEMs of read r: [smem_off[r], smem_off[r+1])
     const int64_t *coords; const int64_t *coord_off;        // SA coordinates of SMEM i: [coord_off[i], coord_off[i+1])
     const int32_t *len; int32_t nseq; int64_t n_smem;
+    int32_t per_read;                                        // mem_chain_new (ERT path): no batch-wide SMEM bound
 };
 
 __device__ __forceinline__ ChainScratch chain_scratch(bwagpu_seed *sd, WChain *ch, BtNode *nodes, int32_t *ord,
@@ -40,7 +41,7 @@ __global__ void __launch_bounds__(CHAIN_TPB, CHAIN_MINB) chain_build_kernel(Chai
     if (r >= in.nseq) return;
     cnt_chains[r] = 0; cnt_seeds[r] = 0;
     const int64_t s0 = in.smem_off[r], s1 = in.smem_off[r + 1];
-    if (s0 == s1 || in.n_smem <= 1 || in.len[r] < o.min_seed_len) return;   // :821-828 (incl. the num_smem - 1 bound)
+    if (s0 == s1 || (!in.per_read && in.n_smem <= 1) || in.len[r] < o.min_seed_len) return;   // :821-828 (incl. the num_smem - 1 bound)
     const int64_t c0 = in.coord_off[s0];
     ChainBuilder b;
     b.init(chain_scratch(sd, ch, nodes, ord, lst, c0, r));
@@ -135,10 +136,10 @@ static int chain_check(bwagpu_ctx *ctx, const bwagpu_chain_opt *o)
     return BWAGPU_OK;
 }
 
-extern "C" int bwagpu_chain_seeds_device(bwagpu_ctx *ctx, const bwagpu_chain_opt *opt, const bwagpu_smem *d_smems,
-                                         int64_t n_smem, const int64_t *d_smem_off, const int64_t *d_coords,
-                                         int64_t n_coords, const int64_t *d_coord_off, const int32_t *d_len,
-                                         int32_t nseq, int32_t max_len, bwagpu_chain_result *res)
+static int chain_device(bwagpu_ctx *ctx, const bwagpu_chain_opt *opt, const bwagpu_smem *d_smems,
+                        int64_t n_smem, const int64_t *d_smem_off, const int64_t *d_coords,
+                        int64_t n_coords, const int64_t *d_coord_off, const int32_t *d_len,
+                        int32_t nseq, int32_t max_len, bwagpu_chain_result *res, int per_read)
 {
     int rc = chain_check(ctx, opt);
     if (rc) return rc;
@@ -153,7 +154,7 @@ extern "C" int bwagpu_chain_seeds_device(bwagpu_ctx *ctx, const bwagpu_chain_opt
                    opt->max_chain_extend, opt->mask_level, opt->drop_ratio };
     RefView rv = { ctx->l_pac, ctx->n_contigs, (const int64_t *)ctx->d_contig_off, (const int32_t *)ctx->d_contig_len,
                    (const uint8_t *)ctx->d_contig_alt };
-    ChainIn in = { d_smems, d_smem_off, d_coords, d_coord_off, d_len, nseq, n_smem };
+    ChainIn in = { d_smems, d_smem_off, d_coords, d_coord_off, d_len, nseq, n_smem, per_read };
     bwagpu_seed *sd; WChain *ch; BtNode *nodes; int32_t *ord, *lst; int64_t *cnt, *offs; float *frac;
     if ((rc = bwagpu_scratch(ctx, SCR_CH_SD, (n_coords + 1) * (int64_t)sizeof(bwagpu_seed), (void **)&sd))) return rc;
     if ((rc = bwagpu_scratch(ctx, SCR_CH_CH, (n_coords + 1) * (int64_t)sizeof(WChain), (void **)&ch))) return rc;
@@ -183,6 +184,22 @@ extern "C" int bwagpu_chain_seeds_device(bwagpu_ctx *ctx, const bwagpu_chain_opt
     BWAGPU_CUDA(ctx, cudaGetLastError());
     res->d_chains = out_c; res->n_chains = tot[0]; res->d_seeds = out_s; res->n_seeds = tot[1];
     return BWAGPU_OK;
+}
+
+extern "C" int bwagpu_chain_seeds_device(bwagpu_ctx *ctx, const bwagpu_chain_opt *opt, const bwagpu_smem *d_smems,
+                                         int64_t n_smem, const int64_t *d_smem_off, const int64_t *d_coords,
+                                         int64_t n_coords, const int64_t *d_coord_off, const int32_t *d_len,
+                                         int32_t nseq, int32_t max_len, bwagpu_chain_result *res)
+{
+    return chain_device(ctx, opt, d_smems, n_smem, d_smem_off, d_coords, n_coords, d_coord_off, d_len, nseq, max_len, res, 0);
+}
+
+extern "C" int bwagpu_chain_mems_device(bwagpu_ctx *ctx, const bwagpu_chain_opt *opt, const bwagpu_smem *d_smems,
+                                        int64_t n_smem, const int64_t *d_smem_off, const int64_t *d_coords,
+                                        int64_t n_coords, const int64_t *d_coord_off, const int32_t *d_len,
+                                        int32_t nseq, int32_t max_len, bwagpu_chain_result *res)
+{
+    return chain_device(ctx, opt, d_smems, n_smem, d_smem_off, d_coords, n_coords, d_coord_off, d_len, nseq, max_len, res, 1);
 }
 
 extern "C" int bwagpu_chain_seeds(bwagpu_ctx *ctx, const bwagpu_chain_opt *opt, const bwagpu_smem *smems, int64_t n_smem,

@@ -72,6 +72,8 @@ extern "C" void bwagpu_destroy(bwagpu_ctx *ctx)
     if (ctx->d_fma_last) cudaFree(ctx->d_fma_last);
     if (ctx->d_emf_loc) cudaFree(ctx->d_emf_loc);
     if (ctx->d_emf_seed) cudaFree(ctx->d_emf_seed);
+    if (ctx->d_ert_kmer) cudaFree(ctx->d_ert_kmer);
+    if (ctx->d_ert_mlt) cudaFree(ctx->d_ert_mlt);
     cudaEventDestroy(ctx->ev_start);
     cudaEventDestroy(ctx->ev_stop);
     cudaEventDestroy(ctx->kev0);

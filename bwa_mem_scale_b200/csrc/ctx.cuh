@@ -14,6 +14,8 @@ enum { SCR_BSW_PAIRS = 0, SCR_BSW_REF, SCR_BSW_QER, SCR_BSW_WORK, SCR_MISC0, SCR
        SCR_C2A_KEYS, SCR_C2A_SRT, SCR_C2A_CHAINOF, SCR_C2A_SIZES, SCR_C2A_OFFS, SCR_C2A_REGS, SCR_C2A_PURGED,
        SCR_C2A_L, SCR_C2A_R, SCR_C2A_LQ, SCR_C2A_LR, SCR_C2A_RQ, SCR_C2A_RR, SCR_C2A_CHAINS, SCR_C2A_SEEDS,
        SCR_CH_SD, SCR_CH_CH, SCR_CH_NODES, SCR_CH_ORD, SCR_CH_CNT, SCR_CH_OFFS, SCR_CH_FRAC,
+       SCR_ERT_MEMS, SCR_ERT_HITS, SCR_ERT_KEYS, SCR_ERT_MEMS2, SCR_ERT_HITS2, SCR_ERT_KEYS2, SCR_ERT_CNT,
+       SCR_ERT_SLAB, SCR_ERT_LIST, SCR_ERT_COFF,
        BWAGPU_NSCRATCH };
 
 struct bwagpu_ctx {
@@ -45,6 +47,10 @@ struct bwagpu_ctx {
     // EMF table replica (bwagpu_emf_load)
     void *d_emf_loc, *d_emf_seed;
     bwagpu_emf_desc emf;
+    // ERT replica (bwagpu_index_load_ert): k-mer table (2^30 x 8 B) and the tree blob, reference format
+    void *d_ert_kmer, *d_ert_mlt;
+    int64_t ert_mlt_bytes;
+    int ert_mem_cap, ert_hit_cap;   // per-read slab capacities of the first ERT pass
     int seed_read_cap;          // per-read SMEM capacity of the seeding scratch (grows on overflow)
     // optional per-kernel CUDA-event timing (bwagpu_set_profiling): bench.py's roofline numbers
     int profiling;

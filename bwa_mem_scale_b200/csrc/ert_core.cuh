@@ -30,6 +30,11 @@
 #define ERT_HDI inline
 #endif
 
+// test scaffolding may define this to log which k-mer entries a walk touches
+#ifndef ERT_KMER_LOAD
+#define ERT_KMER_LOAD(ix, h) ((ix).kmer_offsets[h])
+#endif
+
 #define ERT_KMER 15
 #define ERT_XMER 4
 #define ERT_MAX_READ 151
@@ -91,6 +96,7 @@ struct ErtWalker {
     uint64_t mh_start;
     ErtMemRec *mems; int mem_cap, n_mem;
     int64_t *hits; int hit_cap, n_hit, hit_peak;
+    int watch; int64_t watch_val;
     uint32_t last_visited;          // top of the reference's `visited` path (only ever popped once, then the walk ends)
     int64_t n_bytes;                // index + text bytes touched (algorithmic traffic)
 
@@ -117,11 +123,16 @@ struct ErtWalker {
 
     ERT_HDI void push_hit(int64_t pos)
     {
-        if (n_hit < hit_cap) hits[n_hit] = pos;
+        if (n_hit == watch) watch_val = pos;
+        if ((unsigned)n_hit < (unsigned)hit_cap) hits[n_hit] = pos;
         ++n_hit;
         if (n_hit > hit_peak) hit_peak = n_hit;
     }
-    ERT_HDI int64_t hit_at(int i) const { return (i >= 0 && i < hit_cap) ? hits[i] : 0; }
+    // The walk only ever reads back the FIRST hit of the MEM it is working on.  That value is kept in a register
+    // (watch / watch_val, armed by mark() wherever the reference sets hitbeg = hits->n), so the control flow never
+    // depends on what fits the scratch slab: a read that outgrows it still counts its exact peak.
+    ERT_HDI int mark() { watch = n_hit; return n_hit; }
+    ERT_HDI int64_t hit_at(int i) const { return i == watch ? watch_val : ((unsigned)i < (unsigned)hit_cap ? hits[i] : 0); }
     ERT_HDI void push_mem(const ErtMem &m)
     {
         if (n_mem < mem_cap) {
@@ -475,7 +486,7 @@ struct ErtWalker {
     {
         int flag = 0, first_n = -1;
         const uint32_t h = hash_key(i, ERT_KMER, &flag, &first_n);
-        const uint64_t e = ix.kmer_offsets[h]; n_bytes += 8;
+        const uint64_t e = ERT_KMER_LOAD(ix, h); n_bytes += 8;
         int code = (int)(e & 3);
         const uint64_t start_addr = e >> 24;
         mh_start = 0;
@@ -543,7 +554,7 @@ struct ErtWalker {
         const uint32_t h = hash_key(i, ERT_KMER, &flag, &first_n);
         if (first_n != -1) { i += first_n + 1; return; }
         if (flag) { i = l_seq; return; }
-        const uint64_t e = ix.kmer_offsets[h]; n_bytes += 8;
+        const uint64_t e = ERT_KMER_LOAD(ix, h); n_bytes += 8;
         int code = (int)(e & 3);
         const uint8_t *t = ix.mlt + (e >> 24);
         mh_start = 0;
@@ -591,7 +602,7 @@ struct ErtWalker {
         int first_n = -1;
         const uint32_t h = hash_key(i, ERT_KMER, nullptr, &first_n);
         if (first_n != -1) { i += ERT_KMER + ERT_XMER; m.rc_end = i; return; }
-        const uint64_t e = ix.kmer_offsets[h]; n_bytes += 8;
+        const uint64_t e = ERT_KMER_LOAD(ix, h); n_bytes += 8;
         int code = (int)(e & 3);
         const uint8_t *t = ix.mlt + (e >> 24);
         ptr_width = width_of(e);
@@ -638,7 +649,7 @@ struct ErtWalker {
         int flag = 0, first_n = -1;
         int i = m.start;
         const uint32_t h = hash_key(i, ERT_KMER, &flag, &first_n);
-        const uint64_t e = ix.kmer_offsets[h]; n_bytes += 8;
+        const uint64_t e = ERT_KMER_LOAD(ix, h); n_bytes += 8;
         int code = (int)(e & 3);
         const uint8_t *t = ix.mlt + (e >> 24);
         mh_start = 0;
@@ -687,7 +698,7 @@ struct ErtWalker {
         int i = m.start;
         const int end = m.end;
         const uint32_t h = hash_key(i, ERT_KMER, &flag, &first_n);
-        const uint64_t e = ix.kmer_offsets[h]; n_bytes += 8;
+        const uint64_t e = ERT_KMER_LOAD(ix, h); n_bytes += 8;
         int code = (int)(e & 3);
         const uint8_t *t = ix.mlt + (e >> 24);
         mh_start = 0;
@@ -770,7 +781,7 @@ struct ErtWalker {
             else next_be += min_seed_len - lmemLen;
         } else if (m.fetch_leaves && m.start <= l_seq - min_seed_len) {
             n_hit -= m.hitcount;
-            m.hitbeg = n_hit;
+            m.hitbeg = mark();
             m.hitcount = 0;
             rc = false;
             right_fetch_prefix<RS>(m);
@@ -819,7 +830,7 @@ struct ErtWalker {
         if (lmemLen >= min_seed_len && (m.start < sh.prevMemStart || m.end > sh.prevMemEnd)) {
             if (m.fetch_leaves) {
                 n_hit -= m.hitcount;
-                m.hitbeg = n_hit;
+                m.hitbeg = mark();
                 m.hitcount = 0;
                 rc = false;
                 right_fetch(m);
@@ -849,7 +860,7 @@ struct ErtWalker {
             while (j <= max_j) {
                 ErtMem m; m.zero();
                 const int valid = init_mem(m, j);
-                m.hitbeg = n_hit;
+                m.hitbeg = mark();
                 int next_j = j + 1;
                 if (valid && j + 1 >= min_seed_len) {
                     int rc_i = l_seq - (j + 1);
@@ -865,7 +876,7 @@ struct ErtWalker {
             while (j >= min_j) {
                 ErtMem m; m.zero();
                 const int valid = init_mem(m, j);
-                m.hitbeg = n_hit;
+                m.hitbeg = mark();
                 if (valid && j + 1 >= min_seed_len) {
                     int rc_i = l_seq - (j + 1);
                     rc = true;
@@ -887,7 +898,7 @@ struct ErtWalker {
         clear_lep();
         while (i < l_seq) {
             ErtMem rm; rm.zero();
-            rm.start = i; rm.forward = 1; rm.hitbeg = n_hit;
+            rm.start = i; rm.forward = 1; rm.hitbeg = mark();
             sh.curr_pivot = rm.start;
             rc = false;
             right_extend<false>(i, rm);
@@ -925,7 +936,7 @@ struct ErtWalker {
         int i = start;
         clear_lep();
         ErtMem rm; rm.zero();
-        rm.start = i; rm.forward = 1; rm.hitbeg = n_hit;
+        rm.start = i; rm.forward = 1; rm.hitbeg = mark();
         sh.prev_pivot = (rm.start >= c_pivot) ? p_pivot : pp_pivot;
         rc = false;
         limit = lim;
@@ -950,7 +961,7 @@ struct ErtWalker {
         limit = lim;
         while (i < l_seq) {
             ErtMem rm; rm.zero();
-            rm.start = i; rm.forward = 1; rm.hitbeg = n_hit;
+            rm.start = i; rm.forward = 1; rm.hitbeg = mark();
             rc = false;
             right_extend_last(i, rm);
             if (rm.hitcount > 0 && !rm.skip_ref_fetch) {
@@ -981,7 +992,7 @@ struct ErtWalker {
     // the per-read body of mem_kernel1_core_ert (src/bwamem.cpp:1124-1191), before the sort
     ERT_HD void seed_read(const ErtOpt &o)
     {
-        n_mem = 0; n_hit = 0; hit_peak = 0; n_bytes = 0;
+        n_mem = 0; n_hit = 0; hit_peak = 0; n_bytes = 0; watch = -1; watch_val = 0;
         num_hits = 0; limit = 0; ptr_width = 2; mh_start = 0; next_lep = 0; last_visited = 0;
         min_seed_len = o.min_seed_len;
         bool has_n = false;

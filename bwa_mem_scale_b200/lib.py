@@ -68,6 +68,13 @@ class SeedResult(C.Structure):
                 ("n_cp_records", C.c_int64), ("n_lf_steps", C.c_int64), ("d_smem_off", C.c_void_p)]
 
 
+class ErtResult(C.Structure):
+    """bwagpu_ert_result"""
+    _fields_ = [("d_smems", C.c_void_p), ("n_smem", C.c_int64), ("d_coords", C.c_void_p),
+                ("n_coords", C.c_int64), ("d_coord_off", C.c_void_p), ("d_smem_off", C.c_void_p),
+                ("n_index_bytes", C.c_int64), ("n_hits", C.c_int64), ("n_retry_reads", C.c_int64)]
+
+
 class ChainOpt(C.Structure):
     """bwagpu_chain_opt — the mem_opt_t fields chaining reads (reference src/bwamem.h:89-124)."""
     _fields_ = [(n, C.c_int32) for n in ("w", "max_chain_gap", "max_occ", "min_seed_len", "min_chain_weight",
@@ -110,6 +117,16 @@ _SIGS = {
     "bwagpu_chain_seeds_device": (C.c_int, [C.c_void_p, C.POINTER(ChainOpt), C.c_void_p, C.c_int64, C.c_void_p,
                                             C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32,
                                             C.POINTER(ChainResult)]),
+    "bwagpu_chain_mems_device": (C.c_int, [C.c_void_p, C.POINTER(ChainOpt), C.c_void_p, C.c_int64, C.c_void_p,
+                                           C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32,
+                                           C.POINTER(ChainResult)]),
+    "bwagpu_index_load_ert": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_int64]),
+    "bwagpu_index_unload_ert": (C.c_int, [C.c_void_p]),
+    "bwagpu_seed_ert": (C.c_int, [C.c_void_p, C.POINTER(SeedOpt), C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                  C.c_int32, C.c_void_p, C.c_int64, C.c_void_p, C.c_int64, C.c_void_p,
+                                  C.POINTER(C.c_int64), C.POINTER(C.c_int64)]),
+    "bwagpu_seed_ert_device": (C.c_int, [C.c_void_p, C.POINTER(SeedOpt), C.c_void_p, C.c_void_p, C.c_void_p,
+                                         C.c_void_p, C.c_int32, C.c_int32, C.POINTER(ErtResult)]),
     "bwagpu_chain2aln": (C.c_int, [C.c_void_p, C.POINTER(ExtOpt), C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32,
                                    C.c_void_p, C.c_int64, C.c_void_p, C.c_int64, C.c_void_p]),
     "bwagpu_chain2aln_device": (C.c_int, [C.c_void_p, C.POINTER(ExtOpt), C.c_void_p, C.c_void_p, C.c_void_p,

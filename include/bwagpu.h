@@ -46,6 +46,7 @@ int bwagpu_timer_stop(bwagpu_ctx *ctx, float *elapsed_ms);   /* records, synchro
  * leave it off when measuring whole-step throughput).  set_profiling also clears the counters. */
 enum { BWAGPU_KERN_SEED_COLLECT = 0, BWAGPU_KERN_SEED_SORT = 1, BWAGPU_KERN_SA_WALK = 2,
        BWAGPU_KERN_BSW = 3, BWAGPU_KERN_BSW_GENERIC = 4, BWAGPU_KERN_FMA_BUILD = 5, BWAGPU_KERN_KSW = 6, BWAGPU_KERN_C2A = 7, BWAGPU_KERN_CHAIN = 8, BWAGPU_KERN_EMF = 9,
+       BWAGPU_KERN_ERT_SEED = 10, BWAGPU_KERN_ERT_EMIT = 11,
        BWAGPU_KERN_N = 16 };
 int bwagpu_set_profiling(bwagpu_ctx *ctx, int on);
 int bwagpu_kernel_time(const bwagpu_ctx *ctx, int which, double *ms, int64_t *launches);
@@ -174,6 +175,15 @@ int bwagpu_chain_seeds_device(bwagpu_ctx *ctx, const bwagpu_chain_opt *opt, cons
                               int64_t n_coords, const int64_t *d_coord_off, const int32_t *d_len,
                               int32_t nseq, int32_t max_len, bwagpu_chain_result *res);
 
+/* The ERT path's chaining: mem_chain_new + mem_chain_flt per read (reference src/bwamem.cpp:960-1050, 1194-1202),
+ * over the output of bwagpu_seed_ert_device.  Same B-tree / merge / filter code as bwagpu_chain_seeds_device; the
+ * only difference is that mem_chain_new runs read by read, so the batch-wide `pos < num_smem - 1` bound of
+ * mem_chain_seeds (:819) does not apply. */
+int bwagpu_chain_mems_device(bwagpu_ctx *ctx, const bwagpu_chain_opt *opt, const bwagpu_smem *d_smems,
+                             int64_t n_smem, const int64_t *d_smem_off, const int64_t *d_coords,
+                             int64_t n_coords, const int64_t *d_coord_off, const int32_t *d_len,
+                             int32_t nseq, int32_t max_len, bwagpu_chain_result *res);
+
 /* regs[n_seeds]: the av_v records in creation order — region of the k-th best seed (descending
  * score, ties by descending index) of chain c at regs[c.seed_off + k]; purged regions have
  * qb = qe = -1 exactly as the reference leaves them.  HOST buffers. */
@@ -299,6 +309,52 @@ typedef struct {
 int bwagpu_seed_fm_device(bwagpu_ctx *ctx, const bwagpu_seed_opt *opt, const uint8_t *d_reads,
                           const int64_t *d_off, const int32_t *d_len, const uint8_t *d_skip,
                           int32_t nseq, int32_t max_len, bwagpu_seed_result *res);
+
+/* ---- S1': ERT seeding --------------------------------------------------------------------------
+ * Replaces the per-read seeding body of mem_kernel1_core_ert (reference src/bwamem.cpp:1124-1193):
+ * get_seeds[_prefix] -> reseed[_prefix] -> last (src/ertseeding.cpp:2925/3062, 3200/3315, 3425) and the
+ * ks_introsort(mem_smem_sort_lt) that follows.  The index is the one `index -a ert` writes:
+ * <prefix>.kmer_table (2^30 x 8 B, fmi->kmer_offsets) and <prefix>.mlt_table (fmi->mlt_table),
+ * uploaded verbatim; the text is the replica of bwagpu_index_load_ref.  Reads longer than 151 bases are
+ * rejected with BWAGPU_ERR_RANGE (the reference asserts len <= READ_LEN, bwamem.cpp:1135), and
+ * min_seed_len must be >= 19 (k-mer + x-mer; the reference asserts below that, ertseeding.cpp:2847).
+ *
+ * kmer_offsets: the dense table, or NULL with the non-zero entries given as (sparse_idx, sparse_val) —
+ * absent k-mers are all-zero entries (type INVALID), so both forms load the same table. */
+int bwagpu_index_load_ert(bwagpu_ctx *ctx, const uint64_t *kmer_offsets, const uint32_t *sparse_idx,
+                          const uint64_t *sparse_val, int64_t n_sparse, const uint8_t *mlt_table,
+                          int64_t mlt_bytes);
+int bwagpu_index_unload_ert(bwagpu_ctx *ctx);
+
+/* One maximal exact match of a read: mem_t {start, end, hitcount} (src/ertseeding.h:62-77) with hitbeg
+ * rebased into the batch-wide hit list.  hits[] holds, for every MEM, the coordinate mem_chain_new
+ * derives from each of its hits (src/bwamem.cpp:991-998: forward / re-fetched hits as they are, hits of
+ * backward searches mirrored with the end correction), i.e. s.rbeg in the forward-reverse text; a host
+ * shim passes them on as mem_t{forward = 1, hitbeg = hit_off} + u64v hits. */
+typedef struct { int32_t rid, start, end, hitcount; int64_t hit_off; } bwagpu_ert_mem;
+
+/* HOST buffers.  MEMs come out read by read in the reference's sorted order (start, end ascending;
+ * ties as its unstable introsort leaves them).  mem_off[nseq + 1] (may be NULL) = first MEM of each read.
+ * The full counts are always reported; BWAGPU_ERR_RANGE (nothing written) when a capacity is too small. */
+int bwagpu_seed_ert(bwagpu_ctx *ctx, const bwagpu_seed_opt *opt, const uint8_t *enc_reads, const int64_t *off,
+                    const int32_t *len, const uint8_t *skip, int32_t nseq, bwagpu_ert_mem *mems, int64_t mems_cap,
+                    int64_t *hits, int64_t hits_cap, int64_t *mem_off, int64_t *n_mems, int64_t *n_hits);
+
+/* Device-resident form, shaped like bwagpu_seed_fm_device so that chaining follows without leaving HBM:
+ * d_smems[i] = {rid, m = start, n = end - 1, k = first coordinate index, l = 0, s = hitcount} and the
+ * coordinates are the ones mem_chain_new visits (k = 0, step, 2*step ...; at most opt->max_occ per MEM). */
+typedef struct {
+    const bwagpu_smem *d_smems; int64_t n_smem;
+    const int64_t *d_coords;    int64_t n_coords;
+    const int64_t *d_coord_off;          /* [n_smem + 1] */
+    const int64_t *d_smem_off;           /* [nseq + 1] */
+    int64_t n_index_bytes;               /* k-mer entries, tree bytes, hit records and text bytes read */
+    int64_t n_hits;                      /* sum of hitcount over the MEMs */
+    int64_t n_retry_reads;               /* reads re-run with larger scratch slabs */
+} bwagpu_ert_result;
+int bwagpu_seed_ert_device(bwagpu_ctx *ctx, const bwagpu_seed_opt *opt, const uint8_t *d_reads,
+                           const int64_t *d_off, const int32_t *d_len, const uint8_t *d_skip,
+                           int32_t nseq, int32_t max_len, bwagpu_ert_result *res);
 
 /* ---- S0: EMF, the exact-match filter -----------------------------------------------------------
  * Replaces the per-read loop around find_perfect_match_entry in worker_bwt / mem_kernel1_core

@@ -13,6 +13,7 @@
 #include "bwamem.h"
 #include "FMI_search.h"
 #include "bwa.h"
+#include "ertseeding.h"
 #include <cstdio>
 
 // globals main.cpp owns upstream (src/main.cpp:48)
@@ -131,6 +132,7 @@ struct ref_mem_ctx {
     uint8_t *ref_string;
     mem_cache mmc;
     mem_seed_t *seedBuf;
+    int use_ert;                 // seeding + chaining through mem_kernel1_core_ert (src/bwamem.cpp:1052-1207)
 };
 
 void *ref_mem_open(const char *prefix)
@@ -201,6 +203,14 @@ void *ref_mem_clone(void *h0)
     return c;
 }
 
+// switch this worker to the ERT path: the k-mer table / tree blob come from ref_ert_open (ref_ert_wrap.cpp)
+void ref_mem_use_ert(void *h, uint64_t *kmer_offsets, uint8_t *mlt_table)
+{
+    ref_mem_ctx *c = (ref_mem_ctx *)h;
+    c->fmi->kmer_offsets = kmer_offsets; c->fmi->mlt_table = mlt_table;
+    c->use_ert = kmer_offsets != nullptr;
+}
+
 int64_t ref_mem_l_pac(void *h) { return ((ref_mem_ctx *)h)->fmi->idx->bns->l_pac; }
 int ref_mem_n_seqs(void *h) { return ((ref_mem_ctx *)h)->fmi->idx->bns->n_seqs; }
 void ref_mem_contigs(void *h, int64_t *offset, int32_t *len)
@@ -245,6 +255,13 @@ int ref_mem_core(void *h, const int32_t *opt_i, const float *opt_f, int64_t max_
         mem_chain_v *chain_ar = (mem_chain_v *)malloc(nb * sizeof(mem_chain_v));
         mem_alnreg_v *av = (mem_alnreg_v *)calloc(nb, sizeof(mem_alnreg_v));
         memset(c->seedBuf, 0, sizeof(mem_seed_t) * (size_t)BATCH_SIZE * AVG_SEEDS_PER_READ);
+        if (c->use_ert) {
+            mem_v smems; kv_init(smems); kv_resize(mem_t, smems, 4096);
+            u64v hits; kv_init(hits); kv_resize(uint64_t, hits, 1 << 20);
+            mem_kernel1_core_ert(c->fmi, opt, seqs, nb, chain_ar, c->seedBuf, (int64_t)BATCH_SIZE * AVG_SEEDS_PER_READ,
+                                 c->ref_string, &smems, &hits, 0);
+            kv_destroy(smems); kv_destroy(hits);
+        } else
         mem_kernel1_core(c->fmi, opt, seqs, nb, chain_ar, c->seedBuf, (int64_t)BATCH_SIZE * AVG_SEEDS_PER_READ, &c->mmc, 0);
         const int64_t chain_base = nc;
         for (int i = 0; i < nb; ++i)

@@ -1,9 +1,12 @@
 // TEST SCAFFOLDING — runs the per-thread ERT seeding code of the CUDA kernels
 // (bwa_mem_scale_b200/csrc/ert_core.cuh) on the host, one "thread" (= read) at a time, so that it can be
 // checked against the reference tap without a GPU.  Never part of libbwagpu.so.
+#include <cstdint>
 #include <cstdlib>
 #include <cstring>
 #include <vector>
+static std::vector<uint32_t> *g_touched = nullptr;      // k-mer entries read by the walks (golden fixture maker)
+#define ERT_KMER_LOAD(ix, h) ((g_touched ? g_touched->push_back(h) : (void)0), (ix).kmer_offsets[h])
 #include "../../bwa_mem_scale_b200/csrc/ert_core.cuh"
 
 struct hs_mem { int32_t rid, start, end, hitcount; int64_t hit_off; };
@@ -57,4 +60,15 @@ extern "C" int hostsim_ert_seed(const uint64_t *kmer, const uint8_t *mlt, const 
     mem_off[nseq] = nm;
     n_out[0] = nm; n_out[1] = nh; n_out[2] = bytes;
     return (nm <= mem_cap && nh <= hit_cap) ? 0 : -1;
+}
+
+// start / stop logging the k-mer table indices the walks read; stop copies up to cap of them and returns the count
+extern "C" void hostsim_ert_log_start(void) { delete g_touched; g_touched = new std::vector<uint32_t>(); }
+extern "C" int64_t hostsim_ert_log_stop(uint32_t *out, int64_t cap)
+{
+    if (!g_touched) return 0;
+    const int64_t n = (int64_t)g_touched->size();
+    for (int64_t i = 0; i < n && i < cap; ++i) out[i] = (*g_touched)[i];
+    delete g_touched; g_touched = nullptr;
+    return n;
 }

@@ -24,7 +24,29 @@ def load():
     lib.hostsim_sa_lookup.restype = C.c_int64
     lib.hostsim_chain_seeds.restype = C.c_int64
     lib.hostsim_ert_seed.restype = C.c_int
+    lib.hostsim_ert_log_stop.restype = C.c_int64
+    lib.hostsim_ert_log_stop.argtypes = [C.c_void_p, C.c_int64]
     lib.hostsim_ert_seed.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_float, C.c_int, C.c_int,
                                      C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_int64, C.c_void_p,
                                      C.c_int64, C.c_void_p, C.c_void_p, C.c_int, C.c_int]
     return lib
+
+
+def ert_seed(lib, kmer, mlt, ref_string, flat, off, ln, min_seed_len=19, split_factor=1.5, split_width=10,
+             max_mem_intv=20, per_read_mems=16, per_read_hits=128):
+    """The ERT walker of the CUDA kernels (csrc/ert_core.cuh) run read by read on the host: (mems, hits, mem_off)
+    in the layout of oracle_lib.RefErt.seed.  `kmer` is the dense 2^30-entry table (may be a memory map)."""
+    import numpy as np
+    from oracle_lib import ERT_MEM_DTYPE
+    mem_cap, hit_cap = len(ln) * 16 + 64, len(ln) * 256 + 1024
+    while True:
+        mems, hits = np.zeros(mem_cap, ERT_MEM_DTYPE), np.zeros(hit_cap, np.int64)
+        mem_off, n_out = np.zeros(len(ln) + 1, np.int64), np.zeros(3, np.int64)
+        lib.hostsim_ert_seed(kmer.ctypes.data, mlt.ctypes.data, ref_string.ctypes.data, len(ref_string) // 2,
+                             min_seed_len, split_factor, split_width, max_mem_intv, flat.ctypes.data,
+                             off.ctypes.data, ln.ctypes.data, len(ln), mems.ctypes.data, mem_cap, hits.ctypes.data,
+                             hit_cap, mem_off.ctypes.data, n_out.ctypes.data, per_read_mems, per_read_hits)
+        if n_out[0] <= mem_cap and n_out[1] <= hit_cap:
+            ert_seed.last_bytes = int(n_out[2])
+            return mems[:n_out[0]].copy(), hits[:n_out[1]].copy(), mem_off
+        mem_cap, hit_cap = int(n_out[0]) + 16, int(n_out[1]) + 16

@@ -365,6 +365,16 @@ class RefMem:
         self.contig_off, self.contig_len = np.zeros(n, np.int64), np.zeros(n, np.int32)
         self.lib.ref_mem_contigs(self.h, self.contig_off.ctypes.data, self.contig_len.ctypes.data)
 
+    def use_ert(self, ref_ert):
+        """Switch seeding + chaining to mem_kernel1_core_ert over the tables of a RefErt (None: back to FM)."""
+        self.lib.ref_mem_use_ert.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+        if ref_ert is None:
+            self.lib.ref_mem_use_ert(self.h, None, None)
+        else:
+            n = C.c_int64(0)
+            self.lib.ref_mem_use_ert(self.h, ref_ert.lib.ref_ert_kmer(ref_ert.h), ref_ert.lib.ref_ert_mlt(ref_ert.h, C.byref(n)))
+        self._ert = ref_ert
+
     def clone(self):
         """Another worker on the same loaded index (own scratch arenas), for multi-threaded baselines."""
         return RefMem(*self._args, _parent=self)
