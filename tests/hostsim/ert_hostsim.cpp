@@ -72,3 +72,19 @@ extern "C" int64_t hostsim_ert_log_stop(uint32_t *out, int64_t cap)
     delete g_touched; g_touched = nullptr;
     return n;
 }
+
+// k-mer table low bits from occurrence counts (csrc/ert_build.cuh): out[i] = lep | hits << 16 (hits capped at 2^40)
+#include "../../bwa_mem_scale_b200/csrc/ert_build.cuh"
+extern "C" void hostsim_ert_kmer_lep(const bwagpu_fm_index_desc *d, const uint32_t *idx, int64_t n, uint64_t *out)
+{
+    FmView f;
+    f.fma_all = f.fma_last = nullptr;
+    f.cp_occ = (const int64_t *)d->cp_occ; f.sa_ms_byte = d->sa_ms_byte; f.sa_ls_word = d->sa_ls_word;
+    memcpy(f.count, d->count, sizeof f.count);
+    f.sentinel_index = d->sentinel_index; f.ref_seq_len = d->reference_seq_len;
+    for (int64_t i = 0; i < n; ++i) {
+        int64_t hits;
+        const uint32_t lep = ert_kmer_lep(f, idx[i], &hits);
+        out[i] = (uint64_t)lep | ((uint64_t)hits << 16);
+    }
+}

@@ -14,6 +14,7 @@ OUT = os.path.join(ROOT, "tests", "hostsim", "_build", "libhostsim.so")
 def load():
     deps = [SRC, SRC2, SRC3, os.path.join(ROOT, "bwa_mem_scale_b200", "csrc", "fmi_core.cuh"),
             os.path.join(ROOT, "bwa_mem_scale_b200", "csrc", "ert_core.cuh"),
+            os.path.join(ROOT, "bwa_mem_scale_b200", "csrc", "ert_build.cuh"),
             os.path.join(ROOT, "bwa_mem_scale_b200", "csrc", "chain_core.cuh"),
             os.path.join(ROOT, "include", "bwagpu.h")]
     if not os.path.exists(OUT) or any(os.path.getmtime(d) > os.path.getmtime(OUT) for d in deps):
