@@ -348,10 +348,20 @@ def bench_seed(args, rank, world):
 # configuration (100 Mbp, 1 M reads, FMA on): profiles/r01_ncu_mem_kernels_summary.txt
 NCU_SEED_COLLECT_TRAFFIC = int(61.099131e9 + 10.094755e9)
 KERNELS = {0: "seed_collect", 1: "seed_sort", 2: "sa_walk", 3: "bsw", 4: "bsw_generic", 7: "chain2aln", 8: "chain_seeds",
-           9: "emf_probe"}
+           9: "emf_probe", 10: "ert_seed", 11: "ert_emit"}
 
 
-def cpu_mem_core(prefix, reads, threads):
+def ert_bench_data():
+    """Reference-built ERT index of the small bench genome (scripts/make_ert_bench_data.py): the genome, the k-mer
+    table entries of the k-mers that occur and the tree blob.  The entries of absent k-mers are computed on the
+    device (bwagpu_index_complete_ert)."""
+    p = os.path.join(ROOT, "bench_data", "ert_small_genome.npz")
+    if not os.path.exists(p):
+        raise SystemExit("bench.py --ert 1 needs bench_data/ert_small_genome.npz (scripts/make_ert_bench_data.py)")
+    return np.load(p)
+
+
+def cpu_mem_core(prefix, reads, threads, ert=None):
     """CPU baseline for seed+extend: the REFERENCE's own mem_kernel1_core + mem_chain2aln_across_reads_V2
     (oracle/_ref tap library) over `reads`, one worker per host thread on a shared index.  Returns
     (seconds, kind) — timing excludes loading the index."""
@@ -360,6 +370,9 @@ def cpu_mem_core(prefix, reads, threads):
     isa = "avx2" if os.path.exists(os.path.join(ol.ORACLE_DIR, "_ref", "libref_api_plain_avx2.so")) else "sse41"
     rm0 = ol.RefMem(prefix, "plain", isa)
     workers = [rm0] + [rm0.clone() for _ in range(threads - 1)]
+    if ert is not None:                      # (dense k-mer table, tree blob): mem_kernel1_core_ert instead
+        for w in workers:
+            w.use_ert_tables(*ert)
     chunks = [c for c in np.array_split(np.arange(len(reads)), threads) if len(c)]
     o = ol.mem_opt()
 
@@ -453,11 +466,23 @@ def bench_mem(args, rank, world):
     banded-SW extension -> alignment regions, everything on the device."""
     from bwa_mem_scale_b200 import (Context, Extender, FMI_search, REG_DTYPE, chain_opt, ext_opt, fmindex,
                                     mem_core_device, pack_reads, seed_opt)
-    ref, idx, reads = seed_inputs(args, rank)
+    ert_data = None
+    if args.ert:
+        from bwa_mem_scale_b200 import ErtIndex, ErtSeeding, mem_core_ert_device, synth
+        ert_data = ert_bench_data()
+        ref = np.ascontiguousarray(ert_data["ref"])
+        idx = fmindex.build_fm_index(ref)
+        reads, _, _ = synth.simulate_reads(ref, args.reads, seed=500 + rank, err=0.01)
+        args.ref_mbp = len(ref) / 1e6
+    else:
+        ref, idx, reads = seed_inputs(args, rank)
     n = len(reads)
-    cfg = {"workload": f"seed+extend, BASELINE config 2 shape: {args.ref_mbp:g} Mbp synthetic reference (10% repeats), "
-                       f"{n} x 151 bp SE reads/GPU, 1% substitutions, FM-index" + (" + FMA smem tables" if args.fma else "")
-                       + "; reads -> SMEMs -> SA -> chains -> banded SW (both band tries) -> alignment regions",
+    cfg = {"workload": (f"seed+extend with ERT seeding: {args.ref_mbp:g} Mbp synthetic reference (40% repeats; the ERT index is "
+                        f"the reference's own `index -a ert` build), {n} x 151 bp SE reads/GPU, 1% substitutions; reads -> "
+                        "ERT MEMs + hits -> chains -> banded SW (both band tries) -> alignment regions" if args.ert else
+                        f"seed+extend, BASELINE config 2 shape: {args.ref_mbp:g} Mbp synthetic reference (10% repeats), "
+                        f"{n} x 151 bp SE reads/GPU, 1% substitutions, FM-index" + (" + FMA smem tables" if args.fma else "")
+                        + "; reads -> SMEMs -> SA -> chains -> banded SW (both band tries) -> alignment regions"),
            "reads_per_gpu": n, "ref_mbp": args.ref_mbp,
            "l2_policy": "index (%.0f MB) + reference text + reads larger than L2" % (idx.nbytes() / 1e6)
            if idx.nbytes() > 126e6 else "flush between steps"}
@@ -467,14 +492,25 @@ def bench_mem(args, rank, world):
         import tempfile
         thr = cpu_threads()
         sample = reads[: min(n, 32000 * thr)]
+        tables = None
+        if args.ert:
+            # input preparation only (not timed): the dense k-mer table is completed on the device and read back
+            from bwa_mem_scale_b200 import Context, Extender, FMI_search
+            c0 = Context(0)
+            FMI_search(idx, ctx=c0)
+            Extender(fmindex.text_with_revcomp(ref), len(ref), [0], [len(ref)], ctx=c0)
+            e0 = ErtSeeding(ErtIndex(ert_data["mlt_table"], sparse_idx=ert_data["kmer_idx"], sparse_val=ert_data["kmer_val"]), c0)
+            e0.complete_from_fm()
+            tables = (e0.dense_table(), np.ascontiguousarray(ert_data["mlt_table"]))
+            c0.close()
         with tempfile.TemporaryDirectory() as td:
             prefix = os.path.join(td, "ref")
             fmindex.write_index_files(prefix, ref, idx)
             for _ in range(min(args.warmup, 1)):
-                cpu_mem_core(prefix, sample[: 200 * thr], thr)
+                cpu_mem_core(prefix, sample[: 200 * thr], thr, tables)
             t, kind = 0.0, ""
             for _ in range(args.steps):
-                dt, kind = cpu_mem_core(prefix, sample, thr)
+                dt, kind = cpu_mem_core(prefix, sample, thr, tables)
                 t += dt
         v = len(sample) * args.steps / t
         return {"impl": "reference", "metric": "aligned reads/s (151bp SE, seed+extend)", "value": v, "unit": "reads/s",
@@ -483,7 +519,8 @@ def bench_mem(args, rank, world):
                 "config": cfg,
                 "cpu_baseline": {"value": v, "unit": "reads/s", "cores": thr, "kind": "reference",
                                  "sample": f"{len(sample)} reads of the same set per step, {kind}, "
-                                           "mem_kernel1_core + mem_chain2aln_across_reads_V2"},
+                                           + ("mem_kernel1_core_ert" if args.ert else "mem_kernel1_core")
+                                           + " + mem_chain2aln_across_reads_V2"},
                 "e2e": {"value": v, "unit": "reads/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     local = int(os.environ.get("LOCAL_RANK", rank))
     if args.contexts > 1:
@@ -494,6 +531,19 @@ def bench_mem(args, rank, world):
         fmi.build_fma()
     ext = Extender(fmindex.text_with_revcomp(ref), len(ref), [0], [len(ref)], ctx=ctx)
     so, co, eo = seed_opt(), chain_opt(), ext_opt()
+    ert = None
+    if args.ert:
+        t0 = time.perf_counter()
+        ert = ErtSeeding(ErtIndex(ert_data["mlt_table"], sparse_idx=ert_data["kmer_idx"], sparse_val=ert_data["kmer_val"]), ctx)
+        ert.complete_from_fm()
+        cfg["ert_index"] = {"kmer_table_gb": 8.59, "mlt_table_mb": ert_data["mlt_table"].nbytes / 1e6,
+                            "kmers_present": int(len(ert_data["kmer_idx"])), "load_and_complete_s": time.perf_counter() - t0}
+
+    def core(dr, do, dl):
+        if ert is not None:
+            return mem_core_ert_device(ert, ext, so, co, eo, dr, do, dl, n, 151, emf, d_emf)
+        return mem_core_device(fmi, ext, so, co, eo, dr, do, dl, n, 151, emf, d_emf)
+
     flat, off, ln = pack_reads(reads)
     d_reads, d_off, d_len = ctx.upload(flat), ctx.upload(off), ctx.upload(ln)
     flush = ctx.malloc(256 << 20) if "flush" in cfg["l2_policy"] else None
@@ -508,7 +558,7 @@ def bench_mem(args, rank, world):
         d_emf = (ctx.malloc(4 * n), ctx.malloc(8 * n), ctx.malloc(n))
 
     def step():
-        return mem_core_device(fmi, ext, so, co, eo, d_reads, d_off, d_len, n, 151, emf, d_emf)
+        return core(d_reads, d_off, d_len)
 
     for _ in range(args.warmup):
         sres, cres, ares = step()
@@ -546,7 +596,7 @@ def bench_mem(args, rank, world):
         ctx.h2d_fence()
         if k + 1 < args.steps:
             copy_in(d_in[(k + 1) % 2])
-        sres, cres, ares = mem_core_device(fmi, ext, so, co, eo, cur[0], cur[1], cur[2], n, 151, emf, d_emf)
+        sres, cres, ares = core(cur[0], cur[1], cur[2])
         out = outs[k % 2][:ares.n_regs] if ares.n_regs <= cap else np.zeros(ares.n_regs, REG_DTYPE)
         ctx.d2h_overlap(out, ares.d_regs)
     ctx.copy_synchronize()
@@ -562,8 +612,15 @@ def bench_mem(args, rank, world):
     if rank != 0:
         return None
     pk, pk_kind = peaks()
-    k_ms, k_n = ktimes["seed_collect"]
-    alg_bytes = sres.n_cp_records * 64
+    if args.ert:
+        # ert_seed_kernel: algorithmic bytes = k-mer entries (8 B), tree / hit records and text bytes the walks read,
+        # counted by the kernel itself.  The walk is a chain of dependent 1-8 byte loads, so the HBM fraction is tiny by
+        # construction; the figure that matters is reads in flight x load latency
+        k_ms, k_n = ktimes["ert_seed"]
+        alg_bytes = sres.n_index_bytes
+    else:
+        k_ms, k_n = ktimes["seed_collect"]
+        alg_bytes = sres.n_cp_records * 64
     ach = alg_bytes / (k_ms / max(k_n, 1) * 1e-3) / 1e9
     nprof = max(min(args.steps, 2), 1)
     traffic = None
@@ -578,11 +635,14 @@ def bench_mem(args, rank, world):
            "e2e": {"value": n * world * args.steps / e2e_s, "unit": "reads/s",
                    "h2d_bytes_per_step": int(flat.nbytes + off.nbytes + ln.nbytes),
                    "d2h_bytes_per_step": int(ares.n_regs * REG_DTYPE.itemsize)},
-           "roofline": {"bound": "hbm", "kernel": "seed_collect_kernel", "achieved": ach, "peak": pk["hbm_gbs"],
-                        "unit": "GB/s", "frac": ach / pk["hbm_gbs"], "traffic": traffic, "algorithmic_bytes": int(alg_bytes),
-                        "peak_kind": pk_kind, "kernel_ms": k_ms / max(k_n, 1),
-                        "kernel_ms_per_step": {name: t / nprof for name, (t, c) in ktimes.items()},
-                        "bext_per_read": sres.n_ext / n, "cp_records_per_read": sres.n_cp_records / n},
+           "roofline": dict({"bound": "hbm", "kernel": "ert_seed_kernel" if args.ert else "seed_collect_kernel",
+                             "achieved": ach, "peak": pk["hbm_gbs"],
+                             "unit": "GB/s", "frac": ach / pk["hbm_gbs"], "traffic": traffic, "algorithmic_bytes": int(alg_bytes),
+                             "peak_kind": pk_kind, "kernel_ms": k_ms / max(k_n, 1),
+                             "kernel_ms_per_step": {name: t / nprof for name, (t, c) in ktimes.items()}},
+                            **({"index_bytes_per_read": sres.n_index_bytes / n, "hits_per_read": sres.n_hits / n,
+                                "reads_rerun_with_larger_scratch": int(sres.n_retry_reads)} if args.ert else
+                               {"bext_per_read": sres.n_ext / n, "cp_records_per_read": sres.n_cp_records / n})),
            "work": {"smem_per_read": sres.n_smem / n, "sa_rows_per_read": sres.n_coords / n,
                     "chains_per_read": cres.n_chains / n, "regions_per_read": ares.n_regs / n,
                     "regions_purged_per_read": purged / n, "sw_jobs_per_read": (ares.n_left + ares.n_right) / n,
@@ -599,10 +659,12 @@ def bench_mem(args, rank, world):
         with tempfile.TemporaryDirectory() as td:
             prefix = os.path.join(td, "ref")
             fmindex.write_index_files(prefix, ref, idx)
-            dt, kind = cpu_mem_core(prefix, sample, thr)
+            tables = (ert.dense_table(), np.ascontiguousarray(ert_data["mlt_table"])) if args.ert else None
+            dt, kind = cpu_mem_core(prefix, sample, thr, tables)
         res["cpu_baseline"] = {"value": len(sample) / dt, "unit": "reads/s", "cores": thr, "kind": "reference",
-                               "sample": f"{len(sample)} reads of the same set, {kind}, mem_kernel1_core + "
-                                         f"mem_chain2aln_across_reads_V2, {dt:.1f}s"}
+                               "sample": f"{len(sample)} reads of the same set, {kind}, "
+                                         + ("mem_kernel1_core_ert" if args.ert else "mem_kernel1_core")
+                                         + f" + mem_chain2aln_across_reads_V2, {dt:.1f}s"}
     return res
 
 # ------------------------------------------------------------------------------------------------
@@ -746,6 +808,7 @@ def main():
     ap.add_argument("--band", type=int, default=100)
     ap.add_argument("--kind", type=int, default=16, choices=[8, 16])
     ap.add_argument("--fma", type=int, default=1, help="use the FMA smem tables (config 2)")
+    ap.add_argument("--ert", type=int, default=0, help="mem workload: ERT seeding on the small reference-built index in bench_data/")
     ap.add_argument("--emf", type=int, default=0, help="mem workload: exact-match filter in front (table built on the host)")
     ap.add_argument("--exact-frac", type=float, default=None, help="fraction of error-free reads (default: what 1%% substitutions give)")
     ap.add_argument("--contexts", type=int, default=1, help="mem workload: contexts (streams) per GPU")

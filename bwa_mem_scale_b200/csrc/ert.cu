@@ -14,6 +14,7 @@
 #include <stdlib.h>
 #include "ctx.cuh"
 #include "ert_core.cuh"
+#include "ert_build.cuh"
 
 #define ERT_TPB 128
 #define ERT_KMER_ENTRIES (1LL << 30)
@@ -147,6 +148,80 @@ extern "C" int bwagpu_index_load_ert(bwagpu_ctx *ctx, const uint64_t *kmer_offse
     BWAGPU_CUDA(ctx, cudaMemcpyAsync(ctx->d_ert_mlt, mlt_table, (size_t)mlt_bytes, cudaMemcpyHostToDevice, ctx->stream));
     BWAGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     ctx->ert_mlt_bytes = mlt_bytes;
+    return BWAGPU_OK;
+}
+
+// ---- k-mer table entries of absent k-mers, from the FM-index ---------------------------------------------
+// One thread per 11-base prefix (the low 22 bits of the k-mer index); the 4^4 completions are enumerated depth
+// first so the prefix walk is shared and dead branches are cut: a prefix that no longer occurs gives all of
+// its completions the same LEP mask.  A warp's threads hold consecutive prefixes, so for a fixed completion
+// their 32 table entries are contiguous (256-byte stores).
+#define ERT_FILL_PREFIX 11
+__global__ void __launch_bounds__(128) ert_kmer_fill_kernel(FmView f, uint64_t *__restrict__ table)
+{
+    const uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;          // 4^11 threads exactly
+    ErtKmerWalk w0, w1, w2, w3, w4;                                    // walk state after 11, 12, 13, 14, 15 bases
+    w0.start(f, (int)(p & 3));
+    for (int i = 1; i < ERT_FILL_PREFIX && w0.hits > 0; ++i) w0.step(f, i, (int)((p >> (2 * i)) & 3));
+    if (w0.hits == 0) {
+        const uint64_t e = (uint64_t)(w0.lep & 0x3FFF) << 2;
+        for (uint32_t sfx = 0; sfx < 256; ++sfx) table[p | (sfx << 22)] = e;
+        return;
+    }
+    w1 = w2 = w3 = w0;
+    for (uint32_t t = 0; t < 256; ++t) {
+        // base 11 is the slowest digit of t, base 14 the fastest: a level is re-walked only when its base changes
+        const int b11 = (t >> 6) & 3, b12 = (t >> 4) & 3, b13 = (t >> 2) & 3, b14 = t & 3;
+        if ((t & 63) == 0) { w1 = w0; w1.step(f, 11, b11); }
+        if ((t & 15) == 0) { w2 = w1; if (w1.hits > 0) w2.step(f, 12, b12); }
+        if ((t & 3) == 0) { w3 = w2; if (w2.hits > 0) w3.step(f, 13, b13); }
+        w4 = w3; if (w3.hits > 0) w4.step(f, 14, b14);
+        if (w4.hits == 0) {
+            const uint32_t sfx = (uint32_t)(b11 | (b12 << 2) | (b13 << 4) | (b14 << 6));
+            table[p | (sfx << 22)] = (uint64_t)(w4.lep & 0x3FFF) << 2;
+        }
+    }
+}
+
+extern "C" int bwagpu_index_complete_ert(bwagpu_ctx *ctx)
+{
+    if (!ctx) return BWAGPU_ERR_ARG;
+    if (!ctx->has_fm) BWAGPU_FAIL(ctx, BWAGPU_ERR_ARG, "index_complete_ert: no FM-index loaded (bwagpu_index_load_fm)");
+    if (!ctx->d_ert_kmer) BWAGPU_FAIL(ctx, BWAGPU_ERR_ARG, "index_complete_ert: no ERT index loaded (bwagpu_index_load_ert)");
+    BWAGPU_CUDA(ctx, cudaSetDevice(ctx->device));
+    FmView f;
+    f.cp_occ = (const int64_t *)ctx->d_cp_occ; f.sa_ms_byte = (const int8_t *)ctx->d_sa_ms; f.sa_ls_word = (const uint32_t *)ctx->d_sa_ls;
+    for (int i = 0; i < 5; ++i) f.count[i] = ctx->fm_count[i];
+    f.sentinel_index = ctx->fm_sentinel; f.ref_seq_len = ctx->fm_ref_seq_len;
+    f.fma_all = f.fma_last = nullptr;
+    BWAGPU_KERNEL_BEGIN(ctx);
+    ert_kmer_fill_kernel<<<(1u << 22) / 128, 128, 0, ctx->stream>>>(f, (uint64_t *)ctx->d_ert_kmer);
+    BWAGPU_KERNEL_END(ctx, BWAGPU_KERN_ERT_EMIT);
+    BWAGPU_CUDA(ctx, cudaGetLastError());
+    BWAGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return BWAGPU_OK;
+}
+
+extern "C" int bwagpu_index_get_ert_kmers(bwagpu_ctx *ctx, const uint32_t *idx, int64_t n, uint64_t *out)
+{
+    if (!ctx) return BWAGPU_ERR_ARG;
+    if (!ctx->d_ert_kmer) BWAGPU_FAIL(ctx, BWAGPU_ERR_ARG, "index_get_ert_kmers: no ERT index loaded");
+    if (n < 0 || (n > 0 && (!idx || !out))) BWAGPU_FAIL(ctx, BWAGPU_ERR_ARG, "index_get_ert_kmers: bad argument");
+    BWAGPU_CUDA(ctx, cudaSetDevice(ctx->device));
+    BWAGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    for (int64_t i = 0; i < n; ++i)
+        BWAGPU_CUDA(ctx, cudaMemcpy(out + i, (const uint64_t *)ctx->d_ert_kmer + idx[i], 8, cudaMemcpyDeviceToHost));
+    return BWAGPU_OK;
+}
+
+extern "C" int bwagpu_index_get_ert_table(bwagpu_ctx *ctx, uint64_t *kmer_offsets)
+{
+    if (!ctx) return BWAGPU_ERR_ARG;
+    if (!ctx->d_ert_kmer) BWAGPU_FAIL(ctx, BWAGPU_ERR_ARG, "index_get_ert_table: no ERT index loaded");
+    if (!kmer_offsets) BWAGPU_FAIL(ctx, BWAGPU_ERR_ARG, "index_get_ert_table: output is NULL");
+    BWAGPU_CUDA(ctx, cudaSetDevice(ctx->device));
+    BWAGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    BWAGPU_CUDA(ctx, cudaMemcpy(kmer_offsets, ctx->d_ert_kmer, (size_t)ERT_KMER_ENTRIES * 8, cudaMemcpyDeviceToHost));
     return BWAGPU_OK;
 }
 

@@ -25,9 +25,13 @@
 #if defined(__CUDACC__)
 #define ERT_HD __host__ __device__
 #define ERT_HDI __host__ __device__ __forceinline__
+// One out-of-line copy of every building block on the device: fully inlined, the walker is 55 k SASS instructions
+// (880 KB) and the kernel stalls on instruction fetch 87 % of the time (profiles/r01_ncu_ert_seed_summary.txt).
+#define ERT_FN __host__ __device__ __noinline__
 #else
 #define ERT_HD
 #define ERT_HDI inline
+#define ERT_FN
 #endif
 
 // test scaffolding may define this to log which k-mer entries a walk touches
@@ -113,10 +117,20 @@ struct ErtWalker {
     // ---- index access ------------------------------------------------------------------------------
     ERT_HDI uint64_t ld(const uint8_t *p, int n)
     {
+        n_bytes += n;
+#if defined(__CUDA_ARCH__)
+        // unaligned little-endian load as one or two aligned 64-bit loads (the blob is padded by 16 bytes)
+        const unsigned long long a = (unsigned long long)p;
+        const uint64_t *q = (const uint64_t *)(a & ~7ull);
+        const int sh = (int)(a & 7) * 8;
+        uint64_t v = __ldg(q) >> sh;
+        if (sh + 8 * n > 64) v |= __ldg(q + 1) << (64 - sh);
+        return n == 8 ? v : v & ((1ull << (8 * n)) - 1);
+#else
         uint64_t v = 0;
         for (int b = 0; b < n; ++b) v |= (uint64_t)p[b] << (8 * b);
-        n_bytes += n;
         return v;
+#endif
     }
     ERT_HDI uint8_t ldb(const uint8_t *p) { ++n_bytes; return *p; }
     ERT_HDI int refb(int64_t pos) { ++n_bytes; return ix.ref[pos]; }
@@ -157,7 +171,7 @@ struct ErtWalker {
     }
 
     // getHashKey (:435-453)
-    ERT_HDI uint32_t hash_key(int index, int keysize, int *end_flag, int *first_n) const
+    ERT_FN uint32_t hash_key(int index, int keysize, int *end_flag, int *first_n) const
     {
         uint32_t key = 0;
         int len = keysize;
@@ -171,7 +185,7 @@ struct ErtWalker {
     }
 
     // getOffsetToChildNode (:485-496): nb is just past the code byte on entry
-    ERT_HDI void child(const uint8_t *t, uint8_t code, int c, uint64_t &nb)
+    ERT_FN void child(const uint8_t *t, uint8_t code, int c, uint64_t &nb)
     {
         const uint64_t start = nb - 1;
         const uint32_t d = (uint32_t)ld(t + nb + ert_child_off(ptr_width, code, c), ptr_width);
@@ -180,7 +194,7 @@ struct ErtWalker {
     }
 
     // the LEAF branch shared by most walkers: record at nb (already advanced past the code byte)
-    ERT_HDI void leaf_all(const uint8_t *t, uint64_t nb, uint8_t code, int c, ErtMem &m)
+    ERT_FN void leaf_all(const uint8_t *t, uint64_t nb, uint8_t code, int c, ErtMem &m)
     {
         nb += ert_leaf_off(ptr_width, code, c);
         const uint64_t leaf = ld(t + nb, 5);
@@ -197,7 +211,7 @@ struct ErtWalker {
         }
     }
     // the variant used under a hit limit: count first, then push only when num_hits >= limit
-    ERT_HDI bool leaf_limited(const uint8_t *t, uint64_t nb, uint8_t code, int c, ErtMem &m)
+    ERT_FN bool leaf_limited(const uint8_t *t, uint64_t nb, uint8_t code, int c, ErtMem &m)
     {
         nb += ert_leaf_off(ptr_width, code, c);
         const uint64_t leaf = ld(t + nb, 5);
@@ -210,7 +224,7 @@ struct ErtWalker {
     }
 
     // UNIFORM run at nb (past the code byte): returns the number of leading bases matching the read at i
-    ERT_HDI int uniform(const uint8_t *t, uint64_t &nb, int i, int *count)
+    ERT_FN int uniform(const uint8_t *t, uint64_t &nb, int i, int *count)
     {
         const int cnt = ldb(t + nb); ++nb;
         const int nbytes = (cnt * 2 + 7) >> 3;
@@ -229,7 +243,7 @@ struct ErtWalker {
     }
 
     // leaf_gather + getNextByteIdx_dfs (:521-597)
-    ERT_HD void gather(const uint8_t *t, uint64_t start, ErtMem &m)
+    ERT_FN void gather(const uint8_t *t, uint64_t start, ErtMem &m)
     {
         uint32_t st[176];
         int top = 0;
@@ -257,8 +271,7 @@ struct ErtWalker {
     }
 
     // ---- forward tree walk: getNextByteIdx (:836) and getNextByteIdx_wlimit (:989) --------------------
-    template <bool WL>
-    ERT_HD void walk_fwd(const uint8_t *t, uint64_t nb, int &i, ErtMem &m)
+    ERT_FN void walk_fwd(bool WL, const uint8_t *t, uint64_t nb, int &i, ErtMem &m)
     {
         for (;;) {
             const uint64_t parent = nb;
@@ -306,7 +319,7 @@ struct ErtWalker {
     }
 
     // getNextByteIdx_last (:1168)
-    ERT_HD void walk_last(const uint8_t *t, uint64_t nb, int &i, ErtMem &m)
+    ERT_FN void walk_last(const uint8_t *t, uint64_t nb, int &i, ErtMem &m)
     {
         for (;;) {
             int c = 0, cc = ERT_EMPTY;
@@ -338,8 +351,7 @@ struct ErtWalker {
     }
 
     // getNextByteIdx_backward (:609) and _backward_wlimit (:718)
-    template <bool WL>
-    ERT_HD void walk_bwd(const uint8_t *t, uint64_t nb, int &i, ErtMem &m)
+    ERT_FN void walk_bwd(bool WL, const uint8_t *t, uint64_t nb, int &i, ErtMem &m)
     {
         for (;;) {
             int c = 0, cc = ERT_EMPTY;
@@ -400,8 +412,7 @@ struct ErtWalker {
     }
 
     // getNextByteIdx_fetch_leaves_prefix (:1644) and _prefix_reseed (:1505)
-    template <bool RS>
-    ERT_HD void walk_fetch_prefix(const uint8_t *t, uint64_t nb, int i, ErtMem &m)
+    ERT_FN void walk_fetch_prefix(bool RS, const uint8_t *t, uint64_t nb, int i, ErtMem &m)
     {
         for (;;) {
             const uint64_t parent = nb;
@@ -445,7 +456,7 @@ struct ErtWalker {
     }
 
     // getNextByteIdx_fetch_leaves (:1759): re-walk of a backward MEM, bounded by mem->end
-    ERT_HD void walk_fetch(const uint8_t *t, uint64_t nb, int i, ErtMem &m)
+    ERT_FN void walk_fetch(const uint8_t *t, uint64_t nb, int i, ErtMem &m)
     {
         for (;;) {
             const int c = 3 - rd(i);
@@ -481,8 +492,7 @@ struct ErtWalker {
     ERT_HDI int width_of(uint64_t e) const { const int w = (int)((e >> 22) & 3); return w == 0 ? 4 : w; }
 
     // rightExtend (:2142) and rightExtend_wlimit (:2317)
-    template <bool WL>
-    ERT_HD void right_extend(int &i, ErtMem &m)
+    ERT_FN void right_extend(bool WL, int &i, ErtMem &m)
     {
         int flag = 0, first_n = -1;
         const uint32_t h = hash_key(i, ERT_KMER, &flag, &first_n);
@@ -515,7 +525,7 @@ struct ErtWalker {
             if (i < l_seq) {
                 if (WL) last_visited = 0;
                 mh_start = ld(t, 4);
-                walk_fwd<WL>(t, 4, i, m);
+                walk_fwd(WL, t, 4, i, m);
             } else { set_lep(next_lep); next_lep += 1; }
             return;
         }
@@ -543,12 +553,12 @@ struct ErtWalker {
         if (WL && !(num_hits == 0 || num_hits >= limit)) return;
         if (i < l_seq) {
             if (WL) last_visited = (uint32_t)ptr;
-            walk_fwd<WL>(t, ptr, i, m);
+            walk_fwd(WL, t, ptr, i, m);
         } else { set_lep(next_lep); next_lep += 1; }
     }
 
     // rightExtend_last (:2500)
-    ERT_HD void right_extend_last(int &i, ErtMem &m)
+    ERT_FN void right_extend_last(int &i, ErtMem &m)
     {
         int flag = 0, first_n = -1;
         const uint32_t h = hash_key(i, ERT_KMER, &flag, &first_n);
@@ -596,8 +606,7 @@ struct ErtWalker {
     }
 
     // leftExtend (:1288) and leftExtend_wlimit (:1392); read_buf is the reverse-complemented read
-    template <bool WL>
-    ERT_HD void left_extend(int &i, ErtMem &m)
+    ERT_FN void left_extend(bool WL, int &i, ErtMem &m)
     {
         int first_n = -1;
         const uint32_t h = hash_key(i, ERT_KMER, nullptr, &first_n);
@@ -618,7 +627,7 @@ struct ErtWalker {
         if (code == ERT_INFREQUENT) {
             i += ERT_KMER;
             if (WL && !(num_hits == 0 || num_hits >= limit)) { m.rc_end = i; return; }
-            if (i < l_seq) { mh_start = ld(t, 4); walk_bwd<WL>(t, 4, i, m); }
+            if (i < l_seq) { mh_start = ld(t, 4); walk_bwd(WL, t, 4, i, m); }
             else { m.rc_end = i; if (WL) m.fetch_leaves = 1; }
             return;
         }
@@ -638,13 +647,12 @@ struct ErtWalker {
         }
         i += ERT_XMER;
         if (WL && !(num_hits == 0 || num_hits >= limit)) { m.rc_end = i; return; }
-        if (i < l_seq) walk_bwd<WL>(t, ptr, i, m);
+        if (i < l_seq) walk_bwd(WL, t, ptr, i, m);
         else { m.rc_end = i; if (WL) m.fetch_leaves = 1; }
     }
 
     // rightExtend_fetch_leaves_prefix (:1967) and _prefix_reseed (:1854); read_buf is the forward read
-    template <bool RS>
-    ERT_HD void right_fetch_prefix(ErtMem &m)
+    ERT_FN void right_fetch_prefix(bool RS, ErtMem &m)
     {
         int flag = 0, first_n = -1;
         int i = m.start;
@@ -666,7 +674,7 @@ struct ErtWalker {
             if (RS && !(num_hits == 0 || num_hits >= limit)) { m.end = i; return; }
             i += ERT_KMER;
             mh_start = ld(t, 4);
-            if (i < l_seq) { if (RS) last_visited = 4; walk_fetch_prefix<RS>(t, 4, i, m); }
+            if (i < l_seq) { if (RS) last_visited = 4; walk_fetch_prefix(RS, t, 4, i, m); }
             else { m.end = i; if (m.end - m.start >= min_seed_len) gather(t, 4, m); }
             return;
         }
@@ -687,12 +695,12 @@ struct ErtWalker {
         }
         if (RS && !(num_hits == 0 || num_hits >= limit)) { m.end = i; return; }
         i += ERT_KMER + ERT_XMER;
-        if (i < l_seq) { if (RS) last_visited = (uint32_t)ptr; walk_fetch_prefix<RS>(t, ptr, i, m); }
+        if (i < l_seq) { if (RS) last_visited = (uint32_t)ptr; walk_fetch_prefix(RS, t, ptr, i, m); }
         else { m.end = i; if (m.end - m.start >= min_seed_len) gather(t, ptr, m); }
     }
 
     // rightExtend_fetch_leaves (:2071)
-    ERT_HD void right_fetch(ErtMem &m)
+    ERT_FN void right_fetch(ErtMem &m)
     {
         int flag = 0, first_n = -1;
         int i = m.start;
@@ -731,7 +739,7 @@ struct ErtWalker {
     }
 
     // extension of a forward MEM against the text (shared head of get_seeds / reseed, :2945-2968)
-    ERT_HDI void extend_right_on_text(int &i, const ErtMem &rm)
+    ERT_FN void extend_right_on_text(int &i, const ErtMem &rm)
     {
         int64_t len;
         const int64_t h0 = hit_at(rm.hitbeg);
@@ -746,7 +754,7 @@ struct ErtWalker {
     }
 
     // the two text comparisons that open check_and_add_smem_prefix[_reseed] (:2641-2673)
-    ERT_HDI void lmem_fix_prefix(ErtMem &m)
+    ERT_FN void lmem_fix_prefix(ErtMem &m)
     {
         m.start = l_seq - m.rc_end;
         const int lmemLen = m.end - m.start;
@@ -770,8 +778,7 @@ struct ErtWalker {
     }
 
     // check_and_add_smem_prefix (:2756) and _prefix_reseed (:2639)
-    template <bool RS>
-    ERT_HD int check_add_prefix(ErtMem &m, const ErtHelper &sh)
+    ERT_FN int check_add_prefix(bool RS, ErtMem &m, const ErtHelper &sh)
     {
         lmem_fix_prefix(m);
         const int lmemLen = m.end - m.start;
@@ -784,7 +791,7 @@ struct ErtWalker {
             m.hitbeg = mark();
             m.hitcount = 0;
             rc = false;
-            right_fetch_prefix<RS>(m);
+            right_fetch_prefix(RS, m);
             rc = true;
             int rmemLen = m.end - m.start;
             next_be = m.end;
@@ -811,8 +818,7 @@ struct ErtWalker {
     }
 
     // check_and_add_smem (:2867)
-    template <bool WL>
-    ERT_HD void check_add(ErtMem &m, ErtHelper &sh)
+    ERT_FN void check_add(bool WL, ErtMem &m, ErtHelper &sh)
     {
         m.start = l_seq - m.rc_end;
         int lmemLen = m.end - m.start;
@@ -847,8 +853,7 @@ struct ErtWalker {
     }
 
     // backward extensions of one forward MEM: the LEP loops of get_seeds[_prefix] / reseed[_prefix]
-    template <bool PREFIX, bool WL>
-    ERT_HD void backward_pass(const ErtMem &rm, ErtHelper &sh, int &i)
+    ERT_FN void backward_pass(bool PREFIX, bool WL, const ErtMem &rm, ErtHelper &sh, int &i)
     {
         sh.stop_be = 0;
         const int min_j = (rm.start > min_seed_len) ? (rm.start - 1) : (min_seed_len - 1);
@@ -865,8 +870,8 @@ struct ErtWalker {
                 if (valid && j + 1 >= min_seed_len) {
                     int rc_i = l_seq - (j + 1);
                     rc = true;
-                    left_extend<WL>(rc_i, m);
-                    next_j = check_add_prefix<WL>(m, sh);
+                    left_extend(WL, rc_i, m);
+                    next_j = check_add_prefix(WL, m, sh);
                 }
                 j = next_j;
                 if (!WL && m.end > i) i = m.end;
@@ -880,8 +885,8 @@ struct ErtWalker {
                 if (valid && j + 1 >= min_seed_len) {
                     int rc_i = l_seq - (j + 1);
                     rc = true;
-                    left_extend<WL>(rc_i, m);
-                    check_add<WL>(m, sh);
+                    left_extend(WL, rc_i, m);
+                    check_add(WL, m, sh);
                     if (sh.stop_be) break;
                 }
                 j -= 1;
@@ -890,8 +895,7 @@ struct ErtWalker {
     }
 
     // get_seeds_prefix (:2925) / get_seeds (:3062)
-    template <bool PREFIX>
-    ERT_HD void get_seeds()
+    ERT_FN void get_seeds(bool PREFIX)
     {
         ErtHelper sh = {l_seq, 0, 0, -1, -1, 0, 0};
         int i = 0;
@@ -901,7 +905,7 @@ struct ErtWalker {
             rm.start = i; rm.forward = 1; rm.hitbeg = mark();
             sh.curr_pivot = rm.start;
             rc = false;
-            right_extend<false>(i, rm);
+            right_extend(false, i, rm);
             if (rm.hitcount > 0 && !rm.skip_ref_fetch) extend_right_on_text(i, rm);
             rm.end = i;
             if (rm.start == 0) {
@@ -914,7 +918,7 @@ struct ErtWalker {
                 clear_lep();
             } else {
                 n_hit -= rm.hitcount;
-                backward_pass<PREFIX, false>(rm, sh, i);
+                backward_pass(PREFIX, false, rm, sh, i);
             }
             rc = false;
             while (i < l_seq && rd(i) == 4) ++i;
@@ -929,8 +933,7 @@ struct ErtWalker {
     }
 
     // reseed_prefix (:3200) / reseed (:3315)
-    template <bool PREFIX>
-    ERT_HD void reseed(int start, int lim, int c_pivot, int p_pivot, int pp_pivot)
+    ERT_FN void reseed(bool PREFIX, int start, int lim, int c_pivot, int p_pivot, int pp_pivot)
     {
         ErtHelper sh = {l_seq, 0, 0, 0, 0, 0, 0};
         int i = start;
@@ -940,7 +943,7 @@ struct ErtWalker {
         sh.prev_pivot = (rm.start >= c_pivot) ? p_pivot : pp_pivot;
         rc = false;
         limit = lim;
-        right_extend<true>(i, rm);
+        right_extend(true, i, rm);
         if (rm.hitcount > 0 && !rm.skip_ref_fetch) extend_right_on_text(i, rm);
         rm.end = i;
         if (rm.start == 0) {
@@ -949,12 +952,12 @@ struct ErtWalker {
             clear_lep();
         } else {
             n_hit -= rm.hitcount;
-            backward_pass<PREFIX, true>(rm, sh, i);
+            backward_pass(PREFIX, true, rm, sh, i);
         }
     }
 
     // last (:3425)
-    ERT_HD void last(int lim)
+    ERT_FN void last(int lim)
     {
         int i = 0;
         const int minSeedLen = (uint8_t)(min_seed_len + 1);
@@ -997,13 +1000,12 @@ struct ErtWalker {
         min_seed_len = o.min_seed_len;
         bool has_n = false;
         for (int i = 0; i < l_seq; ++i) has_n |= fwd[i] >= 4;
-        if (has_n) get_seeds<false>(); else get_seeds<true>();
+        get_seeds(!has_n);
         const int old_n = n_mem < mem_cap ? n_mem : mem_cap;
         for (int k = 0; k < old_n; ++k) {
             const ErtMemRec r = mems[k];
             if ((r.end - r.start) < o.split_len || r.hitcount > o.split_width) continue;
-            if (has_n) reseed<false>((r.start + r.end) >> 1, r.hitcount + 1, r.c_pivot, r.p_pivot, r.pp_pivot);
-            else reseed<true>((r.start + r.end) >> 1, r.hitcount + 1, r.c_pivot, r.p_pivot, r.pp_pivot);
+            reseed(!has_n, (r.start + r.end) >> 1, r.hitcount + 1, r.c_pivot, r.p_pivot, r.pp_pivot);
         }
         last(o.max_mem_intv);
     }
@@ -1019,7 +1021,7 @@ struct ErtSort {
         for (int i = lo + 1; i < hi; ++i)
             for (int j = i; j > lo && lt(a[j], a[j - 1]); --j) { const Key t = a[j]; a[j] = a[j - 1]; a[j - 1] = t; }
     }
-    ERT_HD static void combsort(Key *a, int n)
+    ERT_FN static void combsort(Key *a, int n)
     {
         const double shrink = 1.2473309501039786540366528676643;
         int do_swap; size_t gap = (size_t)n;
@@ -1033,7 +1035,7 @@ struct ErtSort {
         } while (do_swap || gap > 2);
         if (gap != 1) insertsort(a, 0, n);
     }
-    ERT_HD static void introsort(Key *a, int n)
+    ERT_FN static void introsort(Key *a, int n)
     {
         if (n < 1) return;
         if (n == 2) { if (lt(a[1], a[0])) { const Key t = a[0]; a[0] = a[1]; a[1] = t; } return; }

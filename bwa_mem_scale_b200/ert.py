@@ -55,6 +55,23 @@ class ErtSeeding:
                 index.sparse_val.ctypes.data if n else None, n, index.mlt_table.ctypes.data, index.mlt_table.nbytes),
                 "bwagpu_index_load_ert")
 
+    def complete_from_fm(self) -> None:
+        """Fill in the entries of absent k-mers from the FM-index resident on the same context."""
+        self.ctx.check(self.ctx.lib.bwagpu_index_complete_ert(self.ctx.h), "bwagpu_index_complete_ert")
+
+    def dense_table(self) -> np.ndarray:
+        """The resident 2^30-entry k-mer table as a host array (8 GiB)."""
+        out = np.empty(N_KMERS, np.uint64)
+        self.ctx.check(self.ctx.lib.bwagpu_index_get_ert_table(self.ctx.h, out.ctypes.data), "bwagpu_index_get_ert_table")
+        return out
+
+    def kmer_entries(self, idx: np.ndarray) -> np.ndarray:
+        idx = np.ascontiguousarray(idx, np.uint32)
+        out = np.zeros(len(idx), np.uint64)
+        self.ctx.check(self.ctx.lib.bwagpu_index_get_ert_kmers(self.ctx.h, idx.ctypes.data, len(idx), out.ctypes.data),
+                       "bwagpu_index_get_ert_kmers")
+        return out
+
     def seed(self, opt: SeedOpt, enc_reads: np.ndarray, off: np.ndarray, ln: np.ndarray, skip: np.ndarray | None = None):
         """(mems, hits, mem_off): sorted MEMs of every read + the coordinates of all their hits."""
         n = len(ln)

@@ -122,6 +122,9 @@ _SIGS = {
                                            C.POINTER(ChainResult)]),
     "bwagpu_index_load_ert": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_int64]),
     "bwagpu_index_unload_ert": (C.c_int, [C.c_void_p]),
+    "bwagpu_index_complete_ert": (C.c_int, [C.c_void_p]),
+    "bwagpu_index_get_ert_table": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "bwagpu_index_get_ert_kmers": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p]),
     "bwagpu_seed_ert": (C.c_int, [C.c_void_p, C.POINTER(SeedOpt), C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                                   C.c_int32, C.c_void_p, C.c_int64, C.c_void_p, C.c_int64, C.c_void_p,
                                   C.POINTER(C.c_int64), C.POINTER(C.c_int64)]),

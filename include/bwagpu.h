@@ -325,6 +325,16 @@ int bwagpu_index_load_ert(bwagpu_ctx *ctx, const uint64_t *kmer_offsets, const u
                           const uint64_t *sparse_val, int64_t n_sparse, const uint8_t *mlt_table,
                           int64_t mlt_bytes);
 int bwagpu_index_unload_ert(bwagpu_ctx *ctx);
+/* Entries of the k-mers that do NOT occur in the reference, computed on the device from the resident FM-index
+ * (bwagpu_index_load_fm): such an entry is (LEP mask << 2) | INVALID, where LEP bit i-1 says that the number of
+ * occurrences changed when base i was appended (reference src/ertindex.cpp, buildIndex); its pointer bits are never
+ * read by seeding and are left 0.  Entries of k-mers that occur are not touched, so an index can be shipped as the
+ * entries of the occurring k-mers (sparse form of bwagpu_index_load_ert) + mlt_table and completed here. */
+int bwagpu_index_complete_ert(bwagpu_ctx *ctx);
+/* read back single k-mer table entries (tests) */
+int bwagpu_index_get_ert_kmers(bwagpu_ctx *ctx, const uint32_t *idx, int64_t n, uint64_t *out);
+/* the whole resident k-mer table (2^30 x 8 B) back to the host, e.g. to hand a completed table to host code */
+int bwagpu_index_get_ert_table(bwagpu_ctx *ctx, uint64_t *kmer_offsets);
 
 /* One maximal exact match of a read: mem_t {start, end, hitcount} (src/ertseeding.h:62-77) with hitbeg
  * rebased into the batch-wide hit list.  hits[] holds, for every MEM, the coordinate mem_chain_new

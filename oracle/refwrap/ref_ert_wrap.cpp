@@ -28,6 +28,7 @@ extern unsigned char code_table[256 * 3][4];
 KSORT_INIT(tap_smem_sort_lt, mem_t, smem_lt_2)          // = KSORT_INIT(mem_smem_sort_lt, ...) src/bwamem.cpp:72-74
 
 struct ErtTap {
+    int borrowed;                 // tables are caller-owned arrays (ref_ert_open_mem)
     uint64_t *kmer; size_t kmer_bytes;
     uint8_t *mlt; size_t mlt_bytes;
     uint8_t *ref; size_t ref_bytes;
@@ -63,9 +64,20 @@ void *ref_ert_open(const char *prefix)
     return t;
 }
 
+// same over caller-owned arrays: dense k-mer table, tree blob, .0123 text (kept alive by the caller)
+void *ref_ert_open_mem(uint64_t *kmer, uint8_t *mlt, int64_t mlt_bytes, uint8_t *ref, int64_t ref_bytes)
+{
+    ErtTap *t = (ErtTap *)calloc(1, sizeof(ErtTap));
+    t->borrowed = 1;
+    t->kmer = kmer; t->mlt = mlt; t->mlt_bytes = (size_t)mlt_bytes; t->ref = ref; t->ref_bytes = (size_t)ref_bytes;
+    t->bns.l_pac = ref_bytes / 2;
+    return t;
+}
+
 void ref_ert_close(void *h)
 {
     ErtTap *t = (ErtTap *)h;
+    if (t->borrowed) { free(t); return; }
     munmap(t->kmer, t->kmer_bytes); munmap(t->mlt, t->mlt_bytes); munmap(t->ref, t->ref_bytes);
     free(t);
 }

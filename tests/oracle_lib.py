@@ -375,6 +375,12 @@ class RefMem:
             self.lib.ref_mem_use_ert(self.h, ref_ert.lib.ref_ert_kmer(ref_ert.h), ref_ert.lib.ref_ert_mlt(ref_ert.h, C.byref(n)))
         self._ert = ref_ert
 
+    def use_ert_tables(self, kmer: np.ndarray, mlt: np.ndarray):
+        """Same with the tables given as host arrays (dense 2^30-entry k-mer table, tree blob)."""
+        self.lib.ref_mem_use_ert.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+        self._ert = (kmer, mlt)
+        self.lib.ref_mem_use_ert(self.h, kmer.ctypes.data, mlt.ctypes.data)
+
     def clone(self):
         """Another worker on the same loaded index (own scratch arenas), for multi-threaded baselines."""
         return RefMem(*self._args, _parent=self)
@@ -503,7 +509,7 @@ ERT_MEM_DTYPE = np.dtype([("rid", "<i4"), ("start", "<i4"), ("end", "<i4"), ("hi
 class RefErt:
     """The reference's own ERT seeding on an index written by its `index -a ert` (files mmap'ed)."""
 
-    def __init__(self, prefix: str, flavor="plain", isa="sse41"):
+    def __init__(self, prefix, flavor="plain", isa="sse41"):
         self.lib = C.CDLL(os.path.join(ORACLE_DIR, "_ref", f"libref_api_{flavor}_{isa}.so"))
         self.lib.ref_ert_open.restype = C.c_void_p
         self.lib.ref_ert_open.argtypes = [C.c_char_p]
@@ -516,7 +522,14 @@ class RefErt:
         self.lib.ref_ert_seed.argtypes = [C.c_void_p, C.c_int, C.c_float, C.c_int, C.c_int, C.c_void_p, C.c_void_p,
                                           C.c_void_p, C.c_int, C.c_void_p, C.c_int64, C.c_void_p, C.c_int64,
                                           C.c_void_p, C.c_void_p]
-        self.h = self.lib.ref_ert_open(prefix.encode())
+        self.lib.ref_ert_open_mem.restype = C.c_void_p
+        self.lib.ref_ert_open_mem.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_int64]
+        if isinstance(prefix, tuple):          # (dense k-mer table, tree blob, .0123 text) as host arrays
+            self._keep = tuple(np.ascontiguousarray(a) for a in prefix)
+            k, m, r = self._keep
+            self.h = self.lib.ref_ert_open_mem(k.ctypes.data, m.ctypes.data, m.nbytes, r.ctypes.data, r.nbytes)
+        else:
+            self.h = self.lib.ref_ert_open(prefix.encode())
         assert self.h, f"cannot map the ERT index {prefix}"
 
     def kmer_table(self) -> np.ndarray:

@@ -97,3 +97,24 @@ def test_gpu_ert_requires_index(gpu_ctx):
         assert rc == -3 and b"no ERT index" in ctx.lib.bwagpu_last_error(ctx.h)
     finally:
         ctx.close()
+
+
+def test_gpu_kmer_table_completion_from_fm_index(tiny_ert, gpu_ctx):
+    """Entries of absent k-mers recomputed on the device from the FM-index == the reference-built table (the bits
+    seeding reads: type, LEP mask, hit count, pointer width); entries of occurring k-mers stay as loaded."""
+    from bwa_mem_scale_b200 import FMI_search
+    ref, ext, ert, flat, off, ln = tiny_ert
+    FMI_search(fmindex.build_fm_index(ref, device="cpu"), ctx=gpu_ctx)
+    idx, val = GOLD["kmer_idx"], GOLD["kmer_val"]
+    rng = np.random.default_rng(5)
+    extra = rng.integers(0, 1 << 30, 20000).astype(np.uint32)
+    assert np.array_equal(ert.kmer_entries(idx), val)
+    assert not np.any(ert.kmer_entries(extra[~np.isin(extra, idx)]))          # sparse load: everything else is 0
+    ert.complete_from_fm()
+    got = ert.kmer_entries(idx)
+    present = (val & 3) != 0
+    assert np.array_equal(got[present], val[present])
+    assert np.array_equal(got[~present], val[~present] & np.uint64(0xFFFFFF))
+    mems, hits, mem_off = ert.seed(sopt_of({}), flat, off, ln)
+    assert np.array_equal(ec.mem_matrix(mems), ec.mem_matrix(GOLD["default_mems"]))
+    assert np.array_equal(hits, GOLD["default_hits"])

@@ -125,3 +125,23 @@ def test_ert_walker_live_against_reference():
         assert np.array_equal(ec.mem_matrix(got[0]), ec.mem_matrix(want[0]))
         assert np.array_equal(got[1], want[1]) and np.array_equal(got[2], want[2])
     tap.close()
+
+
+def test_kmer_entry_bits_from_fm_index(tiny):
+    """csrc/ert_build.cuh: LEP mask, type and reseeding hit count of a k-mer entry follow from occurrence counts in
+    the FM-index; checked on every reference-built entry the golden reads touch (absent and occurring k-mers)."""
+    import ctypes as C
+    from test_seed_hostsim import desc_of
+    ref = tiny[0]
+    idx = fmindex.build_fm_index(ref, device="cpu")
+    kidx, want = np.ascontiguousarray(GOLD["kmer_idx"]), GOLD["kmer_val"]
+    out = np.zeros(len(kidx), np.uint64)
+    d = desc_of(idx)
+    hostsim_lib.load().hostsim_ert_kmer_lep(C.byref(d), C.c_void_p(kidx.ctypes.data), C.c_int64(len(kidx)),
+                                            C.c_void_p(out.ctypes.data))
+    lep, hits = out & np.uint64(0xFFFF), (out >> np.uint64(16)).astype(np.int64)
+    assert np.array_equal(lep, (want >> np.uint64(2)) & np.uint64(0x3FFF))
+    typ = np.where(hits == 0, 0, np.where(hits == 1, 1, np.where(hits <= 256, 2, 3)))
+    assert np.array_equal(typ, (want & np.uint64(3)).astype(np.int64))
+    assert np.array_equal(np.where(hits < 20, hits, 0), ((want >> np.uint64(17)) & np.uint64(0x1F)).astype(np.int64))
+    assert (typ == 0).sum() > 1000 and (typ == 3).sum() > 0
