@@ -16,14 +16,19 @@
 #include "ert_core.cuh"
 #include "ert_build.cuh"
 
+#ifndef ERT_TPB
 #define ERT_TPB 128
+#endif
+#ifndef ERT_MINB
+#define ERT_MINB 1
+#endif
 #define ERT_KMER_ENTRIES (1LL << 30)
 
-struct ErtStats { unsigned long long n_bytes, n_hits; unsigned int max_mem, max_hit, n_ovf, pad_; };
+struct ErtStats { unsigned long long n_bytes, n_hits; unsigned int max_mem, max_hit, n_ovf, pad_; int bad_site, bad_read; long long bad_val; };
 
 struct ErtSlab { ErtMemRec *mems; int64_t *hits; uint64_t *keys; int mem_cap, hit_cap; };
 
-__global__ void __launch_bounds__(ERT_TPB)
+__global__ void __launch_bounds__(ERT_TPB, ERT_MINB)
 ert_seed_kernel(ErtView ix, ErtOpt o, int max_occ, const uint8_t *__restrict__ reads, const int64_t *__restrict__ off,
                 const int32_t *__restrict__ len, const uint8_t *__restrict__ skip, const int32_t *__restrict__ list,
                 int n_items, ErtSlab sl, int32_t *cnt_mem, int64_t *cnt_coord, int32_t *slab_of, int32_t *ovf_list,
@@ -40,6 +45,9 @@ ert_seed_kernel(ErtView ix, ErtOpt o, int max_occ, const uint8_t *__restrict__ r
     w.mems = sl.mems + (int64_t)item * sl.mem_cap; w.mem_cap = sl.mem_cap;
     w.hits = sl.hits + (int64_t)item * sl.hit_cap; w.hit_cap = sl.hit_cap;
     w.seed_read(o);
+#ifdef ERT_GUARD
+    if (w.bad_site && atomicCAS(&st->bad_site, 0, w.bad_site) == 0) { st->bad_read = r; st->bad_val = w.bad_val; }
+#endif
     if (w.n_mem > sl.mem_cap || w.hit_peak > sl.hit_cap) {
         atomicMax(&st->max_mem, (unsigned)w.n_mem);
         atomicMax(&st->max_hit, (unsigned)w.hit_peak);
@@ -280,7 +288,7 @@ static int ert_seed_dev(bwagpu_ctx *ctx, const bwagpu_seed_opt *opt, int max_occ
     if (nseq == 0) return BWAGPU_OK;
     ErtView ix;
     ix.kmer_offsets = (const uint64_t *)ctx->d_ert_kmer; ix.mlt = (const uint8_t *)ctx->d_ert_mlt;
-    ix.ref = (const uint8_t *)ctx->d_ref_string; ix.l_pac = ctx->l_pac;
+    ix.ref = (const uint8_t *)ctx->d_ref_string; ix.l_pac = ctx->l_pac; ix.mlt_bytes = ctx->ert_mlt_bytes;
     ErtOpt o = {opt->min_seed_len, (int)(opt->min_seed_len * opt->split_factor + .499), opt->split_width,
                 (int)opt->max_mem_intv};
     if (ctx->ert_mem_cap < 16) ctx->ert_mem_cap = 16;
@@ -309,6 +317,9 @@ static int ert_seed_dev(bwagpu_ctx *ctx, const bwagpu_seed_opt *opt, int max_occ
     ErtStats st;
     BWAGPU_CUDA(ctx, cudaMemcpyAsync(&st, d_st, sizeof st, cudaMemcpyDeviceToHost, ctx->stream));
     BWAGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+#ifdef ERT_GUARD
+    fprintf(stderr, "ERT_GUARD pass 1: bad_site=%d read=%d val=%lld n_ovf=%u max_mem=%u max_hit=%u\n", st.bad_site, st.bad_read, st.bad_val, st.n_ovf, st.max_mem, st.max_hit);
+#endif
     const int n_ovf = (int)st.n_ovf;
     for (int pass = 0; n_ovf > 0; ++pass) {
         // the reads that outgrew the common slab, re-run with room for the largest of them

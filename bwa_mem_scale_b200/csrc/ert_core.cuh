@@ -50,6 +50,7 @@ struct ErtView {
     const uint8_t *mlt;
     const uint8_t *ref;             // .0123 text, forward + reverse complement
     int64_t l_pac;
+    int64_t mlt_bytes;              // size of the blob (bounds checks of the ERT_GUARD build)
 };
 
 struct ErtOpt { int min_seed_len, split_len, split_width, max_mem_intv; };
@@ -115,25 +116,38 @@ struct ErtWalker {
     ERT_HDI int rdf(int i) const { if (i < 0 || i >= l_seq) return 0; const int b = fwd[i]; return b < 4 ? b : 4; }
 
     // ---- index access ------------------------------------------------------------------------------
+#ifdef ERT_GUARD
+    // debug build: every index / text access is bounds-checked; the first violation is recorded, the access skipped
+    int bad_site; int64_t bad_val;
+    ERT_HDI bool ok_mlt(const uint8_t *p, int n, int site)
+    {
+        const int64_t o = (int64_t)(p - ix.mlt);
+        if (o >= 0 && o + n <= ix.mlt_bytes + 16) return true;
+        if (!bad_site) { bad_site = site; bad_val = o; }
+        return false;
+    }
+#else
+    ERT_HDI bool ok_mlt(const uint8_t *, int, int) { return true; }
+#endif
     ERT_HDI uint64_t ld(const uint8_t *p, int n)
     {
+        // byte loads on purpose: an aligned two-word variant returned wrong MEMs / faulted on the device in some builds
+        // (bit-exact on the host); not understood, not kept (profiles/r01_ert_experiments.txt)
         n_bytes += n;
-#if defined(__CUDA_ARCH__)
-        // unaligned little-endian load as one or two aligned 64-bit loads (the blob is padded by 16 bytes)
-        const unsigned long long a = (unsigned long long)p;
-        const uint64_t *q = (const uint64_t *)(a & ~7ull);
-        const int sh = (int)(a & 7) * 8;
-        uint64_t v = __ldg(q) >> sh;
-        if (sh + 8 * n > 64) v |= __ldg(q + 1) << (64 - sh);
-        return n == 8 ? v : v & ((1ull << (8 * n)) - 1);
-#else
+        if (!ok_mlt(p, n, 1)) return 0;
         uint64_t v = 0;
         for (int b = 0; b < n; ++b) v |= (uint64_t)p[b] << (8 * b);
         return v;
-#endif
     }
-    ERT_HDI uint8_t ldb(const uint8_t *p) { ++n_bytes; return *p; }
-    ERT_HDI int refb(int64_t pos) { ++n_bytes; return ix.ref[pos]; }
+    ERT_HDI uint8_t ldb(const uint8_t *p) { ++n_bytes; return ok_mlt(p, 1, 2) ? *p : 0; }
+    ERT_HDI int refb(int64_t pos)
+    {
+        ++n_bytes;
+#ifdef ERT_GUARD
+        if (pos < 0 || pos >= 2 * ix.l_pac) { if (!bad_site) { bad_site = 3; bad_val = pos; } return 0; }
+#endif
+        return ix.ref[pos];
+    }
 
     ERT_HDI void push_hit(int64_t pos)
     {
@@ -233,7 +247,7 @@ struct ErtWalker {
             if (i + j >= l_seq) break;
             const int b = rd(i + j);
             if (b == 4) break;
-            const int u = (t[nb + (j >> 2)] >> ((~j & 3) << 1)) & 3;
+            const int u = ((ok_mlt(t + nb + (j >> 2), 1, 4) ? t[nb + (j >> 2)] : 0) >> ((~j & 3) << 1)) & 3;
             if (3 - b != u) break;
         }
         n_bytes += nbytes;
@@ -996,6 +1010,9 @@ struct ErtWalker {
     ERT_HD void seed_read(const ErtOpt &o)
     {
         n_mem = 0; n_hit = 0; hit_peak = 0; n_bytes = 0; watch = -1; watch_val = 0;
+#ifdef ERT_GUARD
+        bad_site = 0; bad_val = 0;
+#endif
         num_hits = 0; limit = 0; ptr_width = 2; mh_start = 0; next_lep = 0; last_visited = 0;
         min_seed_len = o.min_seed_len;
         bool has_n = false;
