@@ -12,3 +12,4 @@ from .extend import Extender, ext_opt, chain_opt, mem_core_device, CHAIN_DTYPE, 
 from .emf import PerfectTable, PerfectMatch, SEED_ENTRY_DTYPE, PERFECT_DTYPE  # noqa: F401
 from .shard import shard_bounds, shard_reads, merge_smems, merge_regions  # noqa: F401
 from .ert import ErtIndex, ErtSeeding, ERT_MEM_DTYPE, mem_core_ert_device  # noqa: F401
+from .cigar import RegToAln, cigar_opt, CIGAR_JOB_DTYPE, CIGAR_OUT_DTYPE  # noqa: F401

@@ -1,0 +1,163 @@
+// CIGAR stage of the C ABI: bwagpu_reg2aln_batch (include/bwagpu.h, seam S4).  Replaces the alignment work of
+// mem_reg2aln (reference src/bwamem.cpp:2533-2600); the per-region algorithm lives in cigar_core.cuh.
+// One region per thread: most regions take the gap-free shortcut (a 151-step sum); the rest run a banded global
+// alignment whose backtrack matrix (one byte per cell) lives in a per-job slab of global memory.  Jobs are
+// processed in chunks so that the slabs stay below a fixed budget.  Results are compacted by a scan + copy kernel.
+#include <cub/device/device_scan.cuh>
+#include <stdlib.h>
+#include "ctx.cuh"
+#include "cigar_core.cuh"
+
+struct CigSlabOff { int64_t eh, z, cigar, md; };
+
+__global__ void cigar_kernel(CigarOpt o, int64_t l_pac, const uint8_t *__restrict__ ref_string, const uint8_t *__restrict__ reads,
+                             const int64_t *__restrict__ off, const int32_t *__restrict__ len, const bwagpu_cigar_job *__restrict__ jobs,
+                             int64_t n, const CigSlabOff *__restrict__ so, int32_t *eh, uint8_t *z, uint32_t *cigar, char *md,
+                             bwagpu_cigar_out *outs, int64_t *cnt_cigar, int64_t *cnt_md)
+{
+    const int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= n) return;
+    const bwagpu_cigar_job jb = jobs[j];
+    CigarScratch sc = { eh + so[j].eh, z + so[j].z, cigar + so[j].cigar, md + so[j].md };
+    CigarResult r;
+    r.score = 0;
+    bwagpu_cigar_out out;
+    out.pos = -1; out.cigar_off = out.md_off = 0; out.is_rev = 0; out.n_cigar = 0; out.nm = -1; out.l_md = 0; out.score = 0;
+    out.ok = cig_reg2aln(o, l_pac, ref_string, reads + off[jb.read], jb.qb, jb.qe, jb.rb, jb.re, jb.truesc, jb.w, sc, &r) ? 1 : 0;
+    if (out.ok) {
+        int is_rev;
+        out.n_cigar = cig_finish(l_pac, jb.rb, jb.re, jb.qb, jb.qe, len[jb.read], sc.cigar, r.n_cigar, &out.pos, &is_rev);
+        out.is_rev = is_rev; out.nm = r.nm; out.l_md = r.l_md; out.score = r.score;
+    }
+    outs[j] = out;
+    cnt_cigar[j] = out.n_cigar;
+    cnt_md[j] = out.ok ? out.l_md + 1 : 0;
+}
+
+__global__ void cigar_emit_kernel(int64_t n, const CigSlabOff *__restrict__ so, const uint32_t *__restrict__ cigar, const char *__restrict__ md,
+                                  const int64_t *__restrict__ coff, const int64_t *__restrict__ moff, int64_t cbase, int64_t mbase,
+                                  bwagpu_cigar_out *outs, uint32_t *out_cigar, char *out_md)
+{
+    const int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= n) return;
+    bwagpu_cigar_out o = outs[j];
+    o.cigar_off = cbase + coff[j]; o.md_off = mbase + moff[j];
+    outs[j] = o;
+    for (int k = 0; k < o.n_cigar; ++k) out_cigar[coff[j] + k] = cigar[so[j].cigar + k];
+    if (o.ok) {
+        for (int k = 0; k < o.l_md; ++k) out_md[moff[j] + k] = md[so[j].md + k];
+        out_md[moff[j] + o.l_md] = 0;
+    }
+}
+
+static int cig_scan(bwagpu_ctx *ctx, const int64_t *in, int64_t *out, int64_t n)
+{
+    size_t bytes = 0;
+    cub::DeviceScan::ExclusiveSum((void *)nullptr, bytes, in, out, (int)n, ctx->stream);
+    void *tmp;
+    int rc = bwagpu_scratch(ctx, SCR_CUB, (int64_t)bytes + 256, &tmp);
+    if (rc) return rc;
+    BWAGPU_CUDA(ctx, cub::DeviceScan::ExclusiveSum(tmp, bytes, in, out, (int)n, ctx->stream));
+    ctx->launches += 2;
+    return BWAGPU_OK;
+}
+
+extern "C" int bwagpu_reg2aln_batch(bwagpu_ctx *ctx, const bwagpu_cigar_opt *opt, const uint8_t *enc_reads, const int64_t *off,
+                                    const int32_t *len, int32_t nseq, const bwagpu_cigar_job *jobs, int64_t n_jobs,
+                                    bwagpu_cigar_out *outs, uint32_t *cigar, int64_t cigar_cap, char *md, int64_t md_cap,
+                                    int64_t *n_cigar_total, int64_t *md_bytes)
+{
+    if (!ctx) return BWAGPU_ERR_ARG;
+    if (!opt || !n_cigar_total || !md_bytes || nseq < 0 || n_jobs < 0) BWAGPU_FAIL(ctx, BWAGPU_ERR_ARG, "reg2aln_batch: bad argument");
+    if (!ctx->d_ref_string) BWAGPU_FAIL(ctx, BWAGPU_ERR_ARG, "reg2aln_batch: no reference loaded (bwagpu_index_load_ref)");
+    if (opt->e_del <= 0 || opt->e_ins <= 0 || opt->w < 0) BWAGPU_FAIL(ctx, BWAGPU_ERR_ARG, "reg2aln_batch: gap extension penalties must be positive");
+    *n_cigar_total = 0; *md_bytes = 0;
+    if (n_jobs == 0) return BWAGPU_OK;
+    if (!enc_reads || !off || !len || !jobs || !outs) BWAGPU_FAIL(ctx, BWAGPU_ERR_ARG, "reg2aln_batch: NULL buffer");
+    BWAGPU_CUDA(ctx, cudaSetDevice(ctx->device));
+    int64_t bytes = 0;
+    for (int i = 0; i < nseq; ++i) {
+        if (len[i] < 0 || off[i] < 0) BWAGPU_FAIL(ctx, BWAGPU_ERR_ARG, "reg2aln_batch: read %d has a negative length/offset", i);
+        if (off[i] + len[i] > bytes) bytes = off[i] + len[i];
+    }
+    for (int64_t j = 0; j < n_jobs; ++j) {
+        const bwagpu_cigar_job &b = jobs[j];
+        if (b.read < 0 || b.read >= nseq || b.qb < 0 || b.qe > len[b.read] || b.qb > b.qe || b.re - b.rb > (1 << 20))
+            BWAGPU_FAIL(ctx, BWAGPU_ERR_ARG, "reg2aln_batch: job %lld is out of range", (long long)j);
+    }
+    CigarOpt o;
+    memcpy(o.mat, opt->mat, 25);
+    o.a = opt->a; o.o_del = opt->o_del; o.e_del = opt->e_del; o.o_ins = opt->o_ins; o.e_ins = opt->e_ins; o.w = opt->w;
+    uint8_t *d_reads; int64_t *d_off; int32_t *d_len;
+    int rc;
+    if ((rc = bwagpu_scratch(ctx, SCR_SEED_READS, bytes + 16, (void **)&d_reads))) return rc;
+    if ((rc = bwagpu_scratch(ctx, SCR_SEED_OFF, (int64_t)nseq * 8, (void **)&d_off))) return rc;
+    if ((rc = bwagpu_scratch(ctx, SCR_SEED_LEN, (int64_t)nseq * 4, (void **)&d_len))) return rc;
+    BWAGPU_CUDA(ctx, cudaMemcpyAsync(d_reads, enc_reads, (size_t)bytes, cudaMemcpyHostToDevice, ctx->stream));
+    BWAGPU_CUDA(ctx, cudaMemcpyAsync(d_off, off, (size_t)nseq * 8, cudaMemcpyHostToDevice, ctx->stream));
+    BWAGPU_CUDA(ctx, cudaMemcpyAsync(d_len, len, (size_t)nseq * 4, cudaMemcpyHostToDevice, ctx->stream));
+    const int64_t budget = 4LL << 30;                         // slab bytes per chunk
+    CigSlabOff *h_so = (CigSlabOff *)malloc(sizeof(CigSlabOff) * (size_t)n_jobs);
+    if (!h_so) BWAGPU_FAIL(ctx, BWAGPU_ERR_NOMEM, "reg2aln_batch: host allocation failed");
+    int64_t cbase = 0, mbase = 0;
+    bool fits = true;
+    for (int64_t j0 = 0; j0 < n_jobs;) {
+        CigSlabOff cur = {0, 0, 0, 0};
+        int64_t j1 = j0;
+        while (j1 < n_jobs) {
+            const bwagpu_cigar_job &b = jobs[j1];
+            const int64_t lq = b.qe - b.qb, lt = b.re > b.rb ? b.re - b.rb : 0;
+            const int64_t zb = lq * lt;
+            if (j1 > j0 && cur.z + zb + (cur.eh + cur.cigar) * 4 + cur.md > budget) break;
+            h_so[j1] = cur;
+            cur.eh += 2 * (lq + 1); cur.z += zb; cur.cigar += lq + lt + 4; cur.md += 3 * lt + 16;
+            ++j1;
+        }
+        const int64_t n = j1 - j0;
+        bwagpu_cigar_job *d_jobs; bwagpu_cigar_out *d_out; CigSlabOff *d_so; int32_t *d_eh; uint8_t *d_z; uint32_t *d_cig; char *d_md;
+        int64_t *d_cnt, *d_scan; uint32_t *d_oc; char *d_om;
+        #define CIG_TRY(x) do { if ((rc = (x))) { free(h_so); return rc; } } while (0)
+        CIG_TRY(bwagpu_scratch(ctx, SCR_CIG_JOBS, n * (int64_t)sizeof(bwagpu_cigar_job), (void **)&d_jobs));
+        CIG_TRY(bwagpu_scratch(ctx, SCR_CIG_OUT, n * (int64_t)sizeof(bwagpu_cigar_out), (void **)&d_out));
+        CIG_TRY(bwagpu_scratch(ctx, SCR_CIG_SLABOFF, n * (int64_t)sizeof(CigSlabOff), (void **)&d_so));
+        CIG_TRY(bwagpu_scratch(ctx, SCR_CIG_EH, cur.eh * 4 + 16, (void **)&d_eh));
+        CIG_TRY(bwagpu_scratch(ctx, SCR_CIG_Z, cur.z + 16, (void **)&d_z));
+        CIG_TRY(bwagpu_scratch(ctx, SCR_CIG_CIGAR, cur.cigar * 4 + 16, (void **)&d_cig));
+        CIG_TRY(bwagpu_scratch(ctx, SCR_CIG_MD, cur.md + 16, (void **)&d_md));
+        CIG_TRY(bwagpu_scratch(ctx, SCR_CIG_CNT, (n + 1) * 16, (void **)&d_cnt));
+        CIG_TRY(bwagpu_scratch(ctx, SCR_CIG_SCAN, (n + 1) * 16, (void **)&d_scan));
+        cudaError_t e = cudaMemcpyAsync(d_jobs, jobs + j0, (size_t)n * sizeof(bwagpu_cigar_job), cudaMemcpyHostToDevice, ctx->stream);
+        if (e == cudaSuccess) e = cudaMemcpyAsync(d_so, h_so + j0, (size_t)n * sizeof(CigSlabOff), cudaMemcpyHostToDevice, ctx->stream);
+        if (e == cudaSuccess) e = cudaMemsetAsync(d_cnt, 0, (size_t)(n + 1) * 16, ctx->stream);
+        if (e != cudaSuccess) { free(h_so); BWAGPU_FAIL(ctx, BWAGPU_ERR_CUDA, "reg2aln_batch: upload -> %s", cudaGetErrorString(e)); }
+        BWAGPU_KERNEL_BEGIN(ctx);
+        cigar_kernel<<<(unsigned)((n + 63) / 64), 64, 0, ctx->stream>>>(o, ctx->l_pac, (const uint8_t *)ctx->d_ref_string, d_reads, d_off, d_len,
+                                                                       d_jobs, n, d_so, d_eh, d_z, d_cig, d_md, d_out, d_cnt, d_cnt + n + 1);
+        BWAGPU_KERNEL_END(ctx, BWAGPU_KERN_CIGAR);
+        CIG_TRY(cig_scan(ctx, d_cnt, d_scan, n + 1));
+        CIG_TRY(cig_scan(ctx, d_cnt + n + 1, d_scan + n + 1, n + 1));
+        int64_t tot[2] = {0, 0};
+        e = cudaMemcpyAsync(&tot[0], d_scan + n, 8, cudaMemcpyDeviceToHost, ctx->stream);
+        if (e == cudaSuccess) e = cudaMemcpyAsync(&tot[1], d_scan + 2 * n + 1, 8, cudaMemcpyDeviceToHost, ctx->stream);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+        if (e != cudaSuccess) { free(h_so); BWAGPU_FAIL(ctx, BWAGPU_ERR_CUDA, "reg2aln_batch: kernel -> %s", cudaGetErrorString(e)); }
+        CIG_TRY(bwagpu_scratch(ctx, SCR_CIG_OUTC, tot[0] * 4 + 16, (void **)&d_oc));
+        CIG_TRY(bwagpu_scratch(ctx, SCR_CIG_OUTM, tot[1] + 16, (void **)&d_om));
+        BWAGPU_KERNEL_BEGIN(ctx);
+        cigar_emit_kernel<<<(unsigned)((n + 127) / 128), 128, 0, ctx->stream>>>(n, d_so, d_cig, d_md, d_scan, d_scan + n + 1, cbase, mbase,
+                                                                               d_out, d_oc, d_om);
+        BWAGPU_KERNEL_END(ctx, BWAGPU_KERN_CIGAR);
+        e = cudaMemcpyAsync(outs + j0, d_out, (size_t)n * sizeof(bwagpu_cigar_out), cudaMemcpyDeviceToHost, ctx->stream);
+        if (cbase + tot[0] > cigar_cap || mbase + tot[1] > md_cap) fits = false;
+        if (fits && e == cudaSuccess && tot[0] > 0) e = cudaMemcpyAsync(cigar + cbase, d_oc, (size_t)tot[0] * 4, cudaMemcpyDeviceToHost, ctx->stream);
+        if (fits && e == cudaSuccess && tot[1] > 0) e = cudaMemcpyAsync(md + mbase, d_om, (size_t)tot[1], cudaMemcpyDeviceToHost, ctx->stream);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+        if (e != cudaSuccess) { free(h_so); BWAGPU_FAIL(ctx, BWAGPU_ERR_CUDA, "reg2aln_batch: copy back -> %s", cudaGetErrorString(e)); }
+        cbase += tot[0]; mbase += tot[1];
+        j0 = j1;
+    }
+    free(h_so);
+    *n_cigar_total = cbase; *md_bytes = mbase;
+    if (!fits) BWAGPU_FAIL(ctx, BWAGPU_ERR_RANGE, "reg2aln_batch: %lld cigar ops / %lld MD bytes do not fit the output buffers", (long long)cbase, (long long)mbase);
+    return BWAGPU_OK;
+}

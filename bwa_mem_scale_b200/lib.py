@@ -68,6 +68,11 @@ class SeedResult(C.Structure):
                 ("n_cp_records", C.c_int64), ("n_lf_steps", C.c_int64), ("d_smem_off", C.c_void_p)]
 
 
+class CigarOpt(C.Structure):
+    """bwagpu_cigar_opt"""
+    _fields_ = [("mat", C.c_int8 * 25), ("pad_", C.c_int8 * 3)] + [(n, C.c_int32) for n in ("a", "o_del", "e_del", "o_ins", "e_ins", "w")]
+
+
 class ErtResult(C.Structure):
     """bwagpu_ert_result"""
     _fields_ = [("d_smems", C.c_void_p), ("n_smem", C.c_int64), ("d_coords", C.c_void_p),
@@ -120,6 +125,9 @@ _SIGS = {
     "bwagpu_chain_mems_device": (C.c_int, [C.c_void_p, C.POINTER(ChainOpt), C.c_void_p, C.c_int64, C.c_void_p,
                                            C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32,
                                            C.POINTER(ChainResult)]),
+    "bwagpu_reg2aln_batch": (C.c_int, [C.c_void_p, C.POINTER(CigarOpt), C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32,
+                                       C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_int64,
+                                       C.POINTER(C.c_int64), C.POINTER(C.c_int64)]),
     "bwagpu_index_load_ert": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_int64]),
     "bwagpu_index_unload_ert": (C.c_int, [C.c_void_p]),
     "bwagpu_index_complete_ert": (C.c_int, [C.c_void_p]),

@@ -46,7 +46,7 @@ int bwagpu_timer_stop(bwagpu_ctx *ctx, float *elapsed_ms);   /* records, synchro
  * leave it off when measuring whole-step throughput).  set_profiling also clears the counters. */
 enum { BWAGPU_KERN_SEED_COLLECT = 0, BWAGPU_KERN_SEED_SORT = 1, BWAGPU_KERN_SA_WALK = 2,
        BWAGPU_KERN_BSW = 3, BWAGPU_KERN_BSW_GENERIC = 4, BWAGPU_KERN_FMA_BUILD = 5, BWAGPU_KERN_KSW = 6, BWAGPU_KERN_C2A = 7, BWAGPU_KERN_CHAIN = 8, BWAGPU_KERN_EMF = 9,
-       BWAGPU_KERN_ERT_SEED = 10, BWAGPU_KERN_ERT_EMIT = 11,
+       BWAGPU_KERN_ERT_SEED = 10, BWAGPU_KERN_ERT_EMIT = 11, BWAGPU_KERN_CIGAR = 12,
        BWAGPU_KERN_N = 16 };
 int bwagpu_set_profiling(bwagpu_ctx *ctx, int on);
 int bwagpu_kernel_time(const bwagpu_ctx *ctx, int which, double *ms, int64_t *launches);
@@ -203,6 +203,25 @@ int bwagpu_chain2aln_device(bwagpu_ctx *ctx, const bwagpu_ext_opt *opt, const ui
                             const int64_t *d_off, const int32_t *d_len, int32_t nseq,
                             const bwagpu_chain *d_chains, int64_t n_chains, const bwagpu_seed *d_seeds,
                             int64_t n_seeds, bwagpu_c2a_result *res);
+
+/* ---- S4: CIGAR / NM / MD of final alignment regions -------------------------
+ * Replaces the alignment work of mem_reg2aln (reference src/bwamem.cpp:2533-2600): band inference, up to three
+ * bwa_gen_cigar2 tries (src/bwa.cpp:380-467) each running ksw_global2 (src/ksw.cpp:558-668) with backtrack, NM / MD,
+ * then position, removal of a leading / trailing deletion and soft clips.  One job per region that reaches
+ * mem_reg2aln (worker_sam); mapq, flags and the SAM text stay the reference's host code.
+ * job: the mem_alnreg_t fields read (rb, re, qb, qe, truesc, w) + the read it belongs to.
+ * out: pos = 0-based forward coordinate in the concatenated reference (bns_depos, shifted past a leading deletion),
+ *      is_rev, n_cigar BAM-encoded ops (len << 4 | op, op 0 M / 1 I / 2 D / 3 S) at cigar[cigar_off ..], NM, and the
+ *      NUL-terminated MD text at md[md_off ..]; ok = 0 where the reference would return a NULL cigar. */
+typedef struct { int64_t rb, re; int32_t read, qb, qe, truesc, w, pad_; } bwagpu_cigar_job;
+typedef struct { int64_t pos, cigar_off, md_off; int32_t is_rev, n_cigar, nm, l_md, score, ok; } bwagpu_cigar_out;
+typedef struct { int8_t mat[25]; int8_t pad_[3]; int32_t a, o_del, e_del, o_ins, e_ins, w; } bwagpu_cigar_opt;
+/* HOST buffers.  *n_cigar_total / *md_bytes always report the sizes needed; BWAGPU_ERR_RANGE (outs[] still filled,
+ * cigar / md not written) when cigar_cap / md_cap are too small. */
+int bwagpu_reg2aln_batch(bwagpu_ctx *ctx, const bwagpu_cigar_opt *opt, const uint8_t *enc_reads, const int64_t *off,
+                         const int32_t *len, int32_t nseq, const bwagpu_cigar_job *jobs, int64_t n_jobs,
+                         bwagpu_cigar_out *outs, uint32_t *cigar, int64_t cigar_cap, char *md, int64_t md_cap,
+                         int64_t *n_cigar_total, int64_t *md_bytes);
 
 /* ---- S3: mate-rescue local Smith-Waterman ------------------------------------------------------
  * bwagpu_kswr mirrors kswr_t (reference src/ksw.h), 28 bytes. */

@@ -306,6 +306,48 @@ int ref_mem_core(void *h, const int32_t *opt_i, const float *opt_f, int64_t max_
     return 0;
 }
 
+// ---- CIGAR tap: the reference's own mem_reg2aln (src/bwamem.cpp:2533-2627) over caller-provided regions -------------
+// job: rb, re, read, qb, qe, truesc, w (the mem_alnreg_t fields mem_reg2aln's alignment part reads).
+// out per job: pos, cigar_off, md_off, is_rev, n_cigar, NM, l_md, score (unused: 0), ok; cigar / md are appended.
+struct tap_cigar_job { int64_t rb, re; int32_t read, qb, qe, truesc, w, pad_; };
+struct tap_cigar_out { int64_t pos, cigar_off, md_off; int32_t is_rev, n_cigar, nm, l_md, score, ok; };
+int ref_reg2aln(void *h, const int32_t *opt_i, const uint8_t *reads, const int64_t *off, const int32_t *len,
+                const tap_cigar_job *jobs, int64_t n_jobs, tap_cigar_out *outs, uint32_t *cigar, int64_t cigar_cap,
+                char *md, int64_t md_cap, int64_t *n_out)
+{
+    ref_mem_ctx *c = (ref_mem_ctx *)h;
+    mem_opt_t *opt = mem_opt_init();
+    opt->a = opt_i[0]; opt->b = opt_i[1]; opt->o_del = opt_i[2]; opt->e_del = opt_i[3]; opt->o_ins = opt_i[4];
+    opt->e_ins = opt_i[5]; opt->w = opt_i[8];
+    bwa_fill_scmat(opt->a, opt->b, opt->mat);
+    const bntseq_t *bns = c->fmi->idx->bns;
+    int64_t nc = 0, nm = 0;
+    for (int64_t j = 0; j < n_jobs; ++j) {
+        const tap_cigar_job &b = jobs[j];
+        mem_alnreg_t ar;
+        memset(&ar, 0, sizeof ar);
+        ar.rb = b.rb; ar.re = b.re; ar.qb = b.qb; ar.qe = b.qe; ar.truesc = b.truesc; ar.score = b.truesc; ar.w = b.w;
+        ar.secondary = -1;
+        int is_rev;
+        ar.rid = bns_pos2rid(bns, bns_depos(bns, b.rb < bns->l_pac ? b.rb : b.re - 1, &is_rev));
+        mem_aln_t a = mem_reg2aln(opt, bns, c->fmi->idx->pac, len[b.read], (const char *)(reads + off[b.read]), &ar);
+        tap_cigar_out &o = outs[j];
+        memset(&o, 0, sizeof o);
+        o.pos = a.pos; o.is_rev = a.is_rev; o.n_cigar = a.n_cigar; o.nm = a.NM; o.ok = a.cigar != 0;
+        o.cigar_off = nc; o.md_off = nm;
+        if (a.cigar) {
+            const char *mdp = (const char *)(a.cigar + a.n_cigar);
+            o.l_md = (int32_t)strlen(mdp);
+            for (int k = 0; k < a.n_cigar; ++k, ++nc) if (nc < cigar_cap) cigar[nc] = a.cigar[k];
+            for (int k = 0; k <= o.l_md; ++k, ++nm) if (nm < md_cap) md[nm] = mdp[k];
+            free(a.cigar);
+        }
+    }
+    n_out[0] = nc; n_out[1] = nm;
+    free(opt);
+    return (nc <= cigar_cap && nm <= md_cap) ? 0 : -1;
+}
+
 #ifdef PERFECT_MATCH
 // ---- EMF tap: the reference's own find_perfect_match_entry (src/perfect_map.cpp:638-659) over a table
 // file written by its `perfect-index` sub-command.  The file is read here (header, loc_table,

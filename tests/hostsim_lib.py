@@ -8,18 +8,19 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 SRC = os.path.join(ROOT, "tests", "hostsim", "fmi_hostsim.cpp")
 SRC2 = os.path.join(ROOT, "tests", "hostsim", "chain_hostsim.cpp")
 SRC3 = os.path.join(ROOT, "tests", "hostsim", "ert_hostsim.cpp")
+SRC4 = os.path.join(ROOT, "tests", "hostsim", "cigar_hostsim.cpp")
 OUT = os.path.join(ROOT, "tests", "hostsim", "_build", "libhostsim.so")
 
 
 def load():
-    deps = [SRC, SRC2, SRC3, os.path.join(ROOT, "bwa_mem_scale_b200", "csrc", "fmi_core.cuh"),
+    deps = [SRC, SRC2, SRC3, SRC4, os.path.join(ROOT, "bwa_mem_scale_b200", "csrc", "cigar_core.cuh"), os.path.join(ROOT, "bwa_mem_scale_b200", "csrc", "fmi_core.cuh"),
             os.path.join(ROOT, "bwa_mem_scale_b200", "csrc", "ert_core.cuh"),
             os.path.join(ROOT, "bwa_mem_scale_b200", "csrc", "ert_build.cuh"),
             os.path.join(ROOT, "bwa_mem_scale_b200", "csrc", "chain_core.cuh"),
             os.path.join(ROOT, "include", "bwagpu.h")]
     if not os.path.exists(OUT) or any(os.path.getmtime(d) > os.path.getmtime(OUT) for d in deps):
         os.makedirs(os.path.dirname(OUT), exist_ok=True)
-        subprocess.run(["g++", "-O2", "-fPIC", "-shared", "-x", "c++", "-o", OUT, SRC, SRC2, SRC3], check=True)
+        subprocess.run(["g++", "-O2", "-fPIC", "-shared", "-x", "c++", "-o", OUT, SRC, SRC2, SRC3, SRC4], check=True)
     lib = C.CDLL(OUT)
     lib.hostsim_collect_smem.restype = C.c_int64
     lib.hostsim_sa_lookup.restype = C.c_int64
@@ -51,3 +52,23 @@ def ert_seed(lib, kmer, mlt, ref_string, flat, off, ln, min_seed_len=19, split_f
             ert_seed.last_bytes = int(n_out[2])
             return mems[:n_out[0]].copy(), hits[:n_out[1]].copy(), mem_off
         mem_cap, hit_cap = int(n_out[0]) + 16, int(n_out[1]) + 16
+
+
+def reg2aln(lib, copt, l_pac, ref_string, flat, off, ln, jobs):
+    """The CIGAR code of the CUDA kernel (csrc/cigar_core.cuh) run job by job on the host: (outs, cigar, md)."""
+    import numpy as np
+    from oracle_lib import CIGAR_JOB_DTYPE, CIGAR_OUT_DTYPE
+    jobs = np.ascontiguousarray(jobs, CIGAR_JOB_DTYPE)
+    outs = np.zeros(len(jobs), CIGAR_OUT_DTYPE)
+    ccap, mcap = 8 * len(jobs) + 64, 32 * len(jobs) + 64
+    lib.hostsim_reg2aln.restype = C.c_int
+    lib.hostsim_reg2aln.argtypes = [C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                    C.c_int64, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_int64, C.c_void_p]
+    while True:
+        cigar, md, n_out = np.zeros(ccap, np.uint32), np.zeros(mcap, np.uint8), np.zeros(2, np.int64)
+        lib.hostsim_reg2aln(C.byref(copt), l_pac, ref_string.ctypes.data, flat.ctypes.data, off.ctypes.data, ln.ctypes.data,
+                            jobs.ctypes.data, len(jobs), outs.ctypes.data, cigar.ctypes.data, ccap, md.ctypes.data, mcap,
+                            n_out.ctypes.data)
+        if n_out[0] <= ccap and n_out[1] <= mcap:
+            return outs, cigar[:n_out[0]].copy(), md[:n_out[1]].copy()
+        ccap, mcap = int(n_out[0]) + 16, int(n_out[1]) + 16

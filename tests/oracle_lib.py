@@ -565,3 +565,28 @@ class RefErt:
     def close(self):
         self.lib.ref_ert_close(self.h)
         self.h = None
+
+
+# ---- CIGAR generation (reference mem_reg2aln through oracle/refwrap/ref_api_wrap.cpp) ---------------------------
+CIGAR_JOB_DTYPE = np.dtype([("rb", "<i8"), ("re", "<i8"), ("read", "<i4"), ("qb", "<i4"), ("qe", "<i4"), ("truesc", "<i4"),
+                            ("w", "<i4"), ("pad_", "<i4")])
+CIGAR_OUT_DTYPE = np.dtype([("pos", "<i8"), ("cigar_off", "<i8"), ("md_off", "<i8"), ("is_rev", "<i4"), ("n_cigar", "<i4"),
+                            ("nm", "<i4"), ("l_md", "<i4"), ("score", "<i4"), ("ok", "<i4")])
+
+
+def reference_reg2aln(rm: "RefMem", opt, flat, off, ln, jobs):
+    """The reference's own mem_reg2aln over `jobs` (CIGAR_JOB_DTYPE): (outs, cigar, md)."""
+    lib = rm.lib
+    lib.ref_reg2aln.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64,
+                                C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_int64, C.c_void_p]
+    oi, _ = opt_arrays(opt)
+    jobs = np.ascontiguousarray(jobs, CIGAR_JOB_DTYPE)
+    outs = np.zeros(len(jobs), CIGAR_OUT_DTYPE)
+    ccap, mcap = 8 * len(jobs) + 64, 32 * len(jobs) + 64
+    while True:
+        cigar, md, n_out = np.zeros(ccap, np.uint32), np.zeros(mcap, np.uint8), np.zeros(2, np.int64)
+        lib.ref_reg2aln(rm.h, oi.ctypes.data, flat.ctypes.data, off.ctypes.data, ln.ctypes.data, jobs.ctypes.data, len(jobs),
+                        outs.ctypes.data, cigar.ctypes.data, ccap, md.ctypes.data, mcap, n_out.ctypes.data)
+        if n_out[0] <= ccap and n_out[1] <= mcap:
+            return outs, cigar[:n_out[0]].copy(), md[:n_out[1]].copy()
+        ccap, mcap = int(n_out[0]) + 16, int(n_out[1]) + 16
