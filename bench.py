@@ -768,6 +768,109 @@ def bench_ksw(args, rank, world):
 _dist = None
 
 
+def bench_cigar(args, rank, world):
+    """CIGAR / NM / MD of final alignment regions: jobs = the regions the device pipeline keeps
+    for the default workload's reads, with 0.2 % indels added so that the banded global alignment runs; one step =
+    bwagpu_reg2aln_batch over all of them (host buffers in and out: this seam has no device-resident form yet)."""
+    from bwa_mem_scale_b200 import (CIGAR_JOB_DTYPE, Context, Extender, FMI_search, REG_DTYPE, RegToAln, chain_opt, cigar_opt,
+                                    ext_opt, fmindex, mem_core_device, pack_reads, seed_opt)
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    ref, idx, reads = seed_inputs(args, rank)
+    rng = np.random.default_rng(900 + rank)
+    reads = np.ascontiguousarray(reads).copy()
+    for i in np.flatnonzero(rng.random(len(reads)) < 0.25):          # one short deletion-like shift in a quarter of the reads
+        p, k = int(rng.integers(20, 120)), int(rng.integers(1, 4))
+        reads[i, p:-k] = reads[i, p + k:]
+        reads[i, -k:] = rng.integers(0, 4, k)
+    n = len(reads)
+    cfg = {"workload": f"CIGAR/NM/MD generation (mem_reg2aln): regions kept by seed+extend for {n} x 151 bp reads/GPU on the "
+                       f"{args.ref_mbp:g} Mbp synthetic reference, 25 % of the reads with a 1-3 base indel", "reads_per_gpu": n,
+           "l2_policy": "inputs and backtrack slabs larger than L2"}
+    local = int(os.environ.get("LOCAL_RANK", rank))
+    ctx = Context(local)
+    fmi = FMI_search(idx, ctx=ctx)
+    ref_string = fmindex.text_with_revcomp(ref)
+    ext = Extender(ref_string, len(ref), [0], [len(ref)], ctx=ctx)
+    flat, off, ln = pack_reads(reads)
+    d = (ctx.upload(flat), ctx.upload(off), ctx.upload(ln))
+    sres, cres, ares = mem_core_device(fmi, ext, seed_opt(), chain_opt(), ext_opt(), d[0], d[1], d[2], n, 151)
+    import oracle_lib as ol
+    regs, chains = np.zeros(ares.n_regs, REG_DTYPE), np.zeros(cres.n_chains, ol.CHAIN_DTYPE)
+    ctx.d2h(regs, ares.d_regs); ctx.d2h(chains, cres.d_chains)
+    keep = ~((regs["qb"] == -1) & (regs["qe"] == -1))
+    r = regs[keep]
+    jobs = np.zeros(len(r), CIGAR_JOB_DTYPE)
+    for f in ("rb", "re", "qb", "qe", "truesc", "w"):
+        jobs[f] = r[f]
+    jobs["read"] = chains["seqid"][r["chain"]]
+    cfg["jobs_per_gpu"] = int(len(jobs))
+    if args.impl == "reference" or not args.no_cpu:
+        import tempfile
+        thr = cpu_threads()
+        sample = jobs[: min(len(jobs), 40000 * thr)]
+        with tempfile.TemporaryDirectory() as td:
+            prefix = os.path.join(td, "ref")
+            fmindex.write_index_files(prefix, ref, idx)
+            rm0 = ol.RefMem(prefix)
+            workers = [rm0] + [rm0.clone() for _ in range(thr - 1)]
+            parts = [c for c in np.array_split(np.arange(len(sample)), thr) if len(c)]
+            from concurrent.futures import ThreadPoolExecutor
+            def work(a):
+                ol.reference_reg2aln(a[0], ol.mem_opt(), flat, off, ln, sample[a[1]])
+            t0 = time.perf_counter()
+            reps = args.steps if args.impl == "reference" else 1
+            for _ in range(reps):
+                with ThreadPoolExecutor(thr) as ex:
+                    list(ex.map(work, zip(workers, parts)))
+            dt = (time.perf_counter() - t0) / reps
+        cpu = {"value": len(sample) / dt, "unit": "regions/s", "cores": thr, "kind": "reference",
+               "sample": f"{len(sample)} regions of the same set, the reference's own mem_reg2aln, {dt:.1f}s"}
+        if args.impl == "reference":
+            if rank != 0:
+                return None
+            return {"impl": "reference", "metric": "regions/s (CIGAR/NM/MD generation)", "value": cpu["value"], "unit": "regions/s",
+                    "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt, "higher_is_better": True,
+                    "scaling": "weak", "vs_baseline": None, "dtype": "int32", "data": "synthetic", "config": cfg, "cpu_baseline": cpu,
+                    "e2e": {"value": cpu["value"], "unit": "regions/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    r2a, co = RegToAln(ctx), cigar_opt()
+    for _ in range(args.warmup):
+        outs, cigar, md = r2a.mem_reg2aln(co, flat, off, ln, jobs)
+    barrier()
+    sampler = ClockSampler(local)
+    sampler.start()
+    l0 = ctx.launch_count()
+    ctx.set_profiling(True)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        outs, cigar, md = r2a.mem_reg2aln(co, flat, off, ln, jobs)
+    e2e_s = allreduce_max(time.perf_counter() - t0)
+    k_ms, k_n = ctx.kernel_time(12)
+    ctx.set_profiling(False)
+    launches = ctx.launch_count() - l0
+    clocks = sampler.stop()
+    if rank != 0:
+        return None
+    pk, pk_kind = peaks()
+    dp = outs["n_cigar"] > 1
+    alg = float(((jobs["qe"] - jobs["qb"]).astype(np.int64) + (jobs["re"] - jobs["rb"])).sum() + cigar.nbytes + md.nbytes)
+    ms = allreduce_max(k_ms) / args.steps
+    res = {"metric": "regions/s (CIGAR/NM/MD generation)", "value": len(jobs) * world / (ms * 1e-3), "unit": "regions/s",
+           "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
+           "vs_baseline": None, "dtype": "int32", "data": "synthetic", "config": cfg, "clocks": clocks, "gpu_launches": int(launches),
+           "e2e": {"value": len(jobs) * world * args.steps / e2e_s, "unit": "regions/s",
+                   "h2d_bytes_per_step": int(flat.nbytes + off.nbytes + ln.nbytes + jobs.nbytes),
+                   "d2h_bytes_per_step": int(outs.nbytes + cigar.nbytes + md.nbytes)},
+           "roofline": {"bound": "hbm", "kernel": "cigar_kernel + cigar_emit_kernel", "achieved": alg / (ms * 1e-3) / 1e9, "peak": pk["hbm_gbs"],
+                        "unit": "GB/s", "frac": alg / (ms * 1e-3) / 1e9 / pk["hbm_gbs"], "traffic": None, "peak_kind": pk_kind,
+                        "kernel_ms": ms, "algorithmic_bytes": int(alg),
+                        "note": "value = device time of the two kernels; e2e = the host-buffer call (uploads, chunking, copies back)"},
+           "work": {"regions_per_read": len(jobs) / n, "multi_op_frac": float(dp.mean()), "cigar_ops_per_region": len(cigar) / len(jobs),
+                    "md_bytes_per_region": len(md) / len(jobs)}}
+    if not args.no_cpu:
+        res["cpu_baseline"] = cpu
+    return res
+
+
 def init_dist(world):
     global _dist
     if world > 1:
@@ -801,7 +904,7 @@ def main():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="mem", choices=["mem", "bsw", "seed", "ksw"])
+    ap.add_argument("--workload", default="mem", choices=["mem", "bsw", "seed", "ksw", "cigar"])
     ap.add_argument("--ref-mbp", type=float, default=100.0)
     ap.add_argument("--reads", type=int, default=1_000_000)
     ap.add_argument("--pairs", type=int, default=1_000_000)
@@ -816,7 +919,7 @@ def main():
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", 0))
     world = int(os.environ.get("WORLD_SIZE", 1))
-    fn = {"mem": bench_mem, "bsw": bench_bsw, "seed": bench_seed, "ksw": bench_ksw}[args.workload]
+    fn = {"mem": bench_mem, "bsw": bench_bsw, "seed": bench_seed, "ksw": bench_ksw, "cigar": bench_cigar}[args.workload]
     if args.impl == "reference":
         if rank == 0:
             print(json.dumps(fn(args, 0, world)))

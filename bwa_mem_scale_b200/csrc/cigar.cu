@@ -5,20 +5,32 @@
 // processed in chunks so that the slabs stay below a fixed budget.  Results are compacted by a scan + copy kernel.
 #include <cub/device/device_scan.cuh>
 #include <stdlib.h>
+#include <algorithm>
 #include "ctx.cuh"
 #include "cigar_core.cuh"
 
 struct CigSlabOff { int64_t eh, z, cigar, md; };
 
-__global__ void cigar_kernel(CigarOpt o, int64_t l_pac, const uint8_t *__restrict__ ref_string, const uint8_t *__restrict__ reads,
-                             const int64_t *__restrict__ off, const int32_t *__restrict__ len, const bwagpu_cigar_job *__restrict__ jobs,
-                             int64_t n, const CigSlabOff *__restrict__ so, int32_t *eh, uint8_t *z, uint32_t *cigar, char *md,
-                             bwagpu_cigar_out *outs, int64_t *cnt_cigar, int64_t *cnt_md)
+#define CIG_TPB 64
+#define CIG_SMEM_QLEN 151                      // H/E rows of reads up to this length live in shared memory
+
+// thread t of the launch handles job order[t] (jobs sorted by the host: gap-free ones first, then by DP size, so that
+// the lanes of a warp run similar trip counts); results land at the job's own index
+__global__ void __launch_bounds__(CIG_TPB)
+cigar_kernel(CigarOpt o, int64_t l_pac, const uint8_t *__restrict__ ref_string, const uint8_t *__restrict__ reads,
+             const int64_t *__restrict__ off, const int32_t *__restrict__ len, const bwagpu_cigar_job *__restrict__ jobs,
+             const int32_t *__restrict__ order, int64_t first, int64_t n, const CigSlabOff *__restrict__ so, int32_t *eh, uint8_t *z, uint32_t *cigar,
+             char *md, bwagpu_cigar_out *outs, int64_t *cnt_cigar, int64_t *cnt_md)
 {
-    const int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (j >= n) return;
+    extern __shared__ int32_t cig_smem[];
+    const int64_t t = first + (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= n) return;
+    const int64_t j = order[t];
     const bwagpu_cigar_job jb = jobs[j];
-    CigarScratch sc = { eh + so[j].eh, z + so[j].z, cigar + so[j].cigar, md + so[j].md };
+    CigarScratch sc;
+    if (jb.qe - jb.qb <= CIG_SMEM_QLEN) { sc.eh = cig_smem + threadIdx.x; sc.eh_stride = CIG_TPB; }
+    else { sc.eh = eh + so[j].eh; sc.eh_stride = 1; }
+    sc.z = z + so[j].z; sc.cigar = cigar + so[j].cigar; sc.md = md + so[j].md;
     CigarResult r;
     r.score = 0;
     bwagpu_cigar_out out;
@@ -96,9 +108,13 @@ extern "C" int bwagpu_reg2aln_batch(bwagpu_ctx *ctx, const bwagpu_cigar_opt *opt
     BWAGPU_CUDA(ctx, cudaMemcpyAsync(d_reads, enc_reads, (size_t)bytes, cudaMemcpyHostToDevice, ctx->stream));
     BWAGPU_CUDA(ctx, cudaMemcpyAsync(d_off, off, (size_t)nseq * 8, cudaMemcpyHostToDevice, ctx->stream));
     BWAGPU_CUDA(ctx, cudaMemcpyAsync(d_len, len, (size_t)nseq * 4, cudaMemcpyHostToDevice, ctx->stream));
+    const size_t smem_bytes = (size_t)2 * (CIG_SMEM_QLEN + 1) * CIG_TPB * 4;
+    BWAGPU_CUDA(ctx, cudaFuncSetAttribute(cigar_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
     const int64_t budget = 4LL << 30;                         // slab bytes per chunk
     CigSlabOff *h_so = (CigSlabOff *)malloc(sizeof(CigSlabOff) * (size_t)n_jobs);
-    if (!h_so) BWAGPU_FAIL(ctx, BWAGPU_ERR_NOMEM, "reg2aln_batch: host allocation failed");
+    uint64_t *h_key = (uint64_t *)malloc(8 * (size_t)n_jobs);
+    int32_t *h_order = (int32_t *)malloc(4 * (size_t)n_jobs);
+    if (!h_so || !h_key || !h_order) { free(h_so); free(h_key); free(h_order); BWAGPU_FAIL(ctx, BWAGPU_ERR_NOMEM, "reg2aln_batch: host allocation failed"); }
     int64_t cbase = 0, mbase = 0;
     bool fits = true;
     for (int64_t j0 = 0; j0 < n_jobs;) {
@@ -107,16 +123,20 @@ extern "C" int bwagpu_reg2aln_batch(bwagpu_ctx *ctx, const bwagpu_cigar_opt *opt
         while (j1 < n_jobs) {
             const bwagpu_cigar_job &b = jobs[j1];
             const int64_t lq = b.qe - b.qb, lt = b.re > b.rb ? b.re - b.rb : 0;
-            const int64_t zb = lq * lt;
+            const bool gapfree = cig_is_gapfree(o, b.qb, b.qe, b.rb, b.re, b.truesc, b.w);
+            const int64_t zb = gapfree ? 0 : lq * lt;
             if (j1 > j0 && cur.z + zb + (cur.eh + cur.cigar) * 4 + cur.md > budget) break;
             h_so[j1] = cur;
-            cur.eh += 2 * (lq + 1); cur.z += zb; cur.cigar += lq + lt + 4; cur.md += 3 * lt + 16;
+            if (lq > CIG_SMEM_QLEN) cur.eh += 2 * (lq + 1);
+            cur.z += zb; cur.cigar += lq + lt + 4; cur.md += 3 * lt + 16;
+            // sort key: gap-free jobs first, the others by the size of their backtrack matrix
+            h_key[j1 - j0] = ((uint64_t)(gapfree ? 0 : 1 + (zb < (1 << 30) ? zb : (1 << 30))) << 32) | (uint32_t)(j1 - j0);
             ++j1;
         }
         const int64_t n = j1 - j0;
         bwagpu_cigar_job *d_jobs; bwagpu_cigar_out *d_out; CigSlabOff *d_so; int32_t *d_eh; uint8_t *d_z; uint32_t *d_cig; char *d_md;
         int64_t *d_cnt, *d_scan; uint32_t *d_oc; char *d_om;
-        #define CIG_TRY(x) do { if ((rc = (x))) { free(h_so); return rc; } } while (0)
+        #define CIG_TRY(x) do { if ((rc = (x))) { free(h_so); free(h_key); free(h_order); return rc; } } while (0)
         CIG_TRY(bwagpu_scratch(ctx, SCR_CIG_JOBS, n * (int64_t)sizeof(bwagpu_cigar_job), (void **)&d_jobs));
         CIG_TRY(bwagpu_scratch(ctx, SCR_CIG_OUT, n * (int64_t)sizeof(bwagpu_cigar_out), (void **)&d_out));
         CIG_TRY(bwagpu_scratch(ctx, SCR_CIG_SLABOFF, n * (int64_t)sizeof(CigSlabOff), (void **)&d_so));
@@ -126,13 +146,28 @@ extern "C" int bwagpu_reg2aln_batch(bwagpu_ctx *ctx, const bwagpu_cigar_opt *opt
         CIG_TRY(bwagpu_scratch(ctx, SCR_CIG_MD, cur.md + 16, (void **)&d_md));
         CIG_TRY(bwagpu_scratch(ctx, SCR_CIG_CNT, (n + 1) * 16, (void **)&d_cnt));
         CIG_TRY(bwagpu_scratch(ctx, SCR_CIG_SCAN, (n + 1) * 16, (void **)&d_scan));
-        cudaError_t e = cudaMemcpyAsync(d_jobs, jobs + j0, (size_t)n * sizeof(bwagpu_cigar_job), cudaMemcpyHostToDevice, ctx->stream);
+        std::sort(h_key, h_key + n);
+        for (int64_t k = 0; k < n; ++k) h_order[k] = (int32_t)(h_key[k] & 0xFFFFFFFFu);
+        int32_t *d_order;
+        CIG_TRY(bwagpu_scratch(ctx, SCR_CIG_ORDER, n * 4, (void **)&d_order));
+        cudaError_t e = cudaMemcpyAsync(d_order, h_order, (size_t)n * 4, cudaMemcpyHostToDevice, ctx->stream);
+        if (e == cudaSuccess) e = cudaMemcpyAsync(d_jobs, jobs + j0, (size_t)n * sizeof(bwagpu_cigar_job), cudaMemcpyHostToDevice, ctx->stream);
         if (e == cudaSuccess) e = cudaMemcpyAsync(d_so, h_so + j0, (size_t)n * sizeof(CigSlabOff), cudaMemcpyHostToDevice, ctx->stream);
         if (e == cudaSuccess) e = cudaMemsetAsync(d_cnt, 0, (size_t)(n + 1) * 16, ctx->stream);
-        if (e != cudaSuccess) { free(h_so); BWAGPU_FAIL(ctx, BWAGPU_ERR_CUDA, "reg2aln_batch: upload -> %s", cudaGetErrorString(e)); }
+        if (e != cudaSuccess) { free(h_so); free(h_key); free(h_order); BWAGPU_FAIL(ctx, BWAGPU_ERR_CUDA, "reg2aln_batch: upload -> %s", cudaGetErrorString(e)); }
+        // gap-free jobs (sorted first) need no DP rows: launched without shared memory, at full occupancy
+        int64_t n_gf = 0;
+        while (n_gf < n && (h_key[n_gf] >> 32) == 0) ++n_gf;
         BWAGPU_KERNEL_BEGIN(ctx);
-        cigar_kernel<<<(unsigned)((n + 63) / 64), 64, 0, ctx->stream>>>(o, ctx->l_pac, (const uint8_t *)ctx->d_ref_string, d_reads, d_off, d_len,
-                                                                       d_jobs, n, d_so, d_eh, d_z, d_cig, d_md, d_out, d_cnt, d_cnt + n + 1);
+        if (n_gf > 0)
+            cigar_kernel<<<(unsigned)((n_gf + CIG_TPB - 1) / CIG_TPB), CIG_TPB, 0, ctx->stream>>>(
+                o, ctx->l_pac, (const uint8_t *)ctx->d_ref_string, d_reads, d_off, d_len, d_jobs, d_order, 0, n_gf, d_so, d_eh, d_z, d_cig,
+                d_md, d_out, d_cnt, d_cnt + n + 1);
+        if (n > n_gf)
+            cigar_kernel<<<(unsigned)((n - n_gf + CIG_TPB - 1) / CIG_TPB), CIG_TPB, smem_bytes, ctx->stream>>>(
+                o, ctx->l_pac, (const uint8_t *)ctx->d_ref_string, d_reads, d_off, d_len, d_jobs, d_order, n_gf, n, d_so, d_eh, d_z, d_cig,
+                d_md, d_out, d_cnt, d_cnt + n + 1);
+        ctx->launches += (n_gf > 0 && n > n_gf) ? 1 : 0;
         BWAGPU_KERNEL_END(ctx, BWAGPU_KERN_CIGAR);
         CIG_TRY(cig_scan(ctx, d_cnt, d_scan, n + 1));
         CIG_TRY(cig_scan(ctx, d_cnt + n + 1, d_scan + n + 1, n + 1));
@@ -140,7 +175,7 @@ extern "C" int bwagpu_reg2aln_batch(bwagpu_ctx *ctx, const bwagpu_cigar_opt *opt
         e = cudaMemcpyAsync(&tot[0], d_scan + n, 8, cudaMemcpyDeviceToHost, ctx->stream);
         if (e == cudaSuccess) e = cudaMemcpyAsync(&tot[1], d_scan + 2 * n + 1, 8, cudaMemcpyDeviceToHost, ctx->stream);
         if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
-        if (e != cudaSuccess) { free(h_so); BWAGPU_FAIL(ctx, BWAGPU_ERR_CUDA, "reg2aln_batch: kernel -> %s", cudaGetErrorString(e)); }
+        if (e != cudaSuccess) { free(h_so); free(h_key); free(h_order); BWAGPU_FAIL(ctx, BWAGPU_ERR_CUDA, "reg2aln_batch: kernel -> %s", cudaGetErrorString(e)); }
         CIG_TRY(bwagpu_scratch(ctx, SCR_CIG_OUTC, tot[0] * 4 + 16, (void **)&d_oc));
         CIG_TRY(bwagpu_scratch(ctx, SCR_CIG_OUTM, tot[1] + 16, (void **)&d_om));
         BWAGPU_KERNEL_BEGIN(ctx);
@@ -152,11 +187,11 @@ extern "C" int bwagpu_reg2aln_batch(bwagpu_ctx *ctx, const bwagpu_cigar_opt *opt
         if (fits && e == cudaSuccess && tot[0] > 0) e = cudaMemcpyAsync(cigar + cbase, d_oc, (size_t)tot[0] * 4, cudaMemcpyDeviceToHost, ctx->stream);
         if (fits && e == cudaSuccess && tot[1] > 0) e = cudaMemcpyAsync(md + mbase, d_om, (size_t)tot[1], cudaMemcpyDeviceToHost, ctx->stream);
         if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
-        if (e != cudaSuccess) { free(h_so); BWAGPU_FAIL(ctx, BWAGPU_ERR_CUDA, "reg2aln_batch: copy back -> %s", cudaGetErrorString(e)); }
+        if (e != cudaSuccess) { free(h_so); free(h_key); free(h_order); BWAGPU_FAIL(ctx, BWAGPU_ERR_CUDA, "reg2aln_batch: copy back -> %s", cudaGetErrorString(e)); }
         cbase += tot[0]; mbase += tot[1];
         j0 = j1;
     }
-    free(h_so);
+    free(h_so); free(h_key); free(h_order);
     *n_cigar_total = cbase; *md_bytes = mbase;
     if (!fits) BWAGPU_FAIL(ctx, BWAGPU_ERR_RANGE, "reg2aln_batch: %lld cigar ops / %lld MD bytes do not fit the output buffers", (long long)cbase, (long long)mbase);
     return BWAGPU_OK;

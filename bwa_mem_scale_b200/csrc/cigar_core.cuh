@@ -19,7 +19,8 @@
 struct CigarOpt { int8_t mat[25]; int32_t a, o_del, e_del, o_ins, e_ins, w; };
 
 struct CigarScratch {
-    int32_t *eh;        // 2 x (qlen + 1): H and E rows of ksw_global2
+    int32_t *eh;        // 2 x (qlen + 1) words, element k at eh[k * eh_stride]: H and E rows of ksw_global2
+    int eh_stride;      // 1 for a private slab; blockDim for the interleaved shared-memory layout (bank = thread)
     uint8_t *z;         // backtrack matrix, n_col x tlen for the widest band tried
     uint32_t *cigar;    // qlen + tlen + 2 entries
     char *md;           // MD text, 3 x tlen + 16 bytes
@@ -66,11 +67,12 @@ CIG_HD inline int cig_global2(const CigarOpt &o, const CigarSeqs &s, int w, cons
     const int qlen = s.lq, tlen = s.lt;
     const int oe_del = o.o_del + o.e_del, oe_ins = o.o_ins + o.e_ins;
     const int n_col = qlen < 2 * w + 1 ? qlen : 2 * w + 1;
-    int32_t *H = sc.eh, *E = sc.eh + qlen + 1;
+    const int st = sc.eh_stride;
+    int32_t *H = sc.eh, *E = sc.eh + (int64_t)(qlen + 1) * st;
     H[0] = 0; E[0] = CIG_MINUS_INF;
     int j;
-    for (j = 1; j <= qlen && j <= w; ++j) { H[j] = -(o.o_ins + o.e_ins * j); E[j] = CIG_MINUS_INF; }
-    for (; j <= qlen; ++j) H[j] = E[j] = CIG_MINUS_INF;
+    for (j = 1; j <= qlen && j <= w; ++j) { H[j * st] = -(o.o_ins + o.e_ins * j); E[j * st] = CIG_MINUS_INF; }
+    for (; j <= qlen; ++j) H[j * st] = E[j * st] = CIG_MINUS_INF;
     for (int i = 0; i < tlen; ++i) {
         int32_t f = CIG_MINUS_INF, h1;
         const int8_t *mrow = o.mat + s.ta(i) * 5;
@@ -79,9 +81,9 @@ CIG_HD inline int cig_global2(const CigarOpt &o, const CigarSeqs &s, int w, cons
         h1 = beg == 0 ? -(o.o_del + o.e_del * (i + 1)) : CIG_MINUS_INF;
         uint8_t *zi = sc.z + (int64_t)i * n_col;
         for (j = beg; j < end; ++j) {
-            int32_t m = H[j], e = E[j], h, t;
+            int32_t m = H[j * st], e = E[j * st], h, t;
             uint8_t d;
-            H[j] = h1;
+            H[j * st] = h1;
             m += mrow[s.qa(j)];
             d = m >= e ? 0 : 1;
             h = m >= e ? m : e;
@@ -92,16 +94,16 @@ CIG_HD inline int cig_global2(const CigarOpt &o, const CigarSeqs &s, int w, cons
             e -= o.e_del;
             d |= e > t ? 1 << 2 : 0;
             e = e > t ? e : t;
-            E[j] = e;
+            E[j * st] = e;
             t = m - oe_ins;
             f -= o.e_ins;
             d |= f > t ? 2 << 4 : 0;
             f = f > t ? f : t;
             zi[j - beg] = d;
         }
-        H[end] = h1; E[end] = CIG_MINUS_INF;
+        H[end * st] = h1; E[end * st] = CIG_MINUS_INF;
     }
-    const int score = H[qlen];
+    const int score = H[qlen * st];
     int n = 0, which = 0;
     int i = tlen - 1, k = (i + w + 1 < qlen ? i + w + 1 : qlen) - 1;
     while (i >= 0 && k >= 0) {
@@ -190,6 +192,18 @@ CIG_HD inline bool cig_reg2aln(const CigarOpt &o, int64_t l_pac, const uint8_t *
         w2 <<= 1;
     } while (++i < 3 && res->score < truesc - o.a);
     return true;
+}
+
+// true when cig_reg2aln takes the gap-free shortcut of bwa_gen_cigar2 (first band 0 and equal lengths; a zero band
+// stays zero through the retries)
+CIG_HD inline bool cig_is_gapfree(const CigarOpt &o, int qb, int qe, int64_t rb, int64_t re, int truesc, int reg_w)
+{
+    int tmp = cig_infer_bw(qe - qb, (int)(re - rb), truesc, o.a, o.o_del, o.e_del);
+    int w2 = cig_infer_bw(qe - qb, (int)(re - rb), truesc, o.a, o.o_ins, o.e_ins);
+    w2 = w2 > tmp ? w2 : tmp;
+    if (w2 > o.w) w2 = w2 < reg_w ? w2 : reg_w;
+    w2 = w2 < o.w << 2 ? w2 : o.w << 2;
+    return w2 == 0 && (qe - qb) == (int)(re - rb);
 }
 
 // widest band any try of cig_reg2aln can use for this region (sizes the backtrack scratch)

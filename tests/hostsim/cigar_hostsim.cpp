@@ -21,7 +21,7 @@ extern "C" int hostsim_reg2aln(const bwagpu_cigar_opt *opt, int64_t l_pac, const
         std::vector<uint8_t> z(lq * lt + 16);
         std::vector<uint32_t> cg(lq + lt + 8);
         std::vector<char> mdv(3 * lt + 32);
-        CigarScratch sc = { eh.data(), z.data(), cg.data(), mdv.data() };
+        CigarScratch sc = { eh.data(), 1, z.data(), cg.data(), mdv.data() };
         CigarResult r; r.score = 0;
         bwagpu_cigar_out &out = outs[j];
         memset(&out, 0, sizeof out);
