@@ -9,7 +9,7 @@ import ctypes as C
 
 import numpy as np
 
-from .lib import CigarOpt, Context
+from .lib import CigarOpt, CigarResult, Context
 
 CIGAR_JOB_DTYPE = np.dtype([("rb", "<i8"), ("re", "<i8"), ("read", "<i4"), ("qb", "<i4"), ("qe", "<i4"), ("truesc", "<i4"),
                             ("w", "<i4"), ("pad_", "<i4")])
@@ -56,3 +56,19 @@ class RegToAln:
                 continue
             self.ctx.check(rc, "bwagpu_reg2aln_batch")
             return outs, cigar[:nc.value], md[:nm.value]
+
+    def mem_reg2aln_device(self, opt: CigarOpt, d_reads: int, d_off: int, d_len: int, nseq: int, d_jobs: int, n_jobs: int) -> CigarResult:
+        """Same with reads and jobs resident in HBM; results stay on the device (context-owned)."""
+        res = CigarResult()
+        self.ctx.check(self.ctx.lib.bwagpu_reg2aln_device(
+            self.ctx.h, C.byref(opt), C.c_void_p(d_reads), C.c_void_p(d_off), C.c_void_p(d_len), nseq, C.c_void_p(d_jobs),
+            n_jobs, C.byref(res)), "bwagpu_reg2aln_device")
+        return res
+
+    def fetch(self, res: CigarResult):
+        """Copy a device result back: (outs, cigar, md)."""
+        outs, cigar, md = np.zeros(res.n_jobs, CIGAR_OUT_DTYPE), np.zeros(res.n_cigar, np.uint32), np.zeros(res.md_bytes, np.uint8)
+        for arr, ptr in ((outs, res.d_outs), (cigar, res.d_cigar), (md, res.d_md)):
+            if arr.nbytes:
+                self.ctx.d2h(arr, ptr)
+        return outs, cigar, md

@@ -4,6 +4,7 @@
 // alignment whose backtrack matrix (one byte per cell) lives in a per-job slab of global memory.  Jobs are
 // processed in chunks so that the slabs stay below a fixed budget.  Results are compacted by a scan + copy kernel.
 #include <cub/device/device_scan.cuh>
+#include <cub/device/device_radix_sort.cuh>
 #include <stdlib.h>
 #include <algorithm>
 #include "ctx.cuh"
@@ -74,6 +75,130 @@ static int cig_scan(bwagpu_ctx *ctx, const int64_t *in, int64_t *out, int64_t n)
     return BWAGPU_OK;
 }
 
+// ---- device-resident form ----------------------------------------------------------------------------------
+// per job: slab sizes (eh words, z bytes, cigar words, md bytes) and the sort key (0 = gap-free, else 1 + z bytes)
+__global__ void cigar_plan_kernel(CigarOpt o, const bwagpu_cigar_job *__restrict__ jobs, int64_t n, const int32_t *__restrict__ len,
+                                  int32_t nseq, int64_t *sizes /* 4 x (n + 1) */, uint32_t *keys, int32_t *idx, int32_t *bad)
+{
+    const int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= n) return;
+    const bwagpu_cigar_job b = jobs[j];
+    if (b.read < 0 || b.read >= nseq || b.qb < 0 || b.qb > b.qe || b.qe > len[b.read] || b.re - b.rb > (1 << 20)) { atomicExch(bad, 1); }
+    const int64_t lq = b.qe > b.qb ? b.qe - b.qb : 0, lt = b.re > b.rb ? b.re - b.rb : 0;
+    const bool gapfree = cig_is_gapfree(o, b.qb, b.qe, b.rb, b.re, b.truesc, b.w);
+    const int64_t zb = gapfree ? 0 : cig_z_bytes(o, b.qb, b.qe, b.rb, b.re, b.truesc, b.w);
+    sizes[j] = lq > CIG_SMEM_QLEN ? 2 * (lq + 1) : 0;
+    sizes[(n + 1) + j] = zb;
+    sizes[2 * (n + 1) + j] = lq + lt + 4;
+    sizes[3 * (n + 1) + j] = 3 * lt + 16;
+    keys[j] = gapfree ? 0u : (uint32_t)(1 + (zb < (1 << 30) ? zb : (1 << 30)));
+    idx[j] = (int32_t)j;
+}
+
+__global__ void cigar_slab_kernel(int64_t n, const int64_t *__restrict__ scans, const uint32_t *__restrict__ sorted_keys, CigSlabOff *so,
+                                  int64_t *n_gf)
+{
+    const int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= n) return;
+    CigSlabOff s = { scans[j], scans[(n + 1) + j], scans[2 * (n + 1) + j], scans[3 * (n + 1) + j] };
+    so[j] = s;
+    // number of gap-free jobs = first position of the sorted key list holding a non-zero key
+    if (sorted_keys[j] != 0 && (j == 0 || sorted_keys[j - 1] == 0)) *n_gf = j;
+}
+
+extern "C" int bwagpu_reg2aln_device(bwagpu_ctx *ctx, const bwagpu_cigar_opt *opt, const uint8_t *d_reads, const int64_t *d_off,
+                                     const int32_t *d_len, int32_t nseq, const bwagpu_cigar_job *d_jobs, int64_t n_jobs,
+                                     bwagpu_cigar_result *res)
+{
+    if (!ctx) return BWAGPU_ERR_ARG;
+    if (!opt || !res || nseq < 0 || n_jobs < 0 || n_jobs > 0x7fffffff) BWAGPU_FAIL(ctx, BWAGPU_ERR_ARG, "reg2aln_device: bad argument");
+    if (!ctx->d_ref_string) BWAGPU_FAIL(ctx, BWAGPU_ERR_ARG, "reg2aln_device: no reference loaded (bwagpu_index_load_ref)");
+    if (opt->e_del <= 0 || opt->e_ins <= 0 || opt->w < 0) BWAGPU_FAIL(ctx, BWAGPU_ERR_ARG, "reg2aln_device: gap extension penalties must be positive");
+    memset(res, 0, sizeof *res);
+    if (n_jobs == 0) return BWAGPU_OK;
+    BWAGPU_CUDA(ctx, cudaSetDevice(ctx->device));
+    CigarOpt o;
+    memcpy(o.mat, opt->mat, 25);
+    o.a = opt->a; o.o_del = opt->o_del; o.e_del = opt->e_del; o.o_ins = opt->o_ins; o.e_ins = opt->e_ins; o.w = opt->w;
+    const int64_t n = n_jobs;
+    int rc;
+    int64_t *d_sizes, *d_scans, *d_cnt, *d_scan; uint32_t *d_keys, *d_keys2; int32_t *d_idx, *d_order, *d_flag; CigSlabOff *d_so;
+    bwagpu_cigar_out *d_out;
+    if ((rc = bwagpu_scratch(ctx, SCR_CIG_JOBS, 4 * (n + 1) * 8 + 64, (void **)&d_sizes))) return rc;
+    if ((rc = bwagpu_scratch(ctx, SCR_CIG_EH, 4 * (n + 1) * 8 + 64, (void **)&d_scans))) return rc;
+    if ((rc = bwagpu_scratch(ctx, SCR_MISC0, n * 8 + 64, (void **)&d_keys))) return rc;
+    d_keys2 = d_keys + n;
+    if ((rc = bwagpu_scratch(ctx, SCR_MISC1, n * 4 + 64, (void **)&d_idx))) return rc;
+    if ((rc = bwagpu_scratch(ctx, SCR_CIG_ORDER, n * 4 + 64, (void **)&d_order))) return rc;
+    if ((rc = bwagpu_scratch(ctx, SCR_CIG_SLABOFF, n * (int64_t)sizeof(CigSlabOff), (void **)&d_so))) return rc;
+    if ((rc = bwagpu_scratch(ctx, SCR_CIG_OUT, n * (int64_t)sizeof(bwagpu_cigar_out), (void **)&d_out))) return rc;
+    if ((rc = bwagpu_scratch(ctx, SCR_CIG_CNT, (n + 1) * 16, (void **)&d_cnt))) return rc;
+    if ((rc = bwagpu_scratch(ctx, SCR_CIG_SCAN, (n + 1) * 16 + 64, (void **)&d_scan))) return rc;
+    if ((rc = bwagpu_scratch(ctx, SCR_STATS, 256, (void **)&d_flag))) return rc;
+    BWAGPU_CUDA(ctx, cudaMemsetAsync(d_flag, 0, 16, ctx->stream));
+    BWAGPU_CUDA(ctx, cudaMemsetAsync(d_sizes, 0, (size_t)4 * (n + 1) * 8, ctx->stream));
+    BWAGPU_CUDA(ctx, cudaMemsetAsync(d_cnt, 0, (size_t)(n + 1) * 16, ctx->stream));
+    cigar_plan_kernel<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(o, d_jobs, n, d_len, nseq, d_sizes, d_keys, d_idx, d_flag);
+    ctx->launches++;
+    for (int a = 0; a < 4; ++a)
+        if ((rc = cig_scan(ctx, d_sizes + a * (n + 1), d_scans + a * (n + 1), n + 1))) return rc;
+    size_t sb = 0;
+    cub::DeviceRadixSort::SortPairs((void *)nullptr, sb, d_keys, d_keys2, d_idx, d_order, (int)n, 0, 32, ctx->stream);
+    void *tmp;
+    if ((rc = bwagpu_scratch(ctx, SCR_CUB, (int64_t)sb + 256, &tmp))) return rc;
+    BWAGPU_CUDA(ctx, cub::DeviceRadixSort::SortPairs(tmp, sb, d_keys, d_keys2, d_idx, d_order, (int)n, 0, 32, ctx->stream));
+    ctx->launches += 4;
+    int64_t *d_ngf = (int64_t *)(d_flag + 2);
+    int64_t h_ngf = n;
+    BWAGPU_CUDA(ctx, cudaMemcpyAsync(d_ngf, &h_ngf, 8, cudaMemcpyHostToDevice, ctx->stream));
+    cigar_slab_kernel<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(n, d_scans, d_keys2, d_so, d_ngf);
+    ctx->launches++;
+    int64_t tot[4]; int32_t h_bad = 0;
+    for (int a = 0; a < 4; ++a) BWAGPU_CUDA(ctx, cudaMemcpyAsync(&tot[a], d_scans + a * (n + 1) + n, 8, cudaMemcpyDeviceToHost, ctx->stream));
+    BWAGPU_CUDA(ctx, cudaMemcpyAsync(&h_ngf, d_ngf, 8, cudaMemcpyDeviceToHost, ctx->stream));
+    BWAGPU_CUDA(ctx, cudaMemcpyAsync(&h_bad, d_flag, 4, cudaMemcpyDeviceToHost, ctx->stream));
+    BWAGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    if (h_bad) BWAGPU_FAIL(ctx, BWAGPU_ERR_ARG, "reg2aln_device: a job is out of range (read index, query span or window)");
+    if (tot[1] + (tot[0] + tot[2]) * 4 + tot[3] > (32LL << 30))
+        BWAGPU_FAIL(ctx, BWAGPU_ERR_RANGE, "reg2aln_device: %lld jobs need %.1f GB of scratch; pass smaller batches", (long long)n, (tot[1] + (tot[0] + tot[2]) * 4 + tot[3]) / 1e9);
+    int32_t *d_eh; uint8_t *d_z; uint32_t *d_cig; char *d_md;
+    if ((rc = bwagpu_scratch(ctx, SCR_MISC2, tot[0] * 4 + 16, (void **)&d_eh))) return rc;
+    if ((rc = bwagpu_scratch(ctx, SCR_CIG_Z, tot[1] + 16, (void **)&d_z))) return rc;
+    if ((rc = bwagpu_scratch(ctx, SCR_CIG_CIGAR, tot[2] * 4 + 16, (void **)&d_cig))) return rc;
+    if ((rc = bwagpu_scratch(ctx, SCR_CIG_MD, tot[3] + 16, (void **)&d_md))) return rc;
+    const size_t smem_bytes = (size_t)2 * (CIG_SMEM_QLEN + 1) * CIG_TPB * 4;
+    BWAGPU_CUDA(ctx, cudaFuncSetAttribute(cigar_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
+    const int64_t n_gf = h_ngf;
+    BWAGPU_KERNEL_BEGIN(ctx);
+    if (n_gf > 0)
+        cigar_kernel<<<(unsigned)((n_gf + CIG_TPB - 1) / CIG_TPB), CIG_TPB, 0, ctx->stream>>>(
+            o, ctx->l_pac, (const uint8_t *)ctx->d_ref_string, d_reads, d_off, d_len, d_jobs, d_order, 0, n_gf, d_so, d_eh, d_z, d_cig,
+            d_md, d_out, d_cnt, d_cnt + n + 1);
+    if (n > n_gf)
+        cigar_kernel<<<(unsigned)((n - n_gf + CIG_TPB - 1) / CIG_TPB), CIG_TPB, smem_bytes, ctx->stream>>>(
+            o, ctx->l_pac, (const uint8_t *)ctx->d_ref_string, d_reads, d_off, d_len, d_jobs, d_order, n_gf, n, d_so, d_eh, d_z, d_cig,
+            d_md, d_out, d_cnt, d_cnt + n + 1);
+    ctx->launches += (n_gf > 0 && n > n_gf) ? 1 : 0;
+    BWAGPU_KERNEL_END(ctx, BWAGPU_KERN_CIGAR);
+    BWAGPU_CUDA(ctx, cudaGetLastError());
+    if ((rc = cig_scan(ctx, d_cnt, d_scan, n + 1))) return rc;
+    if ((rc = cig_scan(ctx, d_cnt + n + 1, d_scan + n + 1, n + 1))) return rc;
+    int64_t t2[2] = {0, 0};
+    BWAGPU_CUDA(ctx, cudaMemcpyAsync(&t2[0], d_scan + n, 8, cudaMemcpyDeviceToHost, ctx->stream));
+    BWAGPU_CUDA(ctx, cudaMemcpyAsync(&t2[1], d_scan + 2 * n + 1, 8, cudaMemcpyDeviceToHost, ctx->stream));
+    BWAGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    uint32_t *d_oc; char *d_om;
+    if ((rc = bwagpu_scratch(ctx, SCR_CIG_OUTC, t2[0] * 4 + 16, (void **)&d_oc))) return rc;
+    if ((rc = bwagpu_scratch(ctx, SCR_CIG_OUTM, t2[1] + 16, (void **)&d_om))) return rc;
+    BWAGPU_KERNEL_BEGIN(ctx);
+    cigar_emit_kernel<<<(unsigned)((n + 127) / 128), 128, 0, ctx->stream>>>(n, d_so, d_cig, d_md, d_scan, d_scan + n + 1, 0, 0, d_out, d_oc, d_om);
+    BWAGPU_KERNEL_END(ctx, BWAGPU_KERN_CIGAR);
+    BWAGPU_CUDA(ctx, cudaGetLastError());
+    res->d_outs = d_out; res->n_jobs = n; res->d_cigar = d_oc; res->n_cigar = t2[0]; res->d_md = d_om; res->md_bytes = t2[1];
+    res->n_gapfree = n_gf;
+    return BWAGPU_OK;
+}
+
 extern "C" int bwagpu_reg2aln_batch(bwagpu_ctx *ctx, const bwagpu_cigar_opt *opt, const uint8_t *enc_reads, const int64_t *off,
                                     const int32_t *len, int32_t nseq, const bwagpu_cigar_job *jobs, int64_t n_jobs,
                                     bwagpu_cigar_out *outs, uint32_t *cigar, int64_t cigar_cap, char *md, int64_t md_cap,
@@ -124,7 +249,7 @@ extern "C" int bwagpu_reg2aln_batch(bwagpu_ctx *ctx, const bwagpu_cigar_opt *opt
             const bwagpu_cigar_job &b = jobs[j1];
             const int64_t lq = b.qe - b.qb, lt = b.re > b.rb ? b.re - b.rb : 0;
             const bool gapfree = cig_is_gapfree(o, b.qb, b.qe, b.rb, b.re, b.truesc, b.w);
-            const int64_t zb = gapfree ? 0 : lq * lt;
+            const int64_t zb = gapfree ? 0 : cig_z_bytes(o, b.qb, b.qe, b.rb, b.re, b.truesc, b.w);
             if (j1 > j0 && cur.z + zb + (cur.eh + cur.cigar) * 4 + cur.md > budget) break;
             h_so[j1] = cur;
             if (lq > CIG_SMEM_QLEN) cur.eh += 2 * (lq + 1);

@@ -206,11 +206,28 @@ CIG_HD inline bool cig_is_gapfree(const CigarOpt &o, int qb, int qe, int64_t rb,
     return w2 == 0 && (qe - qb) == (int)(re - rb);
 }
 
-// widest band any try of cig_reg2aln can use for this region (sizes the backtrack scratch)
-CIG_HD inline int cig_max_cols(const CigarOpt &o, int l_query)
+// bytes of backtrack matrix the widest try of cig_reg2aln can need for this region: the band of try k is
+// min((max_gap + diff + 1) >> 1, w2 << k) raised to diff + 3, k = 0..2, w2 << k capped at 4 * opt->w
+CIG_HD inline int64_t cig_z_bytes(const CigarOpt &o, int qb, int qe, int64_t rb, int64_t re, int truesc, int reg_w)
 {
-    const int w = o.w << 2;
-    return l_query < 2 * w + 1 ? l_query : 2 * w + 1;
+    const int lq = qe - qb, lt = (int)(re - rb);
+    if (lq <= 0 || lt <= 0) return 0;
+    int tmp = cig_infer_bw(lq, lt, truesc, o.a, o.o_del, o.e_del);
+    int w2 = cig_infer_bw(lq, lt, truesc, o.a, o.o_ins, o.e_ins);
+    w2 = w2 > tmp ? w2 : tmp;
+    if (w2 > o.w) w2 = w2 < reg_w ? w2 : reg_w;
+    int64_t wt = (int64_t)w2 << 2;
+    if (wt > (o.w << 2)) wt = o.w << 2;
+    const int max_ins = (int)((double)(((lq + 1) >> 1) * o.mat[0] - o.o_ins) / o.e_ins + 1.);
+    const int max_del = (int)((double)(((lq + 1) >> 1) * o.mat[0] - o.o_del) / o.e_del + 1.);
+    int max_gap = max_ins > max_del ? max_ins : max_del;
+    max_gap = max_gap > 1 ? max_gap : 1;
+    const int diff = lt > lq ? lt - lq : lq - lt;
+    int64_t w = (max_gap + diff + 1) >> 1;
+    w = w < wt ? w : wt;
+    w = w > diff + 3 ? w : diff + 3;
+    const int64_t n_col = lq < 2 * w + 1 ? lq : 2 * w + 1;
+    return n_col * lt;
 }
 
 // the tail of mem_reg2aln (src/bwamem.cpp:2571-2600): position, removal of a leading / trailing deletion, soft clips.

@@ -73,6 +73,12 @@ class CigarOpt(C.Structure):
     _fields_ = [("mat", C.c_int8 * 25), ("pad_", C.c_int8 * 3)] + [(n, C.c_int32) for n in ("a", "o_del", "e_del", "o_ins", "e_ins", "w")]
 
 
+class CigarResult(C.Structure):
+    """bwagpu_cigar_result"""
+    _fields_ = [("d_outs", C.c_void_p), ("n_jobs", C.c_int64), ("d_cigar", C.c_void_p), ("n_cigar", C.c_int64),
+                ("d_md", C.c_void_p), ("md_bytes", C.c_int64), ("n_gapfree", C.c_int64)]
+
+
 class ErtResult(C.Structure):
     """bwagpu_ert_result"""
     _fields_ = [("d_smems", C.c_void_p), ("n_smem", C.c_int64), ("d_coords", C.c_void_p),
@@ -128,6 +134,8 @@ _SIGS = {
     "bwagpu_reg2aln_batch": (C.c_int, [C.c_void_p, C.POINTER(CigarOpt), C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32,
                                        C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_int64,
                                        C.POINTER(C.c_int64), C.POINTER(C.c_int64)]),
+    "bwagpu_reg2aln_device": (C.c_int, [C.c_void_p, C.POINTER(CigarOpt), C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32,
+                                        C.c_void_p, C.c_int64, C.POINTER(CigarResult)]),
     "bwagpu_index_load_ert": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_int64]),
     "bwagpu_index_unload_ert": (C.c_int, [C.c_void_p]),
     "bwagpu_index_complete_ert": (C.c_int, [C.c_void_p]),

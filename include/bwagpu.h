@@ -223,6 +223,18 @@ int bwagpu_reg2aln_batch(bwagpu_ctx *ctx, const bwagpu_cigar_opt *opt, const uin
                          bwagpu_cigar_out *outs, uint32_t *cigar, int64_t cigar_cap, char *md, int64_t md_cap,
                          int64_t *n_cigar_total, int64_t *md_bytes);
 
+/* Device-resident form: jobs, reads and results stay in HBM (results context-owned, valid until the next CIGAR
+ * call); the job order and the scratch layout are planned on the device (plan kernel, radix sort, scans). */
+typedef struct {
+    const bwagpu_cigar_out *d_outs; int64_t n_jobs;
+    const uint32_t *d_cigar;        int64_t n_cigar;
+    const char *d_md;               int64_t md_bytes;
+    int64_t n_gapfree;              /* regions that took bwa_gen_cigar2's gap-free shortcut */
+} bwagpu_cigar_result;
+int bwagpu_reg2aln_device(bwagpu_ctx *ctx, const bwagpu_cigar_opt *opt, const uint8_t *d_reads, const int64_t *d_off,
+                          const int32_t *d_len, int32_t nseq, const bwagpu_cigar_job *d_jobs, int64_t n_jobs,
+                          bwagpu_cigar_result *res);
+
 /* ---- S3: mate-rescue local Smith-Waterman ------------------------------------------------------
  * bwagpu_kswr mirrors kswr_t (reference src/ksw.h), 28 bytes. */
 typedef struct {

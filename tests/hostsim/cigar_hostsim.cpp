@@ -18,7 +18,7 @@ extern "C" int hostsim_reg2aln(const bwagpu_cigar_opt *opt, int64_t l_pac, const
         const bwagpu_cigar_job &b = jobs[j];
         const int64_t lq = b.qe - b.qb, lt = b.re > b.rb ? b.re - b.rb : 0;
         std::vector<int32_t> eh(2 * (lq + 1) + 4);
-        std::vector<uint8_t> z(lq * lt + 16);
+        std::vector<uint8_t> z(cig_z_bytes(o, b.qb, b.qe, b.rb, b.re, b.truesc, b.w) + 1);   // exactly what the kernel's planner reserves
         std::vector<uint32_t> cg(lq + lt + 8);
         std::vector<char> mdv(3 * lt + 32);
         CigarScratch sc = { eh.data(), 1, z.data(), cg.data(), mdv.data() };

@@ -43,3 +43,20 @@ def test_gpu_cigar_empty_rejected_and_errors(setup, gpu_ctx):
     jobs["read"] = len(ln)                                   # read index out of range
     with pytest.raises(BwaGpuError):
         r2a.mem_reg2aln(cigar_opt(), flat, off, ln, jobs)
+
+
+@pytest.mark.parametrize("case", gc.OPT_CASES[:2], ids=[c[0] for c in gc.OPT_CASES[:2]])
+def test_gpu_cigar_device_resident_form(setup, gpu_ctx, case):
+    name, kw = case
+    ref, r2a, flat, off, ln = setup
+    o = ol.mem_opt(**kw)
+    jobs = np.ascontiguousarray(GOLD[f"{name}_jobs"])
+    d = [gpu_ctx.upload(a) for a in (flat, off, ln, jobs)]
+    res = r2a.mem_reg2aln_device(cigar_opt(o["a"], o["b"], o["o_del"], o["e_del"], o["o_ins"], o["e_ins"], o["w"]),
+                                 d[0], d[1], d[2], len(ln), d[3], len(jobs))
+    outs, cigar, md = r2a.fetch(res)
+    assert np.array_equal(gc.out_matrix(outs), GOLD[f"{name}_outs"])
+    assert np.array_equal(cigar, GOLD[f"{name}_cigar"]) and np.array_equal(md, GOLD[f"{name}_md"])
+    assert 0 < res.n_gapfree < len(jobs)
+    for p in d:
+        gpu_ctx.free(p)

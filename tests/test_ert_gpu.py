@@ -118,3 +118,51 @@ def test_gpu_kmer_table_completion_from_fm_index(tiny_ert, gpu_ctx):
     mems, hits, mem_off = ert.seed(sopt_of({}), flat, off, ln)
     assert np.array_equal(ec.mem_matrix(mems), ec.mem_matrix(GOLD["default_mems"]))
     assert np.array_equal(hits, GOLD["default_hits"])
+
+
+BENCH_DATA = os.path.join(os.path.dirname(ec.HERE), "bench_data", "ert_small_genome.npz")
+
+
+@pytest.mark.skipif(not (os.path.exists(BENCH_DATA) and ol.ref_binary() is not None),
+                    reason="needs bench_data/ert_small_genome.npz (scripts/make_ert_bench_data.py) and oracle/_ref")
+def test_gpu_ert_live_against_reference_at_scale(gpu_ctx):
+    """60 k fresh reads on the 300 kbp reference-built index (k-mer table completed on the device): MEMs and hits vs the
+    unmodified reference's get_seeds / reseed / last, chains and regions vs its mem_kernel1_core_ert + V2."""
+    import tempfile
+    from bwa_mem_scale_b200 import FMI_search, synth
+    d = np.load(BENCH_DATA)
+    ref = np.ascontiguousarray(d["ref"])
+    ref_string = fmindex.text_with_revcomp(ref)
+    idx = fmindex.build_fm_index(ref, device="cpu")
+    FMI_search(idx, ctx=gpu_ctx)
+    ext = Extender(ref_string, len(ref), [0], [len(ref)], ctx=gpu_ctx)
+    ert = ErtSeeding(ErtIndex(d["mlt_table"], sparse_idx=d["kmer_idx"], sparse_val=d["kmer_val"]), gpu_ctx)
+    ert.complete_from_fm()
+    dense, mlt = ert.dense_table(), np.ascontiguousarray(d["mlt_table"])
+    reads, _, _ = synth.simulate_reads(ref, 60000, seed=4242, err=0.015)
+    rng = np.random.default_rng(8)
+    extra = ec._sim(rng, ref, 1500, 151, 0.02, 0.01) + [ref[1000 + k:1151 + k].copy() for k in range(0, 300, 7)]
+    flat, off, ln = pack_reads(list(reads) + extra)
+    tap = ol.RefErt((dense, mlt, ref_string))
+    want = tap.seed(flat, off, ln)
+    got = ert.seed(sopt_of({}), flat, off, ln)
+    assert np.array_equal(ec.mem_matrix(got[0]), ec.mem_matrix(want[0]))
+    assert np.array_equal(got[1], want[1]) and np.array_equal(got[2], want[2])
+    sub = list(reads[:15000]) + extra
+    flat, off, ln = pack_reads(sub)
+    with tempfile.TemporaryDirectory() as td:
+        prefix = os.path.join(td, "ref")
+        fmindex.write_index_files(prefix, ref, idx)
+        rm = ol.RefMem(prefix)
+        rm.use_ert_tables(dense, mlt)
+        chains, seeds, regs, _ = rm.core(ol.mem_opt(), flat, off, ln)
+    d_reads, d_off, d_len = gpu_ctx.upload(flat), gpu_ctx.upload(off), gpu_ctx.upload(ln)
+    sres, cres, ares = mem_core_ert_device(ert, ext, sopt_of({}), chain_opt(), ext_opt(), d_reads, d_off, d_len, len(ln), int(ln.max()))
+    g_chains, g_seeds = np.zeros(cres.n_chains, ol.CHAIN_DTYPE), np.zeros(cres.n_seeds, ol.SEED_DTYPE)
+    g_regs = np.zeros(ares.n_regs, REG_DTYPE)
+    gpu_ctx.d2h(g_chains, cres.d_chains); gpu_ctx.d2h(g_seeds, cres.d_seeds); gpu_ctx.d2h(g_regs, ares.d_regs)
+    assert np.array_equal(g_chains, chains) and np.array_equal(g_seeds, seeds)
+    assert np.array_equal(cc.reg_matrix(g_regs), cc.reg_matrix(regs))
+    for p in (d_reads, d_off, d_len):
+        gpu_ctx.free(p)
+    gpu_ctx.check(gpu_ctx.lib.bwagpu_index_unload_ert(gpu_ctx.h), "bwagpu_index_unload_ert")
