@@ -29,7 +29,12 @@ cigar_kernel(CigarOpt o, int64_t l_pac, const uint8_t *__restrict__ ref_string, 
     const int64_t j = order[t];
     const bwagpu_cigar_job jb = jobs[j];
     CigarScratch sc;
+#ifdef CIG_EH_LOCAL
+    int32_t eh_local[2 * (CIG_SMEM_QLEN + 1)];
+    if (jb.qe - jb.qb <= CIG_SMEM_QLEN) { sc.eh = eh_local; sc.eh_stride = 1; }
+#else
     if (jb.qe - jb.qb <= CIG_SMEM_QLEN) { sc.eh = cig_smem + threadIdx.x; sc.eh_stride = CIG_TPB; }
+#endif
     else { sc.eh = eh + so[j].eh; sc.eh_stride = 1; }
     sc.z = z + so[j].z; sc.cigar = cigar + so[j].cigar; sc.md = md + so[j].md;
     CigarResult r;
@@ -166,7 +171,11 @@ extern "C" int bwagpu_reg2aln_device(bwagpu_ctx *ctx, const bwagpu_cigar_opt *op
     if ((rc = bwagpu_scratch(ctx, SCR_CIG_Z, tot[1] + 16, (void **)&d_z))) return rc;
     if ((rc = bwagpu_scratch(ctx, SCR_CIG_CIGAR, tot[2] * 4 + 16, (void **)&d_cig))) return rc;
     if ((rc = bwagpu_scratch(ctx, SCR_CIG_MD, tot[3] + 16, (void **)&d_md))) return rc;
+#ifdef CIG_EH_LOCAL
+    const size_t smem_bytes = 0;
+#else
     const size_t smem_bytes = (size_t)2 * (CIG_SMEM_QLEN + 1) * CIG_TPB * 4;
+#endif
     BWAGPU_CUDA(ctx, cudaFuncSetAttribute(cigar_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
     const int64_t n_gf = h_ngf;
     BWAGPU_KERNEL_BEGIN(ctx);
@@ -233,7 +242,11 @@ extern "C" int bwagpu_reg2aln_batch(bwagpu_ctx *ctx, const bwagpu_cigar_opt *opt
     BWAGPU_CUDA(ctx, cudaMemcpyAsync(d_reads, enc_reads, (size_t)bytes, cudaMemcpyHostToDevice, ctx->stream));
     BWAGPU_CUDA(ctx, cudaMemcpyAsync(d_off, off, (size_t)nseq * 8, cudaMemcpyHostToDevice, ctx->stream));
     BWAGPU_CUDA(ctx, cudaMemcpyAsync(d_len, len, (size_t)nseq * 4, cudaMemcpyHostToDevice, ctx->stream));
+#ifdef CIG_EH_LOCAL
+    const size_t smem_bytes = 0;
+#else
     const size_t smem_bytes = (size_t)2 * (CIG_SMEM_QLEN + 1) * CIG_TPB * 4;
+#endif
     BWAGPU_CUDA(ctx, cudaFuncSetAttribute(cigar_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
     const int64_t budget = 4LL << 30;                         // slab bytes per chunk
     CigSlabOff *h_so = (CigSlabOff *)malloc(sizeof(CigSlabOff) * (size_t)n_jobs);
