@@ -12,6 +12,13 @@
 
 struct CigSlabOff { int64_t eh, z, cigar, md; };
 
+// sort key of a job: 0 = gap-free; else (tier + 1) in the top bits, then the size of its backtrack matrix
+__host__ __device__ inline uint32_t cig_key(bool gapfree, int tier, int64_t zb)
+{
+    return gapfree ? 0u : ((uint32_t)(tier + 1) << 28) | (uint32_t)(zb < (1 << 28) - 1 ? zb : (1 << 28) - 1);
+}
+__host__ __device__ inline int cig_key_tier(uint32_t key) { return (int)(key >> 28) - 1; }      // -1 = gap-free
+
 #define CIG_TPB 64
 #define CIG_SMEM_QLEN 151                      // H/E rows of reads up to this length live in shared memory
 
@@ -20,8 +27,8 @@ struct CigSlabOff { int64_t eh, z, cigar, md; };
 __global__ void __launch_bounds__(CIG_TPB)
 cigar_kernel(CigarOpt o, int64_t l_pac, const uint8_t *__restrict__ ref_string, const uint8_t *__restrict__ reads,
              const int64_t *__restrict__ off, const int32_t *__restrict__ len, const bwagpu_cigar_job *__restrict__ jobs,
-             const int32_t *__restrict__ order, int64_t first, int64_t n, const CigSlabOff *__restrict__ so, int32_t *eh, uint8_t *z, uint32_t *cigar,
-             char *md, bwagpu_cigar_out *outs, int64_t *cnt_cigar, int64_t *cnt_md)
+             const int32_t *__restrict__ order, int64_t first, int64_t n, int tier, const CigSlabOff *__restrict__ so, int32_t *eh, uint8_t *z, uint32_t *cigar,
+             char *md, bwagpu_cigar_out *outs, int64_t *cnt_cigar, int64_t *cnt_md, int32_t *redo, unsigned int *n_redo)
 {
     extern __shared__ int32_t cig_smem[];
     const int64_t t = first + (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -29,19 +36,20 @@ cigar_kernel(CigarOpt o, int64_t l_pac, const uint8_t *__restrict__ ref_string, 
     const int64_t j = order[t];
     const bwagpu_cigar_job jb = jobs[j];
     CigarScratch sc;
-#ifdef CIG_EH_LOCAL
-    int32_t eh_local[2 * (CIG_SMEM_QLEN + 1)];
-    if (jb.qe - jb.qb <= CIG_SMEM_QLEN) { sc.eh = eh_local; sc.eh_stride = 1; }
-#else
-    if (jb.qe - jb.qb <= CIG_SMEM_QLEN) { sc.eh = cig_smem + threadIdx.x; sc.eh_stride = CIG_TPB; }
-#endif
-    else { sc.eh = eh + so[j].eh; sc.eh_stride = 1; }
+    // tier -1: gap-free group (no rows); 0-3: circular window of 16 << tier columns; 4: full rows
+    if (jb.qe - jb.qb <= CIG_SMEM_QLEN) { sc.eh = cig_smem + threadIdx.x; sc.eh_stride = CIG_TPB; sc.eh_mask = tier >= 0 && tier < 4 ? (16 << tier) - 1 : 0x7fffffff; }
+    else { sc.eh = eh + so[j].eh; sc.eh_stride = 1; sc.eh_mask = 0x7fffffff; }
     sc.z = z + so[j].z; sc.cigar = cigar + so[j].cigar; sc.md = md + so[j].md;
     CigarResult r;
     r.score = 0;
     bwagpu_cigar_out out;
     out.pos = -1; out.cigar_off = out.md_off = 0; out.is_rev = 0; out.n_cigar = 0; out.nm = -1; out.l_md = 0; out.score = 0;
-    out.ok = cig_reg2aln(o, l_pac, ref_string, reads + off[jb.read], jb.qb, jb.qe, jb.rb, jb.re, jb.truesc, jb.w, sc, &r) ? 1 : 0;
+    const int rcode = cig_reg2aln(o, l_pac, ref_string, reads + off[jb.read], jb.qb, jb.qe, jb.rb, jb.re, jb.truesc, jb.w, sc, &r);
+    if (rcode == 2) {                       // a retry's band outgrew this tier's window: second pass with full rows
+        if (redo) redo[atomicAdd(n_redo, 1u)] = (int32_t)j;
+        return;
+    }
+    out.ok = rcode == 1 ? 1 : 0;
     if (out.ok) {
         int is_rev;
         out.n_cigar = cig_finish(l_pac, jb.rb, jb.re, jb.qb, jb.qe, len[jb.read], sc.cigar, r.n_cigar, &out.pos, &is_rev);
@@ -80,6 +88,45 @@ static int cig_scan(bwagpu_ctx *ctx, const int64_t *in, int64_t *out, int64_t n)
     return BWAGPU_OK;
 }
 
+
+// launches the groups of a sorted job list: bounds[g] = first position of group g (0 = gap-free, 1..5 = tiers 0..4), bounds[6] = n
+static int cig_launch_groups(bwagpu_ctx *ctx, const CigarOpt &o, const uint8_t *d_reads, const int64_t *d_off, const int32_t *d_len,
+                             const bwagpu_cigar_job *d_jobs, const int32_t *d_order, const int64_t *bounds, const CigSlabOff *d_so,
+                             int32_t *d_eh, uint8_t *d_z, uint32_t *d_cig, char *d_md, bwagpu_cigar_out *d_out, int64_t *d_cnt, int64_t n)
+{
+    BWAGPU_CUDA(ctx, cudaFuncSetAttribute(cigar_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                          (int)((size_t)2 * (CIG_SMEM_QLEN + 1) * CIG_TPB * 4)));
+    int32_t *d_redo; unsigned int *d_nredo; void *stats;
+    int rc;
+    if ((rc = bwagpu_scratch(ctx, SCR_CIG_REDO, n * 4 + 16, (void **)&d_redo))) return rc;
+    if ((rc = bwagpu_scratch(ctx, SCR_STATS, 256, &stats))) return rc;
+    d_nredo = (unsigned int *)((char *)stats + 128);
+    BWAGPU_CUDA(ctx, cudaMemsetAsync(d_nredo, 0, 4, ctx->stream));
+    int launched = 0;
+    for (int g = 0; g < 6; ++g) {
+        const int64_t b0 = bounds[g], b1 = bounds[g + 1];
+        if (b1 <= b0) continue;
+        const int tier = g - 1;
+        const size_t smem = tier < 0 ? 0 : tier < 4 ? (size_t)2 * (16 << tier) * CIG_TPB * 4 : (size_t)2 * (CIG_SMEM_QLEN + 1) * CIG_TPB * 4;
+        cigar_kernel<<<(unsigned)((b1 - b0 + CIG_TPB - 1) / CIG_TPB), CIG_TPB, smem, ctx->stream>>>(
+            o, ctx->l_pac, (const uint8_t *)ctx->d_ref_string, d_reads, d_off, d_len, d_jobs, d_order, b0, b1, tier, d_so, d_eh, d_z, d_cig,
+            d_md, d_out, d_cnt, d_cnt + n + 1, d_redo, d_nredo);
+        ++launched;
+    }
+    unsigned int n_redo = 0;
+    BWAGPU_CUDA(ctx, cudaMemcpyAsync(&n_redo, d_nredo, 4, cudaMemcpyDeviceToHost, ctx->stream));
+    BWAGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    if (n_redo > 0) {
+        cigar_kernel<<<(unsigned)((n_redo + CIG_TPB - 1) / CIG_TPB), CIG_TPB, (size_t)2 * (CIG_SMEM_QLEN + 1) * CIG_TPB * 4, ctx->stream>>>(
+            o, ctx->l_pac, (const uint8_t *)ctx->d_ref_string, d_reads, d_off, d_len, d_jobs, d_redo, 0, (int64_t)n_redo, 4, d_so, d_eh, d_z,
+            d_cig, d_md, d_out, d_cnt, d_cnt + n + 1, nullptr, nullptr);
+        ++launched;
+    }
+    ctx->launches += launched > 1 ? launched - 1 : 0;
+    BWAGPU_CUDA(ctx, cudaGetLastError());
+    return BWAGPU_OK;
+}
+
 // ---- device-resident form ----------------------------------------------------------------------------------
 // per job: slab sizes (eh words, z bytes, cigar words, md bytes) and the sort key (0 = gap-free, else 1 + z bytes)
 __global__ void cigar_plan_kernel(CigarOpt o, const bwagpu_cigar_job *__restrict__ jobs, int64_t n, const int32_t *__restrict__ len,
@@ -96,19 +143,26 @@ __global__ void cigar_plan_kernel(CigarOpt o, const bwagpu_cigar_job *__restrict
     sizes[(n + 1) + j] = zb;
     sizes[2 * (n + 1) + j] = lq + lt + 4;
     sizes[3 * (n + 1) + j] = 3 * lt + 16;
-    keys[j] = gapfree ? 0u : (uint32_t)(1 + (zb < (1 << 30) ? zb : (1 << 30)));
+    keys[j] = cig_key(gapfree, lq > CIG_SMEM_QLEN ? 4 : cig_tier(o, b.qb, b.qe, b.rb, b.re, b.truesc, b.w), zb);
     idx[j] = (int32_t)j;
 }
 
 __global__ void cigar_slab_kernel(int64_t n, const int64_t *__restrict__ scans, const uint32_t *__restrict__ sorted_keys, CigSlabOff *so,
-                                  int64_t *n_gf)
+                                  int64_t *first /* [6]: first sorted position of each group, preset to n */)
 {
     const int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (j >= n) return;
     CigSlabOff s = { scans[j], scans[(n + 1) + j], scans[2 * (n + 1) + j], scans[3 * (n + 1) + j] };
     so[j] = s;
-    // number of gap-free jobs = first position of the sorted key list holding a non-zero key
-    if (sorted_keys[j] != 0 && (j == 0 || sorted_keys[j - 1] == 0)) *n_gf = j;
+    const int g = cig_key_tier(sorted_keys[j]) + 1;
+    if (j == 0 || cig_key_tier(sorted_keys[j - 1]) + 1 != g) first[g] = j;
+}
+
+// group bounds from the first positions of the groups present (absent groups are empty: they start where the next one does)
+static void cig_bounds(const int64_t *first, int64_t n, int64_t *bounds)
+{
+    bounds[6] = n;
+    for (int g = 5; g >= 0; --g) bounds[g] = first[g] < bounds[g + 1] ? first[g] : bounds[g + 1];
 }
 
 extern "C" int bwagpu_reg2aln_device(bwagpu_ctx *ctx, const bwagpu_cigar_opt *opt, const uint8_t *d_reads, const int64_t *d_off,
@@ -128,6 +182,7 @@ extern "C" int bwagpu_reg2aln_device(bwagpu_ctx *ctx, const bwagpu_cigar_opt *op
     const int64_t n = n_jobs;
     int rc;
     int64_t *d_sizes, *d_scans, *d_cnt, *d_scan; uint32_t *d_keys, *d_keys2; int32_t *d_idx, *d_order, *d_flag; CigSlabOff *d_so;
+    int64_t h_ngf = 0; (void)h_ngf;
     bwagpu_cigar_out *d_out;
     if ((rc = bwagpu_scratch(ctx, SCR_CIG_JOBS, 4 * (n + 1) * 8 + 64, (void **)&d_sizes))) return rc;
     if ((rc = bwagpu_scratch(ctx, SCR_CIG_EH, 4 * (n + 1) * 8 + 64, (void **)&d_scans))) return rc;
@@ -153,14 +208,14 @@ extern "C" int bwagpu_reg2aln_device(bwagpu_ctx *ctx, const bwagpu_cigar_opt *op
     if ((rc = bwagpu_scratch(ctx, SCR_CUB, (int64_t)sb + 256, &tmp))) return rc;
     BWAGPU_CUDA(ctx, cub::DeviceRadixSort::SortPairs(tmp, sb, d_keys, d_keys2, d_idx, d_order, (int)n, 0, 32, ctx->stream));
     ctx->launches += 4;
-    int64_t *d_ngf = (int64_t *)(d_flag + 2);
-    int64_t h_ngf = n;
-    BWAGPU_CUDA(ctx, cudaMemcpyAsync(d_ngf, &h_ngf, 8, cudaMemcpyHostToDevice, ctx->stream));
-    cigar_slab_kernel<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(n, d_scans, d_keys2, d_so, d_ngf);
+    int64_t *d_first = (int64_t *)(d_flag + 2);
+    int64_t h_first[6] = {n, n, n, n, n, n};
+    BWAGPU_CUDA(ctx, cudaMemcpyAsync(d_first, h_first, sizeof h_first, cudaMemcpyHostToDevice, ctx->stream));
+    cigar_slab_kernel<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(n, d_scans, d_keys2, d_so, d_first);
     ctx->launches++;
     int64_t tot[4]; int32_t h_bad = 0;
     for (int a = 0; a < 4; ++a) BWAGPU_CUDA(ctx, cudaMemcpyAsync(&tot[a], d_scans + a * (n + 1) + n, 8, cudaMemcpyDeviceToHost, ctx->stream));
-    BWAGPU_CUDA(ctx, cudaMemcpyAsync(&h_ngf, d_ngf, 8, cudaMemcpyDeviceToHost, ctx->stream));
+    BWAGPU_CUDA(ctx, cudaMemcpyAsync(h_first, d_first, sizeof h_first, cudaMemcpyDeviceToHost, ctx->stream));
     BWAGPU_CUDA(ctx, cudaMemcpyAsync(&h_bad, d_flag, 4, cudaMemcpyDeviceToHost, ctx->stream));
     BWAGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     if (h_bad) BWAGPU_FAIL(ctx, BWAGPU_ERR_ARG, "reg2aln_device: a job is out of range (read index, query span or window)");
@@ -171,23 +226,11 @@ extern "C" int bwagpu_reg2aln_device(bwagpu_ctx *ctx, const bwagpu_cigar_opt *op
     if ((rc = bwagpu_scratch(ctx, SCR_CIG_Z, tot[1] + 16, (void **)&d_z))) return rc;
     if ((rc = bwagpu_scratch(ctx, SCR_CIG_CIGAR, tot[2] * 4 + 16, (void **)&d_cig))) return rc;
     if ((rc = bwagpu_scratch(ctx, SCR_CIG_MD, tot[3] + 16, (void **)&d_md))) return rc;
-#ifdef CIG_EH_LOCAL
-    const size_t smem_bytes = 0;
-#else
-    const size_t smem_bytes = (size_t)2 * (CIG_SMEM_QLEN + 1) * CIG_TPB * 4;
-#endif
-    BWAGPU_CUDA(ctx, cudaFuncSetAttribute(cigar_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
-    const int64_t n_gf = h_ngf;
+    int64_t bounds[7];
+    cig_bounds(h_first, n, bounds);
+    const int64_t n_gf = bounds[1];
     BWAGPU_KERNEL_BEGIN(ctx);
-    if (n_gf > 0)
-        cigar_kernel<<<(unsigned)((n_gf + CIG_TPB - 1) / CIG_TPB), CIG_TPB, 0, ctx->stream>>>(
-            o, ctx->l_pac, (const uint8_t *)ctx->d_ref_string, d_reads, d_off, d_len, d_jobs, d_order, 0, n_gf, d_so, d_eh, d_z, d_cig,
-            d_md, d_out, d_cnt, d_cnt + n + 1);
-    if (n > n_gf)
-        cigar_kernel<<<(unsigned)((n - n_gf + CIG_TPB - 1) / CIG_TPB), CIG_TPB, smem_bytes, ctx->stream>>>(
-            o, ctx->l_pac, (const uint8_t *)ctx->d_ref_string, d_reads, d_off, d_len, d_jobs, d_order, n_gf, n, d_so, d_eh, d_z, d_cig,
-            d_md, d_out, d_cnt, d_cnt + n + 1);
-    ctx->launches += (n_gf > 0 && n > n_gf) ? 1 : 0;
+    if ((rc = cig_launch_groups(ctx, o, d_reads, d_off, d_len, d_jobs, d_order, bounds, d_so, d_eh, d_z, d_cig, d_md, d_out, d_cnt, n))) return rc;
     BWAGPU_KERNEL_END(ctx, BWAGPU_KERN_CIGAR);
     BWAGPU_CUDA(ctx, cudaGetLastError());
     if ((rc = cig_scan(ctx, d_cnt, d_scan, n + 1))) return rc;
@@ -242,12 +285,6 @@ extern "C" int bwagpu_reg2aln_batch(bwagpu_ctx *ctx, const bwagpu_cigar_opt *opt
     BWAGPU_CUDA(ctx, cudaMemcpyAsync(d_reads, enc_reads, (size_t)bytes, cudaMemcpyHostToDevice, ctx->stream));
     BWAGPU_CUDA(ctx, cudaMemcpyAsync(d_off, off, (size_t)nseq * 8, cudaMemcpyHostToDevice, ctx->stream));
     BWAGPU_CUDA(ctx, cudaMemcpyAsync(d_len, len, (size_t)nseq * 4, cudaMemcpyHostToDevice, ctx->stream));
-#ifdef CIG_EH_LOCAL
-    const size_t smem_bytes = 0;
-#else
-    const size_t smem_bytes = (size_t)2 * (CIG_SMEM_QLEN + 1) * CIG_TPB * 4;
-#endif
-    BWAGPU_CUDA(ctx, cudaFuncSetAttribute(cigar_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
     const int64_t budget = 4LL << 30;                         // slab bytes per chunk
     CigSlabOff *h_so = (CigSlabOff *)malloc(sizeof(CigSlabOff) * (size_t)n_jobs);
     uint64_t *h_key = (uint64_t *)malloc(8 * (size_t)n_jobs);
@@ -268,7 +305,7 @@ extern "C" int bwagpu_reg2aln_batch(bwagpu_ctx *ctx, const bwagpu_cigar_opt *opt
             if (lq > CIG_SMEM_QLEN) cur.eh += 2 * (lq + 1);
             cur.z += zb; cur.cigar += lq + lt + 4; cur.md += 3 * lt + 16;
             // sort key: gap-free jobs first, the others by the size of their backtrack matrix
-            h_key[j1 - j0] = ((uint64_t)(gapfree ? 0 : 1 + (zb < (1 << 30) ? zb : (1 << 30))) << 32) | (uint32_t)(j1 - j0);
+            h_key[j1 - j0] = ((uint64_t)cig_key(gapfree, lq > CIG_SMEM_QLEN ? 4 : cig_tier(o, b.qb, b.qe, b.rb, b.re, b.truesc, b.w), zb) << 32) | (uint32_t)(j1 - j0);
             ++j1;
         }
         const int64_t n = j1 - j0;
@@ -293,19 +330,12 @@ extern "C" int bwagpu_reg2aln_batch(bwagpu_ctx *ctx, const bwagpu_cigar_opt *opt
         if (e == cudaSuccess) e = cudaMemcpyAsync(d_so, h_so + j0, (size_t)n * sizeof(CigSlabOff), cudaMemcpyHostToDevice, ctx->stream);
         if (e == cudaSuccess) e = cudaMemsetAsync(d_cnt, 0, (size_t)(n + 1) * 16, ctx->stream);
         if (e != cudaSuccess) { free(h_so); free(h_key); free(h_order); BWAGPU_FAIL(ctx, BWAGPU_ERR_CUDA, "reg2aln_batch: upload -> %s", cudaGetErrorString(e)); }
-        // gap-free jobs (sorted first) need no DP rows: launched without shared memory, at full occupancy
-        int64_t n_gf = 0;
-        while (n_gf < n && (h_key[n_gf] >> 32) == 0) ++n_gf;
+        // groups of the sorted list: gap-free jobs (no DP rows, full occupancy), then the window tiers
+        int64_t first[6] = {n, n, n, n, n, n}, bounds[7];
+        for (int64_t k = n - 1; k >= 0; --k) first[cig_key_tier((uint32_t)(h_key[k] >> 32)) + 1] = k;
+        cig_bounds(first, n, bounds);
         BWAGPU_KERNEL_BEGIN(ctx);
-        if (n_gf > 0)
-            cigar_kernel<<<(unsigned)((n_gf + CIG_TPB - 1) / CIG_TPB), CIG_TPB, 0, ctx->stream>>>(
-                o, ctx->l_pac, (const uint8_t *)ctx->d_ref_string, d_reads, d_off, d_len, d_jobs, d_order, 0, n_gf, d_so, d_eh, d_z, d_cig,
-                d_md, d_out, d_cnt, d_cnt + n + 1);
-        if (n > n_gf)
-            cigar_kernel<<<(unsigned)((n - n_gf + CIG_TPB - 1) / CIG_TPB), CIG_TPB, smem_bytes, ctx->stream>>>(
-                o, ctx->l_pac, (const uint8_t *)ctx->d_ref_string, d_reads, d_off, d_len, d_jobs, d_order, n_gf, n, d_so, d_eh, d_z, d_cig,
-                d_md, d_out, d_cnt, d_cnt + n + 1);
-        ctx->launches += (n_gf > 0 && n > n_gf) ? 1 : 0;
+        CIG_TRY(cig_launch_groups(ctx, o, d_reads, d_off, d_len, d_jobs, d_order, bounds, d_so, d_eh, d_z, d_cig, d_md, d_out, d_cnt, n));
         BWAGPU_KERNEL_END(ctx, BWAGPU_KERN_CIGAR);
         CIG_TRY(cig_scan(ctx, d_cnt, d_scan, n + 1));
         CIG_TRY(cig_scan(ctx, d_cnt + n + 1, d_scan + n + 1, n + 1));

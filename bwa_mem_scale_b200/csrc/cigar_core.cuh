@@ -21,6 +21,8 @@ struct CigarOpt { int8_t mat[25]; int32_t a, o_del, e_del, o_ins, e_ins, w; };
 struct CigarScratch {
     int32_t *eh;        // 2 x (qlen + 1) words, element k at eh[k * eh_stride]: H and E rows of ksw_global2
     int eh_stride;      // 1 for a private slab; blockDim for the interleaved shared-memory layout (bank = thread)
+    int eh_mask;        // rows are a circular window of eh_mask + 1 columns (a power of two >= 2 * band + 2: the DP
+                        // only ever touches columns beg..end of a row); 0x7fffffff = full rows of qlen + 1 columns
     uint8_t *z;         // backtrack matrix, n_col x tlen for the widest band tried
     uint32_t *cigar;    // qlen + tlen + 2 entries
     char *md;           // MD text, 3 x tlen + 16 bytes
@@ -66,24 +68,29 @@ CIG_HD inline int cig_global2(const CigarOpt &o, const CigarSeqs &s, int w, cons
 {
     const int qlen = s.lq, tlen = s.lt;
     const int oe_del = o.o_del + o.e_del, oe_ins = o.o_ins + o.e_ins;
-    const int n_col = qlen < 2 * w + 1 ? qlen : 2 * w + 1;
-    const int st = sc.eh_stride;
-    int32_t *H = sc.eh, *E = sc.eh + (int64_t)(qlen + 1) * st;
+    // row stride of the backtrack matrix, padded to whole 32-bit words: a row's bytes are stored four at a time
+    const int n_col = ((qlen < 2 * w + 1 ? qlen : 2 * w + 1) + 3) & ~3;
+    const int st = sc.eh_stride, mk = sc.eh_mask;
+    const int rows = mk == 0x7fffffff ? qlen + 1 : mk + 1;
+    int32_t *H = sc.eh, *E = sc.eh + (int64_t)rows * st;
+#define CIG_IX(j) (((j) & mk) * st)
     H[0] = 0; E[0] = CIG_MINUS_INF;
     int j;
-    for (j = 1; j <= qlen && j <= w; ++j) { H[j * st] = -(o.o_ins + o.e_ins * j); E[j * st] = CIG_MINUS_INF; }
-    for (; j <= qlen; ++j) H[j * st] = E[j * st] = CIG_MINUS_INF;
+    for (j = 1; j <= qlen && j <= w; ++j) { H[CIG_IX(j)] = -(o.o_ins + o.e_ins * j); E[CIG_IX(j)] = CIG_MINUS_INF; }
+    for (; j <= qlen && j < rows; ++j) H[CIG_IX(j)] = E[CIG_IX(j)] = CIG_MINUS_INF;   // beyond the window: written before read
     for (int i = 0; i < tlen; ++i) {
         int32_t f = CIG_MINUS_INF, h1;
         const int8_t *mrow = o.mat + s.ta(i) * 5;
         const int beg = i > w ? i - w : 0;
         const int end = i + w + 1 < qlen ? i + w + 1 : qlen;
         h1 = beg == 0 ? -(o.o_del + o.e_del * (i + 1)) : CIG_MINUS_INF;
-        uint8_t *zi = sc.z + (int64_t)i * n_col;
+        uint32_t *zw = (uint32_t *)(sc.z + (int64_t)i * n_col);
+        uint32_t acc = 0;
+        int nb = 0;
         for (j = beg; j < end; ++j) {
-            int32_t m = H[j * st], e = E[j * st], h, t;
+            int32_t m = H[CIG_IX(j)], e = E[CIG_IX(j)], h, t;
             uint8_t d;
-            H[j * st] = h1;
+            H[CIG_IX(j)] = h1;
             m += mrow[s.qa(j)];
             d = m >= e ? 0 : 1;
             h = m >= e ? m : e;
@@ -94,16 +101,19 @@ CIG_HD inline int cig_global2(const CigarOpt &o, const CigarSeqs &s, int w, cons
             e -= o.e_del;
             d |= e > t ? 1 << 2 : 0;
             e = e > t ? e : t;
-            E[j * st] = e;
+            E[CIG_IX(j)] = e;
             t = m - oe_ins;
             f -= o.e_ins;
             d |= f > t ? 2 << 4 : 0;
             f = f > t ? f : t;
-            zi[j - beg] = d;
+            acc |= (uint32_t)d << (8 * nb);
+            if (++nb == 4) { *zw++ = acc; acc = 0; nb = 0; }
         }
-        H[end * st] = h1; E[end * st] = CIG_MINUS_INF;
+        if (nb) *zw = acc;
+        H[CIG_IX(end)] = h1; E[CIG_IX(end)] = CIG_MINUS_INF;
     }
-    const int score = H[qlen * st];
+    const int score = H[CIG_IX(qlen)];
+#undef CIG_IX
     int n = 0, which = 0;
     int i = tlen - 1, k = (i + w + 1 < qlen ? i + w + 1 : qlen) - 1;
     while (i >= 0 && k >= 0) {
@@ -119,13 +129,14 @@ CIG_HD inline int cig_global2(const CigarOpt &o, const CigarSeqs &s, int w, cons
     return score;
 }
 
-// bwa_gen_cigar2; returns false where the reference returns a NULL cigar (empty / strand-bridging / out-of-range window)
-CIG_HD inline bool cig_gen_cigar2(const CigarOpt &o, int w_, int64_t l_pac, const uint8_t *ref_string, const uint8_t *query,
+// bwa_gen_cigar2; returns 0 where the reference returns a NULL cigar (empty / strand-bridging / out-of-range window), 1 when
+// done, 2 when this try's band needs more row columns than the scratch window holds (the caller re-runs the region with full rows)
+CIG_HD inline int cig_gen_cigar2(const CigarOpt &o, int w_, int64_t l_pac, const uint8_t *ref_string, const uint8_t *query,
                                   int l_query, int64_t rb, int64_t re, const CigarScratch &sc, CigarResult *res)
 {
     res->n_cigar = 0; res->nm = -1; res->l_md = 0;
-    if (l_query <= 0 || rb >= re || (rb < l_pac && re > l_pac)) return false;
-    if (rb < 0 || re > (l_pac << 1)) return false;                        // bns_get_seq would clip: re - rb != rlen
+    if (l_query <= 0 || rb >= re || (rb < l_pac && re > l_pac)) return 0;
+    if (rb < 0 || re > (l_pac << 1)) return 0;                        // bns_get_seq would clip: re - rb != rlen
     CigarSeqs s;
     s.q = query; s.lq = l_query; s.t = ref_string + rb; s.lt = (int)(re - rb); s.rev = rb >= l_pac;
     const int rlen = s.lt;
@@ -146,6 +157,7 @@ CIG_HD inline bool cig_gen_cigar2(const CigarOpt &o, int w_, int64_t l_pac, cons
         w = w < w_ ? w : w_;
         const int min_w = diff + 3;
         w = w > min_w ? w : min_w;
+        if (sc.eh_mask != 0x7fffffff && 2 * w + 2 > sc.eh_mask + 1) return 2;
         res->score = cig_global2(o, s, w, sc, &n_cigar);
     }
     // NM and MD (src/bwa.cpp:429-459)
@@ -170,11 +182,11 @@ CIG_HD inline bool cig_gen_cigar2(const CigarOpt &o, int w_, int64_t l_pac, cons
     }
     cig_putw(sc.md, &l, u);
     res->n_cigar = n_cigar; res->nm = n_mm + n_gap; res->l_md = l;
-    return true;
+    return 1;
 }
 
 // the alignment core of mem_reg2aln (src/bwamem.cpp:2551-2570): l_query = qe - qb bases of the read from qb
-CIG_HD inline bool cig_reg2aln(const CigarOpt &o, int64_t l_pac, const uint8_t *ref_string, const uint8_t *read, int qb, int qe,
+CIG_HD inline int cig_reg2aln(const CigarOpt &o, int64_t l_pac, const uint8_t *ref_string, const uint8_t *read, int qb, int qe,
                                int64_t rb, int64_t re, int truesc, int reg_w, const CigarScratch &sc, CigarResult *res)
 {
     int tmp = cig_infer_bw(qe - qb, (int)(re - rb), truesc, o.a, o.o_del, o.e_del);
@@ -182,16 +194,16 @@ CIG_HD inline bool cig_reg2aln(const CigarOpt &o, int64_t l_pac, const uint8_t *
     w2 = w2 > tmp ? w2 : tmp;
     if (w2 > o.w) w2 = w2 < reg_w ? w2 : reg_w;
     int i = 0, last_sc = -(1 << 30);
-    bool ok;
+    int ok;
     do {
         w2 = w2 < o.w << 2 ? w2 : o.w << 2;
         ok = cig_gen_cigar2(o, w2, l_pac, ref_string, read + qb, qe - qb, rb, re, sc, res);
-        if (!ok) return false;
+        if (ok != 1) return ok;
         if (res->score == last_sc || w2 == o.w << 2) break;
         last_sc = res->score;
         w2 <<= 1;
     } while (++i < 3 && res->score < truesc - o.a);
-    return true;
+    return 1;
 }
 
 // true when cig_reg2aln takes the gap-free shortcut of bwa_gen_cigar2 (first band 0 and equal lengths; a zero band
@@ -208,7 +220,7 @@ CIG_HD inline bool cig_is_gapfree(const CigarOpt &o, int qb, int qe, int64_t rb,
 
 // bytes of backtrack matrix the widest try of cig_reg2aln can need for this region: the band of try k is
 // min((max_gap + diff + 1) >> 1, w2 << k) raised to diff + 3, k = 0..2, w2 << k capped at 4 * opt->w
-CIG_HD inline int64_t cig_z_bytes(const CigarOpt &o, int qb, int qe, int64_t rb, int64_t re, int truesc, int reg_w)
+CIG_HD inline int cig_band_max(const CigarOpt &o, int qb, int qe, int64_t rb, int64_t re, int truesc, int reg_w)
 {
     const int lq = qe - qb, lt = (int)(re - rb);
     if (lq <= 0 || lt <= 0) return 0;
@@ -226,8 +238,38 @@ CIG_HD inline int64_t cig_z_bytes(const CigarOpt &o, int qb, int qe, int64_t rb,
     int64_t w = (max_gap + diff + 1) >> 1;
     w = w < wt ? w : wt;
     w = w > diff + 3 ? w : diff + 3;
-    const int64_t n_col = lq < 2 * w + 1 ? lq : 2 * w + 1;
+    return (int)w;
+}
+CIG_HD inline int64_t cig_z_bytes(const CigarOpt &o, int qb, int qe, int64_t rb, int64_t re, int truesc, int reg_w)
+{
+    const int lq = qe - qb, lt = (int)(re - rb);
+    if (lq <= 0 || lt <= 0) return 0;
+    const int64_t w = cig_band_max(o, qb, qe, rb, re, truesc, reg_w);
+    const int64_t n_col = ((lq < 2 * w + 1 ? lq : 2 * w + 1) + 3) & ~3;     // padded row stride, as cig_global2 lays it out
     return n_col * lt;
+}
+// window tier of a region, by the band of its FIRST try (later tries, rare, re-run with full rows): the smallest power of
+// two W in {16, 32, 64, 128} with W >= 2 * band + 2, or 4 = full rows
+CIG_HD inline int cig_tier(const CigarOpt &o, int qb, int qe, int64_t rb, int64_t re, int truesc, int reg_w)
+{
+    const int lq = qe - qb, lt = (int)(re - rb);
+    if (lq <= 0 || lt <= 0) return 0;
+    int tmp = cig_infer_bw(lq, lt, truesc, o.a, o.o_del, o.e_del);
+    int w2 = cig_infer_bw(lq, lt, truesc, o.a, o.o_ins, o.e_ins);
+    w2 = w2 > tmp ? w2 : tmp;
+    if (w2 > o.w) w2 = w2 < reg_w ? w2 : reg_w;
+    w2 = w2 < o.w << 2 ? w2 : o.w << 2;
+    const int max_ins = (int)((double)(((lq + 1) >> 1) * o.mat[0] - o.o_ins) / o.e_ins + 1.);
+    const int max_del = (int)((double)(((lq + 1) >> 1) * o.mat[0] - o.o_del) / o.e_del + 1.);
+    int max_gap = max_ins > max_del ? max_ins : max_del;
+    max_gap = max_gap > 1 ? max_gap : 1;
+    const int diff = lt > lq ? lt - lq : lq - lt;
+    int w = (max_gap + diff + 1) >> 1;
+    w = w < w2 ? w : w2;
+    w = w > diff + 3 ? w : diff + 3;
+    const int need = 2 * w + 2;
+    if (need >= lq + 1) return 4;
+    return need <= 16 ? 0 : need <= 32 ? 1 : need <= 64 ? 2 : need <= 128 ? 3 : 4;
 }
 
 // the tail of mem_reg2aln (src/bwamem.cpp:2571-2600): position, removal of a leading / trailing deletion, soft clips.

@@ -17,7 +17,7 @@ enum { SCR_BSW_PAIRS = 0, SCR_BSW_REF, SCR_BSW_QER, SCR_BSW_WORK, SCR_MISC0, SCR
        SCR_ERT_MEMS, SCR_ERT_HITS, SCR_ERT_KEYS, SCR_ERT_MEMS2, SCR_ERT_HITS2, SCR_ERT_KEYS2, SCR_ERT_CNT,
        SCR_ERT_SLAB, SCR_ERT_LIST, SCR_ERT_COFF,
        SCR_CIG_JOBS, SCR_CIG_OUT, SCR_CIG_SLABOFF, SCR_CIG_EH, SCR_CIG_Z, SCR_CIG_CIGAR, SCR_CIG_MD, SCR_CIG_CNT, SCR_CIG_SCAN,
-       SCR_CIG_OUTC, SCR_CIG_OUTM, SCR_CIG_ORDER,
+       SCR_CIG_OUTC, SCR_CIG_OUTM, SCR_CIG_ORDER, SCR_CIG_REDO,
        BWAGPU_NSCRATCH };
 
 struct bwagpu_ctx {

@@ -13,6 +13,8 @@ OPT_CASES = [
     ("penalties", dict(a=2, b=5, o_del=5, e_del=2, o_ins=7, e_ins=1, pen_clip5=3, pen_clip3=8)),
     ("narrow_band", dict(w=10, zdrop=20)),
 ]
+# golden record sets: the option cases + "retry" (default options, truesc inflated so that the band-doubling retries run)
+GOLDEN_CASES = OPT_CASES + [("retry", {})]
 
 
 def _indel(rng, x, n_events):

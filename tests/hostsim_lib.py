@@ -65,10 +65,11 @@ def reg2aln(lib, copt, l_pac, ref_string, flat, off, ln, jobs):
     lib.hostsim_reg2aln.argtypes = [C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                                     C.c_int64, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_int64, C.c_void_p]
     while True:
-        cigar, md, n_out = np.zeros(ccap, np.uint32), np.zeros(mcap, np.uint8), np.zeros(2, np.int64)
+        cigar, md, n_out = np.zeros(ccap, np.uint32), np.zeros(mcap, np.uint8), np.zeros(3, np.int64)
         lib.hostsim_reg2aln(C.byref(copt), l_pac, ref_string.ctypes.data, flat.ctypes.data, off.ctypes.data, ln.ctypes.data,
                             jobs.ctypes.data, len(jobs), outs.ctypes.data, cigar.ctypes.data, ccap, md.ctypes.data, mcap,
                             n_out.ctypes.data)
         if n_out[0] <= ccap and n_out[1] <= mcap:
+            reg2aln.last_redo = int(n_out[2])
             return outs, cigar[:n_out[0]].copy(), md[:n_out[1]].copy()
         ccap, mcap = int(n_out[0]) + 16, int(n_out[1]) + 16

@@ -20,7 +20,7 @@ def setup(gpu_ctx):
     return ref, RegToAln(gpu_ctx), flat, off, ln
 
 
-@pytest.mark.parametrize("case", gc.OPT_CASES, ids=[c[0] for c in gc.OPT_CASES])
+@pytest.mark.parametrize("case", gc.GOLDEN_CASES, ids=[c[0] for c in gc.GOLDEN_CASES])
 def test_gpu_cigar_matches_reference_records(setup, case):
     name, kw = case
     ref, r2a, flat, off, ln = setup
@@ -45,7 +45,7 @@ def test_gpu_cigar_empty_rejected_and_errors(setup, gpu_ctx):
         r2a.mem_reg2aln(cigar_opt(), flat, off, ln, jobs)
 
 
-@pytest.mark.parametrize("case", gc.OPT_CASES[:2], ids=[c[0] for c in gc.OPT_CASES[:2]])
+@pytest.mark.parametrize("case", [gc.GOLDEN_CASES[0], gc.GOLDEN_CASES[3]], ids=["default", "retry"])
 def test_gpu_cigar_device_resident_form(setup, gpu_ctx, case):
     name, kw = case
     ref, r2a, flat, off, ln = setup
