@@ -924,17 +924,22 @@ def main():
     ap.add_argument("--contexts", type=int, default=1, help="mem workload: contexts (streams) per GPU")
     ap.add_argument("--no-cpu", action="store_true")
     args = ap.parse_args()
+    # stdout carries exactly one JSON line: everything else that writes to fd 1 (NCCL's version banner, the reference's
+    # own printf chatter in the CPU arm) is sent to stderr; the line itself goes to a private copy of the original fd
+    sys.stdout.flush()
+    real_stdout = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
     rank = int(os.environ.get("RANK", 0))
     world = int(os.environ.get("WORLD_SIZE", 1))
     fn = {"mem": bench_mem, "bsw": bench_bsw, "seed": bench_seed, "ksw": bench_ksw, "cigar": bench_cigar}[args.workload]
     if args.impl == "reference":
         if rank == 0:
-            print(json.dumps(fn(args, 0, world)))
+            print(json.dumps(fn(args, 0, world)), file=real_stdout, flush=True)
         return
     init_dist(world)
     out = fn(args, rank, world)
     if rank == 0 and out is not None:
-        print(json.dumps(out))
+        print(json.dumps(out), file=real_stdout, flush=True)
     if _dist is not None:
         _dist.destroy_process_group()
 
