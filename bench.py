@@ -347,6 +347,8 @@ def bench_seed(args, rank, world):
 # dram__bytes_read.sum + dram__bytes_write.sum of seed_collect_kernel<true>, one launch of the default
 # configuration (100 Mbp, 1 M reads, FMA on): profiles/r01_ncu_mem_kernels_summary.txt
 NCU_SEED_COLLECT_TRAFFIC = int(61.099131e9 + 10.094755e9)
+# same for the first (all reads) launch of ert_seed_kernel, bench.py --ert 1, 1 M reads: profiles/r01_ncu_ert_seed_v2_summary.txt
+NCU_ERT_SEED_TRAFFIC = int(4.793306e9 + 1.737873e9)
 KERNELS = {0: "seed_collect", 1: "seed_sort", 2: "sa_walk", 3: "bsw", 4: "bsw_generic", 7: "chain2aln", 8: "chain_seeds",
            9: "emf_probe", 10: "ert_seed", 11: "ert_emit"}
 
@@ -624,7 +626,9 @@ def bench_mem(args, rank, world):
     ach = alg_bytes / (k_ms / max(k_n, 1) * 1e-3) / 1e9
     nprof = max(min(args.steps, 2), 1)
     traffic = None
-    if args.ref_mbp == 100.0 and n == 1_000_000 and args.fma and not args.emf and args.exact_frac is None:
+    if args.ert and n == 1_000_000 and not args.emf:
+        traffic = NCU_ERT_SEED_TRAFFIC         # same configuration as the committed capture (first of the two launches)
+    elif args.ref_mbp == 100.0 and n == 1_000_000 and args.fma and not args.emf and args.exact_frac is None:
         traffic = NCU_SEED_COLLECT_TRAFFIC     # same configuration as the committed capture
     purged = int(((out["qb"] == -1) & (out["qe"] == -1)).sum())
     res = {"metric": "aligned reads/s (151bp SE, seed+extend)", "value": n * world * args.steps / (ms * 1e-3),
