@@ -24,7 +24,7 @@
 #endif
 #define ERT_KMER_ENTRIES (1LL << 30)
 
-struct ErtStats { unsigned long long n_bytes, n_hits; unsigned int max_mem, max_hit, n_ovf, pad_; int bad_site, bad_read; long long bad_val; };
+struct ErtStats { unsigned long long n_bytes, n_hits; unsigned int max_mem, max_hit, n_ovf, pad_; int bad_site, bad_read; long long bad_val; unsigned long long bad_u, bad_v; };
 
 struct ErtSlab { ErtMemRec *mems; int64_t *hits; uint64_t *keys; int mem_cap, hit_cap; };
 
@@ -46,7 +46,7 @@ ert_seed_kernel(ErtView ix, ErtOpt o, int max_occ, const uint8_t *__restrict__ r
     w.hits = sl.hits + (int64_t)item * sl.hit_cap; w.hit_cap = sl.hit_cap;
     w.seed_read(o);
 #ifdef ERT_GUARD
-    if (w.bad_site && atomicCAS(&st->bad_site, 0, w.bad_site) == 0) { st->bad_read = r; st->bad_val = w.bad_val; }
+    if (w.bad_site && atomicCAS(&st->bad_site, 0, w.bad_site) == 0) { st->bad_read = r; st->bad_val = w.bad_val; st->bad_u = w.bad_u; st->bad_v = w.bad_v; }
 #endif
     if (w.n_mem > sl.mem_cap || w.hit_peak > sl.hit_cap) {
         atomicMax(&st->max_mem, (unsigned)w.n_mem);
@@ -318,7 +318,7 @@ static int ert_seed_dev(bwagpu_ctx *ctx, const bwagpu_seed_opt *opt, int max_occ
     BWAGPU_CUDA(ctx, cudaMemcpyAsync(&st, d_st, sizeof st, cudaMemcpyDeviceToHost, ctx->stream));
     BWAGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
 #ifdef ERT_GUARD
-    fprintf(stderr, "ERT_GUARD pass 1: bad_site=%d read=%d val=%lld n_ovf=%u max_mem=%u max_hit=%u\n", st.bad_site, st.bad_read, st.bad_val, st.n_ovf, st.max_mem, st.max_hit);
+    fprintf(stderr, "ERT_GUARD pass 1: bad_site=%d read=%d val=0x%llx u=0x%llx v=0x%llx n_ovf=%u max_mem=%u max_hit=%u mlt_bytes=%lld\n", st.bad_site, st.bad_read, (unsigned long long)st.bad_val, st.bad_u, st.bad_v, st.n_ovf, st.max_mem, st.max_hit, (long long)ctx->ert_mlt_bytes);
 #endif
     const int n_ovf = (int)st.n_ovf;
     for (int pass = 0; n_ovf > 0; ++pass) {

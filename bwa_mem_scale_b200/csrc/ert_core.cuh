@@ -118,7 +118,7 @@ struct ErtWalker {
     // ---- index access ------------------------------------------------------------------------------
 #ifdef ERT_GUARD
     // debug build: every index / text access is bounds-checked; the first violation is recorded, the access skipped
-    int bad_site; int64_t bad_val;
+    int bad_site; int64_t bad_val; uint64_t bad_u, bad_v;
     ERT_HDI bool ok_mlt(const uint8_t *p, int n, int site)
     {
         const int64_t o = (int64_t)(p - ix.mlt);
@@ -137,6 +137,17 @@ struct ErtWalker {
         if (!ok_mlt(p, n, 1)) return 0;
         uint64_t v = 0;
         for (int b = 0; b < n; ++b) v |= (uint64_t)p[b] << (8 * b);
+#if defined(ERT_LD_CHECK) && defined(ERT_GUARD) && defined(__CUDA_ARCH__)
+        {   // experiment: the aligned two-word form next to the byte form; first disagreement is recorded (site 9)
+            const unsigned long long a = (unsigned long long)p;
+            const uint64_t *q = (const uint64_t *)(a & ~7ull);
+            const int sh = (int)(a & 7) * 8;
+            uint64_t u = *q >> sh;
+            if (sh + 8 * n > 64) u |= *(q + 1) << (64 - sh);
+            if (n < 8) u &= (1ull << (8 * n)) - 1;
+            if (u != v && !bad_site) { bad_site = 9; bad_val = (int64_t)(p - ix.mlt) | ((int64_t)n << 56); bad_u = u; bad_v = v; }
+        }
+#endif
         return v;
     }
     ERT_HDI uint8_t ldb(const uint8_t *p) { ++n_bytes; return ok_mlt(p, 1, 2) ? *p : 0; }
