@@ -776,9 +776,8 @@ def bench_cigar(args, rank, world):
     """CIGAR / NM / MD of final alignment regions: jobs = the regions the device pipeline keeps
     for the default workload's reads, with 0.2 % indels added so that the banded global alignment runs; one step =
     bwagpu_reg2aln_batch over all of them (host buffers in and out: this seam has no device-resident form yet)."""
-    from bwa_mem_scale_b200 import (CIGAR_JOB_DTYPE, Context, Extender, FMI_search, REG_DTYPE, RegToAln, chain_opt, cigar_opt,
-                                    ext_opt, fmindex, mem_core_device, pack_reads, seed_opt)
-    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from bwa_mem_scale_b200 import (CHAIN_DTYPE, CIGAR_JOB_DTYPE, Context, Extender, FMI_search, REG_DTYPE, RegToAln, chain_opt,
+                                    cigar_opt, ext_opt, fmindex, mem_core_device, pack_reads, seed_opt)
     ref, idx, reads = seed_inputs(args, rank)
     rng = np.random.default_rng(900 + rank)
     reads = np.ascontiguousarray(reads).copy()
@@ -798,8 +797,7 @@ def bench_cigar(args, rank, world):
     flat, off, ln = pack_reads(reads)
     d = (ctx.upload(flat), ctx.upload(off), ctx.upload(ln))
     sres, cres, ares = mem_core_device(fmi, ext, seed_opt(), chain_opt(), ext_opt(), d[0], d[1], d[2], n, 151)
-    import oracle_lib as ol
-    regs, chains = np.zeros(ares.n_regs, REG_DTYPE), np.zeros(cres.n_chains, ol.CHAIN_DTYPE)
+    regs, chains = np.zeros(ares.n_regs, REG_DTYPE), np.zeros(cres.n_chains, CHAIN_DTYPE)
     ctx.d2h(regs, ares.d_regs); ctx.d2h(chains, cres.d_chains)
     keep = ~((regs["qb"] == -1) & (regs["qe"] == -1))
     r = regs[keep]
@@ -809,7 +807,10 @@ def bench_cigar(args, rank, world):
     jobs["read"] = chains["seqid"][r["chain"]]
     cfg["jobs_per_gpu"] = int(len(jobs))
     if args.impl == "reference" or not args.no_cpu:
+        # CPU arm only: the reference's own mem_reg2aln through the test-side tap library
         import tempfile
+        sys.path.insert(0, os.path.join(ROOT, "tests"))
+        import oracle_lib as ol
         thr = cpu_threads()
         sample = jobs[: min(len(jobs), 40000 * thr)]
         with tempfile.TemporaryDirectory() as td:
