@@ -120,6 +120,8 @@ _SIGS = {
     "bwagpu_bsw_get_scores_device": (C.c_int, [C.c_void_p, C.POINTER(BswParams), C.c_int,
                                                C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p,
                                                C.c_int64, C.c_int32, C.c_int32]),
+    "bwagpu_bsw_get_scores_noalloc": (C.c_int, [C.c_void_p, C.POINTER(BswParams), C.c_int, C.c_void_p, C.c_void_p,
+                                                C.c_void_p, C.c_int32, C.c_int32, C.c_int32]),
     "bwagpu_index_load_ref": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_void_p, C.c_void_p,
                                         C.c_void_p]),
     "bwagpu_chain_seeds": (C.c_int, [C.c_void_p, C.POINTER(ChainOpt), C.c_void_p, C.c_int64, C.c_void_p, C.c_int64,

@@ -120,6 +120,23 @@ int bwagpu_bsw_get_scores_device(bwagpu_ctx *ctx, const bwagpu_bsw_params *prm, 
                                  int64_t ref_bytes, const uint8_t *d_seqBufQer, int64_t qer_bytes,
                                  int32_t numPairs, int32_t w);
 
+/* No counterpart in the reference.
+ * The same banded-SW extension for callers that cannot allocate (code under CUDA graph capture, tight serving
+ * loops, harnesses that forbid cudaMalloc): this call issues no cudaMalloc / cudaFree and no allocating library
+ * routine, and does not synchronise.  Device pointers in, results written into d_pairArray in place, asynchronous on
+ * the context's stream, bit-identical to bwagpu_bsw_get_scores_device.  The DP column state lives in one
+ * file-scope device array of BWAGPU_NOALLOC_SCRATCH_BYTES that every GPU loading the library holds until exit.
+ * max_len2 = the caller's bound on len2 over the batch (it sizes the per-thread columns; a pair with len2 > max_len2 is
+ * not computed and gets -1 in all six result fields); max_len2 > BWAGPU_NOALLOC_MAX_LEN2 is rejected with
+ * BWAGPU_ERR_RANGE.  numPairs and len1 are unbounded.  All calls on one GPU share the array: calls that overlap
+ * on that GPU (other streams or contexts) race; calls on one context are ordered by its stream.  The array keeps the
+ * previous call's contents, which is harmless: every pair initialises the columns it reads. */
+#define BWAGPU_NOALLOC_SCRATCH_BYTES (16 << 20)
+#define BWAGPU_NOALLOC_MAX_LEN2 1020
+int bwagpu_bsw_get_scores_noalloc(bwagpu_ctx *ctx, const bwagpu_bsw_params *prm, int kind,
+                                  bwagpu_seqpair *d_pairArray, const uint8_t *d_seqBufRef,
+                                  const uint8_t *d_seqBufQer, int32_t numPairs, int32_t max_len2, int32_t w);
+
 /* ---- S2': chains -> alignment regions ---------------------------------------------------------
  * The whole of mem_chain2aln_across_reads_V2 (reference src/bwamem.cpp:2810-3745) on the device:
  * extension jobs are built from the chains, the read and the HBM-resident reference text, run through
