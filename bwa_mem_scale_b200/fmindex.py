@@ -215,6 +215,19 @@ def write_fasta(path: str, ref_fwd: np.ndarray, name: str = "chr1", width: int =
             f.write(b"\n".join(rows) + b"\n")
 
 
+def write_fasta_contigs(path: str, ref_fwd: np.ndarray, contig_len, width: int = 80) -> None:
+    """Multi-contig FASTA: `ref_fwd` cut into consecutive contigs chr1, chr2, ... of the given lengths."""
+    letters = np.frombuffer(b"ACGTN", dtype=np.uint8)[np.asarray(ref_fwd, dtype=np.uint8)]
+    assert int(np.sum(contig_len)) == len(letters)
+    o = 0
+    with open(path, "wb") as f:
+        for i, ln in enumerate(contig_len):
+            f.write(b">chr%d\n" % (i + 1))
+            chunk = letters[o:o + int(ln)]
+            f.write(b"\n".join(chunk[j:j + width].tobytes() for j in range(0, len(chunk), width)) + b"\n")
+            o += int(ln)
+
+
 def write_fastq(path: str, reads: np.ndarray, lens=None) -> None:
     letters = np.frombuffer(b"ACGTN", dtype=np.uint8)
     with open(path, "wb") as f:

@@ -251,3 +251,38 @@ def rescue_jobs(n_jobs: int, seed: int = 11, qlen_lo: int = 151, qlen_hi: int = 
         refs.append(win); qers.append(q)
         ro += wl; qo += ql
     return pairs, np.concatenate(refs + [np.zeros(64, np.uint8)]), np.concatenate(qers + [np.zeros(64, np.uint8)])
+
+
+def gapped_reads(text: np.ndarray, n_reads: int, seed: int, read_len: int = 151, err: float = 0.02,
+                 small_indel_frac: float = 0.30, long_indel_frac: float = 0.10, n_run_frac: float = 0.05,
+                 starts=None):
+    """Reads with gaps, as a list of arrays: each read is cut from `text` (any 0..3 array: the concatenated
+    contigs, or the forward + reverse-complement text when reads across the strand boundary are wanted), then
+    a fraction carries one 1-3 base insertion or deletion, a fraction one 5-15 base one (wide enough to push
+    the banded extension's max_off past 3/4 of a narrow band, which triggers the band-doubling retry of
+    mem_chain2aln_across_reads_V2, reference src/bwamem.cpp:3248), a fraction a run of 2-6 N; substitutions at
+    `err`; random strand.  `starts` pins the first reads to given text positions (contig ends etc.)."""
+    rng = np.random.default_rng(seed)
+    out = []
+    for i in range(n_reads):
+        span = read_len + 16
+        s = int(starts[i]) if starts is not None and i < len(starts) else int(rng.integers(0, len(text) - span))
+        src = text[s:s + span].copy()
+        u = rng.random()
+        if u < small_indel_frac + long_indel_frac:
+            g = int(rng.integers(1, 4)) if u < small_indel_frac else int(rng.integers(5, 16))
+            p = int(rng.integers(25, read_len - 25))
+            if rng.random() < 0.5:
+                src = np.concatenate([src[:p], src[p + g:]])                                   # deletion
+            else:
+                src = np.concatenate([src[:p], rng.integers(0, 4, g).astype(np.uint8), src[p:]])   # insertion
+        r = src[:read_len].copy()
+        sub = rng.random(len(r)) < err
+        r[sub] = (r[sub] + rng.integers(1, 4, size=int(sub.sum()))) & 3
+        if rng.random() < n_run_frac:
+            p, g = int(rng.integers(0, len(r) - 6)), int(rng.integers(2, 7))
+            r[p:p + g] = 4
+        if rng.random() < 0.5:
+            r = np.where(r > 3, 4, 3 - r)[::-1].astype(np.uint8)
+        out.append(np.ascontiguousarray(r, np.uint8))
+    return out

@@ -37,5 +37,33 @@ def main():
     print({k: v.shape for k, v in out.items()}, os.path.getsize(os.path.join(HERE, "c2a_golden.npz")))
 
 
+def main_hard():
+    """c2a_hard_golden.npz: the three-contig genome with gapped / boundary reads of c2a_cases.hard_reads."""
+    ref, ref_string = cc.hard_genome()
+    reads = cc.hard_reads(ref)
+    flat, off, ln = ol.pack_reads(reads)
+    out = {}
+    with tempfile.TemporaryDirectory() as td:
+        prefix = os.path.join(td, "ref")
+        fmindex.write_fasta_contigs(prefix + ".fa", ref, cc.HARD_CONTIGS)
+        ol.ref_index(prefix, prefix + ".fa")
+        assert np.array_equal(np.fromfile(prefix + ".0123", np.uint8), ref_string)
+        rm = ol.RefMem(prefix)
+        out["l_pac"] = np.array([rm.l_pac], np.int64)
+        out["contig_off"], out["contig_len"] = rm.contig_off, rm.contig_len
+        assert list(rm.contig_len) == list(cc.HARD_CONTIGS)
+        for name, kw in cc.OPT_CASES_HARD:
+            chains, seeds, regs, reg_off = rm.core(ol.mem_opt(**kw), flat, off, ln)
+            out[f"{name}_chains"], out[f"{name}_seeds"] = chains, seeds
+            out[f"{name}_regs"] = cc.reg_matrix(regs).astype(np.int64)
+            out[f"{name}_frac_rep"] = regs["frac_rep"]
+    np.savez_compressed(os.path.join(HERE, "c2a_hard_golden.npz"), **out)
+    print({k: v.shape for k, v in out.items()}, os.path.getsize(os.path.join(HERE, "c2a_hard_golden.npz")))
+
+
 if __name__ == "__main__":
-    main()
+    if len(sys.argv) > 1 and sys.argv[1] == "hard":
+        main_hard()
+    else:
+        main()
+        main_hard()

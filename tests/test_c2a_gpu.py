@@ -34,6 +34,27 @@ def test_gpu_chain2aln_matches_golden(extender, case):
     assert np.array_equal(got["frac_rep"], GOLD[f"{name}_frac_rep"])
 
 
+HARD = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "c2a_hard_golden.npz"))
+
+
+@pytest.mark.parametrize("case", cc.OPT_CASES_HARD, ids=[c[0] for c in cc.OPT_CASES_HARD])
+def test_gpu_chain2aln_matches_hard_golden(gpu_ctx, extender, case):
+    """Three contigs, gapped reads, boundary reads (reference records; band retries and empty left windows inside)."""
+    name, kw = case
+    ref, ref_string = cc.hard_genome()
+    ext = Extender(ref_string, int(HARD["l_pac"][0]), HARD["contig_off"], HARD["contig_len"], ctx=gpu_ctx)
+    flat, off, ln = ol.pack_reads(cc.hard_reads(ref))
+    chains, seeds = HARD[f"{name}_chains"], HARD[f"{name}_seeds"]
+    o = ol.mem_opt(**kw)
+    got = ext.mem_chain2aln_across_reads_V2(to_ext_opt(o), flat, off, ln, chains, seeds)
+    assert np.array_equal(cc.reg_matrix(got), HARD[f"{name}_regs"])
+    assert np.array_equal(got["frac_rep"], HARD[f"{name}_frac_rep"])
+    if o["w"] <= 12:
+        assert (got["w"][got["qb"] != -1] == 2 * o["w"]).sum() > 10
+    ref0, rs0 = cc.genome()     # restore the module fixture's reference replica on the shared context
+    Extender(rs0, int(GOLD["l_pac"][0]), GOLD["contig_off"], GOLD["contig_len"], ctx=gpu_ctx)
+
+
 def test_gpu_chain2aln_empty_and_subset(extender):
     ref, ref_string, ext = extender
     flat, off, ln = ol.pack_reads(cc.golden_reads(ref))
@@ -53,17 +74,25 @@ def test_gpu_chain2aln_vs_reference_live(gpu_ctx, tmp_path):
         pytest.skip("oracle/_ref not present")
     ref = synth.repeat_reference(2_000_000, 9, n_families=30, repeat_frac=0.2, divergence=0.03)
     prefix = str(tmp_path / "ref")
-    fmindex.write_fasta(prefix + ".fa", ref)
+    contigs = (900_000, 600_000, 300_000, 200_000)
+    fmindex.write_fasta_contigs(prefix + ".fa", ref, contigs)
     ol.ref_index(prefix, prefix + ".fa")
     rm = ol.RefMem(prefix)
+    assert list(rm.contig_len) == list(contigs)
     ref_string = fmindex.text_with_revcomp(ref)
     ext = Extender(ref_string, rm.l_pac, rm.contig_off, rm.contig_len, ctx=gpu_ctx)
-    for seed, kw in ((1, dict(read_len=151, err=0.01)), (2, dict(read_len=250, err=0.05))):
-        reads, _, _ = synth.simulate_reads(ref, 5000, seed=seed, **kw)
+    ends = np.cumsum(contigs)
+    pins = [int(e) - k for e in ends[:-1] for k in range(5, 150, 9)] + [len(ref) - k for k in range(5, 150, 9)]
+    gapped = synth.gapped_reads(ref_string, 5000, seed=3, starts=pins)
+    for reads, okw in ((synth.simulate_reads(ref, 5000, seed=1, read_len=151, err=0.01)[0], {}),
+                       (synth.simulate_reads(ref, 5000, seed=2, read_len=250, err=0.05)[0], {}),
+                       (gapped, {}), (gapped, dict(w=10, zdrop=20)), (gapped, dict(w=4))):
         flat, off, ln = ol.pack_reads(reads)
-        o = ol.mem_opt()
+        o = ol.mem_opt(**okw)
         chains, seeds, regs, _ = rm.core(o, flat, off, ln)
         got = ext.mem_chain2aln_across_reads_V2(to_ext_opt(o), flat, off, ln, chains, seeds)
-        assert np.array_equal(cc.reg_matrix(got), cc.reg_matrix(regs)), kw
+        assert np.array_equal(cc.reg_matrix(got), cc.reg_matrix(regs)), okw
+        if okw:
+            assert (regs["w"][regs["qb"] != -1] == 2 * o["w"]).sum() > 50      # band-doubling retries ran
     ref0, rs0 = cc.genome()     # restore the module fixture's reference replica on the shared context
     Extender(rs0, int(GOLD["l_pac"][0]), GOLD["contig_off"], GOLD["contig_len"], ctx=gpu_ctx)

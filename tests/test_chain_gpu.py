@@ -71,6 +71,29 @@ def test_gpu_reads_to_regions_matches_golden(small, gpu_ctx, case):
     assert ares.n_left > 0 and ares.n_right > 0 and ares.n_pairs8 + ares.n_pairs16 + ares.n_pairs_scalar == ares.n_left + ares.n_right
 
 
+HARD = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "c2a_hard_golden.npz"))
+
+
+@pytest.mark.parametrize("case", cc.OPT_CASES_HARD, ids=[c[0] for c in cc.OPT_CASES_HARD])
+def test_gpu_reads_to_regions_hard_golden(small, gpu_ctx, case):
+    """Device pipeline on the three-contig genome with gapped / boundary reads: chains and regions equal the
+    reference's, and the band-doubling retry path really ran (counted by the launcher)."""
+    from test_chain_hostsim import hard_index
+    name, kw = case
+    ref, idx = hard_index()
+    ext = Extender(fmindex.text_with_revcomp(ref), int(HARD["l_pac"][0]), HARD["contig_off"], HARD["contig_len"], ctx=gpu_ctx)
+    o = ol.mem_opt(**kw)
+    chains, regs, ares = run_device_pipeline(gpu_ctx, idx, ext, o, cc.hard_reads(ref))
+    assert np.array_equal(chains, HARD[f"{name}_chains"])
+    assert np.array_equal(cc.reg_matrix(regs), HARD[f"{name}_regs"])
+    if o["w"] <= 12:
+        assert ares.n_retry_left + ares.n_retry_right > 10
+        assert (regs["w"][regs["qb"] != -1] == 2 * o["w"]).sum() > 10
+    assert ares.n_pairs8 > 0 and ares.n_pairs16 > 0
+    rs0 = fmindex.text_with_revcomp(fc.small_index()[0])   # restore the module fixture's replica
+    Extender(rs0, int(GOLD["l_pac"][0]), GOLD["contig_off"], GOLD["contig_len"], ctx=gpu_ctx)
+
+
 def test_gpu_reads_to_regions_vs_reference_live(gpu_ctx, tmp_path):
     """Config-1 shape (1 Mbp random reference, 10 k x 151 bp, 1 % errors) against the reference run live."""
     if ol.ref_api("plain", "sse41") is None or ol.ref_binary("plain", "sse41") is None:

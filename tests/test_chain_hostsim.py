@@ -57,6 +57,33 @@ def test_chaining_matches_golden(case):
     assert np.bincount(chains["seqid"]).max() > 40
 
 
+HARD = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "c2a_hard_golden.npz"))
+_hard = {}
+
+
+def hard_index():
+    if not _hard:
+        from bwa_mem_scale_b200 import fmindex
+        _hard["ref"] = cc.hard_genome()[0]
+        _hard["idx"] = fmindex.build_fm_index(_hard["ref"], device="cpu")
+    return _hard["ref"], _hard["idx"]
+
+
+@pytest.mark.parametrize("case", cc.OPT_CASES_HARD, ids=[c[0] for c in cc.OPT_CASES_HARD])
+def test_chaining_matches_hard_golden(case):
+    """Multi-contig chaining: seeds that bridge two contigs or the strand boundary are dropped (bns_intv2rid < 0,
+    reference src/bwamem.cpp:872-876), chains never span contigs."""
+    name, kw = case
+    ref, idx = hard_index()
+    flat, off, ln = ol.pack_reads(cc.hard_reads(ref))
+    o = ol.mem_opt(**kw)
+    sm, co = seeds_of(idx, o, flat, off, ln)
+    chains, seeds = hostsim_chains(o, HARD["l_pac"][0], HARD["contig_off"], HARD["contig_len"], sm, co, ln)
+    assert np.array_equal(chains, HARD[f"{name}_chains"])
+    assert np.array_equal(seeds, HARD[f"{name}_seeds"])
+    assert set(chains["rid"]) == {0, 1, 2}
+
+
 def test_chaining_matches_reference_live(tmp_path):
     if ol.ref_api("plain", "sse41") is None or ol.ref_binary("plain", "sse41") is None:
         pytest.skip("oracle/_ref not built (no /root/reference here)")
