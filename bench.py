@@ -357,9 +357,9 @@ def ert_bench_data():
     """Reference-built ERT index of the small bench genome (scripts/make_ert_bench_data.py): the genome, the k-mer
     table entries of the k-mers that occur and the tree blob.  The entries of absent k-mers are computed on the
     device (bwagpu_index_complete_ert)."""
-    p = os.path.join(ROOT, "bench_data", "ert_small_genome.npz")
+    p = os.path.join(ROOT, "tests", "golden", "ert_small_genome.npz")
     if not os.path.exists(p):
-        raise SystemExit("bench.py --ert 1 needs bench_data/ert_small_genome.npz (scripts/make_ert_bench_data.py)")
+        raise SystemExit("bench.py --ert 1 needs tests/golden/ert_small_genome.npz (scripts/make_ert_bench_data.py)")
     return np.load(p)
 
 
@@ -923,7 +923,7 @@ def main():
     ap.add_argument("--band", type=int, default=100)
     ap.add_argument("--kind", type=int, default=16, choices=[8, 16])
     ap.add_argument("--fma", type=int, default=1, help="use the FMA smem tables (config 2)")
-    ap.add_argument("--ert", type=int, default=0, help="mem workload: ERT seeding on the small reference-built index in bench_data/")
+    ap.add_argument("--ert", type=int, default=0, help="mem workload: ERT seeding on the small reference-built index in tests/golden/")
     ap.add_argument("--emf", type=int, default=0, help="mem workload: exact-match filter in front (table built on the host)")
     ap.add_argument("--exact-frac", type=float, default=None, help="fraction of error-free reads (default: what 1%% substitutions give)")
     ap.add_argument("--contexts", type=int, default=1, help="mem workload: contexts (streams) per GPU")

@@ -1,5 +1,5 @@
 """Bench-scale live parity of the ERT path on the GPU box: GPU (sparse index + k-mer table completion on the device)
-against the UNMODIFIED reference (oracle/_ref taps) on fresh simulated reads over bench_data/ert_small_genome.npz.
+against the UNMODIFIED reference (oracle/_ref taps) on fresh simulated reads over tests/golden/ert_small_genome.npz.
   seeding : bwagpu_seed_ert            vs get_seeds[_prefix] / reseed[_prefix] / last
   pipeline: reads -> regions on device vs mem_kernel1_core_ert + mem_chain2aln_across_reads_V2
 Writes a one-line JSON verdict.  Test infrastructure (uses oracle/_ref); not a product path."""
@@ -23,7 +23,7 @@ from bwa_mem_scale_b200 import (Context, ErtIndex, ErtSeeding, Extender, FMI_sea
 
 def main():
     n_seed, n_pipe = int(sys.argv[1]) if len(sys.argv) > 1 else 200000, int(sys.argv[2]) if len(sys.argv) > 2 else 50000
-    d = np.load(os.path.join(ROOT, "bench_data", "ert_small_genome.npz"))
+    d = np.load(os.path.join(ROOT, "tests", "golden", "ert_small_genome.npz"))
     ref = np.ascontiguousarray(d["ref"])
     ref_string = fmindex.text_with_revcomp(ref)
     idx = fmindex.build_fm_index(ref)

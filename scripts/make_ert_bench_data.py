@@ -1,10 +1,10 @@
-"""Makes bench_data/ert_small_genome.npz for `bench.py --ert 1` (run in the build container only).
+"""Makes tests/golden/ert_small_genome.npz for `bench.py --ert 1` (run in the build container only).
 
 The reference's `index -a ert` (oracle/_ref/bwa-mem2.scale.*) is run over tests/fmi_cases.small_genome() (300 kbp,
 40 % repeats, a poly-A and a dinucleotide run) unless argv[1] names the prefix of an existing build.  Kept: the
 genome, the k-mer table entries of the k-mers that OCCUR (type != INVALID) and the tree blob verbatim.  The entries
 of absent k-mers hold nothing but a LEP mask, which bwagpu_index_complete_ert recomputes from the FM-index on the
-device — so 8 GiB of table travel as a few MB.  bench_data/ is git-ignored (it ships to the GPU box with gpurun)."""
+device — so 8 GiB of table travel as a few MB.  the file is a tracked fixture (5 MB)."""
 import os
 import subprocess
 import sys
@@ -34,7 +34,7 @@ def main():
         blk = np.asarray(k[s:s + (1 << 26)])
         idxs.append((np.flatnonzero(blk & 3) + s).astype(np.uint32))
     idx = np.concatenate(idxs)
-    out = os.path.join(ROOT, "bench_data", "ert_small_genome.npz")
+    out = os.path.join(ROOT, "tests", "golden", "ert_small_genome.npz")
     os.makedirs(os.path.dirname(out), exist_ok=True)
     np.savez_compressed(out, ref=ref, kmer_idx=idx, kmer_val=np.asarray(k[idx.astype(np.int64)]),
                         mlt_table=np.fromfile(prefix + ".mlt_table", np.uint8))

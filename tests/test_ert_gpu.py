@@ -120,16 +120,15 @@ def test_gpu_kmer_table_completion_from_fm_index(tiny_ert, gpu_ctx):
     assert np.array_equal(hits, GOLD["default_hits"])
 
 
-BENCH_DATA = os.path.join(os.path.dirname(ec.HERE), "bench_data", "ert_small_genome.npz")
+BENCH_DATA = os.path.join(ec.HERE, "golden", "ert_small_genome.npz")
 
 
-@pytest.mark.skipif(not (os.path.exists(BENCH_DATA) and ol.ref_binary() is not None),
-                    reason="needs bench_data/ert_small_genome.npz (scripts/make_ert_bench_data.py) and oracle/_ref")
 def test_gpu_ert_live_against_reference_at_scale(gpu_ctx):
     """60 k fresh reads on the 300 kbp reference-built index (k-mer table completed on the device): MEMs and hits vs the
     unmodified reference's get_seeds / reseed / last, chains and regions vs its mem_kernel1_core_ert + V2."""
     import tempfile
     from bwa_mem_scale_b200 import FMI_search, synth
+    assert ol.ref_binary() is not None, "oracle/_ref missing: run __graft_entry__.build() where /root/reference exists"
     d = np.load(BENCH_DATA)
     ref = np.ascontiguousarray(d["ref"])
     ref_string = fmindex.text_with_revcomp(ref)
