@@ -13,3 +13,4 @@ from .emf import PerfectTable, PerfectMatch, SEED_ENTRY_DTYPE, PERFECT_DTYPE  # 
 from .shard import shard_bounds, shard_reads, merge_smems, merge_regions  # noqa: F401
 from .ert import ErtIndex, ErtSeeding, ERT_MEM_DTYPE, mem_core_ert_device  # noqa: F401
 from .cigar import RegToAln, cigar_opt, CIGAR_JOB_DTYPE, CIGAR_OUT_DTYPE  # noqa: F401
+from .mem import MemChunk, mem_opt, BATCH_SIZE  # noqa: F401

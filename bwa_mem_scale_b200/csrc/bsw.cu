@@ -7,6 +7,14 @@
 #include "bsw_thread.cuh"
 #include "bsw_fast.cuh"
 
+// DP cells computed (sum over rows of hi - lo), accumulated per warp into the context's counter: the GCUPS numerator
+__device__ __forceinline__ void bsw_add_cells(unsigned long long *cells, int mine)
+{
+    const unsigned m = __activemask();
+    const unsigned tot = __reduce_add_sync(m, (unsigned)mine);
+    if ((threadIdx.x & 31) == (__ffs(m) - 1) && tot) atomicAdd(cells, (unsigned long long)tot);
+}
+
 #define BSW_TPB 128
 #define BSW_FAST_TPB 64          // threads per block of the shared-memory kernel
 #define BSW_FAST_MAX_LEN2 512    // longest query whose column state is kept in shared memory
@@ -18,19 +26,24 @@ template <int KIND>
 __global__ void __launch_bounds__(BSW_FAST_TPB)
 bsw_fast_kernel(bwagpu_bsw_params prm, bwagpu_seqpair *__restrict__ pairs,
                 const uint8_t *__restrict__ ref, const uint8_t *__restrict__ qer,
-                const uint32_t *__restrict__ order, int first, int n, int w, int cols)
+                const uint32_t *__restrict__ order, int first, int n, int w, int cols,
+                unsigned long long *__restrict__ cells)
 {
     extern __shared__ uint32_t colmem[];
     const int slot = first + blockIdx.x * BSW_FAST_TPB + threadIdx.x;
-    if (slot >= n) return;
-    const uint32_t i = order[slot];
-    const bwagpu_seqpair sp = pairs[i];
-    const BswOut o = bsw_lane_fast<KIND, BSW_FAST_TPB>(prm, qer + sp.idq, sp.len2, ref + sp.idr, sp.len1, w,
-                                                        sp.h0, colmem + threadIdx.x,
-                                                        colmem + cols * BSW_FAST_TPB + threadIdx.x);
-    bwagpu_seqpair *d = &pairs[i];
-    d->score = o.score; d->tle = o.tle; d->gtle = o.gtle; d->qle = o.qle;
-    d->gscore = o.gscore; d->max_off = o.max_off;
+    int my_cells = 0;
+    if (slot < n) {
+        const uint32_t i = order[slot];
+        const bwagpu_seqpair sp = pairs[i];
+        const BswOut o = bsw_lane_fast<KIND, BSW_FAST_TPB>(prm, qer + sp.idq, sp.len2, ref + sp.idr, sp.len1, w,
+                                                            sp.h0, colmem + threadIdx.x,
+                                                            colmem + cols * BSW_FAST_TPB + threadIdx.x);
+        bwagpu_seqpair *d = &pairs[i];
+        d->score = o.score; d->tle = o.tle; d->gtle = o.gtle; d->qle = o.qle;
+        d->gscore = o.gscore; d->max_off = o.max_off;
+        my_cells = o.cells;
+    }
+    bsw_add_cells(cells, my_cells);
 }
 
 // generic path over order[0 .. n_long): pairs too long for the shared-memory kernel
@@ -38,11 +51,13 @@ template <int KIND>
 __global__ void __launch_bounds__(BSW_TPB)
 bsw_thread_order_kernel(bwagpu_bsw_params prm, bwagpu_seqpair *__restrict__ pairs,
                         const uint8_t *__restrict__ ref, const uint8_t *__restrict__ qer,
-                        const uint32_t *__restrict__ order, int n, int w, uint32_t *__restrict__ work)
+                        const uint32_t *__restrict__ order, int n, int w, uint32_t *__restrict__ work,
+                        unsigned long long *__restrict__ cells)
 {
     const int64_t T = (int64_t)gridDim.x * blockDim.x;
     const int64_t t0 = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     uint32_t *col = work + t0;
+    unsigned long long mine = 0;
     for (int64_t s = t0; s < n; s += T) {
         const uint32_t i = order[s];
         const bwagpu_seqpair sp = pairs[i];
@@ -50,7 +65,9 @@ bsw_thread_order_kernel(bwagpu_bsw_params prm, bwagpu_seqpair *__restrict__ pair
         bwagpu_seqpair *d = &pairs[i];
         d->score = o.score; d->tle = o.tle; d->gtle = o.gtle; d->qle = o.qle;
         d->gscore = o.gscore; d->max_off = o.max_off;
+        mine += o.cells;
     }
+    if (mine) atomicAdd(cells, mine);
 }
 
 // sort key: query length, then target length (descending order puts the longest pairs first)
@@ -71,11 +88,12 @@ template <int KIND>
 __global__ void __launch_bounds__(BSW_TPB)
 bsw_thread_kernel(bwagpu_bsw_params prm, bwagpu_seqpair *__restrict__ pairs,
                   const uint8_t *__restrict__ ref, const uint8_t *__restrict__ qer, int n, int w,
-                  uint32_t *__restrict__ work)
+                  uint32_t *__restrict__ work, unsigned long long *__restrict__ cells)
 {
     const int64_t T = (int64_t)gridDim.x * blockDim.x;
     const int64_t t0 = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     uint32_t *col = work + t0;
+    unsigned long long mine = 0;
     for (int64_t i = t0; i < n; i += T) {
         bwagpu_seqpair sp = pairs[i];
         const uint8_t *tg = ref + sp.idr, *qr = qer + sp.idq;
@@ -87,7 +105,9 @@ bsw_thread_kernel(bwagpu_bsw_params prm, bwagpu_seqpair *__restrict__ pairs,
         bwagpu_seqpair *d = &pairs[i];
         d->score = o.score; d->tle = o.tle; d->gtle = o.gtle; d->qle = o.qle;
         d->gscore = o.gscore; d->max_off = o.max_off;
+        mine += o.cells;
     }
+    if (mine) atomicAdd(cells, mine);
 }
 
 // Shared memory per thread follows the query length, so the sorted order is cut into length tiers
@@ -124,6 +144,33 @@ __global__ void bsw_maxlen_kernel(const bwagpu_seqpair *__restrict__ pairs, int 
     if ((threadIdx.x & 31) == 0) { atomicMax(&out[0], m1); atomicMax(&out[1], m2); }
 }
 
+// the context's DP-cell counter (device, zeroed when first allocated; bwagpu_bsw_cells reads / resets it)
+static int bsw_cells_ptr(bwagpu_ctx *ctx, unsigned long long **out)
+{
+    const bool fresh = ctx->scratch[SCR_BSW_CELLS] == nullptr;
+    int rc = bwagpu_scratch(ctx, SCR_BSW_CELLS, 64, (void **)out);
+    if (rc) return rc;
+    if (fresh) BWAGPU_CUDA(ctx, cudaMemsetAsync(*out, 0, 64, ctx->stream));
+    return BWAGPU_OK;
+}
+
+extern "C" int bwagpu_bsw_cells(bwagpu_ctx *ctx, int reset, int64_t *cells)
+{
+    if (!ctx) return BWAGPU_ERR_ARG;
+    BWAGPU_CUDA(ctx, cudaSetDevice(ctx->device));
+    unsigned long long *d;
+    int rc = bsw_cells_ptr(ctx, &d);
+    if (rc) return rc;
+    if (cells) {
+        unsigned long long h = 0;
+        BWAGPU_CUDA(ctx, cudaMemcpyAsync(&h, d, 8, cudaMemcpyDeviceToHost, ctx->stream));
+        BWAGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+        *cells = (int64_t)h;
+    }
+    if (reset) BWAGPU_CUDA(ctx, cudaMemsetAsync(d, 0, 8, ctx->stream));
+    return BWAGPU_OK;
+}
+
 static int bsw_check(bwagpu_ctx *ctx, const bwagpu_bsw_params *prm, int kind, int32_t n, int32_t w)
 {
     if (!ctx) return BWAGPU_ERR_ARG;
@@ -149,19 +196,21 @@ static int bsw_launch_thread(bwagpu_ctx *ctx, const bwagpu_bsw_params *prm, int 
     void *work;
     int rc = bwagpu_scratch(ctx, SCR_BSW_WORK, words * 4, &work);
     if (rc) return rc;
+    unsigned long long *cells;
+    if ((rc = bsw_cells_ptr(ctx, &cells))) return rc;
     BWAGPU_KERNEL_BEGIN(ctx);
     switch (kind) {
     case BWAGPU_BSW_16BIT:
         bsw_thread_kernel<16><<<blocks, BSW_TPB, 0, ctx->stream>>>(*prm, d_pairs, d_ref, d_qer, n,
-                                                                  w, (uint32_t *)work);
+                                                                  w, (uint32_t *)work, cells);
         break;
     case BWAGPU_BSW_8BIT:
         bsw_thread_kernel<8><<<blocks, BSW_TPB, 0, ctx->stream>>>(*prm, d_pairs, d_ref, d_qer, n,
-                                                                 w, (uint32_t *)work);
+                                                                 w, (uint32_t *)work, cells);
         break;
     default:
         bsw_thread_kernel<0><<<blocks, BSW_TPB, 0, ctx->stream>>>(*prm, d_pairs, d_ref, d_qer, n,
-                                                                 w, (uint32_t *)work);
+                                                                 w, (uint32_t *)work, cells);
     }
     BWAGPU_KERNEL_END(ctx, BWAGPU_KERN_BSW);
     BWAGPU_CUDA(ctx, cudaGetLastError());
@@ -178,6 +227,8 @@ static int bsw_launch_sorted(bwagpu_ctx *ctx, const bwagpu_bsw_params *prm, bwag
     if ((rc = bwagpu_scratch(ctx, SCR_BSW_KEYS, (int64_t)n * 8, (void **)&keys))) return rc;
     if ((rc = bwagpu_scratch(ctx, SCR_BSW_ORDER, (int64_t)n * 8, (void **)&order))) return rc;
     if ((rc = bwagpu_scratch(ctx, SCR_MISC0, 64, (void **)&d_m))) return rc;
+    unsigned long long *cells;
+    if ((rc = bsw_cells_ptr(ctx, &cells))) return rc;
     uint32_t *keys_out = keys + n, *idx_in = order + n;
     BWAGPU_CUDA(ctx, cudaMemsetAsync(d_m, 0, 16, ctx->stream));
     bsw_key_kernel<<<(n + 255) / 256, 256, 0, ctx->stream>>>(d_pairs, n, keys, idx_in, d_m + 2);
@@ -205,7 +256,7 @@ static int bsw_launch_sorted(bwagpu_ctx *ctx, const bwagpu_bsw_params *prm, bwag
         if ((rc = bwagpu_scratch(ctx, SCR_BSW_WORK, (int64_t)(max_len2 + 4) * T * 4, &work))) return rc;
         BWAGPU_KERNEL_BEGIN(ctx);
         bsw_thread_order_kernel<KIND><<<blocks, BSW_TPB, 0, ctx->stream>>>(*prm, d_pairs, d_ref, d_qer, order, n_long, w,
-                                                                         (uint32_t *)work);
+                                                                         (uint32_t *)work, cells);
         BWAGPU_KERNEL_END(ctx, BWAGPU_KERN_BSW_GENERIC);
         BWAGPU_CUDA(ctx, cudaGetLastError());
     }
@@ -225,7 +276,7 @@ static int bsw_launch_sorted(bwagpu_ctx *ctx, const bwagpu_bsw_params *prm, bwag
                 if (len2 > cap2) len2 = cap2;
                 BWAGPU_KERNEL_BEGIN(ctx);
                 bsw_fast_kernel<KIND><<<(hi - lo + BSW_FAST_TPB - 1) / BSW_FAST_TPB, BSW_FAST_TPB, smem_of(len2), ctx->stream>>>(
-                    *prm, d_pairs, d_ref, d_qer, order, lo, hi, w, len2 + 3);
+                    *prm, d_pairs, d_ref, d_qer, order, lo, hi, w, len2 + 3, cells);
                 BWAGPU_KERNEL_END(ctx, BWAGPU_KERN_BSW);
                 BWAGPU_CUDA(ctx, cudaGetLastError());
             }

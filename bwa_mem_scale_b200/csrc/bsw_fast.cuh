@@ -73,6 +73,7 @@ __device__ BswOut bsw_lane_fast(const bwagpu_bsw_params &p, const uint8_t *__res
     int best = h0, bx = 0, by = 0, gsc = -1, gi = 0, off = 0;
     bool live = true;
     int nlo = 0, nhi = ncol;
+    int cells = 0;
 
     int tc_next = nrow > 0 ? target[0] : 0;       // one row ahead: keeps the byte load off the row's critical path
     for (int i = 0; i < nrow; ++i) {
@@ -84,6 +85,7 @@ __device__ BswOut bsw_lane_fast(const bwagpu_bsw_params &p, const uint8_t *__res
         else tlo = (mis4 & ~(0xFFu << (8 * tc))) | ((uint32_t)(sc_match & 0xFF) << (8 * tc));
 
         const int lo = max(nlo, i - w), hi = min(min(nhi, i + w + 1), ncol);
+        cells += max(hi - lo, 0);
         int left = lo == 0 ? max(h0 - p.o_del - (i + 1) * e_del, 0) : 0;
         int er = 0;
         int key = 0;                              // rowmax << 16 | rowarg
@@ -211,6 +213,6 @@ __device__ BswOut bsw_lane_fast(const bwagpu_bsw_params &p, const uint8_t *__res
     }
 #undef COL
     BswOut o;
-    o.score = best; o.qle = by; o.tle = bx; o.gtle = gi; o.gscore = gsc; o.max_off = off;
+    o.score = best; o.qle = by; o.tle = bx; o.gtle = gi; o.gscore = gsc; o.max_off = off; o.cells = cells;
     return o;
 }

@@ -11,7 +11,7 @@
 #include <stdint.h>
 #include "../../include/bwagpu.h"
 
-struct BswOut { int score, qle, tle, gtle, gscore, max_off; };
+struct BswOut { int score, qle, tle, gtle, gscore, max_off; int cells; };   // cells = sum over rows of (hi - lo): DP cells computed
 
 __device__ __forceinline__ int bsw_sym(uint8_t c, int nsym) { return c == 4 ? nsym : (int)c; }
 
@@ -58,10 +58,12 @@ __device__ BswOut bsw_lane_pair(const bwagpu_bsw_params &p, const uint8_t *__res
     int best = h0, bx = 0, by = 0, gsc = -1, gi = 0, off = 0;
     bool live = true;
     int nlo = 0, nhi = ncol;
+    int cells = 0;
 
     for (int i = 0; i < nrow; ++i) {
         const int t = bsw_sym(target[i], wrap);
         int lo = max(nlo, i - w), hi = min(min(nhi, i + w + 1), ncol);
+        cells += max(hi - lo, 0);
         // first-column value H(i,-1); the SIMD code reads a pad value on the very last row,
         // which can only reach state that is never read again
         int left = lo == 0 ? max(h0 - p.o_del - (i + 1) * p.e_del, 0) : 0;
@@ -132,7 +134,7 @@ __device__ BswOut bsw_lane_pair(const bwagpu_bsw_params &p, const uint8_t *__res
     }
 #undef COL
     BswOut o;
-    o.score = best; o.qle = by; o.tle = bx; o.gtle = gi; o.gscore = gsc; o.max_off = off;
+    o.score = best; o.qle = by; o.tle = bx; o.gtle = gi; o.gscore = gsc; o.max_off = off; o.cells = cells;
     return o;
 }
 
@@ -157,11 +159,12 @@ __device__ BswOut bsw_scalar_pair(const bwagpu_bsw_params &p, const uint8_t *__r
         w = min(w, max(g, 1));
     }
     int best = h0, best_i = -1, best_j = -1, g_i = -1, g_sc = -1, off = 0;
-    int lo = 0, hi = qlen;
+    int lo = 0, hi = qlen, cells = 0;
     for (int i = 0; i < tlen; ++i) {
         const int t = target[i];
         lo = max(lo, i - w);
         hi = min(min(hi, i + w + 1), qlen);
+        cells += max(hi - lo, 0);
         int left = lo == 0 ? max(h0 - (p.o_del + p.e_del * (i + 1)), 0) : 0;
         int f = 0, rowmax = 0, rowarg = -1, j;
         for (j = lo; j < hi; ++j) {
@@ -200,6 +203,6 @@ __device__ BswOut bsw_scalar_pair(const bwagpu_bsw_params &p, const uint8_t *__r
 #undef EC
     BswOut o;
     o.score = best; o.qle = best_j + 1; o.tle = best_i + 1; o.gtle = g_i + 1; o.gscore = g_sc;
-    o.max_off = off;
+    o.max_off = off; o.cells = cells;
     return o;
 }

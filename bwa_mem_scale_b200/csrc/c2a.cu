@@ -536,6 +536,8 @@ extern "C" int bwagpu_chain2aln_device(bwagpu_ctx *ctx, const bwagpu_ext_opt *eo
     memset(res, 0, sizeof *res);
     if (n_chains == 0 || n_seeds == 0) return BWAGPU_OK;
     BWAGPU_CUDA(ctx, cudaSetDevice(ctx->device));
+    int64_t cells0 = 0;
+    if (bwagpu_bsw_cells(ctx, 0, &cells0)) return BWAGPU_ERR_CUDA;
     C2aOpt o = { eo->a, eo->b, eo->o_del, eo->e_del, eo->o_ins, eo->e_ins, eo->pen_clip5, eo->pen_clip3, eo->w, eo->zdrop };
     int rc;
     int64_t *rmax, *first_chain, *last_chain, *sizes, *offs; uint64_t *keys; uint32_t *srt; int32_t *chain_of;
@@ -593,6 +595,9 @@ extern "C" int bwagpu_chain2aln_device(bwagpu_ctx *ctx, const bwagpu_ext_opt *eo
     BWAGPU_KERNEL_END(ctx, BWAGPU_KERN_C2A);
     BWAGPU_CUDA(ctx, cudaGetLastError());
     res->d_regs = regs; res->n_regs = n_seeds;
+    int64_t cells1 = 0;
+    if (bwagpu_bsw_cells(ctx, 0, &cells1)) return BWAGPU_ERR_CUDA;
+    res->sw_cells = cells1 - cells0;
     return BWAGPU_OK;
 }
 

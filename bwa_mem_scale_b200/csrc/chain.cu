@@ -15,6 +15,7 @@ struct ChainIn {
     const int64_t *coords; const int64_t *coord_off;        // SA coordinates of SMEM i: [coord_off[i], coord_off[i+1])
     const int32_t *len; int32_t nseq; int64_t n_smem;
     int32_t per_read;                                        // mem_chain_new (ERT path): no batch-wide SMEM bound
+    int32_t batch;                                           // reads per mem_chain_seeds call upstream (0 = this whole call)
 };
 
 __device__ __forceinline__ ChainScratch chain_scratch(bwagpu_seed *sd, WChain *ch, BtNode *nodes, int32_t *ord,
@@ -41,7 +42,15 @@ __global__ void __launch_bounds__(CHAIN_TPB, CHAIN_MINB) chain_build_kernel(Chai
     if (r >= in.nseq) return;
     cnt_chains[r] = 0; cnt_seeds[r] = 0;
     const int64_t s0 = in.smem_off[r], s1 = in.smem_off[r + 1];
-    if (s0 == s1 || (!in.per_read && in.n_smem <= 1) || in.len[r] < o.min_seed_len) return;   // :821-828 (incl. the num_smem - 1 bound)
+    if (s0 == s1 || in.len[r] < o.min_seed_len) return;                       // :821-828
+    if (!in.per_read) {                                                       // `pos < num_smem - 1` (:819): a batch with <= 1 SMEM yields nothing
+        int64_t nb = in.n_smem;
+        if (in.batch > 0) {
+            const int b0 = (r / in.batch) * in.batch, b1 = min(b0 + in.batch, in.nseq);
+            nb = in.smem_off[b1] - in.smem_off[b0];
+        }
+        if (nb <= 1) return;
+    }
     const int64_t c0 = in.coord_off[s0];
     ChainBuilder b;
     b.init(chain_scratch(sd, ch, nodes, ord, lst, c0, r));
@@ -154,7 +163,7 @@ static int chain_device(bwagpu_ctx *ctx, const bwagpu_chain_opt *opt, const bwag
                    opt->max_chain_extend, opt->mask_level, opt->drop_ratio };
     RefView rv = { ctx->l_pac, ctx->n_contigs, (const int64_t *)ctx->d_contig_off, (const int32_t *)ctx->d_contig_len,
                    (const uint8_t *)ctx->d_contig_alt };
-    ChainIn in = { d_smems, d_smem_off, d_coords, d_coord_off, d_len, nseq, n_smem, per_read };
+    ChainIn in = { d_smems, d_smem_off, d_coords, d_coord_off, d_len, nseq, n_smem, per_read, ctx->chain_batch_reads };
     bwagpu_seed *sd; WChain *ch; BtNode *nodes; int32_t *ord, *lst; int64_t *cnt, *offs; float *frac;
     if ((rc = bwagpu_scratch(ctx, SCR_CH_SD, (n_coords + 1) * (int64_t)sizeof(bwagpu_seed), (void **)&sd))) return rc;
     if ((rc = bwagpu_scratch(ctx, SCR_CH_CH, (n_coords + 1) * (int64_t)sizeof(WChain), (void **)&ch))) return rc;

@@ -18,6 +18,8 @@ enum { SCR_BSW_PAIRS = 0, SCR_BSW_REF, SCR_BSW_QER, SCR_BSW_WORK, SCR_MISC0, SCR
        SCR_ERT_SLAB, SCR_ERT_LIST, SCR_ERT_COFF,
        SCR_CIG_JOBS, SCR_CIG_OUT, SCR_CIG_SLABOFF, SCR_CIG_EH, SCR_CIG_Z, SCR_CIG_CIGAR, SCR_CIG_MD, SCR_CIG_CNT, SCR_CIG_SCAN,
        SCR_CIG_OUTC, SCR_CIG_OUTM, SCR_CIG_ORDER, SCR_CIG_REDO,
+       SCR_MEM_READS, SCR_MEM_OFF, SCR_MEM_LEN, SCR_MEM_EMF_RET, SCR_MEM_PERFECT, SCR_MEM_SKIP, SCR_MEM_CNT, SCR_MEM_KEEP,
+       SCR_MEM_POS, SCR_MEM_REGS, SCR_MEM_REGOFF, SCR_BSW_CELLS,
        BWAGPU_NSCRATCH };
 
 struct bwagpu_ctx {
@@ -53,6 +55,7 @@ struct bwagpu_ctx {
     void *d_ert_kmer, *d_ert_mlt;
     int64_t ert_mlt_bytes;
     int ert_mem_cap, ert_hit_cap;   // per-read slab capacities of the first ERT pass
+    int chain_batch_reads;      // unit of mem_chain_seeds' batch-wide SMEM bound (0 = the whole call); set by bwagpu_mem_process_chunk
     int seed_read_cap;          // per-read SMEM capacity of the seeding scratch (grows on overflow)
     // optional per-kernel CUDA-event timing (bwagpu_set_profiling): bench.py's roofline numbers
     int profiling;

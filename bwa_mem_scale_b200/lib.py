@@ -46,7 +46,34 @@ class ExtOpt(C.Structure):
 class C2aResult(C.Structure):
     _fields_ = [("d_regs", C.c_void_p)] + [(n, C.c_int64) for n in
                 ("n_regs", "n_left", "n_right", "n_retry_left", "n_retry_right", "n_pairs8", "n_pairs16",
-                 "n_pairs_scalar", "seq_bytes")]
+                 "n_pairs_scalar", "seq_bytes", "sw_cells")]
+
+
+class SeedOpt(C.Structure):
+    """bwagpu_seed_opt — the mem_opt_t fields seeding reads (reference src/bwamem.h:89-124)."""
+    _fields_ = [("min_seed_len", C.c_int32), ("split_factor", C.c_float), ("split_width", C.c_int32),
+                ("max_occ", C.c_int32), ("max_mem_intv", C.c_int64)]
+
+
+class ChainOpt(C.Structure):
+    """bwagpu_chain_opt — the mem_opt_t fields chaining reads (reference src/bwamem.h:89-124)."""
+    _fields_ = [(n, C.c_int32) for n in ("w", "max_chain_gap", "max_occ", "min_seed_len", "min_chain_weight",
+                                         "max_chain_extend")] + [("mask_level", C.c_float), ("drop_ratio", C.c_float)]
+
+
+class MemOpt(C.Structure):
+    """bwagpu_mem_opt — everything the worker-level entry needs of mem_opt_t / worker_t."""
+    _fields_ = [("seed", SeedOpt), ("chain", ChainOpt), ("ext", ExtOpt), ("use_ert", C.c_int32), ("use_emf", C.c_int32),
+                ("batch_size", C.c_int32), ("pad_", C.c_int32)]
+
+
+class MemResult(C.Structure):
+    """bwagpu_mem_result"""
+    _fields_ = [("d_regs", C.c_void_p), ("n_regs", C.c_int64), ("d_reg_off", C.c_void_p), ("d_emf_ret", C.c_void_p),
+                ("d_perfect", C.c_void_p)] + [(n, C.c_int64) for n in (
+                    "n_emf_hits", "n_smem", "n_coords", "n_chains", "n_seeds", "n_regs_raw", "n_sw_left", "n_sw_right",
+                    "n_sw_retry", "n_pairs8", "n_pairs16", "n_pairs_scalar", "sw_cells", "n_ext", "n_cp_records",
+                    "n_lf_steps", "n_index_bytes")]
 
 
 class FmIndexDesc(C.Structure):
@@ -54,12 +81,6 @@ class FmIndexDesc(C.Structure):
     (reference src/FMI_search.cpp:1251-1351); count[] in loaded form (file value + 1)."""
     _fields_ = [("reference_seq_len", C.c_int64), ("count", C.c_int64 * 5), ("cp_occ", C.c_void_p),
                 ("sa_ms_byte", C.c_void_p), ("sa_ls_word", C.c_void_p), ("sentinel_index", C.c_int64)]
-
-
-class SeedOpt(C.Structure):
-    """bwagpu_seed_opt — the mem_opt_t fields seeding reads (reference src/bwamem.h:89-124)."""
-    _fields_ = [("min_seed_len", C.c_int32), ("split_factor", C.c_float), ("split_width", C.c_int32),
-                ("max_occ", C.c_int32), ("max_mem_intv", C.c_int64)]
 
 
 class SeedResult(C.Structure):
@@ -84,12 +105,6 @@ class ErtResult(C.Structure):
     _fields_ = [("d_smems", C.c_void_p), ("n_smem", C.c_int64), ("d_coords", C.c_void_p),
                 ("n_coords", C.c_int64), ("d_coord_off", C.c_void_p), ("d_smem_off", C.c_void_p),
                 ("n_index_bytes", C.c_int64), ("n_hits", C.c_int64), ("n_retry_reads", C.c_int64)]
-
-
-class ChainOpt(C.Structure):
-    """bwagpu_chain_opt — the mem_opt_t fields chaining reads (reference src/bwamem.h:89-124)."""
-    _fields_ = [(n, C.c_int32) for n in ("w", "max_chain_gap", "max_occ", "min_seed_len", "min_chain_weight",
-                                         "max_chain_extend")] + [("mask_level", C.c_float), ("drop_ratio", C.c_float)]
 
 
 class ChainResult(C.Structure):
@@ -122,6 +137,13 @@ _SIGS = {
                                                C.c_int64, C.c_int32, C.c_int32]),
     "bwagpu_bsw_get_scores_noalloc": (C.c_int, [C.c_void_p, C.POINTER(BswParams), C.c_int, C.c_void_p, C.c_void_p,
                                                 C.c_void_p, C.c_int32, C.c_int32, C.c_int32]),
+    "bwagpu_bsw_cells": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(C.c_int64)]),
+    "bwagpu_mem_process_chunk": (C.c_int, [C.c_void_p, C.POINTER(MemOpt), C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32,
+                                           C.POINTER(MemResult)]),
+    "bwagpu_mem_process_chunk_device": (C.c_int, [C.c_void_p, C.POINTER(MemOpt), C.c_void_p, C.c_void_p, C.c_void_p,
+                                                  C.c_int32, C.c_int32, C.POINTER(MemResult)]),
+    "bwagpu_mem_fetch": (C.c_int, [C.c_void_p, C.POINTER(MemResult), C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p,
+                                   C.c_void_p]),
     "bwagpu_index_load_ref": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_void_p, C.c_void_p,
                                         C.c_void_p]),
     "bwagpu_chain_seeds": (C.c_int, [C.c_void_p, C.POINTER(ChainOpt), C.c_void_p, C.c_int64, C.c_void_p, C.c_int64,

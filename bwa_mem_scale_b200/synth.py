@@ -286,3 +286,24 @@ def gapped_reads(text: np.ndarray, n_reads: int, seed: int, read_len: int = 151,
             r = np.where(r > 3, 4, 3 - r)[::-1].astype(np.uint8)
         out.append(np.ascontiguousarray(r, np.uint8))
     return out
+
+
+def simulate_pairs(ref: np.ndarray, n_pairs: int, read_len: int = 151, insert_mean: float = 400.0,
+                   insert_sd: float = 50.0, err: float = 0.01, seed: int = 1):
+    """Paired-end reads in FR orientation (BASELINE config 4): fragment length ~ N(insert_mean, insert_sd), read 1 from
+    the fragment's left end on the forward strand, read 2 the reverse complement of its right end; the whole pair is
+    flipped with probability 0.5.  Returns two (n, read_len) uint8 matrices."""
+    rng = np.random.default_rng(seed)
+    frag = np.clip(rng.normal(insert_mean, insert_sd, n_pairs).astype(np.int64), read_len, None)
+    start = (rng.random(n_pairs) * (len(ref) - frag)).astype(np.int64)
+    idx = np.arange(read_len)[None, :]
+    a = ref[start[:, None] + idx]
+    b = 3 - ref[(start + frag)[:, None] - 1 - idx]
+    flip = rng.random(n_pairs) < 0.5
+    r1 = np.where(flip[:, None], b, a)
+    r2 = np.where(flip[:, None], a, b)
+    out = []
+    for r in (r1, r2):
+        sub = rng.random(r.shape) < err
+        out.append(np.where(sub, (r + rng.integers(1, 4, size=r.shape)) & 3, r).astype(np.uint8))
+    return out[0], out[1]

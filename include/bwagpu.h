@@ -120,6 +120,11 @@ int bwagpu_bsw_get_scores_device(bwagpu_ctx *ctx, const bwagpu_bsw_params *prm, 
                                  int64_t ref_bytes, const uint8_t *d_seqBufQer, int64_t qer_bytes,
                                  int32_t numPairs, int32_t w);
 
+/* DP cells computed by every banded-SW launch of this context since the last reset: the sum over pairs and rows of
+ * (end - beg), i.e. one count per execution of the inner-loop body — what the reference counts as SW_cells
+ * (src/bandedSWA.cpp:175-200, :199) — accumulated on the device.  bench.py's GCUPS numerator. */
+int bwagpu_bsw_cells(bwagpu_ctx *ctx, int reset, int64_t *cells);
+
 /* No counterpart in the reference.
  * The same banded-SW extension for callers that cannot allocate (code under CUDA graph capture, tight serving
  * loops, harnesses that forbid cudaMalloc): this call issues no cudaMalloc / cudaFree and no allocating library
@@ -214,6 +219,7 @@ typedef struct {
     int64_t n_retry_left, n_retry_right;               /* jobs re-run with the doubled band */
     int64_t n_pairs8, n_pairs16, n_pairs_scalar;       /* jobs per kernel kind (first try) */
     int64_t seq_bytes;                                 /* bytes of job sequences materialised */
+    int64_t sw_cells;                                  /* DP cells the extension kernels computed (see bwagpu_bsw_cells) */
 } bwagpu_c2a_result;
 /* same with device-resident inputs */
 int bwagpu_chain2aln_device(bwagpu_ctx *ctx, const bwagpu_ext_opt *opt, const uint8_t *d_reads,
@@ -459,6 +465,47 @@ int bwagpu_emf_build(const uint8_t *ref_string, int64_t l_pac, int32_t n_seqs, c
                      int32_t seed_len, double slack, int32_t n_threads, bwagpu_emf_desc *desc,
                      uint32_t **loc_table, bwagpu_seed_entry **seed_table);
 void bwagpu_emf_free_tables(uint32_t *loc_table, bwagpu_seed_entry *seed_table);
+
+/* ---- W: one chunk of reads -> per-read alignment regions (the worker-level entry) -------------------
+ * Replaces the two kt_for passes of mem_process_seqs (reference src/bwamem.cpp:1872-1876), i.e. every
+ * worker_bwt (:1507-1543 -> mem_kernel1_core :1209-1363 / mem_kernel1_core_ert :1056-1207) and worker_aln
+ * (:1489-1505 -> mem_kernel2_core :1365-1487) call of a chunk, up to and including the compaction loop that drops
+ * regions with qe <= qb (:1449-1460).  Left to the host, on the returned lists: mem_sort_dedup_patch (:1462-1468)
+ * and is_alt (:1470-1483), then worker_sam as before.
+ *   use_emf    : probe the exact-match filter first (PERFECT_MATCH builds with a table loaded); reads it answers
+ *                get perfect[i] / emf_ret[i] and no regions (bwamem.cpp:1245-1272, 1402-1410)
+ *   use_ert    : w.useErt — ERT seeding + mem_chain_new instead of SMEM seeding + mem_chain_seeds
+ *   batch_size : BATCH_SIZE of kt_for (src/macro.h:63, 512): mem_chain_seeds runs once per batch upstream and its
+ *                `pos < num_smem - 1` loop bound (:819) makes a batch whose SMEMs total <= 1 yield no chains;
+ *                0 = treat the whole chunk as one batch
+ * enc_reads: one byte per base, 0-3 / >= 4 = N (what worker_bwt leaves in seq, :1226-1233); read i at
+ * enc_reads[off[i] .. off[i] + len[i]).  Results stay in HBM (context-owned, valid until the next call on this
+ * context) and are described by bwagpu_mem_result; bwagpu_mem_fetch copies them into host buffers:
+ * regs[n_regs] read by read in creation order (the order of av_v after the compaction), reg_off[nseq + 1],
+ * emf_ret[nseq] (FIND_PERFECT_* codes, all NO_TABLE without use_emf), perfect[nseq] (seqs[i].perfect). */
+typedef struct {
+    bwagpu_seed_opt seed;
+    bwagpu_chain_opt chain;
+    bwagpu_ext_opt ext;
+    int32_t use_ert, use_emf, batch_size, pad_;
+} bwagpu_mem_opt;
+typedef struct {
+    const bwagpu_alnreg *d_regs; int64_t n_regs;
+    const int64_t *d_reg_off;
+    const int32_t *d_emf_ret; const bwagpu_perfect *d_perfect;     /* NULL without use_emf */
+    /* work done, for throughput / roofline reporting */
+    int64_t n_emf_hits, n_smem, n_coords, n_chains, n_seeds, n_regs_raw;
+    int64_t n_sw_left, n_sw_right, n_sw_retry, n_pairs8, n_pairs16, n_pairs_scalar, sw_cells;
+    int64_t n_ext, n_cp_records, n_lf_steps, n_index_bytes;
+} bwagpu_mem_result;
+int bwagpu_mem_process_chunk(bwagpu_ctx *ctx, const bwagpu_mem_opt *opt, const uint8_t *enc_reads, const int64_t *off,
+                             const int32_t *len, int32_t nseq, bwagpu_mem_result *res);          /* HOST reads */
+int bwagpu_mem_process_chunk_device(bwagpu_ctx *ctx, const bwagpu_mem_opt *opt, const uint8_t *d_reads,
+                                    const int64_t *d_off, const int32_t *d_len, int32_t nseq, int32_t max_len,
+                                    bwagpu_mem_result *res);                                     /* reads in HBM */
+/* any of the four output pointers may be NULL */
+int bwagpu_mem_fetch(bwagpu_ctx *ctx, const bwagpu_mem_result *res, int32_t nseq, bwagpu_alnreg *regs,
+                     int64_t *reg_off, int32_t *emf_ret, bwagpu_perfect *perfect);
 
 #ifdef __cplusplus
 }
