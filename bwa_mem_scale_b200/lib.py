@@ -198,6 +198,9 @@ _SIGS = {
                                    C.POINTER(C.c_void_p), C.POINTER(C.c_void_p)]),
     "bwagpu_emf_free_tables": (None, [C.c_void_p, C.c_void_p]),
     "bwagpu_index_load_fm": (C.c_int, [C.c_void_p, C.POINTER(FmIndexDesc)]),
+    "bwagpu_index_build_fm": (C.c_int, [C.c_void_p]),
+    "bwagpu_index_get_fm": (C.c_int, [C.c_void_p, C.POINTER(C.c_int64), C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                      C.POINTER(C.c_int64)]),
     "bwagpu_index_build_fma": (C.c_int, [C.c_void_p]),
     "bwagpu_index_load_fma": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p]),
     "bwagpu_index_get_fma": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p]),

@@ -44,10 +44,15 @@ def pack_reads(reads):
 
 
 class FMI_search:
-    def __init__(self, index: FMIndex, ctx: Context | None = None, device: int = 0):
+    def __init__(self, index: FMIndex | None, ctx: Context | None = None, device: int = 0):
+        """`index` = an FMIndex to upload (FMI_search::load_index), or None = build it in HBM from the reference
+        text the context already holds (bwagpu_index_build_fm; load the text with Extender first)."""
         self._own = ctx is None
         self.ctx = ctx if ctx is not None else Context(device)
         self.index = index
+        if index is None:
+            self.ctx.check(self.ctx.lib.bwagpu_index_build_fm(self.ctx.h), "bwagpu_index_build_fm")
+            return
         d = FmIndexDesc()
         d.reference_seq_len = index.ref_seq_len
         for i, v in enumerate(index.count_loaded()):
@@ -57,6 +62,17 @@ class FMI_search:
         d.cp_occ, d.sa_ms_byte, d.sa_ls_word = (a.ctypes.data for a in self._keep)
         d.sentinel_index = index.sentinel_index
         self.ctx.check(self.ctx.lib.bwagpu_index_load_fm(self.ctx.h, C.byref(d)), "bwagpu_index_load_fm")
+
+    def get_index(self) -> FMIndex:
+        """The resident FM-index copied back as an FMIndex (count[] converted to the file form)."""
+        n, sent = C.c_int64(0), C.c_int64(0)
+        count = np.zeros(5, np.int64)
+        lib, h = self.ctx.lib, self.ctx.h
+        self.ctx.check(lib.bwagpu_index_get_fm(h, C.byref(n), count.ctypes.data, None, None, None, C.byref(sent)), "bwagpu_index_get_fm")
+        n_cp, n_sa = (n.value >> 6) + 1, (n.value >> 3) + 1
+        cp, ms, ls = np.empty((n_cp, 8), np.int64), np.empty(n_sa, np.int8), np.empty(n_sa, np.uint32)
+        self.ctx.check(lib.bwagpu_index_get_fm(h, None, None, cp.ctypes.data, ms.ctypes.data, ls.ctypes.data, None), "bwagpu_index_get_fm")
+        return FMIndex(int(n.value), count - 1, cp, ms, ls, int(sent.value))
 
     # -- FMA "smem tables" (reference `smem-table` sub-command / FMI_search::load_smem_table,
     #    src/FMI_search.cpp:229-277, 394-410) -------------------------------------------------

@@ -306,6 +306,17 @@ typedef struct {
 
 int bwagpu_index_load_fm(bwagpu_ctx *ctx, const bwagpu_fm_index_desc *desc);
 
+/* Builds the FM-index replica in HBM from the resident reference text (bwagpu_index_load_ref) — what the reference's
+ * `index` sub-command computes for the search side (FMI_search::build_index / build_fm_index, src/FMI_search.cpp:611-849:
+ * suffix array of the forward + reverse-complement text, BWT, CP_OCC, SA sampled every 8th row), same bytes.  Bucketed
+ * radix sort of suffix prefixes with segmented refinement of repeats; no whole-text suffix array is held, so the
+ * 2 x 3.1 G-symbol text of the human-scale configuration is indexed in HBM in seconds.  Not on the per-batch hot path.
+ * bwagpu_index_get_fm copies the resident index out (any pointer may be NULL): count[5] in the LOADED form,
+ * cp_occ[(len >> 6) + 1] x 64 B, sa_ms_byte / sa_ls_word[(len >> 3) + 1] — the members of FMI_search after load_index. */
+int bwagpu_index_build_fm(bwagpu_ctx *ctx);
+int bwagpu_index_get_fm(bwagpu_ctx *ctx, int64_t *reference_seq_len, int64_t *count, void *cp_occ,
+                        int8_t *sa_ms_byte, uint32_t *sa_ls_word, int64_t *sentinel_index);
+
 /* FMA ("smem-table") acceleration tables: all_smem_t[4^11] (128 B each) and last_smem_t[4^13]
  * (16 B each), reference src/FMI_search.h:99-135.  They memoise the first forward extensions of a
  * pivot (src/FMI_search.cpp:1414-1463) and of a round-3 walk (:1708-1752).
