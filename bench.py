@@ -883,6 +883,26 @@ def bench_cigar(args, rank, world):
     return res
 
 
+def bench_peaks(args, rank, world):
+    """Integer / DPX issue-rate micro-benchmarks (the SW roofline's denominator), written to profiles/ by the caller."""
+    from bwa_mem_scale_b200 import Context
+    ctx = Context(int(os.environ.get("LOCAL_RANK", rank)))
+    p = ctx.int_peaks()
+    pk, kind = peaks()
+    return {"metric": "integer issue rate", "unit": "G thread-ops/s", "int_peaks_gops": p, "hbm_gbs": pk["hbm_gbs"],
+            "peak_kind": kind, "sm_count": 148, "how": "bwagpu_measure_int_peak: 8 independent chains per thread, 2^15 iterations, "
+            "8 blocks of 256 threads per SM, best of 3 after a warm-up, CUDA events"}
+
+
+def bench_mem3(args, rank, world):
+    """Default workload: BASELINE config 3 shape through the worker-level C entry (bench_config3.py)."""
+    import types
+    import bench_config3
+    H = types.SimpleNamespace(barrier=barrier, allreduce_max=allreduce_max, ClockSampler=ClockSampler, peaks=peaks,
+                              cpu_threads=cpu_threads)
+    return bench_config3.bench_mem3(args, rank, world, H)
+
+
 def init_dist(world):
     global _dist
     if world > 1:
@@ -916,9 +936,12 @@ def main():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="mem", choices=["mem", "bsw", "seed", "ksw", "cigar"])
-    ap.add_argument("--ref-mbp", type=float, default=100.0)
-    ap.add_argument("--reads", type=int, default=1_000_000)
+    ap.add_argument("--workload", default="mem", choices=["mem", "mem2", "bsw", "seed", "ksw", "cigar", "peaks"],
+                    help="mem = BASELINE config 3 shape (default); mem2 = config 2 shape / --ert 1 (round-1 workload)")
+    ap.add_argument("--ref-mbp", type=float, default=None, help="reference size in Mbp (mem: 3100, mem2: 100)")
+    ap.add_argument("--reads", type=int, default=None, help="reads per GPU (mem: 10 M, mem2: 1 M)")
+    ap.add_argument("--chunk", type=int, default=1_000_000, help="mem: reads per bwagpu_mem_process_chunk call")
+    ap.add_argument("--cpu-reads-per-thread", type=int, default=150_000, help="mem: size of the CPU arm's bounded sample")
     ap.add_argument("--pairs", type=int, default=1_000_000)
     ap.add_argument("--band", type=int, default=100)
     ap.add_argument("--kind", type=int, default=16, choices=[8, 16])
@@ -936,7 +959,12 @@ def main():
     os.dup2(2, 1)
     rank = int(os.environ.get("RANK", 0))
     world = int(os.environ.get("WORLD_SIZE", 1))
-    fn = {"mem": bench_mem, "bsw": bench_bsw, "seed": bench_seed, "ksw": bench_ksw, "cigar": bench_cigar}[args.workload]
+    big = args.workload == "mem"
+    if args.ref_mbp is None:
+        args.ref_mbp = 3100.0 if big else 100.0
+    if args.reads is None:
+        args.reads = 10_000_000 if big else 1_000_000
+    fn = {"mem": bench_mem3, "mem2": bench_mem, "peaks": bench_peaks, "bsw": bench_bsw, "seed": bench_seed, "ksw": bench_ksw, "cigar": bench_cigar}[args.workload]
     if args.impl == "reference":
         if rank == 0:
             print(json.dumps(fn(args, 0, world)), file=real_stdout, flush=True)

@@ -125,6 +125,7 @@ _SIGS = {
     "bwagpu_kernel_time": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_int64)]),
     "bwagpu_timer_start": (C.c_int, [C.c_void_p]),
     "bwagpu_timer_stop": (C.c_int, [C.c_void_p, C.POINTER(C.c_float)]),
+    "bwagpu_measure_int_peak": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(C.c_double)]),
     "bwagpu_malloc": (C.c_int, [C.c_void_p, C.c_int64, C.POINTER(C.c_void_p)]),
     "bwagpu_free": (C.c_int, [C.c_void_p, C.c_void_p]),
     "bwagpu_h2d": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64]),
@@ -295,6 +296,15 @@ class Context:
         ms, n = C.c_double(), C.c_int64()
         self.check(self.lib.bwagpu_kernel_time(self.h, which, C.byref(ms), C.byref(n)), "kernel_time")
         return float(ms.value), int(n.value)
+
+    def int_peaks(self) -> dict:
+        """Measured integer / DPX issue rates in G thread-ops/s (bwagpu_measure_int_peak)."""
+        out = {}
+        for which, name in enumerate(("iadd3", "vimax3_s32", "viaddmax_s32_relu", "viaddmax_s16x2_relu", "add_max_plain")):
+            g = C.c_double()
+            self.check(self.lib.bwagpu_measure_int_peak(self.h, which, C.byref(g)), "measure_int_peak")
+            out[name] = float(g.value)
+        return out
 
     def malloc(self, nbytes: int) -> int:
         p = C.c_void_p()

@@ -51,6 +51,14 @@ enum { BWAGPU_KERN_SEED_COLLECT = 0, BWAGPU_KERN_SEED_SORT = 1, BWAGPU_KERN_SA_W
 int bwagpu_set_profiling(bwagpu_ctx *ctx, int on);
 int bwagpu_kernel_time(const bwagpu_ctx *ctx, int which, double *ms, int64_t *launches);
 
+/* Measured issue rate (G thread-operations / s over the whole GPU) of one integer instruction, from a register-only
+ * loop: the denominator of the banded-SW kernel's roofline.  IADD = IADD3, VIMAX3 = __vimax3_s32,
+ * VIADDMAX = __viaddmax_s32_relu, VIADDMAX_S16X2 = __viaddmax_s16x2_relu (two int16 lanes per operation),
+ * ADDMAX_PLAIN = max(a + b, c) without DPX. */
+enum { BWAGPU_PEAK_IADD = 0, BWAGPU_PEAK_VIMAX3 = 1, BWAGPU_PEAK_VIADDMAX = 2, BWAGPU_PEAK_VIADDMAX_S16X2 = 3,
+       BWAGPU_PEAK_ADDMAX_PLAIN = 4 };
+int bwagpu_measure_int_peak(bwagpu_ctx *ctx, int which, double *gops);
+
 /* raw device memory helpers for callers that keep inputs resident in HBM */
 int bwagpu_malloc(bwagpu_ctx *ctx, int64_t bytes, void **dptr);
 int bwagpu_free(bwagpu_ctx *ctx, void *dptr);

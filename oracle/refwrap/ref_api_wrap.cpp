@@ -10,8 +10,18 @@
 #include <cstdint>
 #include <cstdlib>
 #include <cstring>
-#include "bwamem.h"
+#include <string>
+#include <vector>
+#include <fstream>
+#include <iostream>
+#include <map>
+#include <algorithm>
+#include <immintrin.h>
+// ref_mem_open_arrays below hands an index that is already in memory to FMI_search, whose array members are private
+#define private public
 #include "FMI_search.h"
+#undef private
+#include "bwamem.h"
 #include "bwa.h"
 #include "ertseeding.h"
 #include <cstdio>
@@ -171,6 +181,50 @@ void *ref_mem_open(const char *prefix)
     c->seedBuf = (mem_seed_t *)calloc(sizeof(mem_seed_t), (size_t)BATCH_SIZE * AVG_SEEDS_PER_READ);
     return c;
 }
+
+void *ref_mem_clone(void *h0);
+
+// Same worker over an index that is ALREADY IN MEMORY (bench.py at human scale: the index is built on the GPU and
+// copied back; writing 16 GB of index files only for load_index to read them again would cost minutes).  The arrays
+// are what FMI_search::load_index leaves in its members (src/FMI_search.cpp:1251-1351; count[] in the loaded form);
+// the caller keeps them alive.  bns carries the contig table only (what mem_chain_seeds / V2 read).
+void *ref_mem_open_arrays(int64_t reference_seq_len, const int64_t *count_loaded, void *cp_occ, int8_t *sa_ms_byte,
+                          uint32_t *sa_ls_word, int64_t sentinel_index, uint8_t *ref_string, int64_t l_pac, int n_seqs,
+                          const int64_t *contig_off, const int32_t *contig_len)
+{
+    ref_mem_ctx *p = (ref_mem_ctx *)calloc(1, sizeof(ref_mem_ctx));
+    FMI_search *f = new FMI_search("in-memory");
+    f->one_hot_mask_array = (uint64_t *)_mm_malloc(64 * sizeof(uint64_t), 64);      // as load_index sets it up (:1253-1261)
+    f->one_hot_mask_array[0] = 0;
+    f->one_hot_mask_array[1] = 0x8000000000000000ULL;
+    for (int i = 2; i < 64; ++i) f->one_hot_mask_array[i] = (f->one_hot_mask_array[i - 1] >> 1) | 0x8000000000000000ULL;
+    f->reference_seq_len = reference_seq_len;
+    for (int i = 0; i < 5; ++i) f->count[i] = count_loaded[i];
+    f->cp_occ = (CP_OCC *)cp_occ; f->sa_ms_byte = sa_ms_byte; f->sa_ls_word = sa_ls_word;
+    f->sentinel_index = sentinel_index;
+    bntseq_t *bns = (bntseq_t *)calloc(1, sizeof(bntseq_t));
+    bns->l_pac = l_pac; bns->n_seqs = n_seqs; bns->seed = 11;
+    bns->anns = (bntann1_t *)calloc(n_seqs, sizeof(bntann1_t));
+    for (int i = 0; i < n_seqs; ++i) {
+        bns->anns[i].offset = contig_off[i]; bns->anns[i].len = contig_len[i];
+        bns->anns[i].name = strdup("chr"); bns->anns[i].anno = strdup("");
+    }
+    f->idx->bns = bns;
+    p->fmi = f; p->ref_string = ref_string;
+    ref_mem_ctx *c = (ref_mem_ctx *)ref_mem_clone(p);           // arenas of one worker
+    free(p);
+    return c;
+}
+
+#ifdef SMEM_ACCEL
+// FMA tables already in memory (what FMI_search::load_smem_table leaves, src/FMI_search.cpp:279-356); NULL = off
+void ref_mem_set_fma(void *h, void *all_smem_table, void *last_smem_table)
+{
+    ref_mem_ctx *c = (ref_mem_ctx *)h;
+    c->fmi->all_smem_table = (all_smem_t *)all_smem_table;
+    c->fmi->last_smem_table = (last_smem_t *)last_smem_table;
+}
+#endif
 
 // a second worker on the same (read-only) index: own arenas, shared FMI_search / reference text,
 // like the reference's threads sharing w.fmi (src/bwamem.h:228-253)

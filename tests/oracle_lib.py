@@ -365,6 +365,40 @@ class RefMem:
         self.contig_off, self.contig_len = np.zeros(n, np.int64), np.zeros(n, np.int32)
         self.lib.ref_mem_contigs(self.h, self.contig_off.ctypes.data, self.contig_len.ctypes.data)
 
+    @classmethod
+    def from_arrays(cls, idx, ref_string, contig_off, contig_len, flavor="plain", isa="sse41"):
+        """A worker over an index already in memory (idx: bwa_mem_scale_b200.FMIndex with host arrays; ref_string: the
+        .0123 text).  Nothing is written to disk; the arrays must stay alive as long as the worker (kept here)."""
+        self = cls.__new__(cls)
+        path = os.path.join(ORACLE_DIR, "_ref", f"libref_api_{flavor}_{isa}.so")
+        self.lib = C.CDLL(path)
+        self.lib.ref_mem_clone.restype = C.c_void_p
+        self.lib.ref_mem_clone.argtypes = [C.c_void_p]
+        self.lib.ref_mem_open_arrays.restype = C.c_void_p
+        self.lib.ref_mem_open_arrays.argtypes = [C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64,
+                                                 C.c_void_p, C.c_int64, C.c_int, C.c_void_p, C.c_void_p]
+        self.lib.ref_mem_core.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p,
+                                          C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                          C.c_void_p, C.c_void_p]
+        count = np.ascontiguousarray(idx.count_loaded(), np.int64)
+        co, cl = np.ascontiguousarray(contig_off, np.int64), np.ascontiguousarray(contig_len, np.int32)
+        cp, ms, ls = (np.ascontiguousarray(a) for a in (idx.cp_occ, idx.sa_ms_byte, idx.sa_ls_word))
+        ref_string = np.ascontiguousarray(ref_string, np.uint8)
+        self._keep = (count, co, cl, cp, ms, ls, ref_string)
+        self.h = self.lib.ref_mem_open_arrays(idx.ref_seq_len, count.ctypes.data, cp.ctypes.data, ms.ctypes.data,
+                                              ls.ctypes.data, idx.sentinel_index, ref_string.ctypes.data, idx.l_pac,
+                                              len(co), co.ctypes.data, cl.ctypes.data)
+        self._args = None
+        self.l_pac, self.contig_off, self.contig_len = idx.l_pac, co, cl
+        return self
+
+    def set_fma(self, all_smem, last_smem):
+        """FMA tables already in memory (accel / emf / scale flavours); shared by every clone of this worker."""
+        self.lib.ref_mem_set_fma.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+        self._fma = (all_smem, last_smem)
+        self.lib.ref_mem_set_fma(self.h, None if all_smem is None else all_smem.ctypes.data,
+                                 None if last_smem is None else last_smem.ctypes.data)
+
     def use_ert(self, ref_ert):
         """Switch seeding + chaining to mem_kernel1_core_ert over the tables of a RefErt (None: back to FM)."""
         self.lib.ref_mem_use_ert.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
@@ -383,6 +417,12 @@ class RefMem:
 
     def clone(self):
         """Another worker on the same loaded index (own scratch arenas), for multi-threaded baselines."""
+        if self._args is None:                      # opened from arrays
+            w = RefMem.__new__(RefMem)
+            w.lib, w._args, w._keep = self.lib, None, self._keep
+            w.h = self.lib.ref_mem_clone(self.h)
+            w.l_pac, w.contig_off, w.contig_len = self.l_pac, self.contig_off, self.contig_len
+            return w
         return RefMem(*self._args, _parent=self)
 
     def core(self, opt, flat, off, ln):
