@@ -34,9 +34,15 @@ __device__ __forceinline__ ChainScratch chain_scratch(bwagpu_seed *sd, WChain *c
 #ifndef CHAIN_MINB
 #define CHAIN_MINB 16
 #endif
+// Reads whose chain list is longer than this leave mem_chain_flt's pairwise scan to chain_filter_warp_kernel: for
+// reads from repeats nearly every chain stays in the kept list, the scan is quadratic, and it was 3/4 of this
+// kernel's instructions at one active lane per warp (profiles/r02_ncu_chain_build_hot_lines.txt).
+#ifndef CHAIN_WARP_N
+#define CHAIN_WARP_N 48
+#endif
 __global__ void __launch_bounds__(CHAIN_TPB, CHAIN_MINB) chain_build_kernel(ChainOpt o, RefView rv, ChainIn in, bwagpu_seed *sd, WChain *ch, BtNode *nodes,
                                    int32_t *ord, int32_t *lst, int64_t *cnt_chains, int64_t *cnt_seeds,
-                                   float *frac_rep)
+                                   float *frac_rep, int32_t *heavy_list, int32_t *heavy_cnt)
 {
     const int r = blockIdx.x * blockDim.x + threadIdx.x;
     if (r >= in.nseq) return;
@@ -73,10 +79,68 @@ __global__ void __launch_bounds__(CHAIN_TPB, CHAIN_MINB) chain_build_kernel(Chai
         }
     }
     b.traverse();
-    const int m = b.filter(o);
+    const int n = b.filter_prepare(o);
+    if (n == 0) return;
+    if (n > CHAIN_WARP_N) {                       // deferred: the warp kernel finishes this read
+        heavy_list[atomicAdd(heavy_cnt, 1)] = r;
+        cnt_chains[r] = n;
+        return;
+    }
+    const int m = b.filter_finish(o, n, b.filter_scan(o, n));
     int64_t ns = 0;
     for (int i = 0; i < m; ++i) ns += b.s.ch[b.s.ord[i]].n;
     cnt_chains[r] = m; cnt_seeds[r] = ns;
+}
+
+// One warp per deferred read: the scan of chain i against the kept list runs 32 entries at a time.  Lane l always
+// owns entries l, l + 32, ..., so its own flag updates are in program order; the entry appended by lane 0 is made
+// visible by __syncwarp().  Exactly the sequential semantics: entries up to and including the first one that drops
+// the chain are visited, each overlapping one gets `first` set once, large_ovlp = any overlap among them.
+__global__ void __launch_bounds__(128) chain_filter_warp_kernel(ChainOpt o, ChainIn in, bwagpu_seed *sd, WChain *ch, BtNode *nodes,
+                                                                int32_t *ord, int32_t *lst, int64_t *cnt_chains, int64_t *cnt_seeds,
+                                                                const int32_t *__restrict__ heavy_list, int n_heavy)
+{
+    const int wid = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    if (wid >= n_heavy) return;
+    const int r = heavy_list[wid];
+    const int n = (int)cnt_chains[r];
+    ChainBuilder b;
+    b.s = chain_scratch(sd, ch, nodes, ord, lst, in.coord_off[in.smem_off[r]], r);
+    int32_t *a = b.s.ord;
+    ChainBuilder::Kept *lv = b.kept_list();
+    const int msl2 = o.min_seed_len << 1;
+    int nl = 1;
+    for (int i = 1; i < n; ++i) {
+        const WChain &ci = b.s.ch[a[i]];
+        const int bi = b.chn_beg(ci), ei = b.chn_end(ci), wi = ci.w, alt_i = ci.is_alt;
+        bool large = false, broke = false;
+        for (int k0 = 0; k0 < nl && !broke; k0 += 32) {
+            const int k = k0 + lane;
+            ChainBuilder::Kept kv; kv.beg = kv.end = kv.w = kv.flags = 0;
+            int t = 0;
+            if (k < nl) { kv = lv[k]; t = b.flt_test(o, kv, bi, ei, wi, alt_i, msl2); }
+            const unsigned mb = __ballot_sync(0xffffffffu, t & 2);
+            const int stop = mb ? __ffs(mb) - 1 : 31;                 // last lane the sequential scan would visit
+            const bool mine = t && lane <= stop;
+            if (mine && !(kv.flags & 2)) { b.s.ch[a[b.s.lst[k]]].first = i; lv[k].flags = kv.flags | 2; }
+            large |= __any_sync(0xffffffffu, mine);
+            broke = mb != 0;
+        }
+        if (!broke) {
+            if (lane == 0) {
+                lv[nl].beg = bi; lv[nl].end = ei; lv[nl].w = wi; lv[nl].flags = alt_i ? 1 : 0;
+                b.s.lst[nl] = i; b.s.ch[a[i]].kept = large ? 2 : 3;
+            }
+            ++nl;
+        }
+        __syncwarp();
+    }
+    if (lane == 0) {
+        const int m = b.filter_finish(o, n, nl);
+        int64_t ns = 0;
+        for (int i = 0; i < m; ++i) ns += b.s.ch[a[i]].n;
+        cnt_chains[r] = m; cnt_seeds[r] = ns;
+    }
 }
 
 __global__ void chain_emit_kernel(ChainIn in, const bwagpu_seed *sd, const WChain *ch, const int32_t *ord,
@@ -173,11 +237,25 @@ static int chain_device(bwagpu_ctx *ctx, const bwagpu_chain_opt *opt, const bwag
     if ((rc = bwagpu_scratch(ctx, SCR_CH_CNT, (int64_t)(nseq + 1) * 16, (void **)&cnt))) return rc;
     if ((rc = bwagpu_scratch(ctx, SCR_CH_OFFS, (int64_t)(nseq + 1) * 16, (void **)&offs))) return rc;
     if ((rc = bwagpu_scratch(ctx, SCR_CH_FRAC, (int64_t)(nseq + 1) * 4, (void **)&frac))) return rc;
+    int32_t *heavy;
+    if ((rc = bwagpu_scratch(ctx, SCR_CH_HEAVY, (int64_t)(nseq + 2) * 4, (void **)&heavy))) return rc;
     BWAGPU_CUDA(ctx, cudaMemsetAsync(cnt, 0, (size_t)(nseq + 1) * 16, ctx->stream));
+    BWAGPU_CUDA(ctx, cudaMemsetAsync(heavy, 0, 4, ctx->stream));
     BWAGPU_KERNEL_BEGIN(ctx);
-    chain_build_kernel<<<(nseq + CHAIN_TPB - 1) / CHAIN_TPB, CHAIN_TPB, 0, ctx->stream>>>(o, rv, in, sd, ch, nodes, ord, lst, cnt, cnt + nseq + 1, frac);
+    chain_build_kernel<<<(nseq + CHAIN_TPB - 1) / CHAIN_TPB, CHAIN_TPB, 0, ctx->stream>>>(o, rv, in, sd, ch, nodes, ord, lst, cnt, cnt + nseq + 1, frac,
+                                                                                          heavy + 1, heavy);
     BWAGPU_KERNEL_END(ctx, BWAGPU_KERN_CHAIN);
     BWAGPU_CUDA(ctx, cudaGetLastError());
+    int32_t n_heavy = 0;
+    BWAGPU_CUDA(ctx, cudaMemcpyAsync(&n_heavy, heavy, 4, cudaMemcpyDeviceToHost, ctx->stream));
+    BWAGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    if (n_heavy > 0) {
+        BWAGPU_KERNEL_BEGIN(ctx);
+        chain_filter_warp_kernel<<<(unsigned)(((int64_t)n_heavy * 32 + 127) / 128), 128, 0, ctx->stream>>>(
+            o, in, sd, ch, nodes, ord, lst, cnt, cnt + nseq + 1, heavy + 1, n_heavy);
+        BWAGPU_KERNEL_END(ctx, BWAGPU_KERN_CHAIN);
+        BWAGPU_CUDA(ctx, cudaGetLastError());
+    }
     if ((rc = chain_scan(ctx, cnt, offs, nseq + 1))) return rc;
     if ((rc = chain_scan(ctx, cnt + nseq + 1, offs + nseq + 1, nseq + 1))) return rc;
     int64_t tot[2];

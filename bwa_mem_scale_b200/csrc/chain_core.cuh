@@ -328,9 +328,15 @@ struct ChainBuilder {
     CHAIN_HD int chn_beg(const WChain &c) const { return c.first_qbeg; }
     CHAIN_HD int chn_end(const WChain &c) const { return c.last_qbeg + c.last_len; }
 
-    // mem_chain_flt for this read's chains (:528-646).  On return ord[0..result) are the surviving
-    // chains in their final order; WChain.w/kept/first are set.
-    CHAIN_HD int filter(const ChainOpt &o)
+    // mem_chain_flt for this read's chains (:528-646), in three parts so that the kernels can run the middle one —
+    // the scan of every chain against the list of chains kept so far, quadratic for reads from repeats — with a whole
+    // warp (chain.cu).  On return of filter() ord[0..result) are the surviving chains in their final order;
+    // WChain.w/kept/first are set.
+    struct Kept { int32_t beg, end, w, flags; };      // the fields the scan reads, side by side (flags: 1 = is_alt, 2 = `first` set)
+    CHAIN_HD Kept *kept_list() const { return reinterpret_cast<Kept *>(s.nodes); }   // node storage is dead after traverse()
+
+    // weights, the weight filter, the replayed introsort, the first kept chain.  Returns n (0: nothing to filter).
+    CHAIN_HD int filter_prepare(const ChainOpt &o)
     {
         if (n_chains == 0) return 0;
         int n = 0;
@@ -343,23 +349,39 @@ struct ChainBuilder {
         if (n == 0) return 0;
         int32_t *a = s.ord;
         {
-            SortKey *sk = reinterpret_cast<SortKey *>(s.nodes);       // node storage is dead after traverse()
+            SortKey *sk = reinterpret_cast<SortKey *>(s.nodes);
             for (int i = 0; i < n; ++i) sk[i] = ((SortKey)(uint32_t)s.ch[a[i]].w << 32) | (uint32_t)a[i];
             introsort(sk, n);
             for (int i = 0; i < n; ++i) a[i] = (int32_t)(uint32_t)sk[i];
         }
-        // the kept list is scanned once per chain: keep the fields the scan reads (query span, weight,
-        // is_alt, "first already set") side by side in the tree's node storage, which is dead after
-        // traverse(), instead of chasing lst -> ord -> chain for every test
-        struct Kept { int32_t beg, end, w, flags; };
-        Kept *lv = reinterpret_cast<Kept *>(s.nodes);
-        int nl = 0;
-        {
-            WChain &c0 = s.ch[a[0]];
-            c0.kept = 3;
-            lv[0].beg = chn_beg(c0); lv[0].end = chn_end(c0); lv[0].w = c0.w; lv[0].flags = c0.is_alt ? 1 : 0;
-            s.lst[nl++] = 0;
+        Kept *lv = kept_list();
+        WChain &c0 = s.ch[a[0]];
+        c0.kept = 3;
+        lv[0].beg = chn_beg(c0); lv[0].end = chn_end(c0); lv[0].w = c0.w; lv[0].flags = c0.is_alt ? 1 : 0;
+        s.lst[0] = 0;
+        return n;
+    }
+
+    // does chain (bi, ei, wi, alt_i) overlap kept entry kv by mask_level (bit 0), and is it dropped by it (bit 1)?
+    CHAIN_HD int flt_test(const ChainOpt &o, const Kept &kv, int bi, int ei, int wi, int alt_i, int msl2) const
+    {
+        const int b_max = kv.beg > bi ? kv.beg : bi;
+        const int e_min = kv.end < ei ? kv.end : ei;
+        if (e_min > b_max && (!(kv.flags & 1) || alt_i)) {
+            const int li = ei - bi, lj = kv.end - kv.beg;
+            const int min_l = li < lj ? li : lj;
+            if ((float)(e_min - b_max) >= (float)min_l * o.mask_level && min_l < o.max_chain_gap)
+                return 1 | (((float)wi < (float)kv.w * o.drop_ratio && kv.w - wi >= msl2) ? 2 : 0);
         }
+        return 0;
+    }
+
+    // the pairwise scan, one chain after the other (:560-598).  Returns the length of the kept list.
+    CHAIN_HD int filter_scan(const ChainOpt &o, int n)
+    {
+        int32_t *a = s.ord;
+        Kept *lv = kept_list();
+        int nl = 1;
         const int msl2 = o.min_seed_len << 1;
         for (int i = 1; i < n; ++i) {
             int large_ovlp = 0, k;
@@ -367,16 +389,11 @@ struct ChainBuilder {
             const int bi = chn_beg(ci), ei = chn_end(ci), wi = ci.w, alt_i = ci.is_alt;
             for (k = 0; k < nl; ++k) {
                 const Kept kv = lv[k];
-                const int b_max = kv.beg > bi ? kv.beg : bi;
-                const int e_min = kv.end < ei ? kv.end : ei;
-                if (e_min > b_max && (!(kv.flags & 1) || alt_i)) {
-                    const int li = ei - bi, lj = kv.end - kv.beg;
-                    const int min_l = li < lj ? li : lj;
-                    if ((float)(e_min - b_max) >= (float)min_l * o.mask_level && min_l < o.max_chain_gap) {
-                        large_ovlp = 1;
-                        if (!(kv.flags & 2)) { s.ch[a[s.lst[k]]].first = i; lv[k].flags = kv.flags | 2; }
-                        if ((float)wi < (float)kv.w * o.drop_ratio && kv.w - wi >= msl2) break;
-                    }
+                const int t = flt_test(o, kv, bi, ei, wi, alt_i, msl2);
+                if (t) {
+                    large_ovlp = 1;
+                    if (!(kv.flags & 2)) { s.ch[a[s.lst[k]]].first = i; lv[k].flags = kv.flags | 2; }
+                    if (t & 2) break;
                 }
             }
             if (k == nl) {
@@ -384,6 +401,20 @@ struct ChainBuilder {
                 s.lst[nl++] = i; ci.kept = large_ovlp ? 2 : 3;
             }
         }
+        return nl;
+    }
+
+    CHAIN_HD int filter(const ChainOpt &o)
+    {
+        const int n = filter_prepare(o);
+        if (n == 0) return 0;
+        return filter_finish(o, n, filter_scan(o, n));
+    }
+
+    // kept = 1 marks, the max_chain_extend cut, compaction (:600-646).  Returns the number of surviving chains.
+    CHAIN_HD int filter_finish(const ChainOpt &o, int n, int nl)
+    {
+        int32_t *a = s.ord;
         for (int i = 0; i < nl; ++i) {
             const WChain &c = s.ch[a[s.lst[i]]];
             if (c.first >= 0) s.ch[a[c.first]].kept = 1;
