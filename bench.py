@@ -889,7 +889,21 @@ def bench_peaks(args, rank, world):
     ctx = Context(int(os.environ.get("LOCAL_RANK", rank)))
     p = ctx.int_peaks()
     pk, kind = peaks()
-    return {"metric": "integer issue rate", "unit": "G thread-ops/s", "int_peaks_gops": p, "hbm_gbs": pk["hbm_gbs"],
+    probe = None
+    if args.ref_mbp:
+        # backwardExt design probe on an index of the asked size: one walk per thread vs per 8-lane group
+        import bench_config3 as b3
+        from bwa_mem_scale_b200 import Extender, FMI_search, fmindex
+        n_bp = int(args.ref_mbp * 1e6)
+        ref = b3.make_reference(n_bp, 44)
+        coff, clen = b3.contig_table(n_bp)
+        Extender(fmindex.text_with_revcomp(ref), n_bp, coff, clen, ctx=ctx)
+        FMI_search(None, ctx=ctx)
+        probe = {"ref_mbp": args.ref_mbp, "walks": 8_000_000, "steps": 120,
+                 "thread_per_walk": ctx.probe_bext(0, 8_000_000, 120), "group8_per_walk": ctx.probe_bext(1, 8_000_000, 120),
+                 "group4_per_walk": ctx.probe_bext(2, 8_000_000, 120), "group2_per_walk": ctx.probe_bext(3, 8_000_000, 120)}
+        assert len({v["checksum"] for v in probe.values() if isinstance(v, dict)}) == 1, "the backwardExt designs disagree"
+    return {"metric": "integer issue rate", "unit": "G thread-ops/s", "int_peaks_gops": p, "hbm_gbs": pk["hbm_gbs"], "bext_probe": probe,
             "peak_kind": kind, "sm_count": 148, "how": "bwagpu_measure_int_peak: 8 independent chains per thread, 2^15 iterations, "
             "8 blocks of 256 threads per SM, best of 3 after a warm-up, CUDA events"}
 
@@ -961,7 +975,7 @@ def main():
     world = int(os.environ.get("WORLD_SIZE", 1))
     big = args.workload == "mem"
     if args.ref_mbp is None:
-        args.ref_mbp = 3100.0 if big else 100.0
+        args.ref_mbp = 3100.0 if big or args.workload == "peaks" else 100.0
     if args.reads is None:
         args.reads = 10_000_000 if big else 1_000_000
     fn = {"mem": bench_mem3, "mem2": bench_mem, "peaks": bench_peaks, "bsw": bench_bsw, "seed": bench_seed, "ksw": bench_ksw, "cigar": bench_cigar}[args.workload]

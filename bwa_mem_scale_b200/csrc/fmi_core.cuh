@@ -63,6 +63,32 @@ BWAGPU_HD void fm_load_words4(const uint32_t *p, uint32_t e[4])
 
 struct FmRec { int64_t cnt[4]; uint64_t bits[4]; };
 
+// SEED_PREFETCH: a bi-interval that survives a backward row (or is pushed by the forward walk) WILL be extended again
+// one row later, and the two CP_OCC records that extension reads are known now: ask L2 for them (no register is held),
+// so that the dependent load a row later finds them on chip.  0 = off, 1 = one prefetch per record, 2 = one per sector.
+#ifndef SEED_PREFETCH
+#define SEED_PREFETCH 0
+#endif
+BWAGPU_HD void fm_prefetch_rec(const int64_t *cp_occ, int64_t block)
+{
+#if defined(__CUDA_ARCH__) && SEED_PREFETCH > 0
+    const int64_t *p = cp_occ + block * 8;
+    asm volatile("prefetch.global.L2 [%0];" :: "l"(p));
+#if SEED_PREFETCH > 1
+    asm volatile("prefetch.global.L2 [%0];" :: "l"(p + 4));
+#endif
+#else
+    (void)cp_occ; (void)block;
+#endif
+}
+// records a backward extension of (k, s) will read
+BWAGPU_HD void fm_prefetch_bext(const int64_t *cp_occ, int64_t k, int64_t s)
+{
+    const int64_t b0 = k >> 6, b1 = (k + s) >> 6;
+    fm_prefetch_rec(cp_occ, b0);
+    if (b1 != b0) fm_prefetch_rec(cp_occ, b1);
+}
+
 #ifndef SEED_LD_MODE
 #define SEED_LD_MODE 1      // 0: 4x128-bit __ldg; 1: 2x256-bit cached; 2: 256-bit, L1 no_allocate for narrow intervals
 #endif
@@ -219,6 +245,7 @@ struct SeedMachine {
     Biv cur; int cur_n;
     Biv req; int req_a;          // pending extension request
     int64_t n_ext;
+    const int64_t *pf_cp;        // CP_OCC base for prefetches (NULL: none)
 
     BWAGPU_HD void init(ReadStore q_, int len_, int rid_, PrevStore prev_, bwagpu_smem *out_, int cap_)
     {
@@ -227,6 +254,7 @@ struct SeedMachine {
         round = 1; x = 0; min_intv = 1; state = len > 0 ? ST_PIVOT : ST_DONE; n_ext = 0;
         np = base = p = nc = decided = r1_count = r2_idx = 0; last_s = -1; j = next_x = 0;
         cur.k = cur.l = cur.s = 0; cur_n = 0; req = cur; req_a = 0;
+        pf_cp = nullptr;
     }
 
     BWAGPU_HD void emit(int m, int n, const Biv &v)
@@ -248,6 +276,7 @@ struct SeedMachine {
     BWAGPU_HD void push_prev()                 // forward phase: store below the previous entry
     {
         prev.put(len - 1 - np, cur, cur_n);
+        if (pf_cp && x > 0) fm_prefetch_bext(pf_cp, cur.k, cur.s);      // the backward phase starts from these
     }
 
     BWAGPU_HD void request_fwd(int a)          // forward ext = backward ext of the complement on (l,k,s)
@@ -461,6 +490,7 @@ struct SeedMachine {
             } else if (r.s != (int64_t)last_s) {
                 last_s = (int32_t)r.s;
                 prev.put(base + nc, r, cur_n);
+                if (pf_cp && j > 0) fm_prefetch_bext(pf_cp, r.k, r.s);           // extended again in the next row
                 ++nc;
                 decided = 1;
             }

@@ -86,6 +86,82 @@ __device__ __forceinline__ void seed_stage_read(uint32_t *w, const uint8_t *__re
 
 struct SeedStats { unsigned long long n_ext, n_rec, n_lf, max_cnt; };
 
+// ---- warp-cooperative backwardExt ------------------------------------------------------------------------------
+// SEED_COOP = 1: the reads stay one per thread (so every issued instruction of the state machine still serves all the
+// lanes that are in that state), but the CP_OCC records are fetched by the WARP: the pending requests of the ready lanes
+// are served eight at a time, four lanes per request — lane b of a group loads the 8-byte count and the 8-byte one-hot
+// word of base b from the record at sp and from the record at ep (a group's four lanes read one 32-byte sector per
+// load), popcounts, and shuffles assemble (k, l, s) for the requesting lane.  On the 6.2 GB table of the human-scale
+// index this access shape moves 2.8x the records per second of one thread fetching whole records with 256-bit loads
+// (profiles/r02_dpx_peak_and_bext_probe.json: 2398 vs 863 GB/s), and the two records of a request no longer sit in 32
+// registers of every thread.
+// MEASURED in the full kernel (profiles/r02_seed_ab_config3.txt, 2 M reads on the 3.1 Gbp index): 211 ms with two rounds
+// in flight (118 registers), 237 / 217 / 252 ms with 1 / 3 / 4 rounds, against 195 ms for the per-thread fetch — the
+// kernel is not bound by the fetch shape but by the length of each warp iteration (about 500 warp instructions at 16
+// cycles each, 4.7 warps per scheduler), so the cooperative fetch stays OFF by default and is kept for the record.
+#ifndef SEED_COOP
+#define SEED_COOP 0
+#endif
+__device__ __forceinline__ int64_t seed_shfl64(int64_t v, int src)
+{
+    const int lo = __shfl_sync(0xffffffffu, (int)(uint32_t)v, src);
+    const int hi = __shfl_sync(0xffffffffu, (int)(uint32_t)((uint64_t)v >> 32), src);
+    return (int64_t)(((uint64_t)(uint32_t)hi << 32) | (uint32_t)lo);
+}
+
+// All 32 lanes call this.  `ready` lanes pass their request (q, qa) and receive its result; returns that result.
+// Two phases per pass so that the loads of SEED_COOP_ROUNDS rounds of eight requests are in flight together.
+#ifndef SEED_COOP_ROUNDS
+#define SEED_COOP_ROUNDS 2
+#endif
+__device__ __forceinline__ Biv seed_bext_coop(const FmView &f, unsigned m_ready, bool ready, const Biv &q, int qa)
+{
+    const int lane = threadIdx.x & 31, g = lane >> 2, b = lane & 3;
+    const int my_rank = __popc(m_ready & ((1u << lane) - 1u));      // position of this lane among the ready lanes
+    const int n_req = __popc(m_ready);
+    Biv res; res.k = res.l = res.s = 0;
+    const int gb = lane & ~3;
+  for (int pass = 0; pass < n_req; pass += 8 * SEED_COOP_ROUNDS) {
+    int64_t c0[SEED_COOP_ROUNDS], c1[SEED_COOP_ROUNDS]; uint64_t o0[SEED_COOP_ROUNDS], o1[SEED_COOP_ROUNDS];
+    int src[SEED_COOP_ROUNDS], kx[SEED_COOP_ROUNDS];                 // kx: k & 63 | (ep & 63) << 8 | sentinel << 16
+#pragma unroll
+    for (int i = 0; i < SEED_COOP_ROUNDS; ++i) {
+        const int base = pass + i * 8;
+        if (base < n_req) {                                          // warp-uniform
+            // the request this group serves in round i: the (base + g)-th ready lane
+            const bool have = base + g < n_req;
+            src[i] = have ? (int)__fns(m_ready, 0, base + g + 1) : 0;
+            const int64_t k = seed_shfl64(q.k, src[i]), ep = k + seed_shfl64(q.s, src[i]);
+            c0[i] = c1[i] = 0; o0[i] = o1[i] = 0;
+            if (have) {
+                const int64_t *r0 = f.cp_occ + (k >> 6) * 8, *r1 = f.cp_occ + (ep >> 6) * 8;
+                c0[i] = __ldg(r0 + b); c1[i] = __ldg(r1 + b);
+                o0[i] = (uint64_t)__ldg(r0 + 4 + b); o1[i] = (uint64_t)__ldg(r1 + 4 + b);
+            }
+            kx[i] = (int)(k & 63) | ((int)(ep & 63) << 8) | ((k <= f.sentinel_index && ep > f.sentinel_index) ? 1 << 16 : 0);
+        }
+    }
+#pragma unroll
+    for (int i = 0; i < SEED_COOP_ROUNDS; ++i) {
+        const int base = pass + i * 8;
+        if (base < n_req) {
+            const int64_t osp = c0[i] + __popcll(o0[i] & fm_prefix_mask(kx[i] & 63));
+            const int64_t sz = c1[i] + __popcll(o1[i] & fm_prefix_mask((kx[i] >> 8) & 63)) - osp;
+            const int64_t nk = fm_count(f, b) + osp;
+            // l[b] = l + sentinel + sum of s[c] over c > b
+            const int64_t s1 = seed_shfl64(sz, gb | ((b + 1) & 3)), s2 = seed_shfl64(sz, gb | ((b + 2) & 3)),
+                          s3 = seed_shfl64(sz, gb | ((b + 3) & 3));
+            const int64_t nl = seed_shfl64(q.l, src[i]) + (kx[i] >> 16) + (b < 3 ? s1 : 0) + (b < 2 ? s2 : 0) + (b < 1 ? s3 : 0);
+            // hand the answer for base qa back to the requesting lane: its group in this round is my_rank - base
+            const int from = (((my_rank - base) & 7) << 2) | (qa & 3);
+            const int64_t rk = seed_shfl64(nk, from), rl = seed_shfl64(nl, from), rs = seed_shfl64(sz, from);
+            if (ready && my_rank >= base && my_rank < base + 8) { res.k = rk; res.l = rl; res.s = rs; }
+        }
+    }
+  }
+    return res;
+}
+
 #ifndef SEED_MIN_BLOCKS
 #define SEED_MIN_BLOCKS 1
 #endif
@@ -132,6 +208,7 @@ seed_collect_kernel(FmView f, SeedOpt o, const uint8_t *__restrict__ reads,
                             } else {
                                 m.init(reads + off[i], len[i], i, pv, tmp + (int64_t)i * cap, cap);
                             }
+                            m.pf_cp = f.cp_occ;
                             got = true;
                             break;
                         }
@@ -147,12 +224,21 @@ seed_collect_kernel(FmView f, SeedOpt o, const uint8_t *__restrict__ reads,
             continue;
         }
         if (!m_ready) break;
+#if SEED_COOP
+        const Biv r = seed_bext_coop(f, m_ready, ready, m.req, m.req_a);
+        if (ready) {
+            n_rec += ((m.req.k >> 6) == ((m.req.k + m.req.s) >> 6)) ? 1 : 2;
+            ++n_ext;
+            ready = m.step_fast(r, o);
+        }
+#else
         if (ready) {
             n_rec += ((m.req.k >> 6) == ((m.req.k + m.req.s) >> 6)) ? 1 : 2;
             ++n_ext;
             const Biv r = fm_bext(f, m.req, m.req_a);
             ready = m.step_fast(r, o);
         }
+#endif
     }
     // per-warp then global statistics
     for (int d = 16; d; d >>= 1) {

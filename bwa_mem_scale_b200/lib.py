@@ -126,6 +126,8 @@ _SIGS = {
     "bwagpu_timer_start": (C.c_int, [C.c_void_p]),
     "bwagpu_timer_stop": (C.c_int, [C.c_void_p, C.POINTER(C.c_float)]),
     "bwagpu_measure_int_peak": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(C.c_double)]),
+    "bwagpu_probe_bext": (C.c_int, [C.c_void_p, C.c_int, C.c_int64, C.c_int32, C.POINTER(C.c_double), C.POINTER(C.c_uint64),
+                                    C.POINTER(C.c_float)]),
     "bwagpu_malloc": (C.c_int, [C.c_void_p, C.c_int64, C.POINTER(C.c_void_p)]),
     "bwagpu_free": (C.c_int, [C.c_void_p, C.c_void_p]),
     "bwagpu_h2d": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64]),
@@ -305,6 +307,11 @@ class Context:
             self.check(self.lib.bwagpu_measure_int_peak(self.h, which, C.byref(g)), "measure_int_peak")
             out[name] = float(g.value)
         return out
+
+    def probe_bext(self, mode: int, n_walks: int, steps: int) -> dict:
+        r, c, ms = C.c_double(), C.c_uint64(), C.c_float()
+        self.check(self.lib.bwagpu_probe_bext(self.h, mode, n_walks, steps, C.byref(r), C.byref(c), C.byref(ms)), "probe_bext")
+        return {"records_per_s": r.value, "gbs": r.value * 64 / 1e9, "checksum": int(c.value), "ms": ms.value}
 
     def malloc(self, nbytes: int) -> int:
         p = C.c_void_p()

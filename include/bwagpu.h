@@ -59,6 +59,13 @@ enum { BWAGPU_PEAK_IADD = 0, BWAGPU_PEAK_VIMAX3 = 1, BWAGPU_PEAK_VIADDMAX = 2, B
        BWAGPU_PEAK_ADDMAX_PLAIN = 4 };
 int bwagpu_measure_int_peak(bwagpu_ctx *ctx, int which, double *gops);
 
+/* Design probe (not a product path): FMI_search::backwardExt walks along the resident text, one walk per thread (mode 0,
+ * what the seeding kernel does) or per 8-lane group with coalesced 8-byte loads and shuffles (mode 1, the design
+ * BASELINE.json's north_star describes); CP_OCC records fetched per second and a checksum of the final intervals
+ * (equal between modes).  bench.py --workload peaks records both next to the integer issue rates. */
+int bwagpu_probe_bext(bwagpu_ctx *ctx, int mode, int64_t n_walks, int32_t steps, double *records_per_s,
+                      uint64_t *checksum, float *ms);
+
 /* raw device memory helpers for callers that keep inputs resident in HBM */
 int bwagpu_malloc(bwagpu_ctx *ctx, int64_t bytes, void **dptr);
 int bwagpu_free(bwagpu_ctx *ctx, void *dptr);
