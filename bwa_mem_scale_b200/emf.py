@@ -101,6 +101,22 @@ class PerfectMatch:
         self.ctx.check(self.ctx.lib.bwagpu_emf_load(self.ctx.h, C.byref(d), table.loc_table.ctypes.data,
                                                     table.seed_table.ctypes.data), "bwagpu_emf_load")
 
+    @staticmethod
+    def build_on_device(ctx: Context, seed_len: int = 151, slack: float = 1.1) -> "PerfectMatch":
+        """bwagpu_emf_build_device: the table is built in HBM from the text and contig table the context holds."""
+        pm = PerfectMatch.__new__(PerfectMatch)
+        pm.ctx, pm.table = ctx, None
+        ctx.check(ctx.lib.bwagpu_emf_build_device(ctx.h, int(seed_len), float(slack)), "bwagpu_emf_build_device")
+        return pm
+
+    def get_table(self) -> PerfectTable:
+        """The resident table copied back to the host (bwagpu_emf_get)."""
+        d = EmfDesc()
+        self.ctx.check(self.ctx.lib.bwagpu_emf_get(self.ctx.h, C.byref(d), None, None), "bwagpu_emf_get")
+        loc, seed = np.empty(d.num_loc_entry, np.uint32), np.empty(d.num_seed_entry, SEED_ENTRY_DTYPE)
+        self.ctx.check(self.ctx.lib.bwagpu_emf_get(self.ctx.h, None, loc.ctypes.data, seed.ctypes.data), "bwagpu_emf_get")
+        return PerfectTable(d.seed_len, d.seq_len, loc, seed, d.num_seed_used, d.num_seed_key)
+
     def unload(self):
         self.ctx.check(self.ctx.lib.bwagpu_emf_unload(self.ctx.h), "bwagpu_emf_unload")
 

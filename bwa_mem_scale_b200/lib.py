@@ -199,6 +199,8 @@ _SIGS = {
     "bwagpu_emf_build": (C.c_int, [C.c_void_p, C.c_int64, C.c_int32, C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p,
                                    C.c_void_p, C.c_int32, C.c_double, C.c_int32, C.POINTER(EmfDesc),
                                    C.POINTER(C.c_void_p), C.POINTER(C.c_void_p)]),
+    "bwagpu_emf_build_device": (C.c_int, [C.c_void_p, C.c_int32, C.c_double]),
+    "bwagpu_emf_get": (C.c_int, [C.c_void_p, C.POINTER(EmfDesc), C.c_void_p, C.c_void_p]),
     "bwagpu_emf_free_tables": (None, [C.c_void_p, C.c_void_p]),
     "bwagpu_index_load_fm": (C.c_int, [C.c_void_p, C.POINTER(FmIndexDesc)]),
     "bwagpu_index_build_fm": (C.c_int, [C.c_void_p]),

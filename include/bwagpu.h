@@ -491,6 +491,15 @@ int bwagpu_emf_build(const uint8_t *ref_string, int64_t l_pac, int32_t n_seqs, c
                      int32_t seed_len, double slack, int32_t n_threads, bwagpu_emf_desc *desc,
                      uint32_t **loc_table, bwagpu_seed_entry **seed_table);
 void bwagpu_emf_free_tables(uint32_t *loc_table, bwagpu_seed_entry *seed_table);
+/* The same table built in HBM from the resident reference text and contig table (bwagpu_index_load_ref), in seconds at
+ * human scale where the sequential insertion above — like the reference's perfect-index — needs minutes to hours.  Same
+ * format and same CONTENT (every seed's primary location, strand flag and multi-location lists, src/perfect.h:81-129);
+ * collision entries and lists are placed by a parallel rule, so the bytes differ from the reference-built file while
+ * find_perfect_match_entry answers every read with the same code and location (the list id in perfect.flags >> 2 indexes
+ * THIS table's loc_table).  No holes (.amb) support: use bwagpu_emf_build for references with N runs.
+ * bwagpu_emf_get copies the resident table out (pointers may be NULL to read only the descriptor). */
+int bwagpu_emf_build_device(bwagpu_ctx *ctx, int32_t seed_len, double slack);
+int bwagpu_emf_get(bwagpu_ctx *ctx, bwagpu_emf_desc *desc, uint32_t *loc_table, bwagpu_seed_entry *seed_table);
 
 /* ---- W: one chunk of reads -> per-read alignment regions (the worker-level entry) -------------------
  * Replaces the two kt_for passes of mem_process_seqs (reference src/bwamem.cpp:1872-1876), i.e. every
