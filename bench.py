@@ -961,7 +961,7 @@ def main():
     ap.add_argument("--kind", type=int, default=16, choices=[8, 16])
     ap.add_argument("--fma", type=int, default=1, help="use the FMA smem tables (config 2)")
     ap.add_argument("--ert", type=int, default=0, help="mem workload: ERT seeding on the small reference-built index in tests/golden/")
-    ap.add_argument("--emf", type=int, default=0, help="mem workload: exact-match filter in front (table built on the host)")
+    ap.add_argument("--emf", type=int, default=None, help="exact-match filter in front (mem: default 1, table built in HBM; mem2: default 0, host-built)")
     ap.add_argument("--exact-frac", type=float, default=None, help="fraction of error-free reads (default: what 1%% substitutions give)")
     ap.add_argument("--contexts", type=int, default=1, help="mem workload: contexts (streams) per GPU")
     ap.add_argument("--no-cpu", action="store_true")
@@ -978,6 +978,8 @@ def main():
         args.ref_mbp = 3100.0 if big or args.workload == "peaks" else 100.0
     if args.reads is None:
         args.reads = 10_000_000 if big else 1_000_000
+    if args.emf is None:
+        args.emf = 1 if big else 0
     fn = {"mem": bench_mem3, "mem2": bench_mem, "peaks": bench_peaks, "bsw": bench_bsw, "seed": bench_seed, "ksw": bench_ksw, "cigar": bench_cigar}[args.workload]
     if args.impl == "reference":
         if rank == 0:

@@ -99,17 +99,19 @@ def workload_name(args, n, world, chunk):
             "small reference-built index")
 
 
-def cpu_reference_arm(idx_host, fma_tabs, text, coff, clen, reads, threads):
+def cpu_reference_arm(idx_host, fma_tabs, text, coff, clen, reads, threads, emf_table=None):
     """The reference's own mem_kernel1_core + mem_chain2aln_across_reads_V2 over `reads` (oracle/_ref tap library, AVX2
-    build, the `accel` feature set when the FMA tables are on), one worker per host thread on one shared in-memory index.
+    build; the `accel` feature set when the FMA tables are on, `emf` with the exact-match filter), one worker per host thread on one shared in-memory index.
     Returns (seconds, description)."""
     sys.path.insert(0, os.path.join(ROOT, "tests"))
     import oracle_lib as ol
-    flavor = "accel" if fma_tabs is not None else "plain"
+    flavor = "emf" if emf_table is not None else "accel" if fma_tabs is not None else "plain"
     isa = "avx2" if os.path.exists(os.path.join(ol.ORACLE_DIR, "_ref", f"libref_api_{flavor}_avx2.so")) else "sse41"
     rm0 = ol.RefMem.from_arrays(idx_host, text, coff, clen, flavor, isa)
     if fma_tabs is not None:
         rm0.set_fma(*fma_tabs)
+    if emf_table is not None:
+        rm0.set_perfect(emf_table)
     workers = [rm0] + [rm0.clone() for _ in range(threads - 1)]
     chunks = [c for c in np.array_split(np.arange(len(reads)), threads) if len(c)]
     packed = [ol.pack_reads(reads[c]) for c in chunks]            # outside the timed region
@@ -156,28 +158,32 @@ def bench_mem3(args, rank, world, H):
     log("index:", setup)
     emf = None
     if args.emf:
-        from bwa_mem_scale_b200 import PerfectMatch, PerfectTable
+        if not args.fma:
+            raise SystemExit("--emf 1 needs --fma 1 (the reference's EMF feature set includes the FMA tables)")
+        from bwa_mem_scale_b200 import PerfectMatch
         t0 = time.perf_counter()
-        table = PerfectTable.build(ref, READ_LEN, 1.1, contig_off=coff, contig_len=clen)
-        emf = PerfectMatch(table, ctx)
+        emf = PerfectMatch.build_on_device(ctx, READ_LEN, 1.1)        # bwagpu_emf_build_device: the table is built in HBM
+        ctx.synchronize()
         setup["emf_build_s"] = time.perf_counter() - t0
+        log("EMF table built in", setup["emf_build_s"], "s")
     # reference arm / CPU baseline need the index on the host: copied back once, outside every timed region
     reference_arm = args.impl == "reference"
     want_cpu = reference_arm or (rank == 0 and not args.no_cpu)
-    idx_host = fma_tabs = None
+    idx_host = fma_tabs = emf_table = None
     if want_cpu:
         t0 = time.perf_counter()
         idx_host = fmi.get_index()
         fma_tabs = fmi.get_fma() if args.fma else None
+        emf_table = emf.get_table() if emf is not None else None
         setup["index_copy_back_s"] = time.perf_counter() - t0
     if reference_arm:
         ctx.close()
         per_step = min(n, args.cpu_reads_per_thread * thr)
         reads = make_reads(ref, 0, per_step, seed=500)
-        cpu_reference_arm(idx_host, fma_tabs, text, coff, clen, reads[: 200 * thr], thr)        # warm-up
+        cpu_reference_arm(idx_host, fma_tabs, text, coff, clen, reads[: 200 * thr], thr, emf_table)        # warm-up
         t, kind = 0.0, ""
         for _ in range(args.steps):
-            dt, kind = cpu_reference_arm(idx_host, fma_tabs, text, coff, clen, reads, thr)
+            dt, kind = cpu_reference_arm(idx_host, fma_tabs, text, coff, clen, reads, thr, emf_table)
             t += dt
         v = per_step * args.steps / t
         return {"impl": "reference", "metric": METRIC, "value": v, "unit": "reads/s", "n_gpus": args.gpus,
@@ -262,7 +268,7 @@ def bench_mem3(args, rank, world, H):
     if rank != 0:
         return None
     return report(args, world, H, ctx, cfg, setup, n, ms, e2e_s, launches, clocks, tot, kt, int_peaks, flat1.nbytes + 12 * n, d2h,
-                  dict(ref=ref, text=text, coff=coff, clen=clen, idx_host=idx_host, fma_tabs=fma_tabs, flat=flat, thr=thr,
+                  dict(ref=ref, text=text, coff=coff, clen=clen, idx_host=idx_host, fma_tabs=fma_tabs, emf_table=emf_table, flat=flat, thr=thr,
                        t_all=t_all))
 
 
@@ -320,7 +326,8 @@ def report(args, world, H, ctx, cfg, setup, n, ms, e2e_s, launches, clocks, tot,
     if not args.no_cpu:
         thr = S["thr"]
         m = min(n, args.cpu_reads_per_thread * thr)
-        dt, kind = cpu_reference_arm(S["idx_host"], S["fma_tabs"], S["text"], S["coff"], S["clen"], np.asarray(S["flat"][:m]), thr)
+        dt, kind = cpu_reference_arm(S["idx_host"], S["fma_tabs"], S["text"], S["coff"], S["clen"], np.asarray(S["flat"][:m]), thr,
+                                     S["emf_table"])
         res["cpu_baseline"] = {"value": m / dt, "unit": "reads/s", "cores": thr, "kind": "reference",
                                "sample": f"the first {m} reads of rank 0's read set, {kind}, mem_kernel1_core + "
                                          f"mem_chain2aln_across_reads_V2 on one shared in-memory index, {dt:.1f}s"}

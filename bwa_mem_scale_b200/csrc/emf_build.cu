@@ -28,7 +28,7 @@
 #include "ctx.cuh"
 
 #define EB_NO 0xFFFFFFFFu
-#define EB_MAXC 24                      // distinct seeds per hash slot handled (Poisson(0.91): > 24 never happens)
+#define EB_MAXC 128                     // distinct seeds per hash slot handled (the XOR-of-words hash has weak spots on repeat families)
 #define EB_MAXW 8                       // seed words: seeds up to 256 bases
 
 struct EbText { const uint64_t *pk; int64_t l_pac; int L, nw, r; };   // packed forward + reverse-complement text
@@ -221,7 +221,7 @@ __global__ void eb_fill_kernel(EbText t, const uint32_t *__restrict__ keys, cons
     // balanced tree rooted in the hash slot; the other nodes take this slot's share of the empty slots
     const uint32_t *mine = empties + extra_off[i];
     int next = 0;
-    uint32_t st_slot[8]; int st_lo[8], st_hi[8], sp = 0;             // depth <= log2(24) + 1
+    uint32_t st_slot[12]; int st_lo[12], st_hi[12], sp = 0;          // depth <= log2(EB_MAXC) + 2
     st_slot[0] = k; st_lo[0] = 0; st_hi[0] = nc - 1; sp = 1;
     while (sp > 0) {
         --sp;

@@ -226,6 +226,26 @@ void ref_mem_set_fma(void *h, void *all_smem_table, void *last_smem_table)
 }
 #endif
 
+#ifdef PERFECT_MATCH
+// EMF table already in memory (what load_perfect_table leaves in fmi->perfect_table, src/perfect_map.cpp:204-291);
+// shared by every clone of this worker.  loc_table / seed_table stay the caller's.
+void ref_mem_set_perfect(void *h, int seed_len, uint32_t num_loc_entry, uint32_t num_seed_entry, uint32_t seq_len,
+                         uint32_t *loc_table, void *seed_table)
+{
+    ref_mem_ctx *c = (ref_mem_ctx *)h;
+    if (!seed_table) { c->fmi->perfect_table = NULL; perfect_table_seed_len = PT_SEED_LEN_NO_TABLE; return; }
+    perfect_table_t *pt = (perfect_table_t *)calloc(1, sizeof(perfect_table_t));
+    pt->seed_len = seed_len; pt->num_loc_entry = num_loc_entry; pt->num_seed_entry = num_seed_entry;
+#ifdef MEMSCALE
+    pt->num_seed_load = num_seed_entry;
+#endif
+    pt->ref_string = c->ref_string; pt->loc_table = loc_table; pt->seed_table = (seed_entry_t *)seed_table;
+    pt->seq_len = seq_len;
+    c->fmi->perfect_table = pt;
+    perfect_table_seed_len = seed_len;
+}
+#endif
+
 // a second worker on the same (read-only) index: own arenas, shared FMI_search / reference text,
 // like the reference's threads sharing w.fmi (src/bwamem.h:228-253)
 void *ref_mem_clone(void *h0)

@@ -399,6 +399,16 @@ class RefMem:
         self.lib.ref_mem_set_fma(self.h, None if all_smem is None else all_smem.ctypes.data,
                                  None if last_smem is None else last_smem.ctypes.data)
 
+    def set_perfect(self, table):
+        """EMF table already in memory (emf / scale flavours): a bwa_mem_scale_b200.PerfectTable, or None = off."""
+        self.lib.ref_mem_set_perfect.argtypes = [C.c_void_p, C.c_int, C.c_uint32, C.c_uint32, C.c_uint32, C.c_void_p, C.c_void_p]
+        self._emf = table
+        if table is None:
+            self.lib.ref_mem_set_perfect(self.h, 0, 0, 0, 0, None, None)
+        else:
+            self.lib.ref_mem_set_perfect(self.h, table.seed_len, len(table.loc_table), len(table.seed_table), table.seq_len,
+                                         table.loc_table.ctypes.data, table.seed_table.ctypes.data)
+
     def use_ert(self, ref_ert):
         """Switch seeding + chaining to mem_kernel1_core_ert over the tables of a RefErt (None: back to FM)."""
         self.lib.ref_mem_use_ert.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
