@@ -19,7 +19,7 @@ enum { SCR_BSW_PAIRS = 0, SCR_BSW_REF, SCR_BSW_QER, SCR_BSW_WORK, SCR_MISC0, SCR
        SCR_CIG_JOBS, SCR_CIG_OUT, SCR_CIG_SLABOFF, SCR_CIG_EH, SCR_CIG_Z, SCR_CIG_CIGAR, SCR_CIG_MD, SCR_CIG_CNT, SCR_CIG_SCAN,
        SCR_CIG_OUTC, SCR_CIG_OUTM, SCR_CIG_ORDER, SCR_CIG_REDO,
        SCR_MEM_READS, SCR_MEM_OFF, SCR_MEM_LEN, SCR_MEM_EMF_RET, SCR_MEM_PERFECT, SCR_MEM_SKIP, SCR_MEM_CNT, SCR_MEM_KEEP,
-       SCR_MEM_POS, SCR_MEM_REGS, SCR_MEM_REGOFF, SCR_BSW_CELLS, SCR_CH_HEAVY,
+       SCR_MEM_POS, SCR_MEM_REGS, SCR_MEM_REGOFF, SCR_BSW_CELLS, SCR_CH_HEAVY, SCR_SEED_OVF, SCR_SEED_TMP2,
        BWAGPU_NSCRATCH };
 
 struct bwagpu_ctx {

@@ -11,6 +11,7 @@
 //   sa_count_kernel      rows each SMEM contributes (min(max_occ, ceil(s/step))).
 //   sa_walk_kernel       one thread per output coordinate: LF walk to the next sampled row.
 #include <cub/device/device_scan.cuh>
+#include <stdlib.h>
 #include "ctx.cuh"
 #include "fmi_core.cuh"
 #include <type_traits>
@@ -84,7 +85,7 @@ __device__ __forceinline__ void seed_stage_read(uint32_t *w, const uint8_t *__re
     }
 }
 
-struct SeedStats { unsigned long long n_ext, n_rec, n_lf, max_cnt; };
+struct SeedStats { unsigned long long n_ext, n_rec, n_lf, max_cnt; unsigned int n_ovf, pad_; };
 
 // ---- warp-cooperative backwardExt ------------------------------------------------------------------------------
 // SEED_COOP = 1: the reads stay one per thread (so every issued instruction of the state machine still serves all the
@@ -172,8 +173,12 @@ seed_collect_kernel(FmView f, SeedOpt o, const uint8_t *__restrict__ reads,
                     const int64_t *__restrict__ off, const int32_t *__restrict__ len,
                     const uint8_t *__restrict__ skip, int nseq, bwagpu_smem *__restrict__ tmp,
                     int cap, int32_t *__restrict__ cnt, int64_t *__restrict__ prev_buf,
-                    SeedStats *__restrict__ stats)
+                    SeedStats *__restrict__ stats, const int32_t *__restrict__ list, int32_t *__restrict__ ovf_list,
+                    int32_t *__restrict__ slab_of)
 {
+    // list == NULL: first pass over all nseq reads, read i writes slab i of `tmp`; a read that finds more than `cap`
+    // SMEMs is appended to ovf_list.  list != NULL: second pass over the nseq reads list[0 .. nseq) with the wider private
+    // slabs of `tmp` (slab = position in the list, recorded in slab_of).
     const int64_t T = (int64_t)gridDim.x * blockDim.x;
     const int64_t t0 = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     extern __shared__ uint32_t seed_sm[];
@@ -199,14 +204,16 @@ seed_collect_kernel(FmView f, SeedOpt o, const uint8_t *__restrict__ reads,
                     if (!active) {
                         bool got = false;
                         while (next < nseq) {
-                            const int i = (int)next; next += T;
+                            const int it = (int)next; next += T;
+                            const int i = list ? list[it] : it;
+                            if (list) slab_of[i] = it;
                             if (skip && skip[i]) { cnt[i] = 0; continue; }
                             if constexpr (STAGED) {
                                 seed_stage_read(rd_sm, reads + off[i], len[i]);
                                 SmemRead r; r.w = rd_sm;
-                                m.init(r, len[i], i, pv, tmp + (int64_t)i * cap, cap);
+                                m.init(r, len[i], i, pv, tmp + (int64_t)it * cap, cap);
                             } else {
-                                m.init(reads + off[i], len[i], i, pv, tmp + (int64_t)i * cap, cap);
+                                m.init(reads + off[i], len[i], i, pv, tmp + (int64_t)it * cap, cap);
                             }
                             m.pf_cp = f.cp_occ;
                             got = true;
@@ -218,6 +225,7 @@ seed_collect_kernel(FmView f, SeedOpt o, const uint8_t *__restrict__ reads,
                     if (m.advance(f, o)) { ready = true; break; }
                     cnt[m.rid] = m.n_out;
                     max_cnt = max(max_cnt, (unsigned)m.n_out);
+                    if (!list && m.n_out > cap) ovf_list[atomicAdd(&stats->n_ovf, 1u)] = m.rid;
                     active = false;
                 }
             }
@@ -255,14 +263,15 @@ seed_collect_kernel(FmView f, SeedOpt o, const uint8_t *__restrict__ reads,
 
 // Per read: rank its SMEMs by (m, n) and write them to out[offs[i] ..].  Equal keys are
 // identical entries (same substring => same interval), so any order among them is the reference's.
-__global__ void seed_sort_kernel(const bwagpu_smem *__restrict__ tmp, int cap,
-                                 const int32_t *__restrict__ cnt, const int64_t *__restrict__ offs,
-                                 int nseq, bwagpu_smem *__restrict__ out)
+__global__ void seed_sort_kernel(const bwagpu_smem *__restrict__ tmp, int cap, const bwagpu_smem *__restrict__ tmp2, int cap2,
+                                 const int32_t *__restrict__ slab_of, const int32_t *__restrict__ cnt,
+                                 const int64_t *__restrict__ offs, int nseq, bwagpu_smem *__restrict__ out)
 {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= nseq) return;
     const int n = cnt[i];
-    const bwagpu_smem *src = tmp + (int64_t)i * cap;
+    const int so = slab_of[i];                     // >= 0: the read was re-run with a private slab of cap2 entries
+    const bwagpu_smem *src = so >= 0 ? tmp2 + (int64_t)so * cap2 : tmp + (int64_t)i * cap;
     bwagpu_smem *dst = out + offs[i];
     for (int e = 0; e < n; ++e) {
         const uint64_t key = ((uint64_t)src[e].m << 32) | src[e].n;
@@ -500,33 +509,58 @@ static int seed_collect_dev(bwagpu_ctx *ctx, const bwagpu_seed_opt *opt, const u
     const int need = (nseq + SEED_TPB - 1) / SEED_TPB;
     if (blocks > need) blocks = need;
     const int64_t T = (int64_t)blocks * SEED_TPB;
-    if (ctx->seed_read_cap < 32) ctx->seed_read_cap = 32;
-    int32_t *d_cnt; int64_t *d_offs, *d_prev; SeedStats *d_stats; bwagpu_smem *d_tmp;
-    int rc;
+    // Common slab of up to 128 entries per read (only what a read finds is ever written; per call, never sticky); the few reads that find more (repeats) are collected in a list and
+    // re-run once with private slabs sized for the largest of them, so one repeat-heavy read costs one small launch, not a
+    // second pass over the batch, and the common slab never grows.
+    int cap = 128;                                            // widest slab that keeps the scratch under 6 GiB
+    while (cap > 32 && (int64_t)nseq * cap * (int64_t)sizeof(bwagpu_smem) > (6LL << 30)) cap >>= 1;
+    if (getenv("BWAGPU_SEED_CAP")) cap = atoi(getenv("BWAGPU_SEED_CAP")) > 0 ? atoi(getenv("BWAGPU_SEED_CAP")) : cap;   // tests: force the overflow path
+    int32_t *d_cnt, *d_ovf, *d_slab_of; int64_t *d_offs, *d_prev; SeedStats *d_stats; bwagpu_smem *d_tmp, *d_tmp2 = nullptr;
+    int rc, cap2 = cap;
     if ((rc = bwagpu_scratch(ctx, SCR_SEED_CNT, (int64_t)(nseq + 1) * 4, (void **)&d_cnt))) return rc;
     if ((rc = bwagpu_scratch(ctx, SCR_SEED_SCAN, (int64_t)(nseq + 1) * 8, (void **)&d_offs))) return rc;
     if ((rc = bwagpu_scratch(ctx, SCR_SEED_PREV, T * 3 * (int64_t)(max_len + 1) * 8, (void **)&d_prev))) return rc;
     if ((rc = bwagpu_scratch(ctx, SCR_STATS, sizeof(SeedStats), (void **)&d_stats))) return rc;
-    for (;;) {
-        const int cap = ctx->seed_read_cap;
-        if ((rc = bwagpu_scratch(ctx, SCR_SEED_TMP, (int64_t)nseq * cap * sizeof(bwagpu_smem), (void **)&d_tmp))) return rc;
-        BWAGPU_CUDA(ctx, cudaMemsetAsync(d_stats, 0, sizeof(SeedStats), ctx->stream));
-        BWAGPU_CUDA(ctx, cudaMemsetAsync(d_cnt + nseq, 0, 4, ctx->stream));
+    if ((rc = bwagpu_scratch(ctx, SCR_SEED_OVF, (int64_t)(nseq + 1) * 8, (void **)&d_ovf))) return rc;
+    d_slab_of = d_ovf + nseq + 1;
+    if ((rc = bwagpu_scratch(ctx, SCR_SEED_TMP, (int64_t)nseq * cap * sizeof(bwagpu_smem), (void **)&d_tmp))) return rc;
+    BWAGPU_CUDA(ctx, cudaMemsetAsync(d_stats, 0, sizeof(SeedStats), ctx->stream));
+    BWAGPU_CUDA(ctx, cudaMemsetAsync(d_cnt + nseq, 0, 4, ctx->stream));
+    BWAGPU_CUDA(ctx, cudaMemsetAsync(d_slab_of, 0xFF, (size_t)nseq * 4, ctx->stream));
+    auto launch = [&](int n_items, bwagpu_smem *slab, int slab_cap, const int32_t *list) {
+        int b = blocks;
+        const int nd = (n_items + SEED_TPB - 1) / SEED_TPB;
+        if (b > nd) b = nd;
         BWAGPU_KERNEL_BEGIN(ctx);
         if (staged)
-            seed_collect_kernel<true><<<blocks, SEED_TPB, smem, ctx->stream>>>(fm_view(ctx), so, d_reads, d_off, d_len, d_skip,
-                                                                              nseq, d_tmp, cap, d_cnt, d_prev, d_stats);
+            seed_collect_kernel<true><<<b, SEED_TPB, smem, ctx->stream>>>(fm_view(ctx), so, d_reads, d_off, d_len, d_skip, n_items,
+                                                                         slab, slab_cap, d_cnt, d_prev, d_stats, list, d_ovf, d_slab_of);
         else
-            seed_collect_kernel<false><<<blocks, SEED_TPB, smem, ctx->stream>>>(fm_view(ctx), so, d_reads, d_off, d_len, d_skip,
-                                                                               nseq, d_tmp, cap, d_cnt, d_prev, d_stats);
+            seed_collect_kernel<false><<<b, SEED_TPB, smem, ctx->stream>>>(fm_view(ctx), so, d_reads, d_off, d_len, d_skip, n_items,
+                                                                          slab, slab_cap, d_cnt, d_prev, d_stats, list, d_ovf, d_slab_of);
         BWAGPU_KERNEL_END(ctx, BWAGPU_KERN_SEED_COLLECT);
-        BWAGPU_CUDA(ctx, cudaGetLastError());
-        BWAGPU_CUDA(ctx, cudaMemcpyAsync(h_stats, d_stats, sizeof(SeedStats), cudaMemcpyDeviceToHost, ctx->stream));
-        BWAGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-        if ((int64_t)h_stats->max_cnt <= cap) break;
-        int ncap = cap;
-        while (ncap < (int64_t)h_stats->max_cnt) ncap *= 2;     // some read overflowed: redo with room
-        ctx->seed_read_cap = ncap;
+    };
+    launch(nseq, d_tmp, cap, nullptr);
+    BWAGPU_CUDA(ctx, cudaGetLastError());
+    BWAGPU_CUDA(ctx, cudaMemcpyAsync(h_stats, d_stats, sizeof(SeedStats), cudaMemcpyDeviceToHost, ctx->stream));
+    BWAGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    if (h_stats->n_ovf > 0) {
+        const int n_ovf = (int)h_stats->n_ovf;
+        if (getenv("BWAGPU_VERBOSE")) fprintf(stderr, "[bwagpu] seed: %d of %d reads outgrow the %d-entry slab (max %llu)\n", n_ovf, nseq, cap, h_stats->max_cnt);
+        // a truncated slab also truncates the read's own round-2 input, so the count it reports can still be short of
+        // what it finds with room: repeat until every listed read fits
+        for (int pass = 0;; ++pass) {
+            while (cap2 < (int64_t)h_stats->max_cnt) cap2 *= 2;
+            if (pass > 8 || (int64_t)n_ovf * cap2 * (int64_t)sizeof(bwagpu_smem) > (8LL << 30))
+                BWAGPU_FAIL(ctx, BWAGPU_ERR_RANGE, "seed: %d reads need up to %d SMEM slots each; their scratch would exceed 8 GiB", n_ovf, cap2);
+            if ((rc = bwagpu_scratch(ctx, SCR_SEED_TMP2, (int64_t)n_ovf * cap2 * sizeof(bwagpu_smem), (void **)&d_tmp2))) return rc;
+            BWAGPU_CUDA(ctx, cudaMemsetAsync(&d_stats->max_cnt, 0, 8, ctx->stream));
+            launch(n_ovf, d_tmp2, cap2, d_ovf);          // its extensions add to the statistics: they are work done
+            BWAGPU_CUDA(ctx, cudaGetLastError());
+            BWAGPU_CUDA(ctx, cudaMemcpyAsync(h_stats, d_stats, sizeof(SeedStats), cudaMemcpyDeviceToHost, ctx->stream));
+            BWAGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+            if ((int64_t)h_stats->max_cnt <= cap2) break;
+        }
     }
     if ((rc = scan_i32_to_i64(ctx, d_cnt, d_offs, nseq + 1))) return rc;
     int64_t total = 0;
@@ -535,7 +569,7 @@ static int seed_collect_dev(bwagpu_ctx *ctx, const bwagpu_seed_opt *opt, const u
     bwagpu_smem *out;
     if ((rc = bwagpu_scratch(ctx, SCR_SEED_OUT, (total + 1) * (int64_t)sizeof(bwagpu_smem), (void **)&out))) return rc;
     BWAGPU_KERNEL_BEGIN(ctx);
-    seed_sort_kernel<<<(nseq + 127) / 128, 128, 0, ctx->stream>>>(d_tmp, ctx->seed_read_cap, d_cnt, d_offs, nseq, out);
+    seed_sort_kernel<<<(nseq + 127) / 128, 128, 0, ctx->stream>>>(d_tmp, cap, d_tmp2, cap2, d_slab_of, d_cnt, d_offs, nseq, out);
     BWAGPU_KERNEL_END(ctx, BWAGPU_KERN_SEED_SORT);
     BWAGPU_CUDA(ctx, cudaGetLastError());
     *d_out = out; *tot = total;

@@ -40,6 +40,22 @@ def test_gpu_seeding_matches_golden_and_oracle(small_fmi, case):
     assert np.array_equal(sa, ol.oracle_sa_lookup(idx, want, max_occ)[0])
 
 
+@pytest.mark.parametrize("cap", [2, 5])
+def test_gpu_seeding_overflow_list(small_fmi, cap):
+    """Reads that outgrow the common SMEM slab are re-run from a list with private slabs (several rounds when the
+    truncated first pass under-reports): forced here with a tiny slab, results must not change."""
+    name, kw, max_occ = fc.OPT_CASES[1]                      # short_seeds: up to dozens of SMEMs per read
+    ref, idx, fmi = small_fmi
+    flat, off, ln = ol.pack_reads(fc.small_reads(ref))
+    oo = ol.default_seed_opt(**kw)
+    os.environ["BWAGPU_SEED_CAP"] = str(cap)
+    try:
+        got = fmi.collect_smem(seed_opt(oo.min_seed_len, oo.split_factor, oo.split_width, max_occ, oo.max_mem_intv), flat, off, ln)
+    finally:
+        os.environ.pop("BWAGPU_SEED_CAP")
+    assert np.array_equal(sha(fc.smem_matrix(got)), GOLD[f"{name}_smem_sha256"])
+
+
 def test_gpu_seeding_skip_empty_and_overflow(small_fmi, gpu_ctx):
     ref, idx, fmi = small_fmi
     reads = fc.small_reads(ref)[:300]
