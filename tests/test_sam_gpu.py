@@ -24,7 +24,7 @@ def need(flavour):
 
 def run(cmd, out=None, log=None):
     with open(out or os.devnull, "wb") as fo, open(log or os.devnull, "wb") as fe:
-        subprocess.run(cmd, check=True, stdout=fo, stderr=fe)
+        subprocess.run(cmd, check=True, stdout=fo, stderr=fe, timeout=900)
 
 
 def sam_body(path):
@@ -124,3 +124,47 @@ def test_sam_identical_fma_emf(tmp_path):
     lines, glog = compare(cpu, gpu, prefix, [fq], ["-l", "151"], tmp_path, "emf")
     hits = sum(int(l.split(" EMF hits")[0].split()[-1]) for l in glog.splitlines() if "[bwagpu] chunk of" in l)
     assert hits > 2500                                                          # (1 - 0.005)^151 = 47 % of 8000 reads are exact
+
+
+def test_sam_identical_ert(gpu_ctx, tmp_path):
+    """ERT seeding (the reference's `scale` feature set with its shm index store): the reference-built ERT index of the
+    300 kbp repeat genome (fixture: tree blob + the k-mer entries that occur; the other entries completed on the device
+    from the FM-index, bwagpu_index_complete_ert) is written out as <prefix>.kmer_table / .mlt_table; the unmodified
+    reference and the shim binary both map it through the shm store and must write the same SAM."""
+    cpu, gpu = need("scale")
+    import fmi_cases as fc
+    from bwa_mem_scale_b200 import ErtIndex, ErtSeeding, Extender, FMI_search
+    d = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "ert_small_genome.npz"))
+    ref = np.ascontiguousarray(d["ref"])
+    prefix = str(tmp_path / "g")
+    text = fmindex.write_0123(prefix, ref)
+    fmindex.write_bns_files(prefix, ref)
+    Extender(text, len(ref), [0], [len(ref)], ctx=gpu_ctx)
+    FMI_search(None, ctx=gpu_ctx)                                            # device-built FM-index (for the completion)
+    ert = ErtSeeding(ErtIndex(d["mlt_table"], sparse_idx=d["kmer_idx"], sparse_val=d["kmer_val"]), gpu_ctx)
+    ert.complete_from_fm()
+    ert.dense_table().tofile(prefix + ".kmer_table")
+    np.ascontiguousarray(d["mlt_table"]).tofile(prefix + ".mlt_table")
+    gpu_ctx.check(gpu_ctx.lib.bwagpu_index_unload_ert(gpu_ctx.h), "bwagpu_index_unload_ert")
+    reads = list(synth.simulate_reads(ref, 4000, seed=5, err=0.01)[0]) + synth.gapped_reads(ref, 1500, seed=6)
+    fq = str(tmp_path / "reads.fq")
+    fmindex.write_fastq(fq, reads)
+    # the shm store is loaded once (load-shm: default budget -> k-mer table + tree), both runs then map it read-only;
+    # without this the first `mem` leaves the store in its "manager is modifying" state and the second one waits forever
+    run([cpu, "remove-shm"])
+    llog = str(tmp_path / "load.log")
+    subprocess.run([cpu, "load-shm", prefix], check=True, stdout=open(llog, "wb"), stderr=subprocess.STDOUT, timeout=600)
+    try:
+        a, b = str(tmp_path / "ert_cpu.sam"), str(tmp_path / "ert_gpu.sam")
+        for binary, out, log in ((cpu, a, "ert_cpu.log"), (gpu, b, "ert_gpu.log")):
+            with open(out, "wb") as fo, open(str(tmp_path / log), "wb") as fe:
+                subprocess.run([binary, "mem", "-t", "4", prefix, fq], check=True, stdout=fo, stderr=fe, timeout=600)
+    finally:
+        subprocess.run([cpu, "remove-shm"], stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL, timeout=120)
+    glog = open(str(tmp_path / "ert_gpu.log"), errors="ignore").read()
+    assert "[bwagpu] chunk of" in glog and "useErt: 1" in open(llog, errors="ignore").read() + glog
+    lines, y = sam_body(a), sam_body(b)
+    bad = [i for i in range(min(len(lines), len(y))) if lines[i] != y[i]]
+    assert len(lines) == len(y) and not bad, f"{len(bad)} SAM lines differ, first: {lines[bad[0]] if bad else None!r}"
+    m, n = mapped(lines)
+    assert n >= 5500 and m > 0.97 * 5500
