@@ -692,15 +692,24 @@ def bench_ksw(args, rank, world):
     """Mate-rescue SW (BASELINE config 4's kernel): ksw_align2 jobs shaped like mem_matesw's, 151-bp query
     against an insert-size window, xtra = SUBO | START | BYTE | min_seed_len."""
     from bwa_mem_scale_b200 import Context, KSWR_DTYPE, MateSW, synth
-    uniq = min(args.pairs, 20000)
-    pairs, ref, qer = synth.rescue_jobs(uniq, seed=2000 + rank)
+    if args.harvested:
+        # the ksw_align2 jobs mem_matesw issued in a real paired-end run of the reference (tests/golden/pe_rescue_jobs.npz,
+        # generated by tests/golden/make_golden_pe_jobs.py): real windows, real mismatch structure, real hit/no-hit mix
+        g = np.load(os.path.join(ROOT, "tests", "golden", "pe_rescue_jobs.npz"))
+        pairs, ref, qer = np.ascontiguousarray(g["pairs"]), g["ref"], g["qer"]
+        uniq = len(pairs)
+    else:
+        uniq = min(args.pairs, 20000)
+        pairs, ref, qer = synth.rescue_jobs(uniq, seed=2000 + rank)
     reps = max(args.pairs // uniq, 1)
     pairs = np.tile(pairs, reps)                     # the same windows again: the kernel is compute bound
     pairs["id"] = np.arange(len(pairs))
     n = len(pairs)
     cells = float((pairs["len1"].astype(np.int64) * pairs["len2"]).sum())
-    cfg = {"workload": f"mate-rescue SW (BASELINE config 4 kernel): {n} ksw_align2 jobs/GPU ({uniq} distinct), 151 bp query x "
-                       "200-900 bp window, xtra = SUBO|START|BYTE|19; cell updates = len1 x len2 of the forward pass",
+    shape = ("harvested from a paired-end run of the reference (2 x 151 bp, insert N(400,50), 2 Mbp genome): 151 bp query x "
+             f"{int(pairs['len1'].min())}-{int(pairs['len1'].max())} bp window") if args.harvested else "151 bp query x 200-900 bp window"
+    cfg = {"workload": f"mate-rescue SW (BASELINE config 4 kernel): {n} ksw_align2 jobs/GPU ({uniq} distinct), {shape}, "
+                       "xtra = SUBO|START|BYTE|19; cell updates = len1 x len2 of the forward pass",
            "jobs_per_gpu": n, "l2_policy": "flush between steps"}
     if args.impl == "reference":
         if rank != 0:
@@ -957,6 +966,7 @@ def main():
     ap.add_argument("--chunk", type=int, default=1_000_000, help="mem: reads per bwagpu_mem_process_chunk call")
     ap.add_argument("--cpu-reads-per-thread", type=int, default=150_000, help="mem: size of the CPU arm's bounded sample")
     ap.add_argument("--pairs", type=int, default=1_000_000)
+    ap.add_argument("--harvested", type=int, default=0, help="ksw workload: use the jobs recorded from a real PE run of the reference")
     ap.add_argument("--band", type=int, default=100)
     ap.add_argument("--kind", type=int, default=16, choices=[8, 16])
     ap.add_argument("--fma", type=int, default=1, help="use the FMA smem tables (config 2)")

@@ -59,3 +59,12 @@ def test_gpu_ksw_large_batch_properties(gpu_ctx):
     assert ok.sum() > 10000
     assert np.all(got["tb"][ok] <= got["te"][ok]) and np.all(got["qb"][ok] <= got["qe"][ok])
     assert np.all(got["score2"] <= got["score"])
+
+
+def test_gpu_ksw_harvested_pe_jobs(gpu_ctx):
+    """Row a19 on REAL work: every ksw_align2 job mem_matesw issued in a paired-end run of the reference
+    (2 x 151 bp, insert N(400,50), half of the second mates damaged), answers as the reference returned them."""
+    from test_oracle_ksw import pe_rescue_jobs
+    pairs, ref, qer, want = pe_rescue_jobs()
+    got = MateSW(ctx=gpu_ctx).mem_sam_pe_batch(pairs, ref, qer)
+    assert np.array_equal(as_matrix(got), want)

@@ -39,3 +39,18 @@ def test_golden_exercises_every_output():
     assert (g[:, 3] > 0).sum() > 20 and (g[:, 5] >= 0).sum() > 200        # score2 / tb found
     assert (GOLD["u8_overflow"][:, 0] == 255).sum() > 50                    # 8-bit overflow reported as 255
     assert (GOLD["score_only"][:, 5] == -1).all()                           # no XSTART -> no start
+
+
+def pe_rescue_jobs():
+    """Real mate-rescue jobs recorded from a paired-end run of the reference (tests/golden/make_golden_pe_jobs.py)."""
+    g = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "pe_rescue_jobs.npz"))
+    return np.ascontiguousarray(g["pairs"]), g["ref"], g["qer"], g["kswr"]
+
+
+def test_oracle_matches_harvested_pe_jobs():
+    """mem_matesw's real ksw_align2 calls (reference src/bwamem_pair.cpp:200) and the records they returned."""
+    pairs, ref, qer, want = pe_rescue_jobs()
+    assert len(pairs) > 3000 and (want[:, 0] >= 30).sum() > 2000 and (want[:, 0] < 30).sum() > 300
+    assert np.all(pairs["h0"] & ol.KSW_XSTART) and np.all(pairs["len1"] >= 500)      # insert-size windows
+    got = ol.oracle_ksw(pairs, ref, qer)
+    assert np.array_equal(as_matrix(got), want)
