@@ -70,8 +70,8 @@ __global__ void __launch_bounds__(256) probe_group_kernel(FmView f, const uint8_
             a = text[p - t] & 3;
             const int64_t pos = g < 4 ? k : k + s;                                  // sp for lanes 0-3, ep for lanes 4-7
             const int64_t *rec = f.cp_occ + (pos >> 6) * 8;
-            const int64_t cnt = __ldg(rec + b);
-            const uint64_t bits = (uint64_t)__ldg(rec + 4 + b);
+            const int64_t cnt = __ldg(rec + FM_W_CNT(b));
+            const uint64_t bits = (uint64_t)__ldg(rec + FM_W_BITS(b));
             const int64_t occ = cnt + __popcll(bits & fm_prefix_mask((int)(pos & 63)));     // occ(pos, b)
             const int64_t other = shfl64(occ, g ^ 4, 8);
             const int64_t sz = g < 4 ? other - occ : occ - other;                   // s[b] on every lane
@@ -106,8 +106,8 @@ __global__ void __launch_bounds__(256) probe_group4_kernel(FmView f, const uint8
             a = text[p - t] & 3;
             const int64_t ep = k + s;
             const int64_t *r0 = f.cp_occ + (k >> 6) * 8, *r1 = f.cp_occ + (ep >> 6) * 8;
-            const int64_t c0 = __ldg(r0 + b), c1 = __ldg(r1 + b);
-            const uint64_t o0 = (uint64_t)__ldg(r0 + 4 + b), o1 = (uint64_t)__ldg(r1 + 4 + b);
+            const int64_t c0 = __ldg(r0 + FM_W_CNT(b)), c1 = __ldg(r1 + FM_W_CNT(b));
+            const uint64_t o0 = (uint64_t)__ldg(r0 + FM_W_BITS(b)), o1 = (uint64_t)__ldg(r1 + FM_W_BITS(b));
             const int64_t osp = c0 + __popcll(o0 & fm_prefix_mask((int)(k & 63)));
             const int64_t sz = c1 + __popcll(o1 & fm_prefix_mask((int)(ep & 63))) - osp;
             const int64_t s1 = shfl64(sz, (b + 1) & 3, 4), s2 = shfl64(sz, (b + 2) & 3, 4), s3 = shfl64(sz, (b + 3) & 3, 4);

@@ -24,6 +24,15 @@ __device__ __forceinline__ uint32_t bsw_prmt(uint32_t a, uint32_t b, uint32_t se
     return d;
 }
 
+// Row arg-max bookkeeping: the low half of the packed (row maximum, column) key is a column code.  An exact code names
+// the column (1-based) itself; a word code says "in the 8 columns that end here".  Codes order like the columns they
+// stand for, so the packed maximum still ends up on the LAST column attaining the row maximum (or on its word).
+#ifndef BSW_V2
+#define BSW_V2 1
+#endif
+#define BSW_KEY_EXACT(c1) (((c1) << 1) | 1)
+#define BSW_KEY_WORD(c1) ((c1) << 1)
+
 #ifndef BSW_UNROLL
 #define BSW_UNROLL 4
 #endif
@@ -113,7 +122,7 @@ __device__ BswOut bsw_lane_fast(const bwagpu_bsw_params &p, const uint8_t *__res
             const bool masked = head > (j) || (j) > tail;                             \
             if (masked) { left = 0; fnew = 0; }                                       \
             const bool skip = BITS == 8 ? masked : ((j) + 1 > tail);                  \
-            if (!skip) key = max(key, (h << 16) | ((j) + 1));                         \
+            if (!skip) key = max(key, (h << 16) | BSW_KEY_EXACT((j) + 1));            \
             COL(j) = bsw_pack(left, fnew);                                            \
             left = h;                                                                 \
             if ((j) + 1 == len2 && live && !((j) + 1 > tail)) {                       \
@@ -128,7 +137,7 @@ __device__ BswOut bsw_lane_fast(const bwagpu_bsw_params &p, const uint8_t *__res
         const int jb = min(hi, tail);             // [ja, jb): live range, j >= head and j + 1 <= tail
         if (j < jb) {
             uint32_t *cp = &COL(j);
-            // one live cell: NIB = query code of column J, KEY receives (h << 16) + (J + 1)
+            // one live cell: NIB = query code of column J, KEY receives (h << 16) + the exact-column code of J + 1
 #define LIVE_CELL(NIB, J, KEY)                                                        \
             {                                                                         \
                 const uint32_t cv = *cp;                                              \
@@ -141,7 +150,7 @@ __device__ BswOut bsw_lane_fast(const bwagpu_bsw_params &p, const uint8_t *__res
                 const int h = __vimax3_s32(M, er, fc);                                \
                 er = __viaddmax_s32_relu(M, -gapo_i, er - e_ins);                     \
                 const int fnew = __viaddmax_s32_relu(M, -gapo_d, fc - e_del);         \
-                KEY = (h << 16) + ((J) + 1);                                          \
+                KEY = (h << 16) + BSW_KEY_EXACT((J) + 1);                             \
                 *cp = __byte_perm((uint32_t)left, (uint32_t)fnew, 0x5410);            \
                 left = h;                                                             \
                 cp += STRIDE;                                                         \
@@ -154,6 +163,40 @@ __device__ BswOut bsw_lane_fast(const bwagpu_bsw_params &p, const uint8_t *__res
             }
             // whole words: 8 cells straight-line, shifts known at compile time
             const uint32_t *qp = qsm + (j >> 3) * STRIDE;
+#if BSW_V2
+            // one word of the staged query = 8 cells.  The scores of four cells come from ONE permute: the staged codes are
+            // 4-bit with bit 3 clear, so the word itself (its low 16 bits) is a selector that picks the four score bytes; a
+            // signed byte dot product with a one-hot word then adds byte c to the diagonal (M = diag + s in one operation).
+            // The row's arg-max is kept per WORD here — key = (max h of the 8 cells) << 16 | code of "somewhere up to column
+            // j + 8" — and the exact column is looked up after the row, only when the row's outcome depends on it.
+#define LIVE_CELL4(S, C, H)                                                           \
+            {                                                                         \
+                const uint32_t cv = *cp;                                              \
+                const int diag = (int)(cv & 0xFFFFu), fc = (int)(cv >> 16);           \
+                int M = __dp4a((int)(S), 1 << (8 * (C)), diag);                       \
+                M = diag ? M : 0;                                                     \
+                if (BITS == 8) M = max(M, 0);                                         \
+                H = __vimax3_s32(M, er, fc);                                          \
+                er = __viaddmax_s32_relu(M, -gapo_i, er - e_ins);                     \
+                const int fnew = __viaddmax_s32_relu(M, -gapo_d, fc - e_del);         \
+                *cp = __byte_perm((uint32_t)left, (uint32_t)fnew, 0x5410);            \
+                left = H;                                                             \
+                cp += STRIDE;                                                         \
+            }
+            for (; j + 8 <= jb; j += 8, qp += STRIDE) {
+                const uint32_t wq = *qp;
+                const uint32_t s03 = bsw_prmt(tlo, thi, wq), s47 = bsw_prmt(tlo, thi, wq >> 16);
+                int h0_, h1_, h2_, h3_, h4_, h5_, h6_, h7_;
+                LIVE_CELL4(s03, 0, h0_) LIVE_CELL4(s03, 1, h1_) LIVE_CELL4(s03, 2, h2_) LIVE_CELL4(s03, 3, h3_)
+                LIVE_CELL4(s47, 0, h4_) LIVE_CELL4(s47, 1, h5_) LIVE_CELL4(s47, 2, h6_) LIVE_CELL4(s47, 3, h7_)
+                int bm = __vimax3_s32(h0_, h1_, h2_);
+                bm = __vimax3_s32(bm, h3_, h4_);
+                bm = __vimax3_s32(bm, h5_, h6_);
+                bm = max(bm, h7_);
+                key = max(key, (bm << 16) + BSW_KEY_WORD(j + 8));
+            }
+#undef LIVE_CELL4
+#else
             for (; j + 8 <= jb; j += 8, qp += STRIDE) {
                 const uint32_t wq = *qp;
                 int k0, k1, k2, k3, k4, k5, k6, k7;
@@ -170,6 +213,7 @@ __device__ BswOut bsw_lane_fast(const bwagpu_bsw_params &p, const uint8_t *__res
                 key = __vimax3_s32(key, k4, k5);
                 key = __vimax3_s32(key, k6, k7);
             }
+#endif
             if (j < jb) {
                 uint32_t wq = *qp;
                 for (; j < jb; ++j) { int k1; LIVE_CELL(wq & 7u, j, k1) key = max(key, k1); wq >>= 4; }
@@ -184,8 +228,16 @@ __device__ BswOut bsw_lane_fast(const bwagpu_bsw_params &p, const uint8_t *__res
 #undef GENERAL_CELL
         COL(j) = bsw_pack(left, 0);
 
-        const int rowmax = key >> 16, rowarg = key & 0xFFFF;
+        const int rowmax = key >> 16;
         if (rowmax == 0) break;
+        int rowarg = (key & 0xFFFF) >> 1;
+        if (BSW_V2 && !(key & 1) && ((live && rowmax > best) || best - rowmax > p.zdrop)) {
+            // the maximum sits in a whole-word group ending at column `rowarg` and this row's outcome depends on where: the
+            // last column that attains it (H of column c is the low half of word c + 1 once the row is written)
+            int c = rowarg;
+            while ((int)(COL(c) & 0xFFFFu) != rowmax) --c;
+            rowarg = c;
+        }
         const int prev = best;
         if (live) best = max(best, rowmax);
         if (best > prev) { by = rowarg; bx = i + 1; off = max(off, abs(rowarg - (i + 1))); }

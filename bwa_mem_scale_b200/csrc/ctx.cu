@@ -42,6 +42,10 @@ extern "C" int bwagpu_create(int device, bwagpu_ctx **out)
     } while (0)
     CK(cudaSetDevice(device));
     CK(cudaDeviceGetAttribute(&ctx->sm_count, cudaDevAttrMultiProcessorCount, device));
+    if (getenv("BWAGPU_L2_FETCH")) {                           // experiments: L2 fetch granularity hint (32, 64 or 128 bytes)
+        const int v = atoi(getenv("BWAGPU_L2_FETCH"));
+        if (v == 32 || v == 64 || v == 128) cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, (size_t)v);
+    }
     CK(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
     CK(cudaEventCreate(&ctx->ev_start));
     CK(cudaEventCreate(&ctx->ev_stop));

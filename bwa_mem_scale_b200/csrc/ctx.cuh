@@ -100,3 +100,5 @@ struct bwagpu_ctx {
 
 // ensure scratch slot `slot` holds at least `bytes`; contents are NOT preserved on growth
 int bwagpu_scratch(bwagpu_ctx *ctx, int slot, int64_t bytes, void **out);
+// CP_OCC records between the reference's word order and the replica's (fmi_core.cuh FM_PAIRED); src == dst: in place (seed.cu)
+int bwagpu_fm_convert_layout(bwagpu_ctx *ctx, const void *src, void *dst, int64_t n_cp, int to_paired);

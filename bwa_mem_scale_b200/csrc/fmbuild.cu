@@ -365,6 +365,7 @@ extern "C" int bwagpu_index_build_fm(bwagpu_ctx *ctx)
         BWAGPU_CUDA(ctx, cub::DeviceScan::ExclusiveSum(cp_tmp, x, cnt4 + b4 * (n_cp + 1), pre4 + b4 * (n_cp + 1), (int)(n_cp + 1), st));
     }
     fmb_cp2_kernel<<<(unsigned)((n_cp + 255) / 256), 256, 0, st>>>(pre4, n_cp, (int64_t *)ctx->d_cp_occ);
+    { const int rc = bwagpu_fm_convert_layout(ctx, ctx->d_cp_occ, ctx->d_cp_occ, n_cp, 1); if (rc) return rc; }   // st == ctx->stream
     int64_t tot[4]; long long h_sent = -1;
     for (int b4 = 0; b4 < 4; ++b4)
         BWAGPU_CUDA(ctx, cudaMemcpyAsync(&tot[b4], pre4 + b4 * (n_cp + 1) + n_cp, 8, cudaMemcpyDeviceToHost, st));
@@ -397,9 +398,18 @@ extern "C" int bwagpu_index_get_fm(bwagpu_ctx *ctx, int64_t *reference_seq_len, 
     if (reference_seq_len) *reference_seq_len = n_rows;
     if (count) for (int i = 0; i < 5; ++i) count[i] = ctx->fm_count[i];
     if (sentinel_index) *sentinel_index = ctx->fm_sentinel;
-    if (cp_occ) BWAGPU_CUDA(ctx, cudaMemcpyAsync(cp_occ, ctx->d_cp_occ, (size_t)n_cp * 64, cudaMemcpyDeviceToHost, ctx->stream));
+    void *d_ref_order = nullptr;
+    if (cp_occ) {                                  // the replica is held in the paired word order: hand back the reference's
+        BWAGPU_CUDA(ctx, cudaMalloc(&d_ref_order, (size_t)n_cp * 64));
+        const int rc = bwagpu_fm_convert_layout(ctx, ctx->d_cp_occ, d_ref_order, n_cp, 0);
+        if (rc) { cudaFree(d_ref_order); return rc; }
+        const cudaError_t e = cudaMemcpyAsync(cp_occ, d_ref_order, (size_t)n_cp * 64, cudaMemcpyDeviceToHost, ctx->stream);
+        if (e != cudaSuccess) { cudaFree(d_ref_order); BWAGPU_CUDA(ctx, e); }
+    }
     if (sa_ms_byte) BWAGPU_CUDA(ctx, cudaMemcpyAsync(sa_ms_byte, ctx->d_sa_ms, (size_t)n_sa, cudaMemcpyDeviceToHost, ctx->stream));
     if (sa_ls_word) BWAGPU_CUDA(ctx, cudaMemcpyAsync(sa_ls_word, ctx->d_sa_ls, (size_t)n_sa * 4, cudaMemcpyDeviceToHost, ctx->stream));
-    BWAGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    const cudaError_t e_sync = cudaStreamSynchronize(ctx->stream);
+    if (d_ref_order) cudaFree(d_ref_order);
+    BWAGPU_CUDA(ctx, e_sync);
     return BWAGPU_OK;
 }

@@ -19,9 +19,25 @@
 #define BWAGPU_HD inline
 #endif
 
+// Layout of a 64-byte CP_OCC record.  The reference's is cp_count[4] then one_hot_bwt_str[4] (src/FMI_search.h:76-83).  The
+// replica in HBM is PAIRED: count and one-hot word of a base side by side, bases 0,1 in the first 32-byte sector and bases
+// 2,3 in the second.  A backward extension by base a needs the occurrences of at most two bases (fm_bext), and with this
+// order they always share a sector: one 32-byte load per record instead of the whole record — half the bytes, half the
+// registers.  The loaders (bwagpu_index_load_fm, bwagpu_index_build_fm) convert once; bwagpu_index_get_fm converts back.
+// Host builds of this header (tests/hostsim single-stepping the same logic on reference arrays) keep the reference order.
+#ifndef FM_PAIRED
+#if defined(__CUDACC__)
+#define FM_PAIRED 1
+#else
+#define FM_PAIRED 0
+#endif
+#endif
+#define FM_W_CNT(b) (FM_PAIRED ? 2 * (b) : (b))           // word index of cp_count[b] inside a record
+#define FM_W_BITS(b) (FM_PAIRED ? 2 * (b) + 1 : 4 + (b))  // word index of one_hot_bwt_str[b]
+
 // Device view of the FM-index replica held in HBM.  count[] is the loaded form (file value + 1).
 struct FmView {
-    const int64_t *cp_occ;       // 8 x 64-bit words per record: cp_count[4], one_hot_bwt_str[4]
+    const int64_t *cp_occ;       // 8 x 64-bit words per record, see FM_PAIRED
     const int8_t *sa_ms_byte;
     const uint32_t *sa_ls_word;
     int64_t count[5];
@@ -31,6 +47,12 @@ struct FmView {
     const uint32_t *fma_all;     // 32 words per 11-mer: last_avail, 10 x {k32,l32,s32}, pad
     const uint32_t *fma_last;    // 4 words per 13-mer: bp|kms<<8|lms<<16|sms<<24, kls, lls, sls
 };
+
+// SEED_PAIR2 = 1: in the backward rows of the SMEM search two entries of the row are extended per step (fm_bext2): they
+// are independent until their results are applied, which still happens in list order.
+#ifndef SEED_PAIR2
+#define SEED_PAIR2 1
+#endif
 
 #define FMA_ALL_BP 11
 #define FMA_LAST_BP 13
@@ -89,40 +111,40 @@ BWAGPU_HD void fm_prefetch_bext(const int64_t *cp_occ, int64_t k, int64_t s)
     if (b1 != b0) fm_prefetch_rec(cp_occ, b1);
 }
 
-#ifndef SEED_LD_MODE
-#define SEED_LD_MODE 1      // 0: 4x128-bit __ldg; 1: 2x256-bit cached; 2: 256-bit, L1 no_allocate for narrow intervals
-#endif
 
 // `deep`: the interval is narrow, i.e. this record is a random touch with no reuse inside the SM
 BWAGPU_HD void fm_load_rec(const FmView &f, int64_t block, FmRec &r, bool deep = false)
 {
 #if defined(__CUDA_ARCH__)
     const int64_t *p = f.cp_occ + block * 8;
-#if SEED_LD_MODE == 0
-    const uint4 *p4 = reinterpret_cast<const uint4 *>(p);
-    uint4 a = __ldg(p4), b = __ldg(p4 + 1), c = __ldg(p4 + 2), d = __ldg(p4 + 3);
-    r.cnt[0] = (int64_t)(((uint64_t)a.y << 32) | a.x); r.cnt[1] = (int64_t)(((uint64_t)a.w << 32) | a.z);
-    r.cnt[2] = (int64_t)(((uint64_t)b.y << 32) | b.x); r.cnt[3] = (int64_t)(((uint64_t)b.w << 32) | b.z);
-    r.bits[0] = ((uint64_t)c.y << 32) | c.x; r.bits[1] = ((uint64_t)c.w << 32) | c.z;
-    r.bits[2] = ((uint64_t)d.y << 32) | d.x; r.bits[3] = ((uint64_t)d.w << 32) | d.z;
-#else
+    (void)deep;
     // one 64-byte record = two 256-bit loads (sm_100: LDG.256), one per 32-byte sector
-    if (SEED_LD_MODE == 2 && deep) {
-        asm("ld.global.nc.L1::no_allocate.v4.u64 {%0,%1,%2,%3}, [%4];"
-            : "=l"(r.cnt[0]), "=l"(r.cnt[1]), "=l"(r.cnt[2]), "=l"(r.cnt[3]) : "l"(p));
-        asm("ld.global.nc.L1::no_allocate.v4.u64 {%0,%1,%2,%3}, [%4];"
-            : "=l"(r.bits[0]), "=l"(r.bits[1]), "=l"(r.bits[2]), "=l"(r.bits[3]) : "l"(p + 4));
-    } else {
-        asm("ld.global.nc.v4.u64 {%0,%1,%2,%3}, [%4];"
-            : "=l"(r.cnt[0]), "=l"(r.cnt[1]), "=l"(r.cnt[2]), "=l"(r.cnt[3]) : "l"(p));
-        asm("ld.global.nc.v4.u64 {%0,%1,%2,%3}, [%4];"
-            : "=l"(r.bits[0]), "=l"(r.bits[1]), "=l"(r.bits[2]), "=l"(r.bits[3]) : "l"(p + 4));
-    }
+    uint64_t w0, w1, w2, w3, w4, w5, w6, w7;
+    asm("ld.global.nc.v4.u64 {%0,%1,%2,%3}, [%4];" : "=l"(w0), "=l"(w1), "=l"(w2), "=l"(w3) : "l"(p));
+    asm("ld.global.nc.v4.u64 {%0,%1,%2,%3}, [%4];" : "=l"(w4), "=l"(w5), "=l"(w6), "=l"(w7) : "l"(p + 4));
+#if FM_PAIRED
+    r.cnt[0] = (int64_t)w0; r.bits[0] = w1; r.cnt[1] = (int64_t)w2; r.bits[1] = w3;
+    r.cnt[2] = (int64_t)w4; r.bits[2] = w5; r.cnt[3] = (int64_t)w6; r.bits[3] = w7;
+#else
+    r.cnt[0] = (int64_t)w0; r.cnt[1] = (int64_t)w1; r.cnt[2] = (int64_t)w2; r.cnt[3] = (int64_t)w3;
+    r.bits[0] = w4; r.bits[1] = w5; r.bits[2] = w6; r.bits[3] = w7;
 #endif
 #else
     (void)deep;
     const int64_t *p = f.cp_occ + block * 8;
-    for (int i = 0; i < 4; ++i) { r.cnt[i] = p[i]; r.bits[i] = (uint64_t)p[4 + i]; }
+    for (int i = 0; i < 4; ++i) { r.cnt[i] = p[FM_W_CNT(i)]; r.bits[i] = (uint64_t)p[FM_W_BITS(i)]; }
+#endif
+}
+
+// Half a record: counts and one-hot words of bases 2h and 2h + 1 (one 32-byte sector of the paired layout).
+struct FmHalf { int64_t cnt[2]; uint64_t bits[2]; };
+BWAGPU_HD void fm_load_half(const FmView &f, int64_t block, int h, FmHalf &r)
+{
+    const int64_t *p = f.cp_occ + block * 8;
+#if defined(__CUDA_ARCH__) && FM_PAIRED
+    asm("ld.global.nc.v4.u64 {%0,%1,%2,%3}, [%4];" : "=l"(r.cnt[0]), "=l"(r.bits[0]), "=l"(r.cnt[1]), "=l"(r.bits[1]) : "l"(p + 4 * h));
+#else
+    for (int i = 0; i < 2; ++i) { r.cnt[i] = p[FM_W_CNT(2 * h + i)]; r.bits[i] = (uint64_t)p[FM_W_BITS(2 * h + i)]; }
 #endif
 }
 
@@ -149,24 +171,61 @@ BWAGPU_HD int64_t fm_count(const FmView &f, int a)
 // backward extension of (k,l,s) by base a
 BWAGPU_HD Biv fm_bext(const FmView &f, const Biv &v, int a)
 {
+    // The reference computes k[b], s[b] for all four bases and l[b] = l + sentinel + sum of s[c] over c > b, then keeps
+    // base a's.  The rows of [sp, ep) split into the four bases and the sentinel row, s = s[0] + s[1] + s[2] + s[3] +
+    // sentinel, so l[a] needs the sizes on ONE side of a only:
+    //     a = 0, 1:  l[a] = l + s - (s[0] + .. + s[a])        a = 2, 3:  l[a] = l + sentinel + (s[a+1] + .. + s[3])
+    // i.e. bases {0,1} or bases {2,3}: one half of each record.
     const int64_t sp = v.k, ep = v.k + v.s;
-    FmRec rs, re;
-    const bool deep = v.s < (1 << 14);
-    fm_load_rec(f, sp >> 6, rs, deep);
-    if ((ep >> 6) == (sp >> 6)) re = rs; else fm_load_rec(f, ep >> 6, re, deep);
+    const int h = a >> 1, lo = a & 1;
+    FmHalf rs, re;
+    fm_load_half(f, sp >> 6, h, rs);
+    if ((ep >> 6) == (sp >> 6)) re = rs; else fm_load_half(f, ep >> 6, h, re);
     const uint64_t ms = fm_prefix_mask((int)(sp & 63)), me = fm_prefix_mask((int)(ep & 63));
-    int64_t osp[4], sz[4];
-#pragma unroll
-    for (int b = 0; b < 4; ++b) {
-        osp[b] = rs.cnt[b] + fm_popc(rs.bits[b] & ms);
-        sz[b] = re.cnt[b] + fm_popc(re.bits[b] & me) - osp[b];
-    }
+    const int64_t o0 = rs.cnt[0] + fm_popc(rs.bits[0] & ms), o1 = rs.cnt[1] + fm_popc(rs.bits[1] & ms);
+    const int64_t z0 = re.cnt[0] + fm_popc(re.bits[0] & me) - o0, z1 = re.cnt[1] + fm_popc(re.bits[1] & me) - o1;
     const int64_t sent = (v.k <= f.sentinel_index && ep > f.sentinel_index) ? 1 : 0;
-    int64_t l3 = v.l + sent, l2 = l3 + sz[3], l1 = l2 + sz[2], l0 = l1 + sz[1];
     Biv r;
-    r.k = fm_count(f, a) + (a == 0 ? osp[0] : a == 1 ? osp[1] : a == 2 ? osp[2] : osp[3]);
-    r.s = a == 0 ? sz[0] : a == 1 ? sz[1] : a == 2 ? sz[2] : sz[3];
-    r.l = a == 0 ? l0 : a == 1 ? l1 : a == 2 ? l2 : l3;
+    r.k = fm_count(f, a) + (lo ? o1 : o0);
+    r.s = lo ? z1 : z0;
+    r.l = h == 0 ? v.l + v.s - z0 - (lo ? z1 : 0) : v.l + sent + (lo ? 0 : z1);
+    return r;
+}
+
+// Two backward extensions by the same base a, loads of both issued before either is consumed (the second only when
+// `two`): the entries of one backward row of the SMEM search are independent of each other (SeedMachine, SEED_PAIR2).
+BWAGPU_HD Biv fm_bext2(const FmView &f, const Biv &v, const Biv &v2, bool two, int a, Biv &r2)
+{
+    const int64_t sp = v.k, ep = v.k + v.s, sp2 = v2.k, ep2 = v2.k + v2.s;
+    const int h = a >> 1, lo = a & 1;
+    FmHalf rs, re, qs, qe;
+    fm_load_half(f, sp >> 6, h, rs);
+    if ((ep >> 6) == (sp >> 6)) re = rs; else fm_load_half(f, ep >> 6, h, re);
+    if (two) {
+        fm_load_half(f, sp2 >> 6, h, qs);
+        if ((ep2 >> 6) == (sp2 >> 6)) qe = qs; else fm_load_half(f, ep2 >> 6, h, qe);
+    } else {
+        qs.cnt[0] = qs.cnt[1] = 0; qs.bits[0] = qs.bits[1] = 0; qe = qs;
+    }
+    Biv r;
+    {
+        const uint64_t ms = fm_prefix_mask((int)(sp & 63)), me = fm_prefix_mask((int)(ep & 63));
+        const int64_t o0 = rs.cnt[0] + fm_popc(rs.bits[0] & ms), o1 = rs.cnt[1] + fm_popc(rs.bits[1] & ms);
+        const int64_t z0 = re.cnt[0] + fm_popc(re.bits[0] & me) - o0, z1 = re.cnt[1] + fm_popc(re.bits[1] & me) - o1;
+        const int64_t sent = (v.k <= f.sentinel_index && ep > f.sentinel_index) ? 1 : 0;
+        r.k = fm_count(f, a) + (lo ? o1 : o0);
+        r.s = lo ? z1 : z0;
+        r.l = h == 0 ? v.l + v.s - z0 - (lo ? z1 : 0) : v.l + sent + (lo ? 0 : z1);
+    }
+    {
+        const uint64_t ms = fm_prefix_mask((int)(sp2 & 63)), me = fm_prefix_mask((int)(ep2 & 63));
+        const int64_t o0 = qs.cnt[0] + fm_popc(qs.bits[0] & ms), o1 = qs.cnt[1] + fm_popc(qs.bits[1] & ms);
+        const int64_t z0 = qe.cnt[0] + fm_popc(qe.bits[0] & me) - o0, z1 = qe.cnt[1] + fm_popc(qe.bits[1] & me) - o1;
+        const int64_t sent = (v2.k <= f.sentinel_index && ep2 > f.sentinel_index) ? 1 : 0;
+        r2.k = fm_count(f, a) + (lo ? o1 : o0);
+        r2.s = lo ? z1 : z0;
+        r2.l = h == 0 ? v2.l + v2.s - z0 - (lo ? z1 : 0) : v2.l + sent + (lo ? 0 : z1);
+    }
     return r;
 }
 
@@ -244,6 +303,10 @@ struct SeedMachine {
     int32_t last_s;
     Biv cur; int cur_n;
     Biv req; int req_a;          // pending extension request
+#if SEED_PAIR2
+    Biv req2; int cur_n2;        // backward rows: the next entry of the row rides along (has2)
+#endif
+    bool has2;
     int64_t n_ext;
     const int64_t *pf_cp;        // CP_OCC base for prefetches (NULL: none)
 
@@ -254,7 +317,20 @@ struct SeedMachine {
         round = 1; x = 0; min_intv = 1; state = len > 0 ? ST_PIVOT : ST_DONE; n_ext = 0;
         np = base = p = nc = decided = r1_count = r2_idx = 0; last_s = -1; j = next_x = 0;
         cur.k = cur.l = cur.s = 0; cur_n = 0; req = cur; req_a = 0;
-        pf_cp = nullptr;
+        pf_cp = nullptr; has2 = false;
+    }
+
+    // backward row: entry p becomes the request; with SEED_PAIR2 entry p + 1 (if the row has one) rides along
+    BWAGPU_HD void request_items()
+    {
+        int n_;
+        prev.get(base + p, req, n_);
+        cur_n = n_;
+        req_a = q[j];
+#if SEED_PAIR2
+        has2 = p + 1 < np;
+        if (has2) { prev.get(base + p + 1, req2, n_); cur_n2 = n_; }
+#endif
     }
 
     BWAGPU_HD void emit(int m, int n, const Biv &v)
@@ -389,13 +465,7 @@ struct SeedMachine {
                 break;
             }
             case ST_BITEM: {
-                if (p < np) {
-                    int n_;
-                    prev.get(base + p, req, n_);
-                    cur_n = n_;                  // span end of the entry being extended
-                    req_a = q[j];
-                    return true;
-                }
+                if (p < np) { request_items(); return true; }      // cur_n = span end of the entry being extended
                 np = nc;
                 if (np == 0) { state = ST_NEXT; break; }
                 --j;
@@ -462,6 +532,33 @@ struct SeedMachine {
         }
     }
 
+    // backward row: r extends entry `src` (span end src_n) to the left by q[j]; entries of this row start at m = j + 1
+    BWAGPU_HD void consume_item(const Biv &r, const Biv &src, int src_n, const SeedOpt &o)
+    {
+        if (r.s < min_intv) {
+            if (!decided && src_n - (j + 1) + 1 >= o.min_seed_len) {
+                emit(j + 1, src_n, src);
+                decided = 1;
+            }
+        } else if (r.s != (int64_t)last_s) {
+            last_s = (int32_t)r.s;
+            prev.put(base + nc, r, src_n);
+            if (pf_cp && j > 0) fm_prefetch_bext(pf_cp, r.k, r.s);           // extended again in the next row
+            ++nc;
+            decided = 1;
+        }
+        ++p;
+    }
+
+#if SEED_PAIR2
+    // the second result of a paired request (has2): entry p of the same row, after consume() handled the first
+    BWAGPU_HD void consume_second(const Biv &r2, const SeedOpt &o)
+    {
+        ++n_ext;
+        consume_item(r2, req2, cur_n2, o);
+    }
+#endif
+
     // Consumes the result of the requested extension.
     BWAGPU_HD void consume(const Biv &r, const SeedOpt &o)
     {
@@ -481,20 +578,7 @@ struct SeedMachine {
             }
             cur = nw; cur_n = j; ++j;
         } else if (state == ST_BITEM) {
-            // r extends entry p to the left by q[j]; entries of this row start at m = j + 1
-            if (r.s < min_intv) {
-                if (!decided && cur_n - (j + 1) + 1 >= o.min_seed_len) {
-                    emit(j + 1, cur_n, req);
-                    decided = 1;
-                }
-            } else if (r.s != (int64_t)last_s) {
-                last_s = (int32_t)r.s;
-                prev.put(base + nc, r, cur_n);
-                if (pf_cp && j > 0) fm_prefetch_bext(pf_cp, r.k, r.s);           // extended again in the next row
-                ++nc;
-                decided = 1;
-            }
-            ++p;
+            consume_item(r, req, cur_n, o);
         } else {                                 // ST_LFWD
             cur.k = r.l; cur.l = r.k; cur.s = r.s; cur_n = j;
             if (cur.s < o.max_mem_intv && cur_n - x + 1 >= o.min_seed_len + 1) {
@@ -511,9 +595,14 @@ struct SeedMachine {
     // code: forward step -> forward step, backward item -> next item, backward row -> next row.
     // Returns true when the next request is ready; false when the rarer bookkeeping of advance()
     // is needed (phase changes, pivot ends, round changes, read end).
-    BWAGPU_HD bool step_fast(const Biv &r, const SeedOpt &o)
+    BWAGPU_HD bool step_fast(const Biv &r, const SeedOpt &o, const Biv *r2 = nullptr)
     {
         consume(r, o);
+#if SEED_PAIR2
+        if (has2) { has2 = false; consume_second(*r2, o); }
+#else
+        (void)r2;
+#endif
         if (state == ST_FWD || state == ST_LFWD) {
             if (j < len) {
                 const int a = q[j];
@@ -529,10 +618,7 @@ struct SeedMachine {
                 if (j < 0 || q[j] > 3) { state = ST_BEND; return false; }
                 nc = 0; decided = 0; last_s = -1; p = 0;
             }
-            int n_;
-            prev.get(base + p, req, n_);
-            cur_n = n_;
-            req_a = q[j];
+            request_items();
             return true;
         }
         return false;

@@ -85,7 +85,16 @@ __device__ __forceinline__ void seed_stage_read(uint32_t *w, const uint8_t *__re
     }
 }
 
-struct SeedStats { unsigned long long n_ext, n_rec, n_lf, max_cnt; unsigned int n_ovf, pad_; };
+struct SeedStats { unsigned long long n_ext, n_rec, n_lf, max_cnt; unsigned int n_ovf, next; };
+
+// SEED_DYN = 1: a lane that needs a new read takes the next unclaimed one from a counter in global memory instead of
+// striding through the batch.  Reads differ widely in work (a repeat read costs many times a unique one, an EMF-answered
+// read nothing), so with a fixed stride the lanes of a warp run out of reads at very different times and the extension
+// site sees half-empty warps (15.5 of 32 lanes at config-3 scale, profiles/r02_ncu_seed_collect_hot_lines.txt); with the
+// counter every lane stays busy until the batch is exhausted.  Which lane runs which read does not change any result.
+#ifndef SEED_DYN
+#define SEED_DYN 1
+#endif
 
 // ---- warp-cooperative backwardExt ------------------------------------------------------------------------------
 // SEED_COOP = 1: the reads stay one per thread (so every issued instruction of the state machine still serves all the
@@ -136,8 +145,8 @@ __device__ __forceinline__ Biv seed_bext_coop(const FmView &f, unsigned m_ready,
             c0[i] = c1[i] = 0; o0[i] = o1[i] = 0;
             if (have) {
                 const int64_t *r0 = f.cp_occ + (k >> 6) * 8, *r1 = f.cp_occ + (ep >> 6) * 8;
-                c0[i] = __ldg(r0 + b); c1[i] = __ldg(r1 + b);
-                o0[i] = (uint64_t)__ldg(r0 + 4 + b); o1[i] = (uint64_t)__ldg(r1 + 4 + b);
+                c0[i] = __ldg(r0 + FM_W_CNT(b)); c1[i] = __ldg(r1 + FM_W_CNT(b));
+                o0[i] = (uint64_t)__ldg(r0 + FM_W_BITS(b)); o1[i] = (uint64_t)__ldg(r1 + FM_W_BITS(b));
             }
             kx[i] = (int)(k & 63) | ((int)(ep & 63) << 8) | ((k <= f.sentinel_index && ep > f.sentinel_index) ? 1 << 16 : 0);
         }
@@ -187,7 +196,7 @@ seed_collect_kernel(FmView f, SeedOpt o, const uint8_t *__restrict__ reads,
     uint32_t *rd_sm = seed_sm + SEED_PREV_K * 4 * SEED_TPB + threadIdx.x;
     using Read = typename std::conditional<STAGED, SmemRead, const uint8_t *>::type;
     SeedMachine<DevPrev, Read> m;
-    int64_t next = t0;
+    [[maybe_unused]] int64_t next = t0;
     bool active = false, ready = false, finished = false;
     unsigned long long n_ext = 0, n_rec = 0;
     unsigned int max_cnt = 0;
@@ -203,8 +212,15 @@ seed_collect_kernel(FmView f, SeedOpt o, const uint8_t *__restrict__ reads,
                 for (;;) {
                     if (!active) {
                         bool got = false;
-                        while (next < nseq) {
+                        for (;;) {
+#if SEED_DYN
+                            const int64_t cand = (int64_t)atomicAdd(&stats->next, 1u);
+                            if (cand >= nseq) break;
+                            const int it = (int)cand;
+#else
+                            if (next >= nseq) break;
                             const int it = (int)next; next += T;
+#endif
                             const int i = list ? list[it] : it;
                             if (list) slab_of[i] = it;
                             if (skip && skip[i]) { cnt[i] = 0; continue; }
@@ -243,8 +259,15 @@ seed_collect_kernel(FmView f, SeedOpt o, const uint8_t *__restrict__ reads,
         if (ready) {
             n_rec += ((m.req.k >> 6) == ((m.req.k + m.req.s) >> 6)) ? 1 : 2;
             ++n_ext;
+#if SEED_PAIR2
+            if (m.has2) { n_rec += ((m.req2.k >> 6) == ((m.req2.k + m.req2.s) >> 6)) ? 1 : 2; ++n_ext; }
+            Biv r2;
+            const Biv r = fm_bext2(f, m.req, m.req2, m.has2, m.req_a, r2);
+            ready = m.step_fast(r, o, &r2);
+#else
             const Biv r = fm_bext(f, m.req, m.req_a);
             ready = m.step_fast(r, o);
+#endif
         }
 #endif
     }
@@ -419,6 +442,35 @@ extern "C" int bwagpu_index_use_fma(bwagpu_ctx *ctx, int on)
     return BWAGPU_OK;
 }
 
+// CP_OCC records between the reference's word order and the paired order of the replica (fmi_core.cuh, FM_PAIRED);
+// src == dst converts in place (every thread owns one record).
+__global__ void fm_layout_kernel(const int64_t *src, int64_t *dst, int64_t n_cp, int to_paired)
+{
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_cp) return;
+    int64_t w[8], o[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) w[j] = src[i * 8 + j];
+#pragma unroll
+    for (int b = 0; b < 4; ++b) {
+        if (to_paired) { o[2 * b] = w[b]; o[2 * b + 1] = w[4 + b]; }
+        else { o[b] = w[2 * b]; o[4 + b] = w[2 * b + 1]; }
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) dst[i * 8 + j] = o[j];
+}
+
+int bwagpu_fm_convert_layout(bwagpu_ctx *ctx, const void *src, void *dst, int64_t n_cp, int to_paired)
+{
+#if FM_PAIRED
+    fm_layout_kernel<<<(unsigned)((n_cp + 255) / 256), 256, 0, ctx->stream>>>((const int64_t *)src, (int64_t *)dst, n_cp, to_paired);
+    BWAGPU_CUDA(ctx, cudaGetLastError());
+#else
+    if (src != dst) BWAGPU_CUDA(ctx, cudaMemcpyAsync(dst, src, (size_t)n_cp * 64, cudaMemcpyDeviceToDevice, ctx->stream));
+#endif
+    return BWAGPU_OK;
+}
+
 extern "C" int bwagpu_index_load_fm(bwagpu_ctx *ctx, const bwagpu_fm_index_desc *d)
 {
     if (!ctx) return BWAGPU_ERR_ARG;
@@ -441,6 +493,7 @@ extern "C" int bwagpu_index_load_fm(bwagpu_ctx *ctx, const bwagpu_fm_index_desc 
     BWAGPU_CUDA(ctx, cudaMemcpyAsync(ctx->d_cp_occ, d->cp_occ, (size_t)n_cp * 64, cudaMemcpyHostToDevice, ctx->stream));
     BWAGPU_CUDA(ctx, cudaMemcpyAsync(ctx->d_sa_ms, d->sa_ms_byte, (size_t)n_sa, cudaMemcpyHostToDevice, ctx->stream));
     BWAGPU_CUDA(ctx, cudaMemcpyAsync(ctx->d_sa_ls, d->sa_ls_word, (size_t)n_sa * 4, cudaMemcpyHostToDevice, ctx->stream));
+    { const int rc = bwagpu_fm_convert_layout(ctx, ctx->d_cp_occ, ctx->d_cp_occ, n_cp, 1); if (rc) return rc; }
     BWAGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     for (int i = 0; i < 5; ++i) ctx->fm_count[i] = d->count[i];
     ctx->fm_sentinel = d->sentinel_index;
@@ -505,6 +558,10 @@ static int seed_collect_dev(bwagpu_ctx *ctx, const bwagpu_seed_opt *opt, const u
     if (staged) BWAGPU_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, seed_collect_kernel<true>, SEED_TPB, smem));
     else BWAGPU_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, seed_collect_kernel<false>, SEED_TPB, smem));
     if (per_sm < 1) per_sm = 1;
+    if (getenv("BWAGPU_SEED_BLOCKS_PER_SM")) {                 // experiments: fewer resident blocks than fit
+        const int v = atoi(getenv("BWAGPU_SEED_BLOCKS_PER_SM"));
+        if (v >= 1 && v < per_sm) per_sm = v;
+    }
     int blocks = ctx->sm_count * per_sm;
     const int need = (nseq + SEED_TPB - 1) / SEED_TPB;
     if (blocks > need) blocks = need;
@@ -528,6 +585,7 @@ static int seed_collect_dev(bwagpu_ctx *ctx, const bwagpu_seed_opt *opt, const u
     BWAGPU_CUDA(ctx, cudaMemsetAsync(d_cnt + nseq, 0, 4, ctx->stream));
     BWAGPU_CUDA(ctx, cudaMemsetAsync(d_slab_of, 0xFF, (size_t)nseq * 4, ctx->stream));
     auto launch = [&](int n_items, bwagpu_smem *slab, int slab_cap, const int32_t *list) {
+        cudaMemsetAsync(&d_stats->next, 0, 4, ctx->stream);      // the read counter of SEED_DYN
         int b = blocks;
         const int nd = (n_items + SEED_TPB - 1) / SEED_TPB;
         if (b > nd) b = nd;

@@ -40,8 +40,14 @@ extern "C" int64_t hostsim_collect_smem(const bwagpu_fm_index_desc *d, const bwa
         bool ready = false;
         for (;;) {
             if (!ready && !m.advance(f, so)) break;
+#if SEED_PAIR2
+            Biv r2;
+            Biv r = fm_bext2(f, m.req, m.req2, m.has2, m.req_a, r2);
+            ready = m.step_fast(r, so, &r2);
+#else
             Biv r = fm_bext(f, m.req, m.req_a);
             ready = m.step_fast(r, so);
+#endif
         }
         if (m.n_out > per_read_cap) return -(int64_t)m.n_out;     // caller retries with more room
         if (n_ext) *n_ext += m.n_ext;
