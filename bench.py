@@ -963,7 +963,7 @@ def main():
                     help="mem = BASELINE config 3 shape (default); mem2 = config 2 shape / --ert 1 (round-1 workload)")
     ap.add_argument("--ref-mbp", type=float, default=None, help="reference size in Mbp (mem: 3100, mem2: 100)")
     ap.add_argument("--reads", type=int, default=None, help="reads per GPU (mem: 10 M, mem2: 1 M)")
-    ap.add_argument("--chunk", type=int, default=1_000_000, help="mem: reads per bwagpu_mem_process_chunk call")
+    ap.add_argument("--chunk", type=int, default=2_500_000, help="mem: reads per bwagpu_mem_process_chunk call")
     ap.add_argument("--cpu-reads-per-thread", type=int, default=150_000, help="mem: size of the CPU arm's bounded sample")
     ap.add_argument("--pairs", type=int, default=1_000_000)
     ap.add_argument("--harvested", type=int, default=0, help="ksw workload: use the jobs recorded from a real PE run of the reference")

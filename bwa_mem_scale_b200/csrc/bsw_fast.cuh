@@ -109,7 +109,7 @@ __device__ BswOut bsw_lane_fast(const bwagpu_bsw_params &p, const uint8_t *__res
         // general cell: exactly the body of bsw_lane_pair
 #define GENERAL_CELL(j)                                                               \
         {                                                                             \
-            const int q = bsw_sym(query[j], wrap);                                    \
+            const int q = bsw_sym((uint8_t)((qsm[((j) >> 3) * STRIDE] >> (4 * ((j) & 7))) & 7u), wrap); \
             const uint32_t cv = COL(j);                                               \
             const int diag = bsw_hd(cv), fc = bsw_fc(cv);                             \
             int s = t == q ? sc_match : sc_mis;                                       \
@@ -141,10 +141,11 @@ __device__ BswOut bsw_lane_fast(const bwagpu_bsw_params &p, const uint8_t *__res
 #define LIVE_CELL(NIB, J, KEY)                                                        \
             {                                                                         \
                 const uint32_t cv = *cp;                                              \
-                const uint32_t sel = (NIB) * 0x1111u + 0x8880u;   /* byte = query code, sign-extended */ \
-                const int s = (int)bsw_prmt(tlo, thi, sel);                           \
                 const int diag = (int)(cv & 0xFFFFu), fc = (int)(cv >> 16);           \
-                int M = diag + s;                                                     \
+                /* NIB: a word whose low nibble is the query code (bit 3 of every nibble clear): byte 0 of the permute */ \
+                /* is this cell's score, added to the diagonal as a signed byte */   \
+                int M = BSW_V2 ? __dp4a((int)bsw_prmt(tlo, thi, (NIB)), 1, diag)      \
+                               : diag + (int)bsw_prmt(tlo, thi, ((NIB) & 7u) * 0x1111u + 0x8880u); \
                 M = diag ? M : 0;                                                     \
                 if (BITS == 8) M = max(M, 0);                                         \
                 const int h = __vimax3_s32(M, er, fc);                                \
@@ -155,20 +156,14 @@ __device__ BswOut bsw_lane_fast(const bwagpu_bsw_params &p, const uint8_t *__res
                 left = h;                                                             \
                 cp += STRIDE;                                                         \
             }
-            // columns up to the next multiple of 8 (the query is staged 8 codes per word)
-            const int jpro = min(jb, (j + 7) & ~7);
-            if (j < jpro) {
-                uint32_t wq = qsm[(j >> 3) * STRIDE] >> (4 * (j & 7));
-                for (; j < jpro; ++j) { int k1; LIVE_CELL(wq & 7u, j, k1) key = max(key, k1); wq >>= 4; }
-            }
-            // whole words: 8 cells straight-line, shifts known at compile time
-            const uint32_t *qp = qsm + (j >> 3) * STRIDE;
 #if BSW_V2
-            // one word of the staged query = 8 cells.  The scores of four cells come from ONE permute: the staged codes are
-            // 4-bit with bit 3 clear, so the word itself (its low 16 bits) is a selector that picks the four score bytes; a
-            // signed byte dot product with a one-hot word then adds byte c to the diagonal (M = diag + s in one operation).
-            // The row's arg-max is kept per WORD here — key = (max h of the 8 cells) << 16 | code of "somewhere up to column
-            // j + 8" — and the exact column is looked up after the row, only when the row's outcome depends on it.
+            // The staged query holds 8 codes per word.  Four cells share ONE permute for their scores: the codes are 4-bit
+            // with bit 3 clear, so 16 bits of the word are themselves a selector that picks the four score bytes, and a
+            // signed byte dot product with a one-hot word adds byte c to the diagonal (M = diag + s in one operation).
+            // The live range runs as: single cells up to a multiple of 4, a half word up to a multiple of 8, whole
+            // words, a trailing half word, single cells.  Inside half and whole words the row's arg-max is kept per GROUP —
+            // key = (max h of the group) << 16 | code of "somewhere up to the group's last column" — and the exact column
+            // is looked up after the row, only when the row's outcome depends on it.
 #define LIVE_CELL4(S, C, H)                                                           \
             {                                                                         \
                 const uint32_t cv = *cp;                                              \
@@ -183,6 +178,22 @@ __device__ BswOut bsw_lane_fast(const bwagpu_bsw_params &p, const uint8_t *__res
                 left = H;                                                             \
                 cp += STRIDE;                                                         \
             }
+#define LIVE_HALF(WQ16)                                                               \
+            {                                                                         \
+                const uint32_t s03 = bsw_prmt(tlo, thi, (WQ16));                      \
+                int h0_, h1_, h2_, h3_;                                               \
+                LIVE_CELL4(s03, 0, h0_) LIVE_CELL4(s03, 1, h1_) LIVE_CELL4(s03, 2, h2_) LIVE_CELL4(s03, 3, h3_) \
+                const int bm = max(__vimax3_s32(h0_, h1_, h2_), h3_);                 \
+                key = max(key, (bm << 16) + BSW_KEY_WORD(j + 4));                     \
+                j += 4;                                                               \
+            }
+            const int jpro = min(jb, (j + 3) & ~3);
+            if (j < jpro) {
+                uint32_t wq = qsm[(j >> 3) * STRIDE] >> (4 * (j & 7));
+                for (; j < jpro; ++j) { int k1; LIVE_CELL(wq, j, k1) key = max(key, k1); wq >>= 4; }
+            }
+            if ((j & 4) && j + 4 <= jb) LIVE_HALF(qsm[(j >> 3) * STRIDE] >> 16)
+            const uint32_t *qp = qsm + (j >> 3) * STRIDE;
             for (; j + 8 <= jb; j += 8, qp += STRIDE) {
                 const uint32_t wq = *qp;
                 const uint32_t s03 = bsw_prmt(tlo, thi, wq), s47 = bsw_prmt(tlo, thi, wq >> 16);
@@ -195,8 +206,22 @@ __device__ BswOut bsw_lane_fast(const bwagpu_bsw_params &p, const uint8_t *__res
                 bm = max(bm, h7_);
                 key = max(key, (bm << 16) + BSW_KEY_WORD(j + 8));
             }
+            if (j < jb) {
+                uint32_t wq = qsm[(j >> 3) * STRIDE] >> (4 * (j & 7));
+                if (j + 4 <= jb) { LIVE_HALF(wq) wq >>= 16; }
+                for (; j < jb; ++j) { int k1; LIVE_CELL(wq, j, k1) key = max(key, k1); wq >>= 4; }
+            }
+#undef LIVE_HALF
 #undef LIVE_CELL4
 #else
+            // columns up to the next multiple of 8 (the query is staged 8 codes per word)
+            const int jpro = min(jb, (j + 7) & ~7);
+            if (j < jpro) {
+                uint32_t wq = qsm[(j >> 3) * STRIDE] >> (4 * (j & 7));
+                for (; j < jpro; ++j) { int k1; LIVE_CELL(wq, j, k1) key = max(key, k1); wq >>= 4; }
+            }
+            // whole words: 8 cells straight-line, shifts known at compile time
+            const uint32_t *qp = qsm + (j >> 3) * STRIDE;
             for (; j + 8 <= jb; j += 8, qp += STRIDE) {
                 const uint32_t wq = *qp;
                 int k0, k1, k2, k3, k4, k5, k6, k7;
@@ -213,11 +238,11 @@ __device__ BswOut bsw_lane_fast(const bwagpu_bsw_params &p, const uint8_t *__res
                 key = __vimax3_s32(key, k4, k5);
                 key = __vimax3_s32(key, k6, k7);
             }
-#endif
             if (j < jb) {
                 uint32_t wq = *qp;
-                for (; j < jb; ++j) { int k1; LIVE_CELL(wq & 7u, j, k1) key = max(key, k1); wq >>= 4; }
+                for (; j < jb; ++j) { int k1; LIVE_CELL(wq, j, k1) key = max(key, k1); wq >>= 4; }
             }
+#endif
 #undef LIVE_CELL
             if (jb == len2 && live) {             // the last query column was in the live range
                 if (!(gsc > left)) gi = i + 1;
@@ -246,22 +271,16 @@ __device__ BswOut bsw_lane_fast(const bwagpu_bsw_params &p, const uint8_t *__res
             const int gap = di > dj ? di - dj : dj - di;
             if ((best - rowmax) - gap > p.zdrop) live = false;
         }
-        for (int l = lo; l < hi; ++l) { if (COL(l) == 0) nlo = l; else break; }
-        {
-            int l;
-            for (l = hi; l >= lo; --l) if (COL(l) != 0) break;
-            nhi = min(l + 2, ncol);
-        }
-        if (live) {
-            int l;
-            for (l = lo; l < hi && COL(l) == 0; ++l) {}
-            if (l > lo) head = l;
-            int idx = tail;
-            for (l = hi; l >= lo && COL(l) == 0; --l) idx = l - 1;
-            tail = min(idx + 2, len2);
-        } else {
-            break;
-        }
+        // the row's leading and trailing runs of zero words bound the next row (nlo, nhi) and, while the lane is live,
+        // its head and tail: one scan from each end serves both
+        int lead = lo, trail = hi;
+        while (lead < hi && COL(lead) == 0) ++lead;          // first non-zero word of [lo, hi), or hi
+        while (trail >= lo && COL(trail) == 0) --trail;      // last non-zero word of [lo, hi], or lo - 1
+        if (lead > lo) nlo = lead - 1;
+        nhi = min(trail + 2, ncol);
+        if (!live) break;
+        if (lead > lo) head = lead;
+        tail = min((trail < hi ? trail : tail) + 2, len2);
     }
 #undef COL
     BswOut o;

@@ -18,7 +18,7 @@
 
 #define SEED_TPB 128
 #ifndef SLOW_BATCH
-#define SLOW_BATCH 4
+#define SLOW_BATCH 8
 #endif
 
 // prev list of one thread.  The first SEED_PREV_K entries pushed for a pivot live in shared memory
@@ -173,7 +173,7 @@ __device__ __forceinline__ Biv seed_bext_coop(const FmView &f, unsigned m_ready,
 }
 
 #ifndef SEED_MIN_BLOCKS
-#define SEED_MIN_BLOCKS 1
+#define SEED_MIN_BLOCKS 5      // 5 blocks of 128 per SM = 96 registers; without the bound the paired step takes 98 and drops to 4
 #endif
 // STAGED: every read of the batch is at most SEED_SMEM_BASES long and is staged in shared memory.
 template <bool STAGED>
