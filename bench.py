@@ -973,7 +973,7 @@ def main():
     ap.add_argument("--ert", type=int, default=0, help="mem workload: ERT seeding on the small reference-built index in tests/golden/")
     ap.add_argument("--emf", type=int, default=None, help="exact-match filter in front (mem: default 1, table built in HBM; mem2: default 0, host-built)")
     ap.add_argument("--exact-frac", type=float, default=None, help="fraction of error-free reads (default: what 1%% substitutions give)")
-    ap.add_argument("--contexts", type=int, default=1, help="mem workload: contexts (streams) per GPU")
+    ap.add_argument("--contexts", type=int, default=None, help="worker contexts (host thread + stream + scratch each) per GPU over one index replica (mem: default 2; mem2: 1)")
     ap.add_argument("--no-cpu", action="store_true")
     args = ap.parse_args()
     # stdout carries exactly one JSON line: everything else that writes to fd 1 (NCCL's version banner, the reference's
@@ -984,6 +984,8 @@ def main():
     rank = int(os.environ.get("RANK", 0))
     world = int(os.environ.get("WORLD_SIZE", 1))
     big = args.workload == "mem"
+    if args.contexts is None:
+        args.contexts = 2 if big else 1
     if args.ref_mbp is None:
         args.ref_mbp = 3100.0 if big or args.workload == "peaks" else 100.0
     if args.reads is None:

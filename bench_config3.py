@@ -135,8 +135,9 @@ def bench_mem3(args, rank, world, H):
     n = args.reads
     chunk = min(args.chunk, n)
     thr = H.cpu_threads()
+    K = max(1, int(args.contexts))
     cfg = {"workload": workload_name(args, n, world, chunk), "reads_per_gpu": n, "ref_mbp": args.ref_mbp,
-           "chunk_reads": chunk, "fma": int(args.fma), "emf": int(args.emf),
+           "chunk_reads": chunk, "contexts_per_gpu": K, "fma": int(args.fma), "emf": int(args.emf),
            "l2_policy": "index and reads larger than L2 (CP_OCC %.1f GB, reads %.2f GB per step)" % (2 * n_bp / 1e9, n * READ_LEN / 1e9)}
     t_all = time.perf_counter()
     ref = make_reference(n_bp, 44)
@@ -204,19 +205,28 @@ def bench_mem3(args, rank, world, H):
     off = np.arange(n, dtype=np.int64) * READ_LEN
     ln = np.full(n, READ_LEN, np.int32)
     d_reads, d_off, d_len = ctx.upload(flat1), ctx.upload(off), ctx.upload(ln)
-    mc = MemChunk(ctx)
+    # K worker contexts on this GPU over the one index replica (bwagpu_ctx_share_index), one host thread each: chunk j goes
+    # to context j % K, so one context's host-side waits and copies overlap another's kernels
+    ctxs = [ctx] + [ctx.worker() for _ in range(K - 1)]
+    mcs = [MemChunk(c) for c in ctxs]
+    mc = mcs[0]
+    pool = ThreadPoolExecutor(K) if K > 1 else None
     opt = mem_opt(use_emf=bool(args.emf))
     bounds = [(c0, min(c0 + chunk, n)) for c0 in range(0, n, chunk)]
     STAT = ("n_emf_hits", "n_smem", "n_coords", "n_chains", "n_seeds", "n_regs_raw", "n_regs", "n_sw_left", "n_sw_right",
             "n_sw_retry", "n_pairs8", "n_pairs16", "n_pairs_scalar", "sw_cells", "n_ext", "n_cp_records", "n_lf_steps")
 
     def step_device():
-        tot = dict.fromkeys(STAT, 0)
-        for c0, c1 in bounds:
-            r = mc.process_device(opt, d_reads, d_off + 8 * c0, d_len + 4 * c0, c1 - c0, READ_LEN)
-            for k in STAT:
-                tot[k] += getattr(r, k)
-        return tot
+        def run(k):
+            part = dict.fromkeys(STAT, 0)
+            for c0, c1 in bounds[k::K]:
+                r = mcs[k].process_device(opt, d_reads, d_off + 8 * c0, d_len + 4 * c0, c1 - c0, READ_LEN)
+                for key in STAT:
+                    part[key] += getattr(r, key)
+            ctxs[k].synchronize()
+            return part
+        parts = [run(0)] if K == 1 else list(pool.map(run, range(K)))
+        return {key: sum(p[key] for p in parts) for key in STAT}
 
     for _ in range(args.warmup):
         tot = step_device()
@@ -224,32 +234,36 @@ def bench_mem3(args, rank, world, H):
     H.barrier()
     sampler = H.ClockSampler(local)
     sampler.start()
-    l0 = ctx.launch_count()
+    l0 = sum(c.launch_count() for c in ctxs)
     ms = 0.0
     for _ in range(args.steps):
-        ctx.timer_start()
-        tot = step_device()
+        ctx.timer_start()                   # events on context 0's stream; every context is idle here and again
+        tot = step_device()                 # when step_device returns (each worker synchronises its own stream)
         ms += ctx.timer_stop()
     ms = H.allreduce_max(ms)
-    launches = ctx.launch_count() - l0
+    launches = sum(c.launch_count() for c in ctxs) - l0
 
     # e2e: HOST buffers through bwagpu_mem_process_chunk + bwagpu_mem_fetch, every chunk's reads copied in and its regions,
     # offsets and EMF answers copied out inside the timed region
     cap = int(tot["n_regs"] / len(bounds) * 1.3) + 4096
-    p_regs, p_off = ctx.pinned(cap, REG_DTYPE), ctx.pinned(chunk + 1, np.int64)
-    p_ret, p_perf = ctx.pinned(chunk, np.int32), ctx.pinned(chunk, np.dtype([("flags", "<u4"), ("location", "<u4")]))
+    PERF = np.dtype([("flags", "<u4"), ("location", "<u4")])
+    pin = [dict(regs=c.pinned(cap, REG_DTYPE), off=c.pinned(chunk + 1, np.int64), ret=c.pinned(chunk, np.int32),
+                perf=c.pinned(chunk, PERF)) for c in ctxs]
     off_rel = np.arange(chunk, dtype=np.int64) * READ_LEN
     d2h = 0
 
     def step_host():
         nonlocal d2h
-        d2h = 0
-        for c0, c1 in bounds:
-            nc = c1 - c0
-            r = mc.process(opt, flat1[c0 * READ_LEN:c1 * READ_LEN], off_rel[:nc], ln[c0:c1])
-            regs = p_regs if r.n_regs <= cap else np.zeros(r.n_regs, REG_DTYPE)
-            mc.fetch(r, nc, regs, p_off, p_ret, p_perf)
-            d2h += r.n_regs * REG_DTYPE.itemsize + (nc + 1) * 8 + nc * 12
+        def run(k):
+            out = 0
+            for c0, c1 in bounds[k::K]:
+                nc = c1 - c0
+                r = mcs[k].process(opt, flat1[c0 * READ_LEN:c1 * READ_LEN], off_rel[:nc], ln[c0:c1])
+                regs = pin[k]["regs"] if r.n_regs <= cap else np.zeros(r.n_regs, REG_DTYPE)
+                mcs[k].fetch(r, nc, regs, pin[k]["off"], pin[k]["ret"], pin[k]["perf"])
+                out += r.n_regs * REG_DTYPE.itemsize + (nc + 1) * 8 + nc * 12
+            return out
+        d2h = run(0) if K == 1 else sum(pool.map(run, range(K)))
 
     step_host()
     H.barrier()
@@ -260,7 +274,8 @@ def bench_mem3(args, rank, world, H):
     clocks = sampler.stop()
     # per-kernel device times: one more step with every launch bracketed by events (serialises the stream)
     ctx.set_profiling(True)
-    step_device()
+    for c0, c1 in bounds:                   # all chunks on context 0, one after the other
+        mc.process_device(opt, d_reads, d_off + 8 * c0, d_len + 4 * c0, c1 - c0, READ_LEN)
     KERN = {0: "seed_collect", 1: "seed_sort", 2: "sa_walk", 3: "bsw", 4: "bsw_generic", 7: "chain2aln", 8: "chain_seeds", 9: "emf_probe"}
     kt = {name: ctx.kernel_time(k) for k, name in KERN.items()}
     ctx.set_profiling(False)
@@ -272,8 +287,9 @@ def bench_mem3(args, rank, world, H):
                        t_all=t_all))
 
 
-# SASS instructions per DP cell of bsw_fast_kernel's live-range cell (cuobjdump of the shipped build)
-BSW_SASS_PER_CELL = 23.0
+# SASS instructions per DP cell of bsw_fast_kernel<16>'s whole-word loop (118 instructions per 8 cells in cuobjdump -sass of
+# the shipped build, loop overhead and arg-max bookkeeping included)
+BSW_SASS_PER_CELL = 14.75
 # integer operations a cell needs at best with two int16 cells per DPX operation (~7 instructions / 2 cells)
 BSW_IDEAL_OPS_PER_2CELLS = 7.0
 
@@ -294,10 +310,15 @@ def report(args, world, H, ctx, cfg, setup, n, ms, e2e_s, launches, clocks, tot,
                     "sass_per_cell": BSW_SASS_PER_CELL,
                     "frac_of_issue": gcups * BSW_SASS_PER_CELL / int_peaks["iadd3"] if int_peaks["iadd3"] else None,
                     "cells": int(tot["sw_cells"])})
+    # seeding: algorithmic bytes = SURVEY.md 8(d)'s figure, 64 B per CP_OCC record a backward extension touches (the reference
+    # reads the whole record).  With the paired record layout this kernel asks HBM for one 32-byte half per touch, so the
+    # bytes it really requests are half of that: `requested_*` says so next to the algorithmic figure.
     sc_ms = kms["seed_collect"]
     sc_gbs = tot["n_cp_records"] * 64 / (sc_ms * 1e-3) / 1e9 if sc_ms > 0 else 0.0
     kernels.append({"kernel": "seed_collect_kernel", "ms": sc_ms, "bound": "hbm", "achieved": sc_gbs, "unit": "GB/s",
-                    "peak": pk["hbm_gbs"], "frac": sc_gbs / pk["hbm_gbs"], "algorithmic_bytes": int(tot["n_cp_records"] * 64)})
+                    "peak": pk["hbm_gbs"], "frac": sc_gbs / pk["hbm_gbs"], "algorithmic_bytes": int(tot["n_cp_records"] * 64),
+                    "requested_bytes": int(tot["n_cp_records"] * 32), "requested_gbs": sc_gbs / 2,
+                    "requested_frac": sc_gbs / 2 / pk["hbm_gbs"]})
     sa_ms = kms["sa_walk"]
     sa_gbs = (tot["n_lf_steps"] * 64 + tot["n_coords"] * 5) / (sa_ms * 1e-3) / 1e9 if sa_ms > 0 else 0.0
     kernels.append({"kernel": "sa_walk_kernel", "ms": sa_ms, "bound": "hbm", "achieved": sa_gbs, "unit": "GB/s",

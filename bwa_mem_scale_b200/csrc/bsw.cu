@@ -265,7 +265,8 @@ static int bsw_launch_sorted(bwagpu_ctx *ctx, const bwagpu_bsw_params *prm, bwag
         static const bool one_tier = getenv("BWAGPU_BSW_TIERS") && !strcmp(getenv("BWAGPU_BSW_TIERS"), "0");
         const int cap2 = max_len2 < BSW_FAST_MAX_LEN2 ? max_len2 : BSW_FAST_MAX_LEN2;
         auto smem_of = [](int len2) { const int cols = len2 + 3, qwords = (len2 + 7) / 8 + 1; return (size_t)(cols + qwords) * BSW_FAST_TPB * 4; };
-        BWAGPU_CUDA(ctx, cudaFuncSetAttribute(bsw_fast_kernel<KIND>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_of(cap2)));
+        static BwagpuSmemBound smem_bound;
+        BWAGPU_CUDA(ctx, bwagpu_raise_dyn_smem(smem_bound, ctx->device, bsw_fast_kernel<KIND>, (int)smem_of(cap2)));
         int lo = n_long;
         for (int t = 0; t <= BSW_NTIER; ++t) {
             int hi = t < BSW_NTIER ? h_m[4 + t] : n;           // slots [lo, hi) hold len2 in (TIERS[t], TIERS[t-1]]

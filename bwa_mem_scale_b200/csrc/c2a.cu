@@ -443,6 +443,7 @@ __global__ void c2a_filter_kernel(C2aOpt o, const int32_t *__restrict__ len, int
 extern "C" int bwagpu_index_load_ref(bwagpu_ctx *ctx, const uint8_t *ref_string, int64_t l_pac, int32_t n_seqs,
                                      const int64_t *contig_off, const int32_t *contig_len, const uint8_t *contig_is_alt)
 {
+    BWAGPU_OWNS_INDEX(ctx);
     if (!ctx) return BWAGPU_ERR_ARG;
     if (!ref_string || l_pac <= 0 || n_seqs <= 0 || !contig_off || !contig_len)
         BWAGPU_FAIL(ctx, BWAGPU_ERR_ARG, "index_load_ref: incomplete reference descriptor");

@@ -6,6 +6,7 @@
 // (mem_flt_chained_seeds, :494-526, only acts on reads longer than ~700 bp — min_l = 5.5*log(l) must
 // not exceed 0.05*l — and is not part of this stage; such batches are rejected with BWAGPU_ERR_RANGE.)
 #include <cub/device/device_scan.cuh>
+#include <cub/device/device_radix_sort.cuh>
 #include <stdlib.h>
 #include "ctx.cuh"
 #include "chain_core.cuh"
@@ -40,12 +41,33 @@ __device__ __forceinline__ ChainScratch chain_scratch(bwagpu_seed *sd, WChain *c
 #ifndef CHAIN_WARP_N
 #define CHAIN_WARP_N 48
 #endif
-__global__ void __launch_bounds__(CHAIN_TPB, CHAIN_MINB) chain_build_kernel(ChainOpt o, RefView rv, ChainIn in, bwagpu_seed *sd, WChain *ch, BtNode *nodes,
-                                   int32_t *ord, int32_t *lst, int64_t *cnt_chains, int64_t *cnt_seeds,
-                                   float *frac_rep, int32_t *heavy_list, int32_t *heavy_cnt)
+// CHAIN_SORTED = 1: threads take the reads in order of decreasing work (number of seeds = SA coordinates of the read).
+// A read is one thread's strictly sequential job and reads differ by orders of magnitude (a unique read has a dozen
+// seeds, a repeat read hundreds): in read order a warp runs for as long as its heaviest read with one or two lanes
+// active (1.65 of 32 at config-3 scale, profiles/r02_ncu_chain_build_hot_lines_after_warp_filter.txt); in work order
+// the lanes of a warp finish together.  Which thread runs which read changes no result.
+// MEASURED (scripts/gpu_r2_v.sh, 2 M reads at config-3 scale): 90.5 ms in work order against 48.4 ms in read order — with
+// every resident warp on repeat reads at once their B-trees (tens of KB each) no longer fit L1/L2 and every node visit
+// goes to DRAM, while in read order the one or two heavy lanes of a warp keep theirs on chip.  OFF; kept for the record.
+#ifndef CHAIN_SORTED
+#define CHAIN_SORTED 0
+#endif
+__global__ void chain_work_key_kernel(ChainIn in, uint32_t *__restrict__ keys, int32_t *__restrict__ idx)
 {
     const int r = blockIdx.x * blockDim.x + threadIdx.x;
     if (r >= in.nseq) return;
+    const int64_t n = in.coord_off[in.smem_off[r + 1]] - in.coord_off[in.smem_off[r]];
+    keys[r] = (uint32_t)(n > 0xFFFF ? 0xFFFF : n);
+    idx[r] = r;
+}
+
+__global__ void __launch_bounds__(CHAIN_TPB, CHAIN_MINB) chain_build_kernel(ChainOpt o, RefView rv, ChainIn in, bwagpu_seed *sd, WChain *ch, BtNode *nodes,
+                                   int32_t *ord, int32_t *lst, int64_t *cnt_chains, int64_t *cnt_seeds,
+                                   float *frac_rep, int32_t *heavy_list, int32_t *heavy_cnt, const int32_t *__restrict__ perm)
+{
+    const int t_ = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t_ >= in.nseq) return;
+    const int r = perm ? perm[t_] : t_;
     cnt_chains[r] = 0; cnt_seeds[r] = 0;
     const int64_t s0 = in.smem_off[r], s1 = in.smem_off[r + 1];
     if (s0 == s1 || in.len[r] < o.min_seed_len) return;                       // :821-828
@@ -241,9 +263,24 @@ static int chain_device(bwagpu_ctx *ctx, const bwagpu_chain_opt *opt, const bwag
     if ((rc = bwagpu_scratch(ctx, SCR_CH_HEAVY, (int64_t)(nseq + 2) * 4, (void **)&heavy))) return rc;
     BWAGPU_CUDA(ctx, cudaMemsetAsync(cnt, 0, (size_t)(nseq + 1) * 16, ctx->stream));
     BWAGPU_CUDA(ctx, cudaMemsetAsync(heavy, 0, 4, ctx->stream));
+    int32_t *perm = nullptr;
     BWAGPU_KERNEL_BEGIN(ctx);
+#if CHAIN_SORTED
+    if (nseq > 64) {                               // reads in order of decreasing seed count
+        uint32_t *keys;
+        if ((rc = bwagpu_scratch(ctx, SCR_CH_PERM, (int64_t)nseq * 16, (void **)&keys))) return rc;
+        uint32_t *keys_out = keys + nseq; int32_t *idx = (int32_t *)(keys + 2 * (int64_t)nseq); perm = idx + nseq;
+        chain_work_key_kernel<<<(nseq + 255) / 256, 256, 0, ctx->stream>>>(in, keys, idx);
+        size_t bytes = 0;
+        cub::DeviceRadixSort::SortPairsDescending((void *)nullptr, bytes, keys, keys_out, idx, perm, nseq, 0, 16, ctx->stream);
+        void *tmp;
+        if ((rc = bwagpu_scratch(ctx, SCR_CUB, (int64_t)bytes + 256, &tmp))) return rc;
+        BWAGPU_CUDA(ctx, cub::DeviceRadixSort::SortPairsDescending(tmp, bytes, keys, keys_out, idx, perm, nseq, 0, 16, ctx->stream));
+        ctx->launches += 4;
+    }
+#endif
     chain_build_kernel<<<(nseq + CHAIN_TPB - 1) / CHAIN_TPB, CHAIN_TPB, 0, ctx->stream>>>(o, rv, in, sd, ch, nodes, ord, lst, cnt, cnt + nseq + 1, frac,
-                                                                                          heavy + 1, heavy);
+                                                                                          heavy + 1, heavy, perm);
     BWAGPU_KERNEL_END(ctx, BWAGPU_KERN_CHAIN);
     BWAGPU_CUDA(ctx, cudaGetLastError());
     int32_t n_heavy = 0;

@@ -68,6 +68,9 @@ extern "C" void bwagpu_destroy(bwagpu_ctx *ctx)
     cudaStreamSynchronize(ctx->stream);
     for (int i = 0; i < BWAGPU_NSCRATCH; ++i)
         if (ctx->scratch[i]) cudaFree(ctx->scratch[i]);
+    if (ctx->index_borrowed)
+        ctx->d_cp_occ = ctx->d_sa_ms = ctx->d_sa_ls = ctx->d_ref_string = ctx->d_fma_all = ctx->d_fma_last = ctx->d_emf_loc =
+            ctx->d_emf_seed = ctx->d_ert_kmer = ctx->d_ert_mlt = nullptr;
     if (ctx->d_cp_occ) cudaFree(ctx->d_cp_occ);
     if (ctx->d_sa_ms) cudaFree(ctx->d_sa_ms);
     if (ctx->d_sa_ls) cudaFree(ctx->d_sa_ls);
@@ -87,6 +90,31 @@ extern "C" void bwagpu_destroy(bwagpu_ctx *ctx)
     cudaStreamDestroy(ctx->copy_stream);
     cudaStreamDestroy(ctx->stream);
     free(ctx);
+}
+
+// A second context on the same GPU — its own stream, scratch and error state — that works on the index replica held by
+// `owner`: what a host with several worker threads per GPU uses, so that one thread's copies and host-side waits overlap
+// another's kernels without a second copy of the index in HBM.  The borrower must be destroyed before the owner and can
+// not load, build or unload index parts itself.  Options that live with the index (FMA on/off) are copied as they are now.
+extern "C" int bwagpu_ctx_share_index(bwagpu_ctx *ctx, const bwagpu_ctx *owner)
+{
+    if (!ctx) return BWAGPU_ERR_ARG;
+    if (!owner || owner == ctx) BWAGPU_FAIL(ctx, BWAGPU_ERR_ARG, "ctx_share_index: owner is NULL or the context itself");
+    if (owner->device != ctx->device) BWAGPU_FAIL(ctx, BWAGPU_ERR_ARG, "ctx_share_index: contexts are on different GPUs (%d, %d)", ctx->device, owner->device);
+    if (owner->index_borrowed) BWAGPU_FAIL(ctx, BWAGPU_ERR_ARG, "ctx_share_index: the owner itself borrows its index");
+    if (!ctx->index_borrowed && (ctx->d_cp_occ || ctx->d_ref_string || ctx->d_fma_all || ctx->d_fma_last || ctx->d_emf_seed || ctx->d_ert_kmer))
+        BWAGPU_FAIL(ctx, BWAGPU_ERR_ARG, "ctx_share_index: this context already holds index parts of its own");
+    ctx->index_borrowed = 1;
+    ctx->has_fm = owner->has_fm;
+    ctx->d_cp_occ = owner->d_cp_occ; ctx->d_sa_ms = owner->d_sa_ms; ctx->d_sa_ls = owner->d_sa_ls;
+    for (int i = 0; i < 5; ++i) ctx->fm_count[i] = owner->fm_count[i];
+    ctx->fm_sentinel = owner->fm_sentinel; ctx->fm_ref_seq_len = owner->fm_ref_seq_len;
+    ctx->d_fma_all = owner->d_fma_all; ctx->d_fma_last = owner->d_fma_last; ctx->fma_enabled = owner->fma_enabled;
+    ctx->d_ref_string = owner->d_ref_string; ctx->d_contig_off = owner->d_contig_off; ctx->d_contig_len = owner->d_contig_len;
+    ctx->d_contig_alt = owner->d_contig_alt; ctx->l_pac = owner->l_pac; ctx->n_contigs = owner->n_contigs;
+    ctx->d_emf_loc = owner->d_emf_loc; ctx->d_emf_seed = owner->d_emf_seed; ctx->emf = owner->emf;
+    ctx->d_ert_kmer = owner->d_ert_kmer; ctx->d_ert_mlt = owner->d_ert_mlt; ctx->ert_mlt_bytes = owner->ert_mlt_bytes;
+    return BWAGPU_OK;
 }
 
 extern "C" const char *bwagpu_last_error(const bwagpu_ctx *ctx) { return ctx ? ctx->err : g_err; }

@@ -1,5 +1,6 @@
 // Internal: per-GPU context shared by every kernel family of libbwagpu.so.
 #pragma once
+#include <mutex>
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdio.h>
@@ -20,6 +21,7 @@ enum { SCR_BSW_PAIRS = 0, SCR_BSW_REF, SCR_BSW_QER, SCR_BSW_WORK, SCR_MISC0, SCR
        SCR_CIG_OUTC, SCR_CIG_OUTM, SCR_CIG_ORDER, SCR_CIG_REDO,
        SCR_MEM_READS, SCR_MEM_OFF, SCR_MEM_LEN, SCR_MEM_EMF_RET, SCR_MEM_PERFECT, SCR_MEM_SKIP, SCR_MEM_CNT, SCR_MEM_KEEP,
        SCR_MEM_POS, SCR_MEM_REGS, SCR_MEM_REGOFF, SCR_BSW_CELLS, SCR_CH_HEAVY, SCR_SEED_OVF, SCR_SEED_TMP2,
+       SCR_CH_PERM,
        BWAGPU_NSCRATCH };
 
 struct bwagpu_ctx {
@@ -38,6 +40,8 @@ struct bwagpu_ctx {
     // SURVEY.md §3.1, so no locking is needed)
     void *scratch[BWAGPU_NSCRATCH];
     int64_t scratch_bytes[BWAGPU_NSCRATCH];
+    // 1: every index pointer below belongs to another context of the same GPU (bwagpu_ctx_share_index); never freed or replaced here
+    int index_borrowed;
     // FM-index replica in this GPU's HBM (bwagpu_index_load_fm)
     bool has_fm;
     void *d_cp_occ, *d_sa_ms, *d_sa_ls;
@@ -90,6 +94,30 @@ struct bwagpu_ctx {
                      #call, cudaGetErrorString(e__));                                       \
             return BWAGPU_ERR_CUDA;                                                         \
         }                                                                                   \
+    } while (0)
+
+// cudaFuncAttributeMaxDynamicSharedMemorySize belongs to the kernel (per device), not to a stream or context: two contexts
+// driven by two host threads must never lower each other's bound between setting it and launching.  The bound therefore
+// only ever GROWS, under a lock; a launch that needs less stays valid.  One BwagpuSmemBound per kernel (instantiation).
+struct BwagpuSmemBound { std::mutex mu; int cur[64]; BwagpuSmemBound() { for (int i = 0; i < 64; ++i) cur[i] = 0; } };
+template <class F>
+static inline cudaError_t bwagpu_raise_dyn_smem(BwagpuSmemBound &b, int device, F func, int bytes)
+{
+    std::lock_guard<std::mutex> lk(b.mu);
+    if (device < 0 || device >= 64) return cudaFuncSetAttribute(func, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+    if (bytes <= b.cur[device]) return cudaSuccess;
+    const cudaError_t e = cudaFuncSetAttribute(func, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+    if (e == cudaSuccess) b.cur[device] = bytes;
+    return e;
+}
+
+// first statement of every entry point that loads, builds or unloads a part of the index
+#define BWAGPU_OWNS_INDEX(ctx)                                                                                      \
+    do {                                                                                                            \
+        if ((ctx) && (ctx)->index_borrowed) {                                                                       \
+            snprintf((ctx)->err, sizeof((ctx)->err), "%s: this context borrows its index (bwagpu_ctx_share_index)", __func__); \
+            return BWAGPU_ERR_ARG;                                                                                  \
+        }                                                                                                           \
     } while (0)
 
 #define BWAGPU_FAIL(ctx, code, ...)                                  \

@@ -167,6 +167,7 @@ emf_probe_kernel(EmfView v, const uint8_t *__restrict__ reads, const int64_t *__
 // ---------------------------------------------------------------------------------------------------
 extern "C" int bwagpu_emf_unload(bwagpu_ctx *ctx)
 {
+    BWAGPU_OWNS_INDEX(ctx);
     if (!ctx) return BWAGPU_ERR_ARG;
     BWAGPU_CUDA(ctx, cudaSetDevice(ctx->device));
     BWAGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
@@ -180,6 +181,7 @@ extern "C" int bwagpu_emf_unload(bwagpu_ctx *ctx)
 extern "C" int bwagpu_emf_load(bwagpu_ctx *ctx, const bwagpu_emf_desc *d, const uint32_t *loc_table,
                                const bwagpu_seed_entry *seed_table)
 {
+    BWAGPU_OWNS_INDEX(ctx);
     if (!ctx) return BWAGPU_ERR_ARG;
     if (!d || !loc_table || !seed_table || d->seed_len <= 0 || d->num_seed_entry == 0 || d->num_loc_entry == 0)
         BWAGPU_FAIL(ctx, BWAGPU_ERR_ARG, "emf_load: incomplete table descriptor");

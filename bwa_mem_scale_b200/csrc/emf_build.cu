@@ -253,6 +253,7 @@ struct EbTmp {                    // cudaMalloc'ed working set, freed on every e
 
 extern "C" int bwagpu_emf_build_device(bwagpu_ctx *ctx, int32_t seed_len, double slack)
 {
+    BWAGPU_OWNS_INDEX(ctx);
     if (!ctx) return BWAGPU_ERR_ARG;
     if (!ctx->d_ref_string) BWAGPU_FAIL(ctx, BWAGPU_ERR_ARG, "emf_build_device: no reference text loaded (bwagpu_index_load_ref)");
     if (seed_len < 2 || seed_len > 32 * EB_MAXW) BWAGPU_FAIL(ctx, BWAGPU_ERR_RANGE, "emf_build_device: seed_len %d outside [2, %d]", seed_len, 32 * EB_MAXW);

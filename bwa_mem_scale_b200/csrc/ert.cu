@@ -115,6 +115,7 @@ __global__ void ert_scatter_kernel(const uint32_t *__restrict__ idx, const uint6
 
 extern "C" int bwagpu_index_unload_ert(bwagpu_ctx *ctx)
 {
+    BWAGPU_OWNS_INDEX(ctx);
     if (!ctx) return BWAGPU_ERR_ARG;
     BWAGPU_CUDA(ctx, cudaSetDevice(ctx->device));
     BWAGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
@@ -129,6 +130,7 @@ extern "C" int bwagpu_index_load_ert(bwagpu_ctx *ctx, const uint64_t *kmer_offse
                                      const uint64_t *sparse_val, int64_t n_sparse, const uint8_t *mlt_table,
                                      int64_t mlt_bytes)
 {
+    BWAGPU_OWNS_INDEX(ctx);
     if (!ctx) return BWAGPU_ERR_ARG;
     if (!mlt_table || mlt_bytes <= 0) BWAGPU_FAIL(ctx, BWAGPU_ERR_ARG, "index_load_ert: mlt_table is empty");
     if (!kmer_offsets && (n_sparse < 0 || (n_sparse > 0 && (!sparse_idx || !sparse_val))))
@@ -193,6 +195,7 @@ __global__ void __launch_bounds__(128) ert_kmer_fill_kernel(FmView f, uint64_t *
 
 extern "C" int bwagpu_index_complete_ert(bwagpu_ctx *ctx)
 {
+    BWAGPU_OWNS_INDEX(ctx);
     if (!ctx) return BWAGPU_ERR_ARG;
     if (!ctx->has_fm) BWAGPU_FAIL(ctx, BWAGPU_ERR_ARG, "index_complete_ert: no FM-index loaded (bwagpu_index_load_fm)");
     if (!ctx->d_ert_kmer) BWAGPU_FAIL(ctx, BWAGPU_ERR_ARG, "index_complete_ert: no ERT index loaded (bwagpu_index_load_ert)");

@@ -214,6 +214,7 @@ struct Tmp {                      // cudaMalloc'ed working set of one build, fre
 
 extern "C" int bwagpu_index_build_fm(bwagpu_ctx *ctx)
 {
+    BWAGPU_OWNS_INDEX(ctx);
     if (!ctx) return BWAGPU_ERR_ARG;
     if (!ctx->d_ref_string) BWAGPU_FAIL(ctx, BWAGPU_ERR_ARG, "index_build_fm: no reference text loaded (bwagpu_index_load_ref)");
     BWAGPU_CUDA(ctx, cudaSetDevice(ctx->device));

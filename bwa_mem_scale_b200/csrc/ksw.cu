@@ -229,7 +229,8 @@ static int ksw_launch(bwagpu_ctx *ctx, const KswParams &kp, const bwagpu_seqpair
     while (tpb > 32 && per_group * (tpb / P) > 160 * 1024) tpb >>= 1;
     const size_t smem = per_group * (tpb / P);
     if (smem > 200 * 1024) BWAGPU_FAIL(ctx, BWAGPU_ERR_RANGE, "ksw: query of %d bases does not fit shared memory", max_qlen);
-    BWAGPU_CUDA(ctx, cudaFuncSetAttribute(ksw_align2_kernel<P>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    static BwagpuSmemBound smem_bound;
+    BWAGPU_CUDA(ctx, bwagpu_raise_dyn_smem(smem_bound, ctx->device, ksw_align2_kernel<P>, (int)smem));
     int per_sm = 1;
     BWAGPU_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, ksw_align2_kernel<P>, tpb, smem));
     if (per_sm < 1) per_sm = 1;

@@ -172,6 +172,10 @@ __device__ __forceinline__ Biv seed_bext_coop(const FmView &f, unsigned m_ready,
     return res;
 }
 
+// SEED_STAGE_COOP = 1 (needs SEED_DYN): new reads are staged into shared memory by the whole warp, see the slow pass.
+#ifndef SEED_STAGE_COOP
+#define SEED_STAGE_COOP SEED_DYN
+#endif
 #ifndef SEED_MIN_BLOCKS
 #define SEED_MIN_BLOCKS 5      // 5 blocks of 128 per SM = 96 registers; without the bound the paired step takes 98 and drops to 4
 #endif
@@ -208,6 +212,72 @@ seed_collect_kernel(FmView f, SeedOpt o, const uint8_t *__restrict__ reads,
         const unsigned m_ready = __ballot_sync(0xffffffffu, ready);
         const unsigned m_slow = __ballot_sync(0xffffffffu, !ready && !finished);
         if (m_slow && (__popc(m_slow) >= SLOW_BATCH || !m_ready)) {
+#if SEED_STAGE_COOP
+            // One slow pass = (1) lanes with a read in hand run its bookkeeping up to the next request or to its end,
+            // (2) lanes without a read claim the next one, (3) the WARP stages the claimed reads into shared memory, every
+            // lane packing 8 bases of the same read per step (coalesced, ~20 warp instructions per read instead of ~1200 on
+            // one lane), (4) the new reads run up to their first request.
+            const bool mine = !ready && !finished;
+            if (mine && active) {
+                if (m.advance(f, o)) ready = true;
+                else {
+                    cnt[m.rid] = m.n_out;
+                    max_cnt = max(max_cnt, (unsigned)m.n_out);
+                    if (!list && m.n_out > cap) ovf_list[atomicAdd(&stats->n_ovf, 1u)] = m.rid;
+                    active = false;
+                }
+            }
+            int it = -1, i = -1;
+            if (mine && !ready && !active) {
+                for (;;) {
+                    const int64_t cand = (int64_t)atomicAdd(&stats->next, 1u);
+                    if (cand >= nseq) { finished = true; it = -1; break; }
+                    it = (int)cand;
+                    i = list ? list[it] : it;
+                    if (list) slab_of[i] = it;
+                    if (skip && skip[i]) { cnt[i] = 0; continue; }
+                    break;
+                }
+            }
+            const bool claimed = it >= 0 && !finished;
+            if constexpr (STAGED) {
+                unsigned need = __ballot_sync(0xffffffffu, claimed);
+                const int lane = threadIdx.x & 31;
+                while (need) {
+                    const int src = __ffs(need) - 1;
+                    need &= need - 1;
+                    const int ri = __shfl_sync(0xffffffffu, i, src);
+                    const int L = len[ri];
+                    const uint8_t *base = reads + off[ri];
+                    uint32_t *dst = seed_sm + SEED_PREV_K * 4 * SEED_TPB + (threadIdx.x & ~31) + src;
+                    for (int w = lane; w * 8 < L; w += 32) {
+                        uint32_t v = 0;
+#pragma unroll
+                        for (int b = 0; b < 8; ++b)
+                            if (w * 8 + b < L) { const uint32_t c = base[w * 8 + b]; v |= (c > 4u ? 4u : c) << (4 * b); }
+                        dst[w * SEED_TPB] = v;
+                    }
+                }
+                __syncwarp();
+            }
+            if (claimed) {
+                if constexpr (STAGED) {
+                    SmemRead r; r.w = rd_sm;
+                    m.init(r, len[i], i, pv, tmp + (int64_t)it * cap, cap);
+                } else {
+                    m.init(reads + off[i], len[i], i, pv, tmp + (int64_t)it * cap, cap);
+                }
+                m.pf_cp = f.cp_occ;
+                active = true;
+                if (m.advance(f, o)) ready = true;
+                else {                                   // a read with nothing to search (empty, all N)
+                    cnt[m.rid] = m.n_out;
+                    max_cnt = max(max_cnt, (unsigned)m.n_out);
+                    if (!list && m.n_out > cap) ovf_list[atomicAdd(&stats->n_ovf, 1u)] = m.rid;
+                    active = false;
+                }
+            }
+#else
             if (!ready && !finished) {
                 for (;;) {
                     if (!active) {
@@ -245,6 +315,7 @@ seed_collect_kernel(FmView f, SeedOpt o, const uint8_t *__restrict__ reads,
                     active = false;
                 }
             }
+#endif
             continue;
         }
         if (!m_ready) break;
@@ -387,6 +458,7 @@ static int fma_alloc(bwagpu_ctx *ctx, bool all, bool last)
 
 extern "C" int bwagpu_index_build_fma(bwagpu_ctx *ctx)
 {
+    BWAGPU_OWNS_INDEX(ctx);
     if (!ctx) return BWAGPU_ERR_ARG;
     if (!ctx->has_fm) BWAGPU_FAIL(ctx, BWAGPU_ERR_ARG, "index_build_fma: no FM-index loaded");
     BWAGPU_CUDA(ctx, cudaSetDevice(ctx->device));
@@ -407,6 +479,7 @@ extern "C" int bwagpu_index_build_fma(bwagpu_ctx *ctx)
 
 extern "C" int bwagpu_index_load_fma(bwagpu_ctx *ctx, const void *all_tab, const void *last_tab)
 {
+    BWAGPU_OWNS_INDEX(ctx);
     if (!ctx) return BWAGPU_ERR_ARG;
     BWAGPU_CUDA(ctx, cudaSetDevice(ctx->device));
     BWAGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
@@ -473,6 +546,7 @@ int bwagpu_fm_convert_layout(bwagpu_ctx *ctx, const void *src, void *dst, int64_
 
 extern "C" int bwagpu_index_load_fm(bwagpu_ctx *ctx, const bwagpu_fm_index_desc *d)
 {
+    BWAGPU_OWNS_INDEX(ctx);
     if (!ctx) return BWAGPU_ERR_ARG;
     if (!d || !d->cp_occ || !d->sa_ms_byte || !d->sa_ls_word || d->reference_seq_len <= 0)
         BWAGPU_FAIL(ctx, BWAGPU_ERR_ARG, "index_load_fm: incomplete index descriptor");
@@ -552,8 +626,9 @@ static int seed_collect_dev(bwagpu_ctx *ctx, const bwagpu_seed_opt *opt, const u
     so.max_mem_intv = opt->max_mem_intv;
     const bool staged = max_len <= SEED_SMEM_BASES;
     const size_t smem = (size_t)(SEED_PREV_K * 4 + (staged ? (max_len + 7) / 8 : 0)) * SEED_TPB * 4;
-    if (staged) BWAGPU_CUDA(ctx, cudaFuncSetAttribute(seed_collect_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    else BWAGPU_CUDA(ctx, cudaFuncSetAttribute(seed_collect_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    static BwagpuSmemBound bound_staged, bound_plain;
+    if (staged) BWAGPU_CUDA(ctx, bwagpu_raise_dyn_smem(bound_staged, ctx->device, seed_collect_kernel<true>, (int)smem));
+    else BWAGPU_CUDA(ctx, bwagpu_raise_dyn_smem(bound_plain, ctx->device, seed_collect_kernel<false>, (int)smem));
     int per_sm = 0;
     if (staged) BWAGPU_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, seed_collect_kernel<true>, SEED_TPB, smem));
     else BWAGPU_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, seed_collect_kernel<false>, SEED_TPB, smem));

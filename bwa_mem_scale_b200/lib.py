@@ -117,6 +117,7 @@ _lib = None
 _SIGS = {
     "bwagpu_create": (C.c_int, [C.c_int, C.POINTER(C.c_void_p)]),
     "bwagpu_destroy": (None, [C.c_void_p]),
+    "bwagpu_ctx_share_index": (C.c_int, [C.c_void_p, C.c_void_p]),
     "bwagpu_last_error": (C.c_char_p, [C.c_void_p]),
     "bwagpu_device_count": (C.c_int, []),
     "bwagpu_synchronize": (C.c_int, [C.c_void_p]),
@@ -253,6 +254,14 @@ class Context:
                               f"{self.lib.bwagpu_last_error(None).decode()}")
         self.h = h
         self.device = device
+
+    def worker(self) -> "Context":
+        """A second context on the same GPU (own stream and scratch) working on THIS context's index replica
+        (bwagpu_ctx_share_index): one per extra host thread.  Close it before this one."""
+        w = Context(self.device)
+        w.check(self.lib.bwagpu_ctx_share_index(w.h, self.h), "bwagpu_ctx_share_index")
+        w._owner = self                     # keeps the owner alive as long as the borrower
+        return w
 
     def check(self, rc: int, what: str = "") -> None:
         if rc != 0:

@@ -31,6 +31,13 @@ typedef struct bwagpu_ctx bwagpu_ctx;   /* one per GPU: device id, stream, scrat
 /* ---- context ------------------------------------------------------------------------------- */
 int  bwagpu_create(int device, bwagpu_ctx **out);
 void bwagpu_destroy(bwagpu_ctx *ctx);
+/* Several worker contexts on ONE GPU over one index replica: `ctx` (freshly created, same device) gets its own stream,
+ * scratch and error state but works on the FM-index / FMA tables / reference text / EMF table / ERT held by `owner`.
+ * This is the reference's threading model (src/bwamem.cpp:1872-1876: every kt_for thread runs worker_bwt/worker_aln on
+ * its own slice of the chunk over the shared, read-only index) moved to the GPU: one host thread per context, so that one
+ * thread's copies and host-side waits overlap another's kernels.  Destroy the borrower before the owner; a borrower can
+ * not load, build or unload index parts (BWAGPU_ERR_ARG). */
+int  bwagpu_ctx_share_index(bwagpu_ctx *ctx, const bwagpu_ctx *owner);
 const char *bwagpu_last_error(const bwagpu_ctx *ctx);   /* never NULL; ctx may be NULL */
 int  bwagpu_device_count(void);                          /* 0 when no driver/device */
 int  bwagpu_synchronize(bwagpu_ctx *ctx);                /* wait for ctx's stream */

@@ -115,3 +115,45 @@ def test_chunk_entry_with_emf(gpu_ctx):
     a, b = plain[0][keep].copy(), regs.copy()
     a["chain"] = 0; b["chain"] = 0
     assert np.array_equal(a, b)
+
+
+def test_gpu_worker_contexts_share_one_index(gpu_ctx):
+    """bwagpu_ctx_share_index: two contexts on one GPU, one index replica, one host thread each; same results as
+    one context, a borrower can not touch the index, and the owner still works after the borrower is gone."""
+    from concurrent.futures import ThreadPoolExecutor
+    from bwa_mem_scale_b200 import BwaGpuError
+    ref, idx = hard_index()
+    Extender(fmindex.text_with_revcomp(ref), int(HARD["l_pac"][0]), HARD["contig_off"], HARD["contig_len"], ctx=gpu_ctx)
+    fmi = FMI_search(idx, ctx=gpu_ctx)
+    fmi.build_fma()
+    flat, off, ln = ol.pack_reads(cc.hard_reads(ref))
+    opt = opts(ol.mem_opt(), batch_size=0)
+    whole = MemChunk(gpu_ctx)
+    want = whole.fetch(whole.process(opt, flat, off, ln), len(ln))
+    w = gpu_ctx.worker()
+    try:
+        with pytest.raises(BwaGpuError):
+            FMI_search(idx, ctx=w)                                        # a borrower loads nothing
+        half = len(ln) // 2
+        parts = [(0, half), (half, len(ln))]
+
+        def run(k):
+            c0, c1 = parts[k]
+            mc = MemChunk([gpu_ctx, w][k])
+            out = []
+            for _ in range(3):                                             # overlapping calls on the two streams
+                lo = int(off[c0])
+                hi = int(off[c1 - 1] + ln[c1 - 1])
+                r = mc.process(opt, flat[lo:hi], off[c0:c1] - lo, ln[c0:c1])
+                out = mc.fetch(r, c1 - c0)
+            return out
+        with ThreadPoolExecutor(2) as ex:
+            a, b = list(ex.map(run, range(2)))
+        CH = cc.REG_FIELDS.index("chain")                                  # chain ids count from 0 in every call
+        strip = lambda regs: np.delete(cc.reg_matrix(regs), CH, 1)
+        assert np.array_equal(strip(np.concatenate([a[0], b[0]])), strip(want[0]))
+        assert np.array_equal(np.concatenate([a[1][:-1], b[1] + a[1][-1]]), want[1])
+    finally:
+        w.close()
+    again = whole.fetch(whole.process(opt, flat, off, ln), len(ln))
+    assert np.array_equal(again[0], want[0])
