@@ -974,6 +974,8 @@ def main():
     ap.add_argument("--emf", type=int, default=None, help="exact-match filter in front (mem: default 1, table built in HBM; mem2: default 0, host-built)")
     ap.add_argument("--exact-frac", type=float, default=None, help="fraction of error-free reads (default: what 1%% substitutions give)")
     ap.add_argument("--contexts", type=int, default=None, help="worker contexts (host thread + stream + scratch each) per GPU over one index replica (mem: default 2; mem2: 1)")
+    ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
+                    help="mem workload: weak = --reads per GPU (default); strong = --reads in total, split evenly over the ranks")
     ap.add_argument("--no-cpu", action="store_true")
     args = ap.parse_args()
     # stdout carries exactly one JSON line: everything else that writes to fd 1 (NCCL's version banner, the reference's

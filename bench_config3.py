@@ -132,12 +132,13 @@ def bench_mem3(args, rank, world, H):
     from bwa_mem_scale_b200 import (Context, Extender, FMI_search, MemChunk, REG_DTYPE, fmindex, mem_opt)
     local = int(os.environ.get("LOCAL_RANK", rank))
     n_bp = int(args.ref_mbp * 1e6)
-    n = args.reads
+    strong = getattr(args, "scaling", "weak") == "strong"
+    n = args.reads // world if strong else args.reads         # strong: --reads is the whole job, split evenly over the ranks
     chunk = min(args.chunk, n)
     thr = H.cpu_threads()
     K = max(1, int(args.contexts))
     cfg = {"workload": workload_name(args, n, world, chunk), "reads_per_gpu": n, "ref_mbp": args.ref_mbp,
-           "chunk_reads": chunk, "contexts_per_gpu": K, "fma": int(args.fma), "emf": int(args.emf),
+           "chunk_reads": chunk, "contexts_per_gpu": K, "scaling": "strong" if strong else "weak", "fma": int(args.fma), "emf": int(args.emf),
            "l2_policy": "index and reads larger than L2 (CP_OCC %.1f GB, reads %.2f GB per step)" % (2 * n_bp / 1e9, n * READ_LEN / 1e9)}
     t_all = time.perf_counter()
     ref = make_reference(n_bp, 44)
@@ -189,7 +190,7 @@ def bench_mem3(args, rank, world, H):
         v = per_step * args.steps / t
         return {"impl": "reference", "metric": METRIC, "value": v, "unit": "reads/s", "n_gpus": args.gpus,
                 "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * t / args.steps, "higher_is_better": True,
-                "scaling": "weak", "vs_baseline": None, "dtype": "int64/int16", "data": "synthetic", "config": cfg,
+                "scaling": cfg["scaling"], "vs_baseline": None, "dtype": "int64/int16", "data": "synthetic", "config": cfg,
                 "cpu_baseline": {"value": v, "unit": "reads/s", "cores": thr, "kind": "reference",
                                  "sample": f"the first {per_step} reads of rank 0's read set per step, {kind}, mem_kernel1_core + "
                                            "mem_chain2aln_across_reads_V2 on one shared index (built on the GPU, handed over in "
@@ -334,7 +335,7 @@ def report(args, world, H, ctx, cfg, setup, n, ms, e2e_s, launches, clocks, tot,
             "int_peaks_gops": int_peaks, "gcups": gcups}
     nsw = tot["n_sw_left"] + tot["n_sw_right"]
     res = {"metric": METRIC, "value": n * world * steps / (ms * 1e-3), "unit": "reads/s", "n_gpus": world, "steps": steps,
-           "warmup": args.warmup, "ms_per_step": ms / steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+           "warmup": args.warmup, "ms_per_step": ms / steps, "higher_is_better": True, "scaling": cfg["scaling"], "vs_baseline": None,
            "dtype": "int64/int16", "data": "synthetic", "config": cfg, "clocks": clocks, "gpu_launches": int(launches),
            "e2e": {"value": n * world * steps / e2e_s, "unit": "reads/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h)},
            "gcups": gcups, "roofline": roof, "setup": setup,

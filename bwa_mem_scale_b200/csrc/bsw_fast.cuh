@@ -33,6 +33,22 @@ __device__ __forceinline__ uint32_t bsw_prmt(uint32_t a, uint32_t b, uint32_t se
 #define BSW_KEY_EXACT(c1) (((c1) << 1) | 1)
 #define BSW_KEY_WORD(c1) ((c1) << 1)
 
+// BSW_FMA_PIPE: 1 = upper half-word, gap-extension decrements and (left, F) packing as integer multiply-adds; 2 = the same
+// with a run-time 1 as multiplier so that the compiler keeps both decrements on the FMA pipe (ALU : FMA instructions per
+// 8 cells 73 : 16 -> 61 : 35 -> 52 : 43).  MEASURED (scripts/gpu_r2_aa.sh, ms per 5 M reads at config-3 scale): 265.2 off,
+// 272.8 with 1, 263.8 with 2 — no gain, so it stays OFF: the ALU-pipe figure of the ncu capture is one tier's, the sum
+// over the tiers is bound by issue and by the rows' serial bookkeeping.
+#ifndef BSW_FMA_PIPE
+#define BSW_FMA_PIPE 0
+#endif
+// a * b + c as an integer multiply-add that stays one (the compiler would turn a * 1 + c back into an add)
+__device__ __forceinline__ int bsw_mad(int a, int b, int c)
+{
+    int d;
+    asm("mad.lo.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+    return d;
+}
+
 #ifndef BSW_UNROLL
 #define BSW_UNROLL 4
 #endif
@@ -44,6 +60,9 @@ __device__ BswOut bsw_lane_fast(const bwagpu_bsw_params &p, const uint8_t *__res
                                 int h0, uint32_t *__restrict__ col, uint32_t *__restrict__ qsm)
 {
 #define COL(j) col[(j) * STRIDE]
+    // (asking for every 128-byte line of query and target up front with prefetch.global.L1 was measured: the staging loop
+    // below shows 8 % of the stall samples, profiles/r02_ncu_bsw_fast_v3_lines.txt, but the kernel time did not move —
+    // 264.6 vs 260.3 ms per 5 M reads, scripts/gpu_r2_z.sh — other warps already cover it)
     // stage the query once: 4-bit codes, 8 per word, word k of this thread at qsm[k * STRIDE]
     // (a byte load per cell from global memory was the kernel's bottleneck: L1 request rate)
     for (int k = 0; k * 8 < len2; ++k) {
@@ -52,6 +71,7 @@ __device__ BswOut bsw_lane_fast(const bwagpu_bsw_params &p, const uint8_t *__res
         qsm[k * STRIDE] = v;
     }
     const int wrap = BITS == 8 ? 0xFF : 0xFFFF;
+    [[maybe_unused]] const int one_rt = (int)(blockDim.x / STRIDE);     // 1, but not to the compiler (BSW_FMA_PIPE 2)
     const int gapo_d = p.o_del + p.e_del, gapo_i = p.o_ins + p.e_ins;
     const int e_del = p.e_del, e_ins = p.e_ins;
     const int sc_match = p.w_match, sc_mis = -p.w_mismatch, sc_amb = -1;
@@ -164,17 +184,30 @@ __device__ BswOut bsw_lane_fast(const bwagpu_bsw_params &p, const uint8_t *__res
             // words, a trailing half word, single cells.  Inside half and whole words the row's arg-max is kept per GROUP —
             // key = (max h of the group) << 16 | code of "somewhere up to the group's last column" — and the exact column
             // is looked up after the row, only when the row's outcome depends on it.
+            // The cell is bound by the ALU pipe (logic, shifts, selects, permutes and the DPX min/max operations all issue
+            // there at 16 lanes per clock and scheduler: 81 % busy against 21 % for the FMA pipe, profiles/
+            // r02_ncu_bsw_fast_v3_lines.txt), so whatever can be phrased as an integer multiply-add goes to the FMA pipe:
+            // the upper half-word as a high multiply, the two gap-extension decrements and the packing of (left, F).
+#if BSW_FMA_PIPE
+#define BSW_HI16(x) ((int)__umulhi((x), 0x10000u))
+#define BSW_SUB(x, c) bsw_mad((x), BSW_FMA_PIPE > 1 ? one_rt : 1, -(c))
+#define BSW_PACK(lo, hi) ((uint32_t)bsw_mad((hi), 0x10000, (lo)))
+#else
+#define BSW_HI16(x) ((int)((x) >> 16))
+#define BSW_SUB(x, c) ((x) - (c))
+#define BSW_PACK(lo, hi) __byte_perm((uint32_t)(lo), (uint32_t)(hi), 0x5410)
+#endif
 #define LIVE_CELL4(S, C, H)                                                           \
             {                                                                         \
                 const uint32_t cv = *cp;                                              \
-                const int diag = (int)(cv & 0xFFFFu), fc = (int)(cv >> 16);           \
+                const int diag = (int)(cv & 0xFFFFu), fc = BSW_HI16(cv);              \
                 int M = __dp4a((int)(S), 1 << (8 * (C)), diag);                       \
-                M = diag ? M : 0;                                                     \
+                M = diag ? M : 0;            /* (a predicated dot product comes back from ptxas as IDP + SEL) */ \
                 if (BITS == 8) M = max(M, 0);                                         \
                 H = __vimax3_s32(M, er, fc);                                          \
-                er = __viaddmax_s32_relu(M, -gapo_i, er - e_ins);                     \
-                const int fnew = __viaddmax_s32_relu(M, -gapo_d, fc - e_del);         \
-                *cp = __byte_perm((uint32_t)left, (uint32_t)fnew, 0x5410);            \
+                er = __viaddmax_s32_relu(M, -gapo_i, BSW_SUB(er, e_ins));             \
+                const int fnew = __viaddmax_s32_relu(M, -gapo_d, BSW_SUB(fc, e_del)); \
+                *cp = BSW_PACK(left, fnew);                                           \
                 left = H;                                                             \
                 cp += STRIDE;                                                         \
             }
@@ -213,6 +246,9 @@ __device__ BswOut bsw_lane_fast(const bwagpu_bsw_params &p, const uint8_t *__res
             }
 #undef LIVE_HALF
 #undef LIVE_CELL4
+#undef BSW_HI16
+#undef BSW_SUB
+#undef BSW_PACK
 #else
             // columns up to the next multiple of 8 (the query is staged 8 codes per word)
             const int jpro = min(jb, (j + 7) & ~7);
@@ -275,7 +311,10 @@ __device__ BswOut bsw_lane_fast(const bwagpu_bsw_params &p, const uint8_t *__res
         // its head and tail: one scan from each end serves both
         int lead = lo, trail = hi;
         while (lead < hi && COL(lead) == 0) ++lead;          // first non-zero word of [lo, hi), or hi
-        while (trail >= lo && COL(trail) == 0) --trail;      // last non-zero word of [lo, hi], or lo - 1
+        if (left == 0) {                                     // word hi was just written: (left, 0)
+            --trail;
+            while (trail >= lo && COL(trail) == 0) --trail;  // last non-zero word of [lo, hi], or lo - 1
+        }
         if (lead > lo) nlo = lead - 1;
         nhi = min(trail + 2, ncol);
         if (!live) break;

@@ -73,7 +73,12 @@ CHAIN_HD int chain_intv2rid(const RefView &r, int64_t rb, int64_t re)  // bns_in
     const int64_t fb = rb >= r.l_pac ? (r.l_pac << 1) - 1 - rb : rb;
     const int rid_b = chain_pos2rid(r, fb);
     int rid_e = rid_b;
-    if (rb < re) { const int64_t e = re - 1; rid_e = chain_pos2rid(r, e >= r.l_pac ? (r.l_pac << 1) - 1 - e : e); }
+    if (rb < re) {
+        const int64_t e = re - 1, fe = e >= r.l_pac ? (r.l_pac << 1) - 1 - e : e;
+        // nearly always the interval ends in the contig it starts in: one look at that contig's bounds instead of a second search
+        const bool same = rid_b >= 0 && fe >= r.contig_off[rid_b] && (rid_b == r.n_seqs - 1 || fe < r.contig_off[rid_b + 1]);
+        rid_e = same ? rid_b : chain_pos2rid(r, fe);
+    }
     return rid_b == rid_e ? rid_b : -1;
 }
 
