@@ -61,6 +61,38 @@ __global__ void chain_work_key_kernel(ChainIn in, uint32_t *__restrict__ keys, i
     idx[r] = r;
 }
 
+// CHAIN_SORTED = 2: a middle way — only the heavy reads (>= CHAIN_HEAVY_MIN seeds) are placed, `hl` of them per warp in its
+// first lanes, in order of decreasing work; every other lane takes a light read.  Heavy lanes then run `hl` wide instead of
+// one or two, without every resident warp being all-heavy.
+// MEASURED (scripts/gpu_r2_ab.sh, ms per 5 M reads): read order 117, hl = 2: 115, 4: 125, 8: 138, 16: 161 — the more heavy
+// reads share a warp the slower: their B-tree walks take different branches, so the lanes do not run in lockstep anyway,
+// and what is lost is the parallelism ACROSS warps.  OFF as well.
+#ifndef CHAIN_HEAVY_MIN
+#define CHAIN_HEAVY_MIN 64
+#endif
+__global__ void chain_heavy_count_kernel(const uint32_t *__restrict__ keys_sorted_desc, int n, int32_t *__restrict__ n_heavy)
+{
+    // first index whose key is below the threshold (keys are sorted in decreasing order)
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        int lo = 0, hi = n;
+        while (lo < hi) { const int mid = (lo + hi) >> 1; if (keys_sorted_desc[mid] >= CHAIN_HEAVY_MIN) lo = mid + 1; else hi = mid; }
+        *n_heavy = lo;
+    }
+}
+__global__ void chain_mix_perm_kernel(const int32_t *__restrict__ sorted, int n, const int32_t *__restrict__ n_heavy, int hl,
+                                      int32_t *__restrict__ perm)
+{
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= n) return;
+    int nh = *n_heavy;
+    if ((int64_t)nh > (int64_t)(n >> 5) * hl) nh = (n >> 5) * hl;          // more heavy reads than heavy slots: the rest count as light
+    const int warp = t >> 5, lane = t & 31;
+    const int64_t before = (int64_t)warp * hl + (lane < hl ? lane : hl);    // heavy slots before slot t
+    const int hb = before < nh ? (int)before : nh;
+    const bool heavy_slot = lane < hl && before < nh;
+    perm[t] = heavy_slot ? sorted[before] : sorted[nh + (t - hb)];
+}
+
 __global__ void __launch_bounds__(CHAIN_TPB, CHAIN_MINB) chain_build_kernel(ChainOpt o, RefView rv, ChainIn in, bwagpu_seed *sd, WChain *ch, BtNode *nodes,
                                    int32_t *ord, int32_t *lst, int64_t *cnt_chains, int64_t *cnt_seeds,
                                    float *frac_rep, int32_t *heavy_list, int32_t *heavy_cnt, const int32_t *__restrict__ perm)
@@ -277,6 +309,17 @@ static int chain_device(bwagpu_ctx *ctx, const bwagpu_chain_opt *opt, const bwag
         if ((rc = bwagpu_scratch(ctx, SCR_CUB, (int64_t)bytes + 256, &tmp))) return rc;
         BWAGPU_CUDA(ctx, cub::DeviceRadixSort::SortPairsDescending(tmp, bytes, keys, keys_out, idx, perm, nseq, 0, 16, ctx->stream));
         ctx->launches += 4;
+#if CHAIN_SORTED == 2
+        {
+            static const int hl = getenv("BWAGPU_CHAIN_HEAVY_LANES") ? atoi(getenv("BWAGPU_CHAIN_HEAVY_LANES")) : 8;
+            int32_t *n_heavy_d = (int32_t *)keys;                  // the unsorted keys are dead now
+            int32_t *mixed = idx;                                   // and so are the identity indices
+            chain_heavy_count_kernel<<<1, 32, 0, ctx->stream>>>(keys_out, nseq, n_heavy_d);
+            chain_mix_perm_kernel<<<(nseq + 255) / 256, 256, 0, ctx->stream>>>(perm, nseq, n_heavy_d, hl < 1 ? 1 : (hl > 32 ? 32 : hl), mixed);
+            perm = mixed;
+            ctx->launches += 2;
+        }
+#endif
     }
 #endif
     chain_build_kernel<<<(nseq + CHAIN_TPB - 1) / CHAIN_TPB, CHAIN_TPB, 0, ctx->stream>>>(o, rv, in, sd, ch, nodes, ord, lst, cnt, cnt + nseq + 1, frac,
