@@ -16,6 +16,7 @@
 static FmView probe_view(const bwagpu_ctx *ctx)
 {
     FmView f;
+    f.count_tab = nullptr;
     f.cp_occ = (const int64_t *)ctx->d_cp_occ; f.sa_ms_byte = (const int8_t *)ctx->d_sa_ms; f.sa_ls_word = (const uint32_t *)ctx->d_sa_ls;
     for (int i = 0; i < 5; ++i) f.count[i] = ctx->fm_count[i];
     f.sentinel_index = ctx->fm_sentinel; f.ref_seq_len = ctx->fm_ref_seq_len; f.fma_all = nullptr; f.fma_last = nullptr;

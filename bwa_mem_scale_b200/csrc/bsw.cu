@@ -15,6 +15,23 @@ __device__ __forceinline__ void bsw_add_cells(unsigned long long *cells, int min
     if ((threadIdx.x & 31) == (__ffs(m) - 1) && tot) atomicAdd(cells, (unsigned long long)tot);
 }
 
+// Where a pair's sequences are.  Arena mode (the C ABI's SeqPair contract): bytes ascend from seqBufQer + idq and
+// seqBufRef + idr.  Direct mode (internal, chain2aln): `qer` is the chunk's read buffer and `ref` the resident reference
+// text; idq / idr hold the low 32 bits of the first byte's position, regid bit 0 says "descending" (a left extension
+// walks the read and the text backwards) and regid >> 8 carries the text position's bits above 32.
+struct BswView { const uint8_t *q, *t; int dir; };
+__device__ __forceinline__ BswView bsw_pair_view(const bwagpu_seqpair &sp, const uint8_t *ref, const uint8_t *qer, int direct)
+{
+    BswView v;
+    if (!direct) { v.q = qer + sp.idq; v.t = ref + sp.idr; v.dir = 1; }
+    else {
+        v.q = qer + (uint32_t)sp.idq;
+        v.t = ref + (int64_t)(((uint64_t)((uint32_t)sp.regid >> 8) << 32) | (uint32_t)sp.idr);
+        v.dir = (sp.regid & 1) ? -1 : 1;
+    }
+    return v;
+}
+
 #define BSW_TPB 128
 #define BSW_FAST_TPB 64          // threads per block of the shared-memory kernel
 #define BSW_FAST_MAX_LEN2 512    // longest query whose column state is kept in shared memory
@@ -27,7 +44,7 @@ __global__ void __launch_bounds__(BSW_FAST_TPB)
 bsw_fast_kernel(bwagpu_bsw_params prm, bwagpu_seqpair *__restrict__ pairs,
                 const uint8_t *__restrict__ ref, const uint8_t *__restrict__ qer,
                 const uint32_t *__restrict__ order, int first, int n, int w, int cols,
-                unsigned long long *__restrict__ cells)
+                unsigned long long *__restrict__ cells, int direct)
 {
     extern __shared__ uint32_t colmem[];
     const int slot = first + blockIdx.x * BSW_FAST_TPB + threadIdx.x;
@@ -35,9 +52,10 @@ bsw_fast_kernel(bwagpu_bsw_params prm, bwagpu_seqpair *__restrict__ pairs,
     if (slot < n) {
         const uint32_t i = order[slot];
         const bwagpu_seqpair sp = pairs[i];
-        const BswOut o = bsw_lane_fast<KIND, BSW_FAST_TPB>(prm, qer + sp.idq, sp.len2, ref + sp.idr, sp.len1, w,
+        const BswView v = bsw_pair_view(sp, ref, qer, direct);
+        const BswOut o = bsw_lane_fast<KIND, BSW_FAST_TPB>(prm, v.q, sp.len2, v.t, sp.len1, w,
                                                             sp.h0, colmem + threadIdx.x,
-                                                            colmem + cols * BSW_FAST_TPB + threadIdx.x);
+                                                            colmem + cols * BSW_FAST_TPB + threadIdx.x, v.dir);
         bwagpu_seqpair *d = &pairs[i];
         d->score = o.score; d->tle = o.tle; d->gtle = o.gtle; d->qle = o.qle;
         d->gscore = o.gscore; d->max_off = o.max_off;
@@ -52,7 +70,7 @@ __global__ void __launch_bounds__(BSW_TPB)
 bsw_thread_order_kernel(bwagpu_bsw_params prm, bwagpu_seqpair *__restrict__ pairs,
                         const uint8_t *__restrict__ ref, const uint8_t *__restrict__ qer,
                         const uint32_t *__restrict__ order, int n, int w, uint32_t *__restrict__ work,
-                        unsigned long long *__restrict__ cells)
+                        unsigned long long *__restrict__ cells, int direct)
 {
     const int64_t T = (int64_t)gridDim.x * blockDim.x;
     const int64_t t0 = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -61,7 +79,8 @@ bsw_thread_order_kernel(bwagpu_bsw_params prm, bwagpu_seqpair *__restrict__ pair
     for (int64_t s = t0; s < n; s += T) {
         const uint32_t i = order[s];
         const bwagpu_seqpair sp = pairs[i];
-        const BswOut o = bsw_lane_pair<KIND>(prm, qer + sp.idq, sp.len2, ref + sp.idr, sp.len1, w, sp.h0, col, T);
+        const BswView v = bsw_pair_view(sp, ref, qer, direct);
+        const BswOut o = bsw_lane_pair<KIND>(prm, v.q, sp.len2, v.t, sp.len1, w, sp.h0, col, T, v.dir);
         bwagpu_seqpair *d = &pairs[i];
         d->score = o.score; d->tle = o.tle; d->gtle = o.gtle; d->qle = o.qle;
         d->gscore = o.gscore; d->max_off = o.max_off;
@@ -88,7 +107,7 @@ template <int KIND>
 __global__ void __launch_bounds__(BSW_TPB)
 bsw_thread_kernel(bwagpu_bsw_params prm, bwagpu_seqpair *__restrict__ pairs,
                   const uint8_t *__restrict__ ref, const uint8_t *__restrict__ qer, int n, int w,
-                  uint32_t *__restrict__ work, unsigned long long *__restrict__ cells)
+                  uint32_t *__restrict__ work, unsigned long long *__restrict__ cells, int direct)
 {
     const int64_t T = (int64_t)gridDim.x * blockDim.x;
     const int64_t t0 = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -96,12 +115,12 @@ bsw_thread_kernel(bwagpu_bsw_params prm, bwagpu_seqpair *__restrict__ pairs,
     unsigned long long mine = 0;
     for (int64_t i = t0; i < n; i += T) {
         bwagpu_seqpair sp = pairs[i];
-        const uint8_t *tg = ref + sp.idr, *qr = qer + sp.idq;
+        const BswView v = bsw_pair_view(sp, ref, qer, direct);
         BswOut o;
         if (KIND == BWAGPU_BSW_SCALAR)
-            o = bsw_scalar_pair(prm, qr, sp.len2, tg, sp.len1, w, sp.h0, col, T);
+            o = bsw_scalar_pair(prm, v.q, sp.len2, v.t, sp.len1, w, sp.h0, col, T, v.dir);
         else
-            o = bsw_lane_pair<KIND>(prm, qr, sp.len2, tg, sp.len1, w, sp.h0, col, T);
+            o = bsw_lane_pair<KIND>(prm, v.q, sp.len2, v.t, sp.len1, w, sp.h0, col, T, v.dir);
         bwagpu_seqpair *d = &pairs[i];
         d->score = o.score; d->tle = o.tle; d->gtle = o.gtle; d->qle = o.qle;
         d->gscore = o.gscore; d->max_off = o.max_off;
@@ -114,9 +133,20 @@ bsw_thread_kernel(bwagpu_bsw_params prm, bwagpu_seqpair *__restrict__ pairs,
 // and each tier is launched with the column count it needs: short tiers get several times the
 // resident warps of the longest one.  out[t] = first slot of the descending order whose len2 is
 // <= BSW_TIERS[t].
+// BSW_FINE_TIERS = 1: a tier every 16 query bases instead of four tiers: a launch's shared memory per thread follows its
+// longest query, so finer tiers waste less of it and more blocks fit per SM in the middle of the length range.
+#ifndef BSW_FINE_TIERS
+#define BSW_FINE_TIERS 1
+#endif
+#if BSW_FINE_TIERS
+#define BSW_NTIER 8
+#define BSW_TIER_LIST {136, 120, 104, 88, 72, 56, 40, 24}
+#else
 #define BSW_NTIER 4
-__constant__ int BSW_TIERS[BSW_NTIER] = {112, 80, 56, 40};
-static const int BSW_TIERS_H[BSW_NTIER] = {112, 80, 56, 40};
+#define BSW_TIER_LIST {112, 80, 56, 40}
+#endif
+__constant__ int BSW_TIERS[BSW_NTIER] = BSW_TIER_LIST;
+static const int BSW_TIERS_H[BSW_NTIER] = BSW_TIER_LIST;
 __global__ void bsw_tier_kernel(const uint32_t *__restrict__ keys_desc, int n, int *__restrict__ out)
 {
     const int t = threadIdx.x;
@@ -202,15 +232,15 @@ static int bsw_launch_thread(bwagpu_ctx *ctx, const bwagpu_bsw_params *prm, int 
     switch (kind) {
     case BWAGPU_BSW_16BIT:
         bsw_thread_kernel<16><<<blocks, BSW_TPB, 0, ctx->stream>>>(*prm, d_pairs, d_ref, d_qer, n,
-                                                                  w, (uint32_t *)work, cells);
+                                                                  w, (uint32_t *)work, cells, ctx->bsw_direct);
         break;
     case BWAGPU_BSW_8BIT:
         bsw_thread_kernel<8><<<blocks, BSW_TPB, 0, ctx->stream>>>(*prm, d_pairs, d_ref, d_qer, n,
-                                                                 w, (uint32_t *)work, cells);
+                                                                 w, (uint32_t *)work, cells, ctx->bsw_direct);
         break;
     default:
         bsw_thread_kernel<0><<<blocks, BSW_TPB, 0, ctx->stream>>>(*prm, d_pairs, d_ref, d_qer, n,
-                                                                 w, (uint32_t *)work, cells);
+                                                                 w, (uint32_t *)work, cells, ctx->bsw_direct);
     }
     BWAGPU_KERNEL_END(ctx, BWAGPU_KERN_BSW);
     BWAGPU_CUDA(ctx, cudaGetLastError());
@@ -242,8 +272,8 @@ static int bsw_launch_sorted(bwagpu_ctx *ctx, const bwagpu_bsw_params *prm, bwag
     ctx->launches += 5;      // CUB onesweep: histogram + 4 digit passes
     bsw_tier_kernel<<<1, 32, 0, ctx->stream>>>(keys_out, n, d_m + 4);
     ctx->launches += 1;
-    int h_m[8];
-    BWAGPU_CUDA(ctx, cudaMemcpyAsync(h_m, d_m, 32, cudaMemcpyDeviceToHost, ctx->stream));
+    int h_m[16];
+    BWAGPU_CUDA(ctx, cudaMemcpyAsync(h_m, d_m, 64, cudaMemcpyDeviceToHost, ctx->stream));
     BWAGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     const int max_len2 = h_m[1], n_long = h_m[2];
     // 2. the few long pairs (front of the order) take the generic global-scratch kernel
@@ -256,7 +286,7 @@ static int bsw_launch_sorted(bwagpu_ctx *ctx, const bwagpu_bsw_params *prm, bwag
         if ((rc = bwagpu_scratch(ctx, SCR_BSW_WORK, (int64_t)(max_len2 + 4) * T * 4, &work))) return rc;
         BWAGPU_KERNEL_BEGIN(ctx);
         bsw_thread_order_kernel<KIND><<<blocks, BSW_TPB, 0, ctx->stream>>>(*prm, d_pairs, d_ref, d_qer, order, n_long, w,
-                                                                         (uint32_t *)work, cells);
+                                                                         (uint32_t *)work, cells, ctx->bsw_direct);
         BWAGPU_KERNEL_END(ctx, BWAGPU_KERN_BSW_GENERIC);
         BWAGPU_CUDA(ctx, cudaGetLastError());
     }
@@ -277,7 +307,7 @@ static int bsw_launch_sorted(bwagpu_ctx *ctx, const bwagpu_bsw_params *prm, bwag
                 if (len2 > cap2) len2 = cap2;
                 BWAGPU_KERNEL_BEGIN(ctx);
                 bsw_fast_kernel<KIND><<<(hi - lo + BSW_FAST_TPB - 1) / BSW_FAST_TPB, BSW_FAST_TPB, smem_of(len2), ctx->stream>>>(
-                    *prm, d_pairs, d_ref, d_qer, order, lo, hi, w, len2 + 3, cells);
+                    *prm, d_pairs, d_ref, d_qer, order, lo, hi, w, len2 + 3, cells, ctx->bsw_direct);
                 BWAGPU_KERNEL_END(ctx, BWAGPU_KERN_BSW);
                 BWAGPU_CUDA(ctx, cudaGetLastError());
             }
@@ -312,6 +342,22 @@ static int bsw_device_maxlen(bwagpu_ctx *ctx, const bwagpu_seqpair *d_pairs, int
     BWAGPU_CUDA(ctx, cudaMemcpyAsync(out, d_m, 8, cudaMemcpyDeviceToHost, ctx->stream));
     BWAGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     return BWAGPU_OK;
+}
+
+// chain2aln's jobs: sequences read straight from the chunk's read buffer and the resident reference text (BswView)
+int bwagpu_bsw_scores_direct(bwagpu_ctx *ctx, const bwagpu_bsw_params *prm, int kind, bwagpu_seqpair *d_pairs,
+                             const uint8_t *d_ref_string, const uint8_t *d_reads, int32_t numPairs, int32_t w)
+{
+    int rc = bsw_check(ctx, prm, kind, numPairs, w);
+    if (rc) return rc;
+    if (numPairs == 0) return BWAGPU_OK;
+    int ml[2];
+    rc = bsw_device_maxlen(ctx, d_pairs, numPairs, ml);
+    if (rc) return rc;
+    ctx->bsw_direct = 1;
+    rc = bsw_launch(ctx, prm, kind, d_pairs, d_ref_string, d_reads, numPairs, w, ml[1]);
+    ctx->bsw_direct = 0;
+    return rc;
 }
 
 extern "C" int bwagpu_bsw_get_scores_device(bwagpu_ctx *ctx, const bwagpu_bsw_params *prm,

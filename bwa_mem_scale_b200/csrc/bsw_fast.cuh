@@ -57,7 +57,7 @@ constexpr int kBswUnroll = BSW_UNROLL;
 template <int BITS, int STRIDE>
 __device__ BswOut bsw_lane_fast(const bwagpu_bsw_params &p, const uint8_t *__restrict__ query,
                                 int len2, const uint8_t *__restrict__ target, int len1, int w,
-                                int h0, uint32_t *__restrict__ col, uint32_t *__restrict__ qsm)
+                                int h0, uint32_t *__restrict__ col, uint32_t *__restrict__ qsm, int dir = 1)
 {
 #define COL(j) col[(j) * STRIDE]
     // (asking for every 128-byte line of query and target up front with prefetch.global.L1 was measured: the staging loop
@@ -67,7 +67,7 @@ __device__ BswOut bsw_lane_fast(const bwagpu_bsw_params &p, const uint8_t *__res
     // (a byte load per cell from global memory was the kernel's bottleneck: L1 request rate)
     for (int k = 0; k * 8 < len2; ++k) {
         uint32_t v = 0;
-        for (int b = 0; b < 8 && k * 8 + b < len2; ++b) v |= (uint32_t)(query[k * 8 + b] & 7u) << (4 * b);
+        for (int b = 0; b < 8 && k * 8 + b < len2; ++b) v |= (uint32_t)(query[(k * 8 + b) * dir] & 7u) << (4 * b);
         qsm[k * STRIDE] = v;
     }
     const int wrap = BITS == 8 ? 0xFF : 0xFFFF;
@@ -107,7 +107,7 @@ __device__ BswOut bsw_lane_fast(const bwagpu_bsw_params &p, const uint8_t *__res
     int tc_next = nrow > 0 ? target[0] : 0;       // one row ahead: keeps the byte load off the row's critical path
     for (int i = 0; i < nrow; ++i) {
         const int tc = tc_next;
-        if (i + 1 < nrow) tc_next = target[i + 1];
+        if (i + 1 < nrow) tc_next = target[(i + 1) * dir];
         const int t = bsw_sym((uint8_t)tc, wrap);
         uint32_t tlo, thi = amb4;
         if (tc > 3) tlo = amb4;

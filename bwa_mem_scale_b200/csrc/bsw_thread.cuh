@@ -26,8 +26,10 @@ __device__ __forceinline__ int bsw_fc(uint32_t v) { return (int)(int16_t)(v >> 1
 template <int BITS>
 __device__ BswOut bsw_lane_pair(const bwagpu_bsw_params &p, const uint8_t *__restrict__ query,
                                 int len2, const uint8_t *__restrict__ target, int len1, int w,
-                                int h0, uint32_t *__restrict__ col, int64_t stride)
+                                int h0, uint32_t *__restrict__ col, int64_t stride, int dir = 1)
 {
+    // dir: +1 = query[j] / target[i] ascend in memory (sequence arenas); -1 = they descend from the given bytes (a left
+    // extension read straight out of the read / the resident reference text, see bsw_pair_view in bsw.cu)
 #define COL(j) col[(int64_t)(j) * stride]
     const int wrap = BITS == 8 ? 0xFF : 0xFFFF;
     const int gapo_d = p.o_del + p.e_del, gapo_i = p.o_ins + p.e_ins;
@@ -61,7 +63,7 @@ __device__ BswOut bsw_lane_pair(const bwagpu_bsw_params &p, const uint8_t *__res
     int cells = 0;
 
     for (int i = 0; i < nrow; ++i) {
-        const int t = bsw_sym(target[i], wrap);
+        const int t = bsw_sym(target[i * dir], wrap);
         int lo = max(nlo, i - w), hi = min(min(nhi, i + w + 1), ncol);
         cells += max(hi - lo, 0);
         // first-column value H(i,-1); the SIMD code reads a pad value on the very last row,
@@ -78,7 +80,7 @@ __device__ BswOut bsw_lane_pair(const bwagpu_bsw_params &p, const uint8_t *__res
 
         int j;
         for (j = lo; j < hi; ++j) {
-            const int q = bsw_sym(query[j], wrap);
+            const int q = bsw_sym(query[j * dir], wrap);
             const uint32_t cv = COL(j);
             const int diag = bsw_hd(cv), fc = bsw_fc(cv);
             int s = t == q ? sc_match : sc_mis;
@@ -141,7 +143,7 @@ __device__ BswOut bsw_lane_pair(const bwagpu_bsw_params &p, const uint8_t *__res
 // scalarBandedSWA: int32 state, two scratch words per column (H carry, E)
 __device__ BswOut bsw_scalar_pair(const bwagpu_bsw_params &p, const uint8_t *__restrict__ query,
                                   int qlen, const uint8_t *__restrict__ target, int tlen, int w,
-                                  int h0, uint32_t *__restrict__ col, int64_t stride)
+                                  int h0, uint32_t *__restrict__ col, int64_t stride, int dir = 1)
 {
 #define HC(j) col[(int64_t)(2 * (j)) * stride]
 #define EC(j) col[(int64_t)(2 * (j) + 1) * stride]
@@ -161,7 +163,7 @@ __device__ BswOut bsw_scalar_pair(const bwagpu_bsw_params &p, const uint8_t *__r
     int best = h0, best_i = -1, best_j = -1, g_i = -1, g_sc = -1, off = 0;
     int lo = 0, hi = qlen, cells = 0;
     for (int i = 0; i < tlen; ++i) {
-        const int t = target[i];
+        const int t = target[i * dir];
         lo = max(lo, i - w);
         hi = min(min(hi, i + w + 1), qlen);
         cells += max(hi - lo, 0);
@@ -170,7 +172,7 @@ __device__ BswOut bsw_scalar_pair(const bwagpu_bsw_params &p, const uint8_t *__r
         for (j = lo; j < hi; ++j) {
             const int diag = (int)HC(j), e = (int)EC(j);
             HC(j) = (uint32_t)left;
-            const int q = query[j];
+            const int q = query[j * dir];
             const int s = (t > 3 || q > 3) ? -1 : (t == q ? sc_match : sc_mis);
             const int M = diag ? diag + s : 0;
             const int h = max(max(M, e), f);

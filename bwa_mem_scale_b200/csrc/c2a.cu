@@ -143,6 +143,22 @@ __global__ void c2a_size_kernel(const int32_t *__restrict__ len, const bwagpu_ch
     sizes[5 * stride + ri] = hr ? r1 - r0 - (s.rbeg + s.len - r0) : 0;
 }
 
+// C2A_DIRECT = 1: the extension jobs do not carry copies of their sequences.  A job names where its query starts in the
+// chunk's read buffer and where its window starts in the resident reference text, plus a direction (left extensions walk
+// both backwards), and the SW kernels read from there (BswView, bsw.cu).  No sequence arenas (2.3 GB written and read
+// again per million reads), no 2^31-byte limit on a chunk's extension sequences, four prefix sums fewer.
+#ifndef C2A_DIRECT
+#define C2A_DIRECT 1
+#endif
+__device__ __forceinline__ void c2a_direct_addr(bwagpu_seqpair &sp, int64_t qpos, int64_t rpos, int descending, int *err)
+{
+    if (qpos < 0 || qpos >= (1LL << 32) || rpos >= (1LL << 56)) *err = 1;     // outside what the job record can name
+    if (rpos < 0) rpos = 0;                                                    // empty window at the very start of the text
+    sp.idq = (int32_t)(uint32_t)qpos;
+    sp.idr = (int32_t)(uint32_t)rpos;
+    sp.regid = (int32_t)(((uint32_t)(rpos >> 32) << 8) | (uint32_t)(descending & 1));
+}
+
 __global__ void c2a_fill_kernel(C2aOpt o, const uint8_t *__restrict__ ref_string, const uint8_t *__restrict__ reads,
                                 const int64_t *__restrict__ off, const int32_t *__restrict__ len,
                                 const bwagpu_chain *__restrict__ chains, const bwagpu_seed *__restrict__ seeds,
@@ -150,20 +166,25 @@ __global__ void c2a_fill_kernel(C2aOpt o, const uint8_t *__restrict__ ref_string
                                 const int64_t *__restrict__ rmax, int64_t n_regs, const int64_t *__restrict__ offs,
                                 int64_t stride, bwagpu_alnreg *__restrict__ regs, bwagpu_seqpair *__restrict__ L,
                                 bwagpu_seqpair *__restrict__ R, uint8_t *__restrict__ LQ, uint8_t *__restrict__ LR,
-                                uint8_t *__restrict__ RQ, uint8_t *__restrict__ RR)
+                                uint8_t *__restrict__ RQ, uint8_t *__restrict__ RR, int *__restrict__ err)
 {
     // one warp per region: every lane derives the same scalars, lane 0 stores the records, all 32
     // lanes copy the sequence bytes (coalesced instead of one serial byte loop per region)
+#if C2A_DIRECT
+    const int64_t ri = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;          // nothing to copy: one thread per region
+    const int lane = 0;
+#else
     const int64_t ri = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const int lane = threadIdx.x & 31;
+#endif
     if (ri >= n_regs) return;
     const int ci = chain_of[ri];
     const bwagpu_chain c = chains[ci];
     const bwagpu_seed s = c2a_seed_of(c, seeds, srt, ri);
     const int l_query = len[c.seqid];
-    const uint8_t *query = reads + off[c.seqid];
+    [[maybe_unused]] const uint8_t *query = reads + off[c.seqid];
     const int64_t r0 = rmax[2 * ci], r1 = rmax[2 * ci + 1];
-    const uint8_t *rseq = ref_string + r0;
+    [[maybe_unused]] const uint8_t *rseq = ref_string + r0;
     bwagpu_alnreg a;
     a.w = o.w; a.score = a.truesc = -1; a.rid = c.rid; a.frac_rep = c.frac_rep; a.seedlen0 = s.len;
     a.chain = ci; a.seedcov = 0;
@@ -172,10 +193,16 @@ __global__ void c2a_fill_kernel(C2aOpt o, const uint8_t *__restrict__ ref_string
         bwagpu_seqpair sp;
         sp.h0 = s.len * o.a; sp.seqid = c.seqid; sp.regid = 0;
         sp.id = (int32_t)ri;
-        const int64_t qo = offs[2 * stride + ri], ro = offs[3 * stride + ri], tmp = s.rbeg - r0;
+        const int64_t tmp = s.rbeg - r0;
+#if C2A_DIRECT
+        // query[j] = read[qbeg - 1 - j], target[i] = text[rbeg - 1 - i]
+        c2a_direct_addr(sp, off[c.seqid] + s.qbeg - 1, s.rbeg - 1, 1, err);
+#else
+        const int64_t qo = offs[2 * stride + ri], ro = offs[3 * stride + ri];
         sp.idq = (int32_t)qo; sp.idr = (int32_t)ro;
         for (int i = lane; i < s.qbeg; i += 32) LQ[qo + i] = query[s.qbeg - 1 - i];
         for (int64_t i = lane; i < tmp; i += 32) LR[ro + i] = rseq[tmp - 1 - i];
+#endif
         sp.len2 = s.qbeg; sp.len1 = (int32_t)tmp;
         sp.score = sp.tle = sp.gtle = sp.qle = sp.gscore = sp.max_off = 0;
         if (lane == 0) L[offs[ri]] = sp;
@@ -188,10 +215,14 @@ __global__ void c2a_fill_kernel(C2aOpt o, const uint8_t *__restrict__ ref_string
         bwagpu_seqpair sp;
         sp.h0 = H0_; sp.seqid = c.seqid; sp.regid = 0; sp.id = (int32_t)ri;
         sp.len2 = (int32_t)(l_query - qe); sp.len1 = (int32_t)(r1 - r0 - re);
+#if C2A_DIRECT
+        c2a_direct_addr(sp, off[c.seqid] + qe, r0 + re, 0, err);                // query[j] = read[qe + j], target[i] = text[r0 + re + i]
+#else
         const int64_t qo = offs[4 * stride + ri], ro = offs[5 * stride + ri];
         sp.idq = (int32_t)qo; sp.idr = (int32_t)ro;
         for (int i = lane; i < sp.len2; i += 32) RQ[qo + i] = query[qe + i];
         for (int i = lane; i < sp.len1; i += 32) RR[ro + i] = rseq[re + i];
+#endif
         sp.score = sp.tle = sp.gtle = sp.qle = sp.gscore = sp.max_off = 0;
         if (lane == 0) R[offs[stride + ri]] = sp;
         a.qe = (int32_t)qe; a.re = r0 + re;
@@ -507,7 +538,12 @@ static int c2a_side(bwagpu_ctx *ctx, const C2aOpt &o, const bwagpu_ext_opt *eo, 
         bwagpu_seqpair *cur = bk[k], *nxt = retry;
         for (int t = 0; t < 2 && nump > 0; ++t) {
             const int w = o.w << t;
+#if C2A_DIRECT
+            (void)rbytes; (void)qbytes;
+            if ((rc = bwagpu_bsw_scores_direct(ctx, &P, kinds[k], cur, d_rbuf, d_qbuf, nump, w))) return rc;
+#else
             if ((rc = bwagpu_bsw_get_scores_device(ctx, &P, kinds[k], cur, d_rbuf, rbytes, d_qbuf, qbytes, nump, w))) return rc;
+#endif
             BWAGPU_CUDA(ctx, cudaMemsetAsync(d_cnt + 8, 0, 4, ctx->stream));
             c2a_apply_kernel<<<C2A_GRID(nump)>>>(o, left, w, t == 1, cur, nump, d_regs, d_chains, d_seeds, d_len, nxt, d_cnt + 8);
             ctx->launches++;
@@ -563,31 +599,43 @@ extern "C" int bwagpu_chain2aln_device(bwagpu_ctx *ctx, const bwagpu_ext_opt *eo
     c2a_size_kernel<<<C2A_GRID(n_seeds)>>>(d_len, d_chains, d_seeds, srt, chain_of, rmax, n_seeds, sizes, stride);
     ctx->launches++;
     BWAGPU_KERNEL_END(ctx, BWAGPU_KERN_C2A);
-    for (int k = 0; k < 6; ++k)
+    const int n_scan = C2A_DIRECT ? 2 : 6;            // job counts only, or job counts and the four arena sizes
+    for (int k = 0; k < n_scan; ++k)
         if ((rc = c2a_scan(ctx, sizes + k * stride, offs + k * stride, stride))) return rc;
-    int64_t tot[6];
-    for (int k = 0; k < 6; ++k)
+    int64_t tot[6] = {0, 0, 0, 0, 0, 0};
+    for (int k = 0; k < n_scan; ++k)
         BWAGPU_CUDA(ctx, cudaMemcpyAsync(&tot[k], offs + k * stride + n_seeds, 8, cudaMemcpyDeviceToHost, ctx->stream));
     BWAGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-    for (int k = 2; k < 6; ++k)
+    for (int k = 2; k < n_scan; ++k)
         if (tot[k] >= (1LL << 31)) BWAGPU_FAIL(ctx, BWAGPU_ERR_RANGE, "chain2aln: extension sequences exceed 2 GiB; split the batch");
-    bwagpu_seqpair *L, *R; uint8_t *LQ, *LR, *RQ, *RR;
+    if (tot[0] >= (1LL << 31) || tot[1] >= (1LL << 31)) BWAGPU_FAIL(ctx, BWAGPU_ERR_RANGE, "chain2aln: more than 2^31 extension jobs; split the batch");
+    bwagpu_seqpair *L, *R; uint8_t *LQ = nullptr, *LR = nullptr, *RQ = nullptr, *RR = nullptr; int *d_err;
     if ((rc = bwagpu_scratch(ctx, SCR_C2A_L, (tot[0] + 1) * (int64_t)sizeof(bwagpu_seqpair), (void **)&L))) return rc;
     if ((rc = bwagpu_scratch(ctx, SCR_C2A_R, (tot[1] + 1) * (int64_t)sizeof(bwagpu_seqpair), (void **)&R))) return rc;
+    if ((rc = bwagpu_scratch(ctx, SCR_MISC3, 64, (void **)&d_err))) return rc;
+    BWAGPU_CUDA(ctx, cudaMemsetAsync(d_err, 0, 4, ctx->stream));
+#if !C2A_DIRECT
     if ((rc = bwagpu_scratch(ctx, SCR_C2A_LQ, tot[2] + 64, (void **)&LQ))) return rc;
     if ((rc = bwagpu_scratch(ctx, SCR_C2A_LR, tot[3] + 64, (void **)&LR))) return rc;
     if ((rc = bwagpu_scratch(ctx, SCR_C2A_RQ, tot[4] + 64, (void **)&RQ))) return rc;
     if ((rc = bwagpu_scratch(ctx, SCR_C2A_RR, tot[5] + 64, (void **)&RR))) return rc;
+#endif
     BWAGPU_KERNEL_BEGIN(ctx);
-    c2a_fill_kernel<<<C2A_GRID(n_seeds * 32)>>>(o, (const uint8_t *)ctx->d_ref_string, d_reads, d_off, d_len, d_chains, d_seeds, srt,
-                                           chain_of, rmax, n_seeds, offs, stride, regs, L, R, LQ, LR, RQ, RR);
+    c2a_fill_kernel<<<C2A_GRID(C2A_DIRECT ? n_seeds : n_seeds * 32)>>>(o, (const uint8_t *)ctx->d_ref_string, d_reads, d_off, d_len, d_chains,
+                                           d_seeds, srt, chain_of, rmax, n_seeds, offs, stride, regs, L, R, LQ, LR, RQ, RR, d_err);
     BWAGPU_KERNEL_END(ctx, BWAGPU_KERN_C2A);
     BWAGPU_CUDA(ctx, cudaGetLastError());
+    int h_err = 0;
+    BWAGPU_CUDA(ctx, cudaMemcpyAsync(&h_err, d_err, 4, cudaMemcpyDeviceToHost, ctx->stream));
+    BWAGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    if (h_err) BWAGPU_FAIL(ctx, BWAGPU_ERR_RANGE, "chain2aln: read buffer of 4 GiB or more; split the batch");
     res->n_left = tot[0]; res->n_right = tot[1];
     res->seq_bytes = tot[2] + tot[3] + tot[4] + tot[5];
-    if ((rc = c2a_side(ctx, o, eo, 1, L, tot[0], LR, tot[3], LQ, tot[2], regs, d_chains, d_seeds, d_len, res))) return rc;
+    // direct mode: the jobs read from the chunk's reads and from the reference text themselves
+    const uint8_t *text = (const uint8_t *)ctx->d_ref_string;
+    if ((rc = c2a_side(ctx, o, eo, 1, L, tot[0], C2A_DIRECT ? text : LR, tot[3], C2A_DIRECT ? d_reads : LQ, tot[2], regs, d_chains, d_seeds, d_len, res))) return rc;
     if (tot[1] > 0) { c2a_h0_kernel<<<C2A_GRID(tot[1])>>>(R, tot[1], regs); ctx->launches++; }
-    if ((rc = c2a_side(ctx, o, eo, 0, R, tot[1], RR, tot[5], RQ, tot[4], regs, d_chains, d_seeds, d_len, res))) return rc;
+    if ((rc = c2a_side(ctx, o, eo, 0, R, tot[1], C2A_DIRECT ? text : RR, tot[5], C2A_DIRECT ? d_reads : RQ, tot[4], regs, d_chains, d_seeds, d_len, res))) return rc;
     BWAGPU_KERNEL_BEGIN(ctx);
     c2a_filter_kernel<<<C2A_GRID(nseq)>>>(o, d_len, nseq, d_chains, d_seeds, srt, first_chain, last_chain, regs, purged);
     c2a_filter_warp_kernel<<<(unsigned)(((int64_t)nseq * 32 + 127) / 128), 128, 0, ctx->stream>>>(

@@ -59,6 +59,7 @@ struct bwagpu_ctx {
     void *d_ert_kmer, *d_ert_mlt;
     int64_t ert_mlt_bytes;
     int ert_mem_cap, ert_hit_cap;   // per-read slab capacities of the first ERT pass
+    int bsw_direct;             // set around bsw_launch by bwagpu_bsw_scores_direct: pairs address the reads / the text directly
     int chain_batch_reads;      // unit of mem_chain_seeds' batch-wide SMEM bound (0 = the whole call); set by bwagpu_mem_process_chunk
     int seed_read_cap;          // per-read SMEM capacity of the seeding scratch (grows on overflow)
     // optional per-kernel CUDA-event timing (bwagpu_set_profiling): bench.py's roofline numbers
@@ -128,5 +129,7 @@ static inline cudaError_t bwagpu_raise_dyn_smem(BwagpuSmemBound &b, int device, 
 
 // ensure scratch slot `slot` holds at least `bytes`; contents are NOT preserved on growth
 int bwagpu_scratch(bwagpu_ctx *ctx, int slot, int64_t bytes, void **out);
+int bwagpu_bsw_scores_direct(bwagpu_ctx *ctx, const bwagpu_bsw_params *prm, int kind, bwagpu_seqpair *d_pairs,
+                             const uint8_t *d_ref_string, const uint8_t *d_reads, int32_t numPairs, int32_t w);   // bsw.cu
 // CP_OCC records between the reference's word order and the replica's (fmi_core.cuh FM_PAIRED); src == dst: in place (seed.cu)
 int bwagpu_fm_convert_layout(bwagpu_ctx *ctx, const void *src, void *dst, int64_t n_cp, int to_paired);

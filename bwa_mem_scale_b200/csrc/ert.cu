@@ -201,6 +201,7 @@ extern "C" int bwagpu_index_complete_ert(bwagpu_ctx *ctx)
     if (!ctx->d_ert_kmer) BWAGPU_FAIL(ctx, BWAGPU_ERR_ARG, "index_complete_ert: no ERT index loaded (bwagpu_index_load_ert)");
     BWAGPU_CUDA(ctx, cudaSetDevice(ctx->device));
     FmView f;
+    f.count_tab = nullptr;
     f.cp_occ = (const int64_t *)ctx->d_cp_occ; f.sa_ms_byte = (const int8_t *)ctx->d_sa_ms; f.sa_ls_word = (const uint32_t *)ctx->d_sa_ls;
     for (int i = 0; i < 5; ++i) f.count[i] = ctx->fm_count[i];
     f.sentinel_index = ctx->fm_sentinel; f.ref_seq_len = ctx->fm_ref_seq_len;

@@ -46,6 +46,7 @@ struct FmView {
     // FMA tables (reference all_smem_t / last_smem_t, src/FMI_search.h:99-135); NULL = not loaded
     const uint32_t *fma_all;     // 32 words per 11-mer: last_avail, 10 x {k32,l32,s32}, pad
     const uint32_t *fma_last;    // 4 words per 13-mer: bp|kms<<8|lms<<16|sms<<24, kls, lls, sls
+    const int64_t *count_tab;    // NULL, or an indexable copy of count[5] the kernel made (fm_count)
 };
 
 // SEED_PAIR2 = 1: in the backward rows of the SMEM search two entries of the row are extended per step (fm_bext2): they
@@ -162,9 +163,14 @@ BWAGPU_HD uint64_t fm_prefix_mask(int y) { return y ? (~0ULL << (64 - y)) : 0ULL
 
 struct Biv { int64_t k, l, s; };
 
-// count[a] without dynamic indexing of the kernel-parameter struct (keeps it out of local memory)
+// count[a] without dynamic indexing of the kernel-parameter struct (that would move it to local memory): a select chain,
+// or — when the kernel has put a copy of count[] where it can be indexed (count_tab: shared memory) — one load.  The chain
+// was 7.8 % of seed_collect_kernel's instructions (profiles/r02_ncu_seed_collect_v2_lines.txt).
 BWAGPU_HD int64_t fm_count(const FmView &f, int a)
 {
+#if defined(__CUDA_ARCH__)
+    if (f.count_tab) return f.count_tab[a];
+#endif
     return a == 0 ? f.count[0] : a == 1 ? f.count[1] : a == 2 ? f.count[2] : a == 3 ? f.count[3] : f.count[4];
 }
 

@@ -32,13 +32,35 @@
 #endif
 #define SEED_SMEM_BASES 256      // reads up to this long are staged in shared memory (4-bit codes)
 
+// SEED_PREV16 = 1: an entry is ONE 16-byte word pair in a region of the scratch that belongs to the thread alone
+// (k, l, s in 38 bits each — the text is shorter than 2^38 — and the span end n in 14): one 128-bit load or store per entry,
+// and the 32-byte sectors it touches hold this thread's entries only.  The interleaved 3 x 8-byte layout put word w of
+// entry e of four neighbouring threads into one sector, which lanes at different depths used an eighth of: the prev-list
+// load was the kernel's largest single stall (17.7 % of the samples) and its partial-sector write-backs a good part of the
+// 57 GB written / 285 GB read per 2.5 M reads against 82 GB of records asked for (profiles/r02_ncu_seed_collect_v2_lines.txt).
+// Reads of 16384 bases or more keep the interleaved layout (n does not fit).
+// MEASURED (scripts/gpu_r2_ac.sh, ms per 5 M reads at config-3 scale): 259.0 with it against 245.7 with the interleaved
+// layout — slower: a thread-private region means a 128-byte line serves one thread, the interleaved lines serve sixteen,
+// and the hot entries of a warp no longer share L1 lines.  OFF; kept for the record.
+#ifndef SEED_PREV16
+#define SEED_PREV16 0
+#endif
 struct DevPrev {
     uint32_t *sm;
     int64_t *buf;
+    ulonglong2 *own;             // this thread's 16-byte entries (SEED_PREV16), NULL: interleaved layout
     int stride, top;
     __device__ __forceinline__ void reset(int len) { top = len - 1; }
     __device__ __forceinline__ void put(int e, const Biv &v, int n)
     {
+        if (SEED_PREV16 && own) {
+            const uint64_t s = (uint64_t)v.s;
+            ulonglong2 w;
+            w.x = (uint64_t)v.k | (s << 38);
+            w.y = (uint64_t)v.l | ((s >> 26) << 38) | ((uint64_t)n << 50);
+            own[e] = w;
+            return;
+        }
         const int i = top - e;
         if (SEED_PREV_K > 0 && i < SEED_PREV_K) {
             uint32_t *p = sm + i * 4 * SEED_TPB;
@@ -52,6 +74,14 @@ struct DevPrev {
     }
     __device__ __forceinline__ void get(int e, Biv &v, int &n) const
     {
+        if (SEED_PREV16 && own) {
+            const ulonglong2 w = own[e];
+            const uint64_t m38 = (1ULL << 38) - 1;
+            v.k = (int64_t)(w.x & m38); v.l = (int64_t)(w.y & m38);
+            v.s = (int64_t)((w.x >> 38) | (((w.y >> 38) & 0xFFFULL) << 26));
+            n = (int)(w.y >> 50);
+            return;
+        }
         const int i = top - e;
         if (SEED_PREV_K > 0 && i < SEED_PREV_K) {
             const uint32_t *p = sm + i * 4 * SEED_TPB;
@@ -182,12 +212,12 @@ __device__ __forceinline__ Biv seed_bext_coop(const FmView &f, unsigned m_ready,
 // STAGED: every read of the batch is at most SEED_SMEM_BASES long and is staged in shared memory.
 template <bool STAGED>
 __global__ void __launch_bounds__(SEED_TPB, SEED_MIN_BLOCKS)
-seed_collect_kernel(FmView f, SeedOpt o, const uint8_t *__restrict__ reads,
+seed_collect_kernel(FmView f_in, SeedOpt o, const uint8_t *__restrict__ reads,
                     const int64_t *__restrict__ off, const int32_t *__restrict__ len,
                     const uint8_t *__restrict__ skip, int nseq, bwagpu_smem *__restrict__ tmp,
                     int cap, int32_t *__restrict__ cnt, int64_t *__restrict__ prev_buf,
                     SeedStats *__restrict__ stats, const int32_t *__restrict__ list, int32_t *__restrict__ ovf_list,
-                    int32_t *__restrict__ slab_of)
+                    int32_t *__restrict__ slab_of, int prev_cap16)
 {
     // list == NULL: first pass over all nseq reads, read i writes slab i of `tmp`; a read that finds more than `cap`
     // SMEMs is appended to ovf_list.  list != NULL: second pass over the nseq reads list[0 .. nseq) with the wider private
@@ -195,7 +225,13 @@ seed_collect_kernel(FmView f, SeedOpt o, const uint8_t *__restrict__ reads,
     const int64_t T = (int64_t)gridDim.x * blockDim.x;
     const int64_t t0 = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     extern __shared__ uint32_t seed_sm[];
+    __shared__ int64_t s_count[5];                     // count[] where fm_count can index it
+    if (threadIdx.x < 5) s_count[threadIdx.x] = fm_count(f_in, (int)threadIdx.x);
+    __syncthreads();
+    FmView f = f_in;
+    f.count_tab = s_count;
     DevPrev pv; pv.buf = prev_buf + t0; pv.stride = (int)T; pv.top = 0;
+    pv.own = prev_cap16 > 0 ? reinterpret_cast<ulonglong2 *>(prev_buf) + t0 * (int64_t)prev_cap16 : nullptr;
     pv.sm = seed_sm + threadIdx.x;
     uint32_t *rd_sm = seed_sm + SEED_PREV_K * 4 * SEED_TPB + threadIdx.x;
     using Read = typename std::conditional<STAGED, SmemRead, const uint8_t *>::type;
@@ -412,6 +448,7 @@ __global__ void sa_walk_kernel(FmView f, const bwagpu_smem *__restrict__ sm, int
 static FmView fm_view(const bwagpu_ctx *ctx)
 {
     FmView f;
+    f.count_tab = nullptr;
     f.cp_occ = (const int64_t *)ctx->d_cp_occ;
     f.sa_ms_byte = (const int8_t *)ctx->d_sa_ms;
     f.sa_ls_word = (const uint32_t *)ctx->d_sa_ls;
@@ -659,6 +696,8 @@ static int seed_collect_dev(bwagpu_ctx *ctx, const bwagpu_seed_opt *opt, const u
     BWAGPU_CUDA(ctx, cudaMemsetAsync(d_stats, 0, sizeof(SeedStats), ctx->stream));
     BWAGPU_CUDA(ctx, cudaMemsetAsync(d_cnt + nseq, 0, 4, ctx->stream));
     BWAGPU_CUDA(ctx, cudaMemsetAsync(d_slab_of, 0xFF, (size_t)nseq * 4, ctx->stream));
+    // prev-list entries per thread in the 16-byte layout (0 = interleaved 24-byte layout: reads too long for 14 bits of n)
+    const int prev_cap16 = (SEED_PREV16 && max_len < 16384) ? max_len + 1 : 0;
     auto launch = [&](int n_items, bwagpu_smem *slab, int slab_cap, const int32_t *list) {
         cudaMemsetAsync(&d_stats->next, 0, 4, ctx->stream);      // the read counter of SEED_DYN
         int b = blocks;
@@ -667,10 +706,10 @@ static int seed_collect_dev(bwagpu_ctx *ctx, const bwagpu_seed_opt *opt, const u
         BWAGPU_KERNEL_BEGIN(ctx);
         if (staged)
             seed_collect_kernel<true><<<b, SEED_TPB, smem, ctx->stream>>>(fm_view(ctx), so, d_reads, d_off, d_len, d_skip, n_items,
-                                                                         slab, slab_cap, d_cnt, d_prev, d_stats, list, d_ovf, d_slab_of);
+                                                                         slab, slab_cap, d_cnt, d_prev, d_stats, list, d_ovf, d_slab_of, prev_cap16);
         else
             seed_collect_kernel<false><<<b, SEED_TPB, smem, ctx->stream>>>(fm_view(ctx), so, d_reads, d_off, d_len, d_skip, n_items,
-                                                                          slab, slab_cap, d_cnt, d_prev, d_stats, list, d_ovf, d_slab_of);
+                                                                          slab, slab_cap, d_cnt, d_prev, d_stats, list, d_ovf, d_slab_of, prev_cap16);
         BWAGPU_KERNEL_END(ctx, BWAGPU_KERN_SEED_COLLECT);
     };
     launch(nseq, d_tmp, cap, nullptr);

@@ -240,7 +240,7 @@ typedef struct {
     int64_t n_left, n_right;                           /* extension jobs built */
     int64_t n_retry_left, n_retry_right;               /* jobs re-run with the doubled band */
     int64_t n_pairs8, n_pairs16, n_pairs_scalar;       /* jobs per kernel kind (first try) */
-    int64_t seq_bytes;                                 /* bytes of job sequences materialised */
+    int64_t seq_bytes;                                 /* bytes of job sequences materialised (0: the jobs read the reads and the text in place) */
     int64_t sw_cells;                                  /* DP cells the extension kernels computed (see bwagpu_bsw_cells) */
 } bwagpu_c2a_result;
 /* same with device-resident inputs */
