@@ -54,6 +54,11 @@ struct FmView {
 #ifndef SEED_PAIR2
 #define SEED_PAIR2 1
 #endif
+// SEED_ROW_FWD (SeedMachine::step_fast): MEASURED 247.3 ms per 5 M reads with it against 239.0 without (scripts/gpu_r2_af.sh,
+// bit-exact either way) — the load it saves was hidden behind other warps, the longer step is not.  OFF; kept for the record.
+#ifndef SEED_ROW_FWD
+#define SEED_ROW_FWD 0
+#endif
 
 #define FMA_ALL_BP 11
 #define FMA_LAST_BP 13
@@ -539,8 +544,10 @@ struct SeedMachine {
     }
 
     // backward row: r extends entry `src` (span end src_n) to the left by q[j]; entries of this row start at m = j + 1
-    BWAGPU_HD void consume_item(const Biv &r, const Biv &src, int src_n, const SeedOpt &o)
+    // Returns true when r became an entry of the next row (stored at base + nc).
+    BWAGPU_HD bool consume_item(const Biv &r, const Biv &src, int src_n, const SeedOpt &o)
     {
+        bool kept = false;
         if (r.s < min_intv) {
             if (!decided && src_n - (j + 1) + 1 >= o.min_seed_len) {
                 emit(j + 1, src_n, src);
@@ -552,8 +559,10 @@ struct SeedMachine {
             if (pf_cp && j > 0) fm_prefetch_bext(pf_cp, r.k, r.s);           // extended again in the next row
             ++nc;
             decided = 1;
+            kept = true;
         }
         ++p;
+        return kept;
     }
 
 #if SEED_PAIR2
@@ -603,6 +612,28 @@ struct SeedMachine {
     // is needed (phase changes, pivot ends, round changes, read end).
     BWAGPU_HD bool step_fast(const Biv &r, const SeedOpt &o, const Biv *r2 = nullptr)
     {
+#if SEED_PAIR2 && SEED_ROW_FWD
+        // A backward row of one or two entries is handled by ONE paired step, and the entries of the next row are then
+        // exactly the results of this step that were kept: they go on as the next request straight from registers.  The
+        // stores into the list still happen (the row's end states read it), the load of what was just stored does not —
+        // that load, an L2 round trip in front of every row's DRAM round trip, was the kernel's largest single stall
+        // (17.7 % of the samples, profiles/r02_ncu_seed_collect_v2_lines.txt).
+        if (state == ST_BITEM && p == 0 && np <= (has2 ? 2 : 1)) {
+            ++n_ext;
+            const bool k1 = consume_item(r, req, cur_n, o);
+            bool k2 = false;
+            if (has2) { has2 = false; ++n_ext; k2 = consume_item(*r2, req2, cur_n2, o); }
+            np = nc;                             // the row is finished (p == np)
+            if (np == 0) { state = ST_NEXT; return false; }
+            --j;
+            if (j < 0 || q[j] > 3) { state = ST_BEND; return false; }
+            nc = 0; decided = 0; last_s = -1; p = 0;
+            if (k1) { req = r; if (k2) { req2 = *r2; has2 = true; } }        // cur_n / cur_n2 stay: span ends do not change
+            else { req = *r2; cur_n = cur_n2; }
+            req_a = q[j];
+            return true;
+        }
+#endif
         consume(r, o);
 #if SEED_PAIR2
         if (has2) { has2 = false; consume_second(*r2, o); }
