@@ -194,7 +194,7 @@ extern "C" int bwagpu_bsw_cells(bwagpu_ctx *ctx, int reset, int64_t *cells)
     if (cells) {
         unsigned long long h = 0;
         BWAGPU_CUDA(ctx, cudaMemcpyAsync(&h, d, 8, cudaMemcpyDeviceToHost, ctx->stream));
-        BWAGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+        BWAGPU_CUDA(ctx, bwagpu_stream_sync(ctx));
         *cells = (int64_t)h;
     }
     if (reset) BWAGPU_CUDA(ctx, cudaMemsetAsync(d, 0, 8, ctx->stream));
@@ -274,7 +274,7 @@ static int bsw_launch_sorted(bwagpu_ctx *ctx, const bwagpu_bsw_params *prm, bwag
     ctx->launches += 1;
     int h_m[16];
     BWAGPU_CUDA(ctx, cudaMemcpyAsync(h_m, d_m, 64, cudaMemcpyDeviceToHost, ctx->stream));
-    BWAGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    BWAGPU_CUDA(ctx, bwagpu_stream_sync(ctx));
     const int max_len2 = h_m[1], n_long = h_m[2];
     // 2. the few long pairs (front of the order) take the generic global-scratch kernel
     if (n_long > 0) {
@@ -340,7 +340,7 @@ static int bsw_device_maxlen(bwagpu_ctx *ctx, const bwagpu_seqpair *d_pairs, int
     bsw_maxlen_kernel<<<blocks, 256, 0, ctx->stream>>>(d_pairs, n, d_m);
     ctx->launches++;
     BWAGPU_CUDA(ctx, cudaMemcpyAsync(out, d_m, 8, cudaMemcpyDeviceToHost, ctx->stream));
-    BWAGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    BWAGPU_CUDA(ctx, bwagpu_stream_sync(ctx));
     return BWAGPU_OK;
 }
 
@@ -414,6 +414,6 @@ extern "C" int bwagpu_bsw_get_scores(bwagpu_ctx *ctx, const bwagpu_bsw_params *p
     if (rc) return rc;
     BWAGPU_CUDA(ctx, cudaMemcpyAsync(pairArray, d_pairs, (size_t)numPairs * sizeof(bwagpu_seqpair),
                                      cudaMemcpyDeviceToHost, ctx->stream));
-    BWAGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    BWAGPU_CUDA(ctx, bwagpu_stream_sync(ctx));
     return BWAGPU_OK;
 }

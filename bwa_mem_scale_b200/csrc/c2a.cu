@@ -479,7 +479,7 @@ extern "C" int bwagpu_index_load_ref(bwagpu_ctx *ctx, const uint8_t *ref_string,
     if (!ref_string || l_pac <= 0 || n_seqs <= 0 || !contig_off || !contig_len)
         BWAGPU_FAIL(ctx, BWAGPU_ERR_ARG, "index_load_ref: incomplete reference descriptor");
     BWAGPU_CUDA(ctx, cudaSetDevice(ctx->device));
-    BWAGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    BWAGPU_CUDA(ctx, bwagpu_stream_sync(ctx));
     if (ctx->d_ref_string) { cudaFree(ctx->d_ref_string); cudaFree(ctx->d_contig_off); cudaFree(ctx->d_contig_len); cudaFree(ctx->d_contig_alt); }
     ctx->d_ref_string = ctx->d_contig_off = ctx->d_contig_len = ctx->d_contig_alt = nullptr;
     BWAGPU_CUDA(ctx, cudaMalloc(&ctx->d_ref_string, (size_t)(2 * l_pac) + 64));
@@ -491,7 +491,7 @@ extern "C" int bwagpu_index_load_ref(bwagpu_ctx *ctx, const uint8_t *ref_string,
     BWAGPU_CUDA(ctx, cudaMemcpyAsync(ctx->d_ref_string, ref_string, (size_t)(2 * l_pac), cudaMemcpyHostToDevice, ctx->stream));
     BWAGPU_CUDA(ctx, cudaMemcpyAsync(ctx->d_contig_off, contig_off, (size_t)n_seqs * 8, cudaMemcpyHostToDevice, ctx->stream));
     BWAGPU_CUDA(ctx, cudaMemcpyAsync(ctx->d_contig_len, contig_len, (size_t)n_seqs * 4, cudaMemcpyHostToDevice, ctx->stream));
-    BWAGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    BWAGPU_CUDA(ctx, bwagpu_stream_sync(ctx));
     ctx->l_pac = l_pac; ctx->n_contigs = n_seqs;
     return BWAGPU_OK;
 }
@@ -528,7 +528,7 @@ static int c2a_side(bwagpu_ctx *ctx, const C2aOpt &o, const bwagpu_ext_opt *eo, 
     ctx->launches++;
     int h_cnt[4];
     BWAGPU_CUDA(ctx, cudaMemcpyAsync(h_cnt, d_cnt, 16, cudaMemcpyDeviceToHost, ctx->stream));
-    BWAGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    BWAGPU_CUDA(ctx, bwagpu_stream_sync(ctx));
     res->n_pairs_scalar += h_cnt[0]; res->n_pairs16 += h_cnt[1]; res->n_pairs8 += h_cnt[2];
     bwagpu_bsw_params P = { eo->o_del, eo->e_del, eo->o_ins, eo->e_ins, eo->zdrop, left ? eo->pen_clip5 : eo->pen_clip3,
                             eo->a, eo->b };
@@ -549,7 +549,7 @@ static int c2a_side(bwagpu_ctx *ctx, const C2aOpt &o, const bwagpu_ext_opt *eo, 
             ctx->launches++;
             int nr = 0;
             BWAGPU_CUDA(ctx, cudaMemcpyAsync(&nr, d_cnt + 8, 4, cudaMemcpyDeviceToHost, ctx->stream));
-            BWAGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+            BWAGPU_CUDA(ctx, bwagpu_stream_sync(ctx));
             if (left) res->n_retry_left += nr; else res->n_retry_right += nr;
             nump = nr;
             bwagpu_seqpair *tmp = cur; cur = nxt; nxt = tmp;
@@ -605,7 +605,7 @@ extern "C" int bwagpu_chain2aln_device(bwagpu_ctx *ctx, const bwagpu_ext_opt *eo
     int64_t tot[6] = {0, 0, 0, 0, 0, 0};
     for (int k = 0; k < n_scan; ++k)
         BWAGPU_CUDA(ctx, cudaMemcpyAsync(&tot[k], offs + k * stride + n_seeds, 8, cudaMemcpyDeviceToHost, ctx->stream));
-    BWAGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    BWAGPU_CUDA(ctx, bwagpu_stream_sync(ctx));
     for (int k = 2; k < n_scan; ++k)
         if (tot[k] >= (1LL << 31)) BWAGPU_FAIL(ctx, BWAGPU_ERR_RANGE, "chain2aln: extension sequences exceed 2 GiB; split the batch");
     if (tot[0] >= (1LL << 31) || tot[1] >= (1LL << 31)) BWAGPU_FAIL(ctx, BWAGPU_ERR_RANGE, "chain2aln: more than 2^31 extension jobs; split the batch");
@@ -627,7 +627,7 @@ extern "C" int bwagpu_chain2aln_device(bwagpu_ctx *ctx, const bwagpu_ext_opt *eo
     BWAGPU_CUDA(ctx, cudaGetLastError());
     int h_err = 0;
     BWAGPU_CUDA(ctx, cudaMemcpyAsync(&h_err, d_err, 4, cudaMemcpyDeviceToHost, ctx->stream));
-    BWAGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    BWAGPU_CUDA(ctx, bwagpu_stream_sync(ctx));
     if (h_err) BWAGPU_FAIL(ctx, BWAGPU_ERR_RANGE, "chain2aln: read buffer of 4 GiB or more; split the batch");
     res->n_left = tot[0]; res->n_right = tot[1];
     res->seq_bytes = tot[2] + tot[3] + tot[4] + tot[5];
@@ -686,6 +686,6 @@ extern "C" int bwagpu_chain2aln(bwagpu_ctx *ctx, const bwagpu_ext_opt *eo, const
     bwagpu_c2a_result res;
     if ((rc = bwagpu_chain2aln_device(ctx, eo, d_reads, d_off, d_len, nseq, d_chains, n_chains, d_seeds, n_seeds, &res))) return rc;
     BWAGPU_CUDA(ctx, cudaMemcpyAsync(regs, res.d_regs, (size_t)n_seeds * sizeof(bwagpu_alnreg), cudaMemcpyDeviceToHost, ctx->stream));
-    BWAGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    BWAGPU_CUDA(ctx, bwagpu_stream_sync(ctx));
     return BWAGPU_OK;
 }

@@ -328,7 +328,7 @@ static int chain_device(bwagpu_ctx *ctx, const bwagpu_chain_opt *opt, const bwag
     BWAGPU_CUDA(ctx, cudaGetLastError());
     int32_t n_heavy = 0;
     BWAGPU_CUDA(ctx, cudaMemcpyAsync(&n_heavy, heavy, 4, cudaMemcpyDeviceToHost, ctx->stream));
-    BWAGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    BWAGPU_CUDA(ctx, bwagpu_stream_sync(ctx));
     if (n_heavy > 0) {
         BWAGPU_KERNEL_BEGIN(ctx);
         chain_filter_warp_kernel<<<(unsigned)(((int64_t)n_heavy * 32 + 127) / 128), 128, 0, ctx->stream>>>(
@@ -341,7 +341,7 @@ static int chain_device(bwagpu_ctx *ctx, const bwagpu_chain_opt *opt, const bwag
     int64_t tot[2];
     BWAGPU_CUDA(ctx, cudaMemcpyAsync(&tot[0], offs + nseq, 8, cudaMemcpyDeviceToHost, ctx->stream));
     BWAGPU_CUDA(ctx, cudaMemcpyAsync(&tot[1], offs + 2 * nseq + 1, 8, cudaMemcpyDeviceToHost, ctx->stream));
-    BWAGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    BWAGPU_CUDA(ctx, bwagpu_stream_sync(ctx));
     bwagpu_chain *out_c; bwagpu_seed *out_s;
     if ((rc = bwagpu_scratch(ctx, SCR_C2A_CHAINS, (tot[0] + 1) * (int64_t)sizeof(bwagpu_chain), (void **)&out_c))) return rc;
     if ((rc = bwagpu_scratch(ctx, SCR_C2A_SEEDS, (tot[1] + 1) * (int64_t)sizeof(bwagpu_seed), (void **)&out_s))) return rc;
@@ -403,7 +403,7 @@ extern "C" int bwagpu_chain_seeds(bwagpu_ctx *ctx, const bwagpu_chain_opt *opt, 
     if ((rc = chain_scan(ctx, d_rows, d_coff, n_smem + 1))) return rc;
     int64_t tot = 0;
     BWAGPU_CUDA(ctx, cudaMemcpyAsync(&tot, d_coff + n_smem, 8, cudaMemcpyDeviceToHost, ctx->stream));
-    BWAGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    BWAGPU_CUDA(ctx, bwagpu_stream_sync(ctx));
     if (tot != n_coords)
         BWAGPU_FAIL(ctx, BWAGPU_ERR_ARG, "chain_seeds: the SMEMs call for %lld SA coordinates, %lld were passed", (long long)tot, (long long)n_coords);
     bwagpu_chain_result res;
@@ -416,6 +416,6 @@ extern "C" int bwagpu_chain_seeds(bwagpu_ctx *ctx, const bwagpu_chain_opt *opt, 
         BWAGPU_CUDA(ctx, cudaMemcpyAsync(chains, res.d_chains, (size_t)res.n_chains * sizeof(bwagpu_chain), cudaMemcpyDeviceToHost, ctx->stream));
         BWAGPU_CUDA(ctx, cudaMemcpyAsync(seeds, res.d_seeds, (size_t)res.n_seeds * sizeof(bwagpu_seed), cudaMemcpyDeviceToHost, ctx->stream));
     }
-    BWAGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    BWAGPU_CUDA(ctx, bwagpu_stream_sync(ctx));
     return BWAGPU_OK;
 }

@@ -115,7 +115,7 @@ static int cig_launch_groups(bwagpu_ctx *ctx, const CigarOpt &o, const uint8_t *
     }
     unsigned int n_redo = 0;
     BWAGPU_CUDA(ctx, cudaMemcpyAsync(&n_redo, d_nredo, 4, cudaMemcpyDeviceToHost, ctx->stream));
-    BWAGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    BWAGPU_CUDA(ctx, bwagpu_stream_sync(ctx));
     if (n_redo > 0) {
         cigar_kernel<<<(unsigned)((n_redo + CIG_TPB - 1) / CIG_TPB), CIG_TPB, (size_t)2 * (CIG_SMEM_QLEN + 1) * CIG_TPB * 4, ctx->stream>>>(
             o, ctx->l_pac, (const uint8_t *)ctx->d_ref_string, d_reads, d_off, d_len, d_jobs, d_redo, 0, (int64_t)n_redo, 4, d_so, d_eh, d_z,
@@ -217,7 +217,7 @@ extern "C" int bwagpu_reg2aln_device(bwagpu_ctx *ctx, const bwagpu_cigar_opt *op
     for (int a = 0; a < 4; ++a) BWAGPU_CUDA(ctx, cudaMemcpyAsync(&tot[a], d_scans + a * (n + 1) + n, 8, cudaMemcpyDeviceToHost, ctx->stream));
     BWAGPU_CUDA(ctx, cudaMemcpyAsync(h_first, d_first, sizeof h_first, cudaMemcpyDeviceToHost, ctx->stream));
     BWAGPU_CUDA(ctx, cudaMemcpyAsync(&h_bad, d_flag, 4, cudaMemcpyDeviceToHost, ctx->stream));
-    BWAGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    BWAGPU_CUDA(ctx, bwagpu_stream_sync(ctx));
     if (h_bad) BWAGPU_FAIL(ctx, BWAGPU_ERR_ARG, "reg2aln_device: a job is out of range (read index, query span or window)");
     if (tot[1] + (tot[0] + tot[2]) * 4 + tot[3] > (32LL << 30))
         BWAGPU_FAIL(ctx, BWAGPU_ERR_RANGE, "reg2aln_device: %lld jobs need %.1f GB of scratch; pass smaller batches", (long long)n, (tot[1] + (tot[0] + tot[2]) * 4 + tot[3]) / 1e9);
@@ -238,7 +238,7 @@ extern "C" int bwagpu_reg2aln_device(bwagpu_ctx *ctx, const bwagpu_cigar_opt *op
     int64_t t2[2] = {0, 0};
     BWAGPU_CUDA(ctx, cudaMemcpyAsync(&t2[0], d_scan + n, 8, cudaMemcpyDeviceToHost, ctx->stream));
     BWAGPU_CUDA(ctx, cudaMemcpyAsync(&t2[1], d_scan + 2 * n + 1, 8, cudaMemcpyDeviceToHost, ctx->stream));
-    BWAGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    BWAGPU_CUDA(ctx, bwagpu_stream_sync(ctx));
     uint32_t *d_oc; char *d_om;
     if ((rc = bwagpu_scratch(ctx, SCR_CIG_OUTC, t2[0] * 4 + 16, (void **)&d_oc))) return rc;
     if ((rc = bwagpu_scratch(ctx, SCR_CIG_OUTM, t2[1] + 16, (void **)&d_om))) return rc;
@@ -342,7 +342,7 @@ extern "C" int bwagpu_reg2aln_batch(bwagpu_ctx *ctx, const bwagpu_cigar_opt *opt
         int64_t tot[2] = {0, 0};
         e = cudaMemcpyAsync(&tot[0], d_scan + n, 8, cudaMemcpyDeviceToHost, ctx->stream);
         if (e == cudaSuccess) e = cudaMemcpyAsync(&tot[1], d_scan + 2 * n + 1, 8, cudaMemcpyDeviceToHost, ctx->stream);
-        if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+        if (e == cudaSuccess) e = bwagpu_stream_sync(ctx);
         if (e != cudaSuccess) { free(h_so); free(h_key); free(h_order); BWAGPU_FAIL(ctx, BWAGPU_ERR_CUDA, "reg2aln_batch: kernel -> %s", cudaGetErrorString(e)); }
         CIG_TRY(bwagpu_scratch(ctx, SCR_CIG_OUTC, tot[0] * 4 + 16, (void **)&d_oc));
         CIG_TRY(bwagpu_scratch(ctx, SCR_CIG_OUTM, tot[1] + 16, (void **)&d_om));
@@ -354,7 +354,7 @@ extern "C" int bwagpu_reg2aln_batch(bwagpu_ctx *ctx, const bwagpu_cigar_opt *opt
         if (cbase + tot[0] > cigar_cap || mbase + tot[1] > md_cap) fits = false;
         if (fits && e == cudaSuccess && tot[0] > 0) e = cudaMemcpyAsync(cigar + cbase, d_oc, (size_t)tot[0] * 4, cudaMemcpyDeviceToHost, ctx->stream);
         if (fits && e == cudaSuccess && tot[1] > 0) e = cudaMemcpyAsync(md + mbase, d_om, (size_t)tot[1], cudaMemcpyDeviceToHost, ctx->stream);
-        if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+        if (e == cudaSuccess) e = bwagpu_stream_sync(ctx);
         if (e != cudaSuccess) { free(h_so); free(h_key); free(h_order); BWAGPU_FAIL(ctx, BWAGPU_ERR_CUDA, "reg2aln_batch: copy back -> %s", cudaGetErrorString(e)); }
         cbase += tot[0]; mbase += tot[1];
         j0 = j1;

@@ -52,6 +52,8 @@ extern "C" int bwagpu_create(int device, bwagpu_ctx **out)
     CK(cudaEventCreate(&ctx->kev0));
     CK(cudaEventCreate(&ctx->kev1));
     CK(cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking));
+    CK(cudaEventCreateWithFlags(&ctx->ev_block, cudaEventBlockingSync | cudaEventDisableTiming));
+    ctx->blocking_sync = getenv("BWAGPU_BLOCKING_SYNC") && atoi(getenv("BWAGPU_BLOCKING_SYNC")) > 0;
     CK(cudaEventCreateWithFlags(&ctx->ev_main_done, cudaEventDisableTiming));
     CK(cudaEventCreateWithFlags(&ctx->ev_h2d_done, cudaEventDisableTiming));
     CK(cudaEventCreateWithFlags(&ctx->ev_d2h_done, cudaEventDisableTiming));
@@ -65,7 +67,7 @@ extern "C" void bwagpu_destroy(bwagpu_ctx *ctx)
 {
     if (!ctx) return;
     cudaSetDevice(ctx->device);
-    cudaStreamSynchronize(ctx->stream);
+    bwagpu_stream_sync(ctx);
     for (int i = 0; i < BWAGPU_NSCRATCH; ++i)
         if (ctx->scratch[i]) cudaFree(ctx->scratch[i]);
     if (ctx->index_borrowed)
@@ -81,6 +83,7 @@ extern "C" void bwagpu_destroy(bwagpu_ctx *ctx)
     if (ctx->d_emf_seed) cudaFree(ctx->d_emf_seed);
     if (ctx->d_ert_kmer) cudaFree(ctx->d_ert_kmer);
     if (ctx->d_ert_mlt) cudaFree(ctx->d_ert_mlt);
+    cudaEventDestroy(ctx->ev_block);
     cudaEventDestroy(ctx->ev_start);
     cudaEventDestroy(ctx->ev_stop);
     cudaEventDestroy(ctx->kev0);
@@ -141,7 +144,7 @@ extern "C" int bwagpu_synchronize(bwagpu_ctx *ctx)
 {
     if (!ctx) return BWAGPU_ERR_ARG;
     BWAGPU_CUDA(ctx, cudaSetDevice(ctx->device));
-    BWAGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    BWAGPU_CUDA(ctx, bwagpu_stream_sync(ctx));
     return BWAGPU_OK;
 }
 
@@ -175,7 +178,7 @@ extern "C" int bwagpu_free(bwagpu_ctx *ctx, void *dptr)
 {
     if (!ctx) return BWAGPU_ERR_ARG;
     BWAGPU_CUDA(ctx, cudaSetDevice(ctx->device));
-    BWAGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    BWAGPU_CUDA(ctx, bwagpu_stream_sync(ctx));
     BWAGPU_CUDA(ctx, cudaFree(dptr));
     return BWAGPU_OK;
 }
@@ -185,7 +188,7 @@ extern "C" int bwagpu_h2d(bwagpu_ctx *ctx, void *dst, const void *src, int64_t b
     if (!ctx || bytes < 0) return BWAGPU_ERR_ARG;
     BWAGPU_CUDA(ctx, cudaSetDevice(ctx->device));
     BWAGPU_CUDA(ctx, cudaMemcpyAsync(dst, src, (size_t)bytes, cudaMemcpyHostToDevice, ctx->stream));
-    BWAGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    BWAGPU_CUDA(ctx, bwagpu_stream_sync(ctx));
     return BWAGPU_OK;
 }
 
@@ -194,7 +197,7 @@ extern "C" int bwagpu_d2h(bwagpu_ctx *ctx, void *dst, const void *src, int64_t b
     if (!ctx || bytes < 0) return BWAGPU_ERR_ARG;
     BWAGPU_CUDA(ctx, cudaSetDevice(ctx->device));
     BWAGPU_CUDA(ctx, cudaMemcpyAsync(dst, src, (size_t)bytes, cudaMemcpyDeviceToHost, ctx->stream));
-    BWAGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    BWAGPU_CUDA(ctx, bwagpu_stream_sync(ctx));
     return BWAGPU_OK;
 }
 
@@ -296,7 +299,7 @@ int bwagpu_scratch(bwagpu_ctx *ctx, int slot, int64_t bytes, void **out)
     }
     if (bytes > ctx->scratch_bytes[slot]) {
         if (ctx->scratch[slot]) {
-            BWAGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+            BWAGPU_CUDA(ctx, bwagpu_stream_sync(ctx));
             BWAGPU_CUDA(ctx, cudaFree(ctx->scratch[slot]));
             ctx->scratch[slot] = nullptr;
             ctx->scratch_bytes[slot] = 0;

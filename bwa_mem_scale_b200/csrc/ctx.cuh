@@ -59,6 +59,8 @@ struct bwagpu_ctx {
     void *d_ert_kmer, *d_ert_mlt;
     int64_t ert_mlt_bytes;
     int ert_mem_cap, ert_hit_cap;   // per-read slab capacities of the first ERT pass
+    int blocking_sync;          // 1: host waits sleep on a blocking event instead of spinning (BWAGPU_BLOCKING_SYNC=1, bwagpu_stream_sync)
+    cudaEvent_t ev_block;
     int bsw_direct;             // set around bsw_launch by bwagpu_bsw_scores_direct: pairs address the reads / the text directly
     int chain_batch_reads;      // unit of mem_chain_seeds' batch-wide SMEM bound (0 = the whole call); set by bwagpu_mem_process_chunk
     int seed_read_cap;          // per-read SMEM capacity of the seeding scratch (grows on overflow)
@@ -110,6 +112,16 @@ static inline cudaError_t bwagpu_raise_dyn_smem(BwagpuSmemBound &b, int device, 
     const cudaError_t e = cudaFuncSetAttribute(func, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
     if (e == cudaSuccess) b.cur[device] = bytes;
     return e;
+}
+
+// Every host-side wait for the context's stream goes through here.  cudaStreamSynchronize spins; with several ranks and
+// worker contexts per host (8 GPUs x 2 contexts on 32 cores) the spinning threads take the cores the other ranks' launches
+// need, so the wait can instead sleep on an event created with cudaEventBlockingSync (BWAGPU_BLOCKING_SYNC=1).
+static inline cudaError_t bwagpu_stream_sync(bwagpu_ctx *ctx)
+{
+    if (!ctx->blocking_sync) return cudaStreamSynchronize(ctx->stream);
+    const cudaError_t e = cudaEventRecord(ctx->ev_block, ctx->stream);
+    return e != cudaSuccess ? e : cudaEventSynchronize(ctx->ev_block);
 }
 
 // first statement of every entry point that loads, builds or unloads a part of the index

@@ -170,7 +170,7 @@ extern "C" int bwagpu_emf_unload(bwagpu_ctx *ctx)
     BWAGPU_OWNS_INDEX(ctx);
     if (!ctx) return BWAGPU_ERR_ARG;
     BWAGPU_CUDA(ctx, cudaSetDevice(ctx->device));
-    BWAGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    BWAGPU_CUDA(ctx, bwagpu_stream_sync(ctx));
     if (ctx->d_emf_loc) cudaFree(ctx->d_emf_loc);
     if (ctx->d_emf_seed) cudaFree(ctx->d_emf_seed);
     ctx->d_emf_loc = ctx->d_emf_seed = nullptr;
@@ -196,7 +196,7 @@ extern "C" int bwagpu_emf_load(bwagpu_ctx *ctx, const bwagpu_emf_desc *d, const 
     BWAGPU_CUDA(ctx, cudaMalloc(&ctx->d_emf_seed, (size_t)ctx->emf.num_seed_load * 16));
     BWAGPU_CUDA(ctx, cudaMemcpyAsync(ctx->d_emf_loc, loc_table, (size_t)d->num_loc_entry * 4, cudaMemcpyHostToDevice, ctx->stream));
     BWAGPU_CUDA(ctx, cudaMemcpyAsync(ctx->d_emf_seed, seed_table, (size_t)ctx->emf.num_seed_load * 16, cudaMemcpyHostToDevice, ctx->stream));
-    BWAGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    BWAGPU_CUDA(ctx, bwagpu_stream_sync(ctx));
     return BWAGPU_OK;
 }
 
@@ -253,7 +253,7 @@ extern "C" int bwagpu_emf_probe(bwagpu_ctx *ctx, const uint8_t *reads, const int
     BWAGPU_CUDA(ctx, cudaMemcpyAsync(ret, d_ret, (size_t)nseq * 4, cudaMemcpyDeviceToHost, ctx->stream));
     BWAGPU_CUDA(ctx, cudaMemcpyAsync(perfect, d_perf, (size_t)nseq * 8, cudaMemcpyDeviceToHost, ctx->stream));
     if (skip) BWAGPU_CUDA(ctx, cudaMemcpyAsync(skip, d_skip, (size_t)nseq, cudaMemcpyDeviceToHost, ctx->stream));
-    BWAGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    BWAGPU_CUDA(ctx, bwagpu_stream_sync(ctx));
     return BWAGPU_OK;
 }
 

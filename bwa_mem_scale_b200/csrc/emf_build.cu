@@ -368,6 +368,6 @@ extern "C" int bwagpu_emf_get(bwagpu_ctx *ctx, bwagpu_emf_desc *desc, uint32_t *
     if (desc) { *desc = ctx->emf; if (desc->num_seed_load == desc->num_seed_entry) desc->num_seed_load = 0; }
     if (loc_table) BWAGPU_CUDA(ctx, cudaMemcpyAsync(loc_table, ctx->d_emf_loc, (size_t)ctx->emf.num_loc_entry * 4, cudaMemcpyDeviceToHost, ctx->stream));
     if (seed_table) BWAGPU_CUDA(ctx, cudaMemcpyAsync(seed_table, ctx->d_emf_seed, (size_t)ctx->emf.num_seed_load * 16, cudaMemcpyDeviceToHost, ctx->stream));
-    BWAGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    BWAGPU_CUDA(ctx, bwagpu_stream_sync(ctx));
     return BWAGPU_OK;
 }

@@ -118,7 +118,7 @@ extern "C" int bwagpu_index_unload_ert(bwagpu_ctx *ctx)
     BWAGPU_OWNS_INDEX(ctx);
     if (!ctx) return BWAGPU_ERR_ARG;
     BWAGPU_CUDA(ctx, cudaSetDevice(ctx->device));
-    BWAGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    BWAGPU_CUDA(ctx, bwagpu_stream_sync(ctx));
     if (ctx->d_ert_kmer) cudaFree(ctx->d_ert_kmer);
     if (ctx->d_ert_mlt) cudaFree(ctx->d_ert_mlt);
     ctx->d_ert_kmer = ctx->d_ert_mlt = nullptr;
@@ -156,7 +156,7 @@ extern "C" int bwagpu_index_load_ert(bwagpu_ctx *ctx, const uint64_t *kmer_offse
     }
     BWAGPU_CUDA(ctx, cudaMemsetAsync((uint8_t *)ctx->d_ert_mlt + mlt_bytes, 0, 16, ctx->stream));
     BWAGPU_CUDA(ctx, cudaMemcpyAsync(ctx->d_ert_mlt, mlt_table, (size_t)mlt_bytes, cudaMemcpyHostToDevice, ctx->stream));
-    BWAGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    BWAGPU_CUDA(ctx, bwagpu_stream_sync(ctx));
     ctx->ert_mlt_bytes = mlt_bytes;
     return BWAGPU_OK;
 }
@@ -210,7 +210,7 @@ extern "C" int bwagpu_index_complete_ert(bwagpu_ctx *ctx)
     ert_kmer_fill_kernel<<<(1u << 22) / 128, 128, 0, ctx->stream>>>(f, (uint64_t *)ctx->d_ert_kmer);
     BWAGPU_KERNEL_END(ctx, BWAGPU_KERN_ERT_EMIT);
     BWAGPU_CUDA(ctx, cudaGetLastError());
-    BWAGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    BWAGPU_CUDA(ctx, bwagpu_stream_sync(ctx));
     return BWAGPU_OK;
 }
 
@@ -220,7 +220,7 @@ extern "C" int bwagpu_index_get_ert_kmers(bwagpu_ctx *ctx, const uint32_t *idx, 
     if (!ctx->d_ert_kmer) BWAGPU_FAIL(ctx, BWAGPU_ERR_ARG, "index_get_ert_kmers: no ERT index loaded");
     if (n < 0 || (n > 0 && (!idx || !out))) BWAGPU_FAIL(ctx, BWAGPU_ERR_ARG, "index_get_ert_kmers: bad argument");
     BWAGPU_CUDA(ctx, cudaSetDevice(ctx->device));
-    BWAGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    BWAGPU_CUDA(ctx, bwagpu_stream_sync(ctx));
     for (int64_t i = 0; i < n; ++i)
         BWAGPU_CUDA(ctx, cudaMemcpy(out + i, (const uint64_t *)ctx->d_ert_kmer + idx[i], 8, cudaMemcpyDeviceToHost));
     return BWAGPU_OK;
@@ -232,7 +232,7 @@ extern "C" int bwagpu_index_get_ert_table(bwagpu_ctx *ctx, uint64_t *kmer_offset
     if (!ctx->d_ert_kmer) BWAGPU_FAIL(ctx, BWAGPU_ERR_ARG, "index_get_ert_table: no ERT index loaded");
     if (!kmer_offsets) BWAGPU_FAIL(ctx, BWAGPU_ERR_ARG, "index_get_ert_table: output is NULL");
     BWAGPU_CUDA(ctx, cudaSetDevice(ctx->device));
-    BWAGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    BWAGPU_CUDA(ctx, bwagpu_stream_sync(ctx));
     BWAGPU_CUDA(ctx, cudaMemcpy(kmer_offsets, ctx->d_ert_kmer, (size_t)ERT_KMER_ENTRIES * 8, cudaMemcpyDeviceToHost));
     return BWAGPU_OK;
 }
@@ -320,7 +320,7 @@ static int ert_seed_dev(bwagpu_ctx *ctx, const bwagpu_seed_opt *opt, int max_occ
     BWAGPU_CUDA(ctx, cudaGetLastError());
     ErtStats st;
     BWAGPU_CUDA(ctx, cudaMemcpyAsync(&st, d_st, sizeof st, cudaMemcpyDeviceToHost, ctx->stream));
-    BWAGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    BWAGPU_CUDA(ctx, bwagpu_stream_sync(ctx));
 #ifdef ERT_GUARD
     fprintf(stderr, "ERT_GUARD pass 1: bad_site=%d read=%d val=0x%llx u=0x%llx v=0x%llx n_ovf=%u max_mem=%u max_hit=%u mlt_bytes=%lld\n", st.bad_site, st.bad_read, (unsigned long long)st.bad_val, st.bad_u, st.bad_v, st.n_ovf, st.max_mem, st.max_hit, (long long)ctx->ert_mlt_bytes);
 #endif
@@ -341,7 +341,7 @@ static int ert_seed_dev(bwagpu_ctx *ctx, const bwagpu_seed_opt *opt, int max_occ
         BWAGPU_KERNEL_END(ctx, BWAGPU_KERN_ERT_SEED);
         BWAGPU_CUDA(ctx, cudaGetLastError());
         BWAGPU_CUDA(ctx, cudaMemcpyAsync(&st, d_st, sizeof st, cudaMemcpyDeviceToHost, ctx->stream));
-        BWAGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+        BWAGPU_CUDA(ctx, bwagpu_stream_sync(ctx));
         if ((int64_t)st.max_mem <= mc && (int64_t)st.max_hit <= hc) break;      // hit_peak is exact, so one pass suffices
     }
     if ((rc = ert_scan_i32(ctx, cnt_mem, mem_off, nseq + 1))) return rc;
@@ -349,7 +349,7 @@ static int ert_seed_dev(bwagpu_ctx *ctx, const bwagpu_seed_opt *opt, int max_occ
     int64_t tot[2] = {0, 0};
     BWAGPU_CUDA(ctx, cudaMemcpyAsync(&tot[0], mem_off + nseq, 8, cudaMemcpyDeviceToHost, ctx->stream));
     BWAGPU_CUDA(ctx, cudaMemcpyAsync(&tot[1], coord_base + nseq, 8, cudaMemcpyDeviceToHost, ctx->stream));
-    BWAGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    BWAGPU_CUDA(ctx, bwagpu_stream_sync(ctx));
     bwagpu_smem *out; int64_t *coord_off, *coords;
     if ((rc = bwagpu_scratch(ctx, SCR_SEED_OUT, (tot[0] + 1) * (int64_t)sizeof(bwagpu_smem), (void **)&out))) return rc;
     if ((rc = bwagpu_scratch(ctx, SCR_SA_OFF, (tot[0] + 1) * 8, (void **)&coord_off))) return rc;
@@ -424,7 +424,7 @@ extern "C" int bwagpu_seed_ert(bwagpu_ctx *ctx, const bwagpu_seed_opt *opt, cons
             if (!hits) { free(tmp); BWAGPU_FAIL(ctx, BWAGPU_ERR_ARG, "seed_ert: hits is NULL"); }
             e = cudaMemcpyAsync(hits, r.d_coords, (size_t)r.n_coords * 8, cudaMemcpyDeviceToHost, ctx->stream);
         }
-        if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+        if (e == cudaSuccess) e = bwagpu_stream_sync(ctx);
         if (e != cudaSuccess) { free(tmp); BWAGPU_FAIL(ctx, BWAGPU_ERR_CUDA, "seed_ert: copy back -> %s", cudaGetErrorString(e)); }
         for (int64_t i = 0; i < r.n_smem; ++i) {
             mems[i].rid = (int32_t)tmp[i].rid; mems[i].start = (int32_t)tmp[i].m; mems[i].end = (int32_t)tmp[i].n + 1;
@@ -432,6 +432,6 @@ extern "C" int bwagpu_seed_ert(bwagpu_ctx *ctx, const bwagpu_seed_opt *opt, cons
         }
         free(tmp);
     }
-    BWAGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    BWAGPU_CUDA(ctx, bwagpu_stream_sync(ctx));
     return BWAGPU_OK;
 }

@@ -218,7 +218,7 @@ extern "C" int bwagpu_index_build_fm(bwagpu_ctx *ctx)
     if (!ctx) return BWAGPU_ERR_ARG;
     if (!ctx->d_ref_string) BWAGPU_FAIL(ctx, BWAGPU_ERR_ARG, "index_build_fm: no reference text loaded (bwagpu_index_load_ref)");
     BWAGPU_CUDA(ctx, cudaSetDevice(ctx->device));
-    BWAGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    BWAGPU_CUDA(ctx, bwagpu_stream_sync(ctx));
     cudaStream_t st = ctx->stream;
     const int64_t n = 2 * ctx->l_pac, n_rows = n + 1;
     if (n_rows >= (1LL << 38)) BWAGPU_FAIL(ctx, BWAGPU_ERR_RANGE, "index_build_fm: text longer than 2^38 symbols is not supported");
@@ -409,7 +409,7 @@ extern "C" int bwagpu_index_get_fm(bwagpu_ctx *ctx, int64_t *reference_seq_len, 
     }
     if (sa_ms_byte) BWAGPU_CUDA(ctx, cudaMemcpyAsync(sa_ms_byte, ctx->d_sa_ms, (size_t)n_sa, cudaMemcpyDeviceToHost, ctx->stream));
     if (sa_ls_word) BWAGPU_CUDA(ctx, cudaMemcpyAsync(sa_ls_word, ctx->d_sa_ls, (size_t)n_sa * 4, cudaMemcpyDeviceToHost, ctx->stream));
-    const cudaError_t e_sync = cudaStreamSynchronize(ctx->stream);
+    const cudaError_t e_sync = bwagpu_stream_sync(ctx);
     if (d_ref_order) cudaFree(d_ref_order);
     BWAGPU_CUDA(ctx, e_sync);
     return BWAGPU_OK;

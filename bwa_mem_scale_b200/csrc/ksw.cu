@@ -276,7 +276,7 @@ extern "C" int bwagpu_ksw_align2_batch_device(bwagpu_ctx *ctx, const bwagpu_ksw_
     ksw_scan_kernel<<<ctx->sm_count * 2, 256, 0, ctx->stream>>>(d_pairArray, numPairs, d_m);
     ctx->launches++;
     BWAGPU_CUDA(ctx, cudaMemcpyAsync(h_m, d_m, 16, cudaMemcpyDeviceToHost, ctx->stream));
-    BWAGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    BWAGPU_CUDA(ctx, bwagpu_stream_sync(ctx));
     return ksw_run(ctx, kp, d_pairArray, d_seqBufRef, d_seqBufQer, d_aln, numPairs, h_m[0], h_m[1], h_m[2]);
 }
 
@@ -315,6 +315,6 @@ extern "C" int bwagpu_ksw_align2_batch(bwagpu_ctx *ctx, const bwagpu_ksw_params 
     BWAGPU_CUDA(ctx, cudaMemcpyAsync(d_qer, seqBufQer, (size_t)qer_bytes, cudaMemcpyHostToDevice, ctx->stream));
     if ((rc = ksw_run(ctx, kp, d_pairs, d_ref, d_qer, d_aln, numPairs, max_t, max_q, n8))) return rc;
     BWAGPU_CUDA(ctx, cudaMemcpyAsync(aln, d_aln, (size_t)numPairs * sizeof(bwagpu_kswr), cudaMemcpyDeviceToHost, ctx->stream));
-    BWAGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    BWAGPU_CUDA(ctx, bwagpu_stream_sync(ctx));
     return BWAGPU_OK;
 }

@@ -95,7 +95,7 @@ extern "C" int bwagpu_mem_process_chunk_device(bwagpu_ctx *ctx, const bwagpu_mem
         ctx->launches++;
         unsigned long long h = 0;
         BWAGPU_CUDA(ctx, cudaMemcpyAsync(&h, d_n, 8, cudaMemcpyDeviceToHost, ctx->stream));
-        BWAGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+        BWAGPU_CUDA(ctx, bwagpu_stream_sync(ctx));
         res->d_emf_ret = d_ret; res->d_perfect = d_perfect; res->n_emf_hits = (int64_t)h;
     }
     // S1 / S1': seeding (+ SA), then chaining
@@ -149,7 +149,7 @@ extern "C" int bwagpu_mem_process_chunk_device(bwagpu_ctx *ctx, const bwagpu_mem
     ctx->launches += 2;
     int64_t total = 0;
     BWAGPU_CUDA(ctx, cudaMemcpyAsync(&total, pos + n, 8, cudaMemcpyDeviceToHost, ctx->stream));
-    BWAGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    BWAGPU_CUDA(ctx, bwagpu_stream_sync(ctx));
     bwagpu_alnreg *out;
     if ((rc = bwagpu_scratch(ctx, SCR_MEM_REGS, (total + 1) * (int64_t)sizeof(bwagpu_alnreg), (void **)&out))) return rc;
     mem_compact_kernel<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(ar.d_regs, n, pos, out);
@@ -205,6 +205,6 @@ extern "C" int bwagpu_mem_fetch(bwagpu_ctx *ctx, const bwagpu_mem_result *res, i
         if (res->d_perfect) BWAGPU_CUDA(ctx, cudaMemcpyAsync(perfect, res->d_perfect, (size_t)nseq * 8, cudaMemcpyDeviceToHost, ctx->stream));
         else memset(perfect, 0, (size_t)nseq * 8);
     }
-    BWAGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    BWAGPU_CUDA(ctx, bwagpu_stream_sync(ctx));
     return BWAGPU_OK;
 }

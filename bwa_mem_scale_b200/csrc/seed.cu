@@ -509,7 +509,7 @@ extern "C" int bwagpu_index_build_fma(bwagpu_ctx *ctx)
     fma_build_last_kernel<<<(1u << (2 * FMA_LAST_BP)) / 128, 128, 0, ctx->stream>>>(f, (uint32_t *)ctx->d_fma_last);
     BWAGPU_KERNEL_END(ctx, BWAGPU_KERN_FMA_BUILD);
     BWAGPU_CUDA(ctx, cudaGetLastError());
-    BWAGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    BWAGPU_CUDA(ctx, bwagpu_stream_sync(ctx));
     ctx->fma_enabled = 1;
     return BWAGPU_OK;
 }
@@ -519,14 +519,14 @@ extern "C" int bwagpu_index_load_fma(bwagpu_ctx *ctx, const void *all_tab, const
     BWAGPU_OWNS_INDEX(ctx);
     if (!ctx) return BWAGPU_ERR_ARG;
     BWAGPU_CUDA(ctx, cudaSetDevice(ctx->device));
-    BWAGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    BWAGPU_CUDA(ctx, bwagpu_stream_sync(ctx));
     if (!all_tab && ctx->d_fma_all) { cudaFree(ctx->d_fma_all); ctx->d_fma_all = nullptr; }
     if (!last_tab && ctx->d_fma_last) { cudaFree(ctx->d_fma_last); ctx->d_fma_last = nullptr; }
     int rc = fma_alloc(ctx, all_tab != nullptr, last_tab != nullptr);
     if (rc) return rc;
     if (all_tab) BWAGPU_CUDA(ctx, cudaMemcpyAsync(ctx->d_fma_all, all_tab, (size_t)BWAGPU_FMA_ALL_BYTES, cudaMemcpyHostToDevice, ctx->stream));
     if (last_tab) BWAGPU_CUDA(ctx, cudaMemcpyAsync(ctx->d_fma_last, last_tab, (size_t)BWAGPU_FMA_LAST_BYTES, cudaMemcpyHostToDevice, ctx->stream));
-    BWAGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    BWAGPU_CUDA(ctx, bwagpu_stream_sync(ctx));
     ctx->fma_enabled = (all_tab || last_tab) ? 1 : 0;
     return BWAGPU_OK;
 }
@@ -539,7 +539,7 @@ extern "C" int bwagpu_index_get_fma(bwagpu_ctx *ctx, void *all_tab, void *last_t
         BWAGPU_FAIL(ctx, BWAGPU_ERR_ARG, "index_get_fma: table not resident");
     if (all_tab) BWAGPU_CUDA(ctx, cudaMemcpyAsync(all_tab, ctx->d_fma_all, (size_t)BWAGPU_FMA_ALL_BYTES, cudaMemcpyDeviceToHost, ctx->stream));
     if (last_tab) BWAGPU_CUDA(ctx, cudaMemcpyAsync(last_tab, ctx->d_fma_last, (size_t)BWAGPU_FMA_LAST_BYTES, cudaMemcpyDeviceToHost, ctx->stream));
-    BWAGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    BWAGPU_CUDA(ctx, bwagpu_stream_sync(ctx));
     return BWAGPU_OK;
 }
 
@@ -590,7 +590,7 @@ extern "C" int bwagpu_index_load_fm(bwagpu_ctx *ctx, const bwagpu_fm_index_desc 
     if (d->reference_seq_len >= (1LL << 38))
         BWAGPU_FAIL(ctx, BWAGPU_ERR_RANGE, "index_load_fm: text longer than 2^38 symbols is not supported");
     BWAGPU_CUDA(ctx, cudaSetDevice(ctx->device));
-    BWAGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    BWAGPU_CUDA(ctx, bwagpu_stream_sync(ctx));
     if (ctx->d_cp_occ) { cudaFree(ctx->d_cp_occ); cudaFree(ctx->d_sa_ms); cudaFree(ctx->d_sa_ls); }
     ctx->d_cp_occ = ctx->d_sa_ms = ctx->d_sa_ls = nullptr;
     ctx->has_fm = false;
@@ -605,7 +605,7 @@ extern "C" int bwagpu_index_load_fm(bwagpu_ctx *ctx, const bwagpu_fm_index_desc 
     BWAGPU_CUDA(ctx, cudaMemcpyAsync(ctx->d_sa_ms, d->sa_ms_byte, (size_t)n_sa, cudaMemcpyHostToDevice, ctx->stream));
     BWAGPU_CUDA(ctx, cudaMemcpyAsync(ctx->d_sa_ls, d->sa_ls_word, (size_t)n_sa * 4, cudaMemcpyHostToDevice, ctx->stream));
     { const int rc = bwagpu_fm_convert_layout(ctx, ctx->d_cp_occ, ctx->d_cp_occ, n_cp, 1); if (rc) return rc; }
-    BWAGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    BWAGPU_CUDA(ctx, bwagpu_stream_sync(ctx));
     for (int i = 0; i < 5; ++i) ctx->fm_count[i] = d->count[i];
     ctx->fm_sentinel = d->sentinel_index;
     ctx->fm_ref_seq_len = d->reference_seq_len;
@@ -715,7 +715,7 @@ static int seed_collect_dev(bwagpu_ctx *ctx, const bwagpu_seed_opt *opt, const u
     launch(nseq, d_tmp, cap, nullptr);
     BWAGPU_CUDA(ctx, cudaGetLastError());
     BWAGPU_CUDA(ctx, cudaMemcpyAsync(h_stats, d_stats, sizeof(SeedStats), cudaMemcpyDeviceToHost, ctx->stream));
-    BWAGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    BWAGPU_CUDA(ctx, bwagpu_stream_sync(ctx));
     if (h_stats->n_ovf > 0) {
         const int n_ovf = (int)h_stats->n_ovf;
         if (getenv("BWAGPU_VERBOSE")) fprintf(stderr, "[bwagpu] seed: %d of %d reads outgrow the %d-entry slab (max %llu)\n", n_ovf, nseq, cap, h_stats->max_cnt);
@@ -730,14 +730,14 @@ static int seed_collect_dev(bwagpu_ctx *ctx, const bwagpu_seed_opt *opt, const u
             launch(n_ovf, d_tmp2, cap2, d_ovf);          // its extensions add to the statistics: they are work done
             BWAGPU_CUDA(ctx, cudaGetLastError());
             BWAGPU_CUDA(ctx, cudaMemcpyAsync(h_stats, d_stats, sizeof(SeedStats), cudaMemcpyDeviceToHost, ctx->stream));
-            BWAGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+            BWAGPU_CUDA(ctx, bwagpu_stream_sync(ctx));
             if ((int64_t)h_stats->max_cnt <= cap2) break;
         }
     }
     if ((rc = scan_i32_to_i64(ctx, d_cnt, d_offs, nseq + 1))) return rc;
     int64_t total = 0;
     BWAGPU_CUDA(ctx, cudaMemcpyAsync(&total, d_offs + nseq, 8, cudaMemcpyDeviceToHost, ctx->stream));
-    BWAGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    BWAGPU_CUDA(ctx, bwagpu_stream_sync(ctx));
     bwagpu_smem *out;
     if ((rc = bwagpu_scratch(ctx, SCR_SEED_OUT, (total + 1) * (int64_t)sizeof(bwagpu_smem), (void **)&out))) return rc;
     BWAGPU_KERNEL_BEGIN(ctx);
@@ -768,7 +768,7 @@ static int sa_lookup_dev(bwagpu_ctx *ctx, const bwagpu_smem *d_sm, int64_t n, in
     if ((rc = scan_i64(ctx, rows, offs, n + 1))) return rc;
     int64_t total = 0;
     BWAGPU_CUDA(ctx, cudaMemcpyAsync(&total, offs + n, 8, cudaMemcpyDeviceToHost, ctx->stream));
-    BWAGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    BWAGPU_CUDA(ctx, bwagpu_stream_sync(ctx));
     int64_t *coords;
     if ((rc = bwagpu_scratch(ctx, SCR_SA_COORD, (total + 1) * 8, (void **)&coords))) return rc;
     if (total > 0) {
@@ -780,7 +780,7 @@ static int sa_lookup_dev(bwagpu_ctx *ctx, const bwagpu_smem *d_sm, int64_t n, in
     }
     if (h_stats) {
         BWAGPU_CUDA(ctx, cudaMemcpyAsync(&h_stats->n_lf, &d_stats->n_lf, 8, cudaMemcpyDeviceToHost, ctx->stream));
-        BWAGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+        BWAGPU_CUDA(ctx, bwagpu_stream_sync(ctx));
     }
     *d_coords = coords; *n_coords = total;
     return BWAGPU_OK;
@@ -847,7 +847,7 @@ extern "C" int bwagpu_collect_smem(bwagpu_ctx *ctx, const bwagpu_seed_opt *opt, 
         if (!out) BWAGPU_FAIL(ctx, BWAGPU_ERR_ARG, "collect_smem: out is NULL");
         BWAGPU_CUDA(ctx, cudaMemcpyAsync(out, d_sm, (size_t)tot * sizeof(bwagpu_smem), cudaMemcpyDeviceToHost, ctx->stream));
     }
-    BWAGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    BWAGPU_CUDA(ctx, bwagpu_stream_sync(ctx));
     return BWAGPU_OK;
 }
 
@@ -873,6 +873,6 @@ extern "C" int bwagpu_get_sa_entries(bwagpu_ctx *ctx, const bwagpu_smem *smems, 
         if (!coords) BWAGPU_FAIL(ctx, BWAGPU_ERR_ARG, "get_sa_entries: coords is NULL");
         BWAGPU_CUDA(ctx, cudaMemcpyAsync(coords, d_coords, (size_t)nc * 8, cudaMemcpyDeviceToHost, ctx->stream));
     }
-    BWAGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    BWAGPU_CUDA(ctx, bwagpu_stream_sync(ctx));
     return BWAGPU_OK;
 }
