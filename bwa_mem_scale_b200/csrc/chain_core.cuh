@@ -24,6 +24,11 @@
 #define CHAIN_HD inline
 #endif
 
+// CHAIN_LINEAR_SEARCH (getp_aux): early-exit scan of a node's sorted keys instead of nine predicated compares.  MEASURED
+// 117.9 vs 116.2 ms per 5 M reads (scripts/gpu_r2_ai.sh): no gain — the dependent loads cost what the compares saved.  OFF.
+#ifndef CHAIN_LINEAR_SEARCH
+#define CHAIN_LINEAR_SEARCH 0
+#endif
 #define CHAIN_BT_T 5                        // kb_init: ((520 - 4 - 8) / (8 + 48) + 1) >> 1
 #define CHAIN_BT_MAXKEYS (2 * CHAIN_BT_T - 1)
 
@@ -102,6 +107,12 @@ struct ChainBuilder {
         const int n = x.n;
         if (n == 0) return -1;
         int begin = 0, eq = 0;
+#if CHAIN_LINEAR_SEARCH
+        // the keys of a node are sorted: stop at the first one that is not below k (on average half the node instead of
+        // always nine predicated compares — the kernel runs one or two lanes per warp, so instructions are what counts)
+        while (begin < n && x.kpos[begin] < k) ++begin;
+        eq = begin < n && x.kpos[begin] == k;
+#else
 #if defined(__CUDA_ARCH__)
 #pragma unroll
 #endif
@@ -110,6 +121,7 @@ struct ChainBuilder {
             begin += p < k;
             eq |= p == k;
         }
+#endif
         if (begin == n) { *r = 1; return n - 1; }
         *r = eq ? 0 : -1;
         return eq ? begin : begin - 1;

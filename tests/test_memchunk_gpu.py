@@ -45,7 +45,9 @@ def test_chunk_entry_matches_hard_golden(gpu_ctx, case):
     Extender(fmindex.text_with_revcomp(ref), int(HARD["l_pac"][0]), HARD["contig_off"], HARD["contig_len"], ctx=gpu_ctx)
     flat, off, ln = ol.pack_reads(cc.hard_reads(ref))
     mc = MemChunk(gpu_ctx)
-    # the golden records come from ONE mem_kernel1_core call over all reads, i.e. one batch
+    # the golden records come from the tap's mem_kernel1_core calls, 512 reads at a time like worker_bwt; no 512-read slice
+    # of this read set totals <= 1 SMEM, so the single-SMEM rule never fires and one call-wide batch gives the same chains
+    # (the rule itself is covered by test_chunk_entry_batch_rule_and_empty)
     res = mc.process(opts(ol.mem_opt(**kw), batch_size=0), flat, off, ln)
     regs, reg_off, emf_ret, perfect = mc.fetch(res, len(ln))
     want, want_off = expected(HARD, name, len(ln))
