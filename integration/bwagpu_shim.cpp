@@ -76,6 +76,7 @@ template <typename T> void grow(T *&p, int64_t n)
 void init(worker_t &w)
 {
     FMI_search *fmi = w.fmi;
+    const double t_init = realtime();
     int dev = getenv("BWAGPU_DEVICE") ? atoi(getenv("BWAGPU_DEVICE")) : 0;
     if (bwagpu_create(dev, &g.ctx)) die("bwagpu_create (libbwagpu has no CPU path)");
     const bntseq_t *bns = fmi->idx->bns;
@@ -114,6 +115,7 @@ void init(worker_t &w)
     }
 #endif
     g.fmi = fmi;
+    fprintf(stderr, "[bwagpu] index replicated in HBM (context + uploads): %.3f s\n", realtime() - t_init);
 }
 
 struct Job { worker_t *w; const bwagpu_mem_result *res; };
@@ -185,7 +187,9 @@ void process_chunk(mem_opt_t *opt, int n, bseq1_t *seqs, worker_t &w)
     for (int i = 0; i < n; ++i) { g.off[i] = pos; g.len[i] = seqs[i].l_seq; pos += seqs[i].l_seq; }
     if (pos + 64 > g.enc_cap) { g.enc_cap = pos + pos / 4 + 4096; grow(g.enc, g.enc_cap); }
     g_job.w = &w;
+    const double t0 = realtime();
     kt_for(pack_worker, &w, n);
+    const double t1 = realtime();
 
     bwagpu_mem_opt mo;
     memset(&mo, 0, sizeof mo);
@@ -201,13 +205,18 @@ void process_chunk(mem_opt_t *opt, int n, bseq1_t *seqs, worker_t &w)
 
     bwagpu_mem_result res;
     CK(bwagpu_mem_process_chunk(g.ctx, &mo, g.enc, g.off, g.len, n, &res));
+    const double t2 = realtime();
     if (res.n_regs + 1 > g.regs_cap) { g.regs_cap = res.n_regs + res.n_regs / 4 + 4096; grow(g.regs, g.regs_cap); }
     CK(bwagpu_mem_fetch(g.ctx, &res, n, g.regs, g.reg_off, g.emf_ret, g.perfect));
+    const double t3 = realtime();
     g_job.res = &res;
     kt_for(unpack_worker, &w, n);
+    const double t4 = realtime();
     fprintf(stderr, "[bwagpu] chunk of %d reads: %lld EMF hits, %lld SMEMs, %lld chains, %lld SW jobs (%lld retried), %lld regions\n",
             n, (long long)res.n_emf_hits, (long long)res.n_smem, (long long)res.n_chains,
             (long long)(res.n_sw_left + res.n_sw_right), (long long)res.n_sw_retry, (long long)res.n_regs);
+    fprintf(stderr, "[bwagpu] chunk times (s): pack %.3f, reads -> regions on the GPU (copies in, scratch growth included) %.3f, "
+                    "results out %.3f, mem_alnreg_v + mem_sort_dedup_patch %.3f\n", t1 - t0, t2 - t1, t3 - t2, t4 - t3);
 }
 
 }  // namespace

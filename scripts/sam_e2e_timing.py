@@ -34,10 +34,10 @@ with tempfile.TemporaryDirectory() as td:
             subprocess.run([binary, "mem", "-t", str(threads), prefix, fq], check=True, stdout=fo, stderr=fe, timeout=1500)
         out[name + "_wall_s"] = time.perf_counter() - t0
         text = open(log, errors="ignore").read()
-        keep = ("Overall time", "MEM_PROCESS_SEQ", "Total kernel", "SAM Processing", "Reading IO", "Index read", "bwagpu", "Writing IO")
+        keep = ("Overall time", "MEM_PROCESS_SEQ", "Total kernel", "SAM Processing", "Reading IO", "Index read", "bwagpu", "Writing IO", "index replicated")
         lines = text.splitlines()
         out[name + "_profile"] = [(l.strip() + " " + (lines[i + 1].strip() if l.rstrip().endswith(":") and i + 1 < len(lines) else "")).strip()
-                                  for i, l in enumerate(lines) if any(k in l for k in keep)][-14:]
+                                  for i, l in enumerate(lines) if any(k in l for k in keep)][-24:]
         sams[name] = [l for l in open(sam, "rb") if not l.startswith(b"@PG")]
     a, b = sams["reference"], sams["gpu"]
     out["sam_lines"] = len(a)
