@@ -96,3 +96,32 @@ def test_gpu_chain2aln_vs_reference_live(gpu_ctx, tmp_path):
             assert (regs["w"][regs["qb"] != -1] == 2 * o["w"]).sum() > 50      # band-doubling retries ran
     ref0, rs0 = cc.genome()     # restore the module fixture's reference replica on the shared context
     Extender(rs0, int(GOLD["l_pac"][0]), GOLD["contig_off"], GOLD["contig_len"], ctx=gpu_ctx)
+
+
+def test_gpu_pipeline_long_reads_in_place_windows(gpu_ctx):
+    """600-base reads with indels on the three-contig genome: extension queries longer than the shared-memory SW kernel
+    takes (len2 > 512) go through the generic kernel, and every job reads its query and its reference window IN PLACE
+    (read buffer / resident text, backwards for left extensions) — regions must equal the oracle's for the same chains."""
+    from bwa_mem_scale_b200 import FMI_search, REG_DTYPE, chain_opt, mem_core_device, pack_reads, seed_opt
+    from test_chain_hostsim import hard_index
+    ref, idx = hard_index()
+    hard = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "c2a_hard_golden.npz"))
+    text = fmindex.text_with_revcomp(ref)
+    l_pac, coff, clen = int(hard["l_pac"][0]), hard["contig_off"], hard["contig_len"]
+    fmi = FMI_search(idx, ctx=gpu_ctx)
+    ext = Extender(text, l_pac, coff, clen, ctx=gpu_ctx)
+    reads = synth.gapped_reads(ref, 600, seed=5, read_len=600, err=0.02) + synth.gapped_reads(ref, 200, seed=6, read_len=540, err=0.01)
+    flat, off, ln = pack_reads(reads)
+    d = [gpu_ctx.upload(a) for a in (flat, off, ln)]
+    sres, cres, ares = mem_core_device(fmi, ext, seed_opt(), chain_opt(), ext_opt(), d[0], d[1], d[2], len(ln), int(ln.max()))
+    chains, seeds = np.zeros(cres.n_chains, ol.CHAIN_DTYPE), np.zeros(cres.n_seeds, ol.SEED_DTYPE)
+    regs = np.zeros(ares.n_regs, REG_DTYPE)
+    gpu_ctx.d2h(chains, cres.d_chains); gpu_ctx.d2h(seeds, cres.d_seeds); gpu_ctx.d2h(regs, ares.d_regs)
+    for p in d:
+        gpu_ctx.free(p)
+    want = ol.oracle_chain2aln(ol.mem_opt(), l_pac, coff, clen, text, flat, off, ln, chains, seeds)
+    assert len(regs) > 1000 and np.array_equal(cc.reg_matrix(regs), cc.reg_matrix(want))
+    assert ares.seq_bytes == 0                                        # nothing was materialised
+    # some jobs had queries beyond the shared-memory kernel's reach
+    s = seeds
+    assert (s["qbeg"] > 512).any() or ((np.repeat(600, len(s)) - s["qbeg"] - s["len"]) > 512).any()
